@@ -1,0 +1,165 @@
+/* ihm2b.h -- C ABI of libihm2b.so, the B200-native batched NMPC engine for the ihm2
+ * path-parametric bicycle-model controller.
+ *
+ * This is the drop-in boundary for the one hot path named by BASELINE.json: what the
+ * reference reaches through `AcadosOcpSolver` (ctypes over the acados-generated
+ * libacados_ocp_solver_ihm2_fkin6.so) and, in C++, through the generated
+ * `ihm2_fkin6_acados_*` capsule API.  Each entry point cites the reference call it
+ * replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, int return (0 = IHM2B_OK); no exceptions.
+ *  - `_dev` pointers are CUDA device pointers owned by the caller (PyTorch tensors);
+ *    `_host` pointers are host memory.  The handle owns all workspace.
+ *  - `stream` is a cudaStream_t passed as void*; every `_dev` call is asynchronous on it.
+ *  - One handle per (device, stream); a handle is not thread-safe (same as an acados capsule,
+ *    src/ihm2/src/mpc_control_node.cpp:274-304).
+ *  - Batch-major row layouts at the boundary: x [B][N+1][8], u [B][N][2], x0 [B][8] ...
+ *    (the reference keeps one row per stage, mpc_control_node.cpp:71); the library
+ *    transposes to its internal structure-of-arrays layout on the device.
+ *  - Per-instance NLP status codes follow acados (dpc/main.py:287-293):
+ *    0 success, 1 failure (NaN), 2 max iterations, 3 min step, 4 QP failure.
+ */
+#ifndef IHM2B_H
+#define IHM2B_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IHM2B_NX 8   /* IHM2_FKIN6_NX */
+#define IHM2B_NU 2   /* IHM2_FKIN6_NU */
+#define IHM2B_NY 12  /* IHM2_FKIN6_NY  (python/mpc.py:48) */
+#define IHM2B_NYN 8  /* IHM2_FKIN6_NYN (python/mpc.py:62) */
+#define IHM2B_NP 20  /* per-instance vehicle parameters, see ihm2b_param_index */
+
+enum ihm2b_error { IHM2B_OK = 0, IHM2B_EINVAL = 1, IHM2B_ECUDA = 2, IHM2B_ENOMEM = 3 };
+enum ihm2b_integrator { IHM2B_ERK4 = 0, IHM2B_IRK_GL4 = 1 };
+enum ihm2b_nlp_solver { IHM2B_SQP_RTI = 0, IHM2B_SQP = 1 };
+enum ihm2b_globalization { IHM2B_FIXED_STEP = 0, IHM2B_MERIT_BACKTRACKING = 1 };
+enum ihm2b_sim_model { IHM2B_SIM_FKIN6 = 0, IHM2B_SIM_FDYN6 = 1, IHM2B_SIM_KIN6_DYN6 = 2 };
+enum ihm2b_status {
+  IHM2B_SUCCESS = 0, IHM2B_FAILURE = 1, IHM2B_MAXITER = 2, IHM2B_MINSTEP = 3, IHM2B_QP_FAILURE = 4
+};
+
+/* per-instance vehicle parameter vector (python/constants.py:43-111) */
+enum ihm2b_param_index {
+  IHM2B_P_M = 0, IHM2B_P_IZ, IHM2B_P_LR, IHM2B_P_LF, IHM2B_P_CM0, IHM2B_P_CR0, IHM2B_P_CR1,
+  IHM2B_P_CR2, IHM2B_P_TT, IHM2B_P_TD, IHM2B_P_ZCG, IHM2B_P_TRACKW, IHM2B_P_CDOWN,
+  IHM2B_P_KTV, IHM2B_P_BA, IHM2B_P_CA, IHM2B_P_DA, IHM2B_P_EA, IHM2B_P_G,
+  IHM2B_P_CROSS /* 1: literal slip-angle cross assignment of python/models.py:543-546 */
+};
+
+/* Everything `IHM2Controller.__init__` fixes at construction
+ * (new_python/controller.py:250-366, python/mpc.py:29-101). */
+typedef struct ihm2b_config {
+  int32_t batch;          /* B independent problems */
+  int32_t N;              /* horizon Nf (controller.py:254) */
+  int32_t n_tracks;       /* number of (s_ref, kappa_ref) tables */
+  int32_t n_grid;         /* entries per table (3 * NUMBER_SPLINE_INTERVALS = 1500) */
+  int32_t integrator;     /* ihm2b_integrator (controller.py:305 / old/generate.py:24) */
+  int32_t nlp_solver;     /* ihm2b_nlp_solver (controller.py:301 / old/generate.py:21) */
+  int32_t nlp_max_iter;   /* nlp_solver_max_iter (controller.py:302); ignored for RTI */
+  int32_t globalization;  /* ihm2b_globalization (controller.py:308) */
+  int32_t qp_max_iter;    /* interior-point iteration cap */
+  int32_t nonlinear_constraints; /* 1: add soft h(x,u) of old/generate_acaods_interface.py:190-212 */
+  int32_t sim_model;      /* ihm2b_sim_model (python/main.py:346, 475-502) */
+  int32_t sim_steps;      /* integrator sub-steps of the plant (python/main.py:398: 100) */
+  double dt;              /* sampling time (controller.py:255) */
+  double s_target;        /* controller.py:256 */
+  double n_max, v_x_max, T_max, delta_max; /* python/mpc.py:77-89 */
+  double g_T_max;         /* t_T * T_dot_max      (python/mpc.py:98-99) */
+  double g_delta_max;     /* t_delta * delta_dot_max */
+  double a_lat_max;       /* only with nonlinear_constraints */
+  double W[IHM2B_NY];     /* diag of stage W (controller.py:326-343) */
+  double W_e[IHM2B_NYN];  /* diag of terminal W (controller.py:350-363) */
+  double cost_scale_stage;    /* acados multiplies stage costs by tf/N */
+  double cost_scale_terminal; /* and leaves the terminal cost unscaled */
+  double qp_mu0;          /* IPM start barrier parameter */
+  double qp_tol;          /* IPM tolerance on stationarity / equality / inequality residuals (relative) */
+  double qp_tol_comp;     /* IPM tolerance on complementarity; the barrier parameter is floored at 0.1 x this */
+  double nlp_tol;         /* SQP KKT tolerance (SQP mode) */
+  double irk_A[16], irk_b[4]; /* 4-stage collocation tableau of the controller integrator */
+  double sim_A[16], sim_b[4]; /* 4-stage tableau of the plant integrator (Radau IIA) */
+  double sim_switch;      /* fkin6 -> fdyn6 when v^2 sin(beta)/l_R > sim_switch (main.py:482-489) */
+  double track_half_L, track_half_W; /* car half length / width for the track constraint */
+  double slack_z, slack_Z; /* L1 / L2 slack penalties (old/...interface.py:383-390) */
+} ihm2b_config;
+
+typedef struct ihm2b_handle ihm2b_handle;
+
+/* ---- life cycle ----------------------------------------------------------------------
+ * replaces ihm2_fkin6_acados_create_capsule / _create / _free / _free_capsule
+ * (mpc_control_node.cpp:274-284, 399-411) and AcadosOcpSolver(...) (python/mpc.py:111). */
+int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out);
+int ihm2b_destroy(ihm2b_handle* h);
+const char* ihm2b_last_error(void);
+int ihm2b_version(void);
+
+/* ---- problem data --------------------------------------------------------------------
+ * replaces solver.set(i, "p", p) for all stages (controller.py:320-323,
+ * ihm2_fkin6_acados_update_params, mpc_control_node.cpp:360-364).
+ * s_ref / kappa_ref: host, [n_tracks][n_grid]; widths (optional, may be NULL): right/left
+ * track widths, same shape.  track_index: host int32 [B].  params: host [B][IHM2B_NP]. */
+int ihm2b_set_tracks(ihm2b_handle* h, const double* s_ref_host, const double* kappa_ref_host,
+                     const double* right_width_host, const double* left_width_host);
+int ihm2b_set_track_index(ihm2b_handle* h, const int32_t* track_index_host);
+int ihm2b_set_params(ihm2b_handle* h, const double* params_host);
+
+/* ---- iterate (x_pred / u_pred) -------------------------------------------------------
+ * replaces solver.set(j, "x"|"u", v) and solver.get(i, "x"|"u")
+ * (controller.py:388-393, 402-403; ocp_nlp_out_get, mpc_control_node.cpp:202-206). */
+int ihm2b_set_iterate_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev, void* stream);
+int ihm2b_get_iterate_dev(ihm2b_handle* h, double* x_dev, double* u_dev, void* stream);
+/* controller.py:313-317: x_j = (-6 + j dt, 0...), u_j = (T_max, 0) */
+int ihm2b_reset_iterate(ihm2b_handle* h, void* stream);
+/* controller.py:388-393 shift warm start (literal: x_{N-1} = x_N = old x_N, u_{N-1} = 0) */
+int ihm2b_shift_iterate(ihm2b_handle* h, void* stream);
+
+/* ---- the hot entry point -------------------------------------------------------------
+ * replaces the body of IHM2Controller.compute_control after the shift
+ * (controller.py:370-385 x0 embedding + yref, :396 solver.solve(), :405 get(0,"u");
+ * ihm2_fkin6_acados_solve, mpc_control_node.cpp:177-206).
+ * x0_dev [B][8] in; u0_dev [B][2], status_dev [B] out. */
+int ihm2b_solve_dev(ihm2b_handle* h, const double* x0_dev, double* u0_dev, int32_t* status_dev,
+                    void* stream);
+/* Same call with HOST buffers: H2D of x0, shift (if do_shift), solve, D2H of u0/status,
+ * synchronous.  This is the shape of the reference's numpy-in / numpy-out call. */
+int ihm2b_compute_control_host(ihm2b_handle* h, const double* x0_host, double* u0_host,
+                               int32_t* status_host, int do_shift);
+
+/* ---- pieces of the path, exposed for parity tests ------------------------------------
+ * integrator + forward sensitivities at the current iterate (acados sim_erk / sim_irk inside
+ * the SQP preparation phase).  Outputs batch-major: A [B][N][8][8], Bm [B][N][8][2],
+ * phi [B][N][8] (phi_k = integrator(x_k, u_k)). */
+int ihm2b_linearize_dev(ihm2b_handle* h, double* A_dev, double* B_dev, double* phi_dev,
+                        void* stream);
+/* per-instance statistics [B][8]: qp iterations, sqp iterations, final mu, res_stat, res_eq,
+ * res_ineq, res_comp, cost */
+int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats_dev, void* stream);
+
+/* ---- plant ---------------------------------------------------------------------------
+ * replaces AcadosSimSolver.simulate(x, u) with the model switch of python/main.py:475-502.
+ * x_dev [B][8], u_dev [B][2] -> xnext_dev [B][8]; model_dev (optional) gets the model used. */
+int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev,
+                       double* xnext_dev, int32_t* model_dev, void* stream);
+
+/* ---- closed loop ---------------------------------------------------------------------
+ * python/main.py:448-517 with the NMPC call enabled: n_steps iterations of
+ * shift -> solve -> plant step on the device, no host round trips.
+ * x_dev [B][8] in/out (current state); lap_length_host [n_tracks].
+ * Optional logs (may be NULL): xlog_dev [n_steps+1][B][8], ulog_dev [n_steps][B][2].
+ * done_dev [B]: step index at which s > lap_length + 1 (or -1), fail_dev [B]: step index of
+ * the first failure (solver status not in {0,2} or NaN in the plant), or -1. */
+int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x_dev,
+                          const double* lap_length_host, double* xlog_dev, double* ulog_dev,
+                          int32_t* done_dev, int32_t* fail_dev, void* stream);
+
+/* number of kernel launches issued by this handle since creation (bench bookkeeping) */
+int64_t ihm2b_launch_count(const ihm2b_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IHM2B_H */

@@ -1,0 +1,1124 @@
+// ihm2_oracle.cpp -- CPU fp64 restatement of the ihm2 NMPC hot path.
+//
+// TEST INFRASTRUCTURE ONLY.  Nothing in ihm2_b200/ may import, link or call this file.
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+// legs use it, as the checker and the timed CPU baseline.
+//
+// PARITY UNPINNED: the reference (tudoroancea/ihm2) ships no tests, fixtures or golden
+// vectors, and the arithmetic of this path lives in acados / HPIPM / BLASFEO / CasADi,
+// which are neither vendored nor version-pinned (README.md:54-57, env.yml:17-19) and are
+// absent from this image.  This file restates (i) the reference's own model/OCP
+// definitions and (ii) the published algorithms of those libraries (ERK4 / Gauss-Legendre
+// and Radau-IIA collocation with forward sensitivities, Gauss-Newton SQP(-RTI),
+// Mehrotra primal-dual IPM with a Riccati KKT solve).  It is pinned only by the
+// independent mathematical checks in tests/ (finite differences, scipy ODE solutions,
+// KKT optimality certificates).
+//
+// Everything here is deliberately generic and dense (plain loops over small dense
+// matrices); the CUDA product path is a separate, structured implementation.
+//
+// Reference sites restated (paths relative to the reference tree):
+//   fkin6 ODE ......................... python/models.py:232-307
+//   smooth_sgn ........................ python/utils.py:23-24
+//   constants ......................... python/constants.py:43-111
+//   kappa interpolant (exact, linear) . python/models.py:290-295
+//   OCP cost / bounds / C,D ........... python/mpc.py:29-101
+//   weights, yref, warm start, status . new_python/controller.py:313-405
+//   solver options .................... new_python/controller.py:298-309, old/generate.py:18-26
+//   fdyn6 plant ....................... python/models.py:455-606
+//   sim options / switch / lap ........ python/main.py:395-400, 475-517, 561-570
+//   nonlinear h(x,u) + slacks ......... old/generate_acaods_interface.py:190-212, 351-449
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+namespace {
+
+constexpr int NX = 8, NU = 2, NZ = 10;
+
+// ---------------------------------------------------------------------------------------
+// vehicle parameters (python/constants.py:43-111).  Index layout shared with the tests.
+// ---------------------------------------------------------------------------------------
+enum {
+  P_M = 0, P_IZ, P_LR, P_LF, P_CM0, P_CR0, P_CR1, P_CR2, P_TT, P_TD,
+  P_ZCG, P_TRACKW, P_CDOWN, P_KTV, P_BA, P_CA, P_DA, P_EA, P_G, P_CROSS, NP
+};
+
+struct Track {
+  int n;              // table length (3 laps x 500 in the reference)
+  const double* s;    // s_ref[n], strictly increasing
+  const double* k;    // kappa_ref[n]
+};
+
+// CasADi interpolant("linear", lookup_mode "exact"): binary search for the interval that
+// contains s, clamped to [0, n-2] so that values outside the grid extrapolate linearly
+// (python/models.py:290-295).  Returns kappa and the slope of the active segment.
+inline void kappa_lookup(const Track& tr, double s, double& kap, double& dkap) {
+  int lo = 0, hi = tr.n;  // upper_bound
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (tr.s[mid] <= s) lo = mid + 1; else hi = mid;
+  }
+  int i = lo - 1;
+  if (i < 0) i = 0;
+  if (i > tr.n - 2) i = tr.n - 2;
+  dkap = (tr.k[i + 1] - tr.k[i]) / (tr.s[i + 1] - tr.s[i]);
+  kap = tr.k[i] + dkap * (s - tr.s[i]);
+}
+
+// fkin6 continuous dynamics and (optionally) its Jacobian J[8][10] w.r.t. (x,u),
+// columns ordered (x0..x7, u0, u1).  python/models.py:232-307.
+void fkin6(const double* x, const double* u, const double* p, const Track& tr, double* f,
+           double (*J)[NX + NU]) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
+  const double m = p[P_M], lR = p[P_LR], lF = p[P_LF];
+  const double C = lR / (lR + lF);  // rear_weight_distribution
+  const double tT = p[P_TT], tD = p[P_TD];
+
+  const double ddot = (u[1] - dl) / tD;
+  const double Tdot = (u[0] - T) / tT;
+
+  const double Fm = p[P_CM0] * T;
+  const double th = std::tanh(10.0 * vx);
+  const double poly = p[P_CR0] + p[P_CR1] * vx + p[P_CR2] * vx * vx;
+  const double Fd = -poly * th;
+  const double FRx = 0.5 * Fm + Fd, FFx = 0.5 * Fm;
+
+  const double td = std::tan(dl);
+  const double beta = std::atan(C * td);
+  const double cb = std::cos(beta), sb = std::sin(beta);
+  const double sec2 = 1.0 + td * td, den = 1.0 + C * C * td * td;
+  const double G = C * sec2 / den;  // d beta / d delta
+  const double bdot = G * ddot;
+  const double cdb = std::cos(dl - beta), sdb = std::sin(dl - beta);
+  const double vdot = (FRx * cb + FFx * cdb) / m;
+
+  double kap, dkap;
+  kappa_lookup(tr, x[0], kap, dkap);
+  const double cp = std::cos(psi), sp = std::sin(psi);
+  const double D = 1.0 + kap * n;
+  const double num = vx * cp - vy * sp;
+  const double sdot = num / D;
+  const double vydot = vdot * sb + bdot * vx;
+
+  f[0] = sdot;
+  f[1] = vx * sp + vy * cp;
+  f[2] = r - kap * sdot;
+  f[3] = vdot * cb - bdot * vy;
+  f[4] = vydot;
+  f[5] = lR * vydot - bdot;
+  f[6] = Tdot;
+  f[7] = ddot;
+  if (!J) return;
+
+  for (int i = 0; i < NX; i++)
+    for (int j = 0; j < NX + NU; j++) J[i][j] = 0.0;
+  // row 0: sdot
+  const double ds_ds = -num * dkap * n / (D * D);
+  const double ds_dn = -num * kap / (D * D);
+  const double ds_dpsi = (-vx * sp - vy * cp) / D;
+  const double ds_dvx = cp / D, ds_dvy = -sp / D;
+  J[0][0] = ds_ds; J[0][1] = ds_dn; J[0][2] = ds_dpsi; J[0][3] = ds_dvx; J[0][4] = ds_dvy;
+  // row 1: ndot
+  J[1][2] = num; J[1][3] = sp; J[1][4] = cp;
+  // row 2: psidot = r - kappa * sdot
+  J[2][0] = -dkap * sdot - kap * ds_ds;
+  J[2][1] = -kap * ds_dn;
+  J[2][2] = -kap * ds_dpsi;
+  J[2][3] = -kap * ds_dvx;
+  J[2][4] = -kap * ds_dvy;
+  J[2][5] = 1.0;
+  // derivatives of the longitudinal / lateral block
+  const double dFd_dvx = -(p[P_CR1] + 2.0 * p[P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th);
+  const double dG_ddl = 2.0 * C * (1.0 - C * C) * td * sec2 / (den * den);
+  const double dbdot_ddl = dG_ddl * ddot - G / tD;
+  const double dbdot_du = G / tD;
+  const double dvdot_dvx = dFd_dvx * cb / m;
+  const double dvdot_dT = 0.5 * p[P_CM0] * (cb + cdb) / m;
+  const double dvdot_ddl = (-FRx * sb * G - FFx * sdb * (1.0 - G)) / m;
+  // row 3: vxdot = vdot cb - bdot vy
+  J[3][3] = dvdot_dvx * cb;
+  J[3][4] = -bdot;
+  J[3][6] = dvdot_dT * cb;
+  J[3][7] = dvdot_ddl * cb - vdot * sb * G - dbdot_ddl * vy;
+  J[3][9] = -dbdot_du * vy;
+  // row 4: vydot = vdot sb + bdot vx
+  J[4][3] = dvdot_dvx * sb + bdot;
+  J[4][6] = dvdot_dT * sb;
+  J[4][7] = dvdot_ddl * sb + vdot * cb * G + dbdot_ddl * vx;
+  J[4][9] = dbdot_du * vx;
+  // row 5: rdot = lR vydot - bdot   (literal, python/models.py:304)
+  for (int j = 0; j < NX + NU; j++) J[5][j] = lR * J[4][j];
+  J[5][7] -= dbdot_ddl;
+  J[5][9] -= dbdot_du;
+  // rows 6, 7: actuators
+  J[6][6] = -1.0 / tT; J[6][8] = 1.0 / tT;
+  J[7][7] = -1.0 / tD; J[7][9] = 1.0 / tD;
+}
+
+// ---------------------------------------------------------------------------------------
+// fdyn6 plant (python/models.py:455-606).  The reference states it implicitly,
+// F(xdot, x, u) = 0; F is affine in (a_x, a_y, rdot), so the explicit right-hand side is
+// obtained from three evaluations of the force balance (exact for an affine map).
+// ---------------------------------------------------------------------------------------
+inline double smooth_abs_nonzero(double v) {  // python/utils.py:27-32 (min_val 1e-6)
+  return std::tanh(10.0 * v) * v + 1e-6 * std::exp(-v * v);
+}
+inline double lat_pacejka(const double* p, double a) {  // python/models.py:69-74
+  const double Ba = p[P_BA] * a;
+  return p[P_DA] * std::sin(p[P_CA] * std::atan(Ba - p[P_EA] * (Ba - std::atan(Ba))));
+}
+
+// total body-frame forces / yaw moment for given accelerations (a_x, a_y)
+void fdyn6_forces(const double* x, const double* p, double ax, double ay, double* FxFyMz) {
+  const double vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
+  const double m = p[P_M], g = p[P_G], lR = p[P_LR], lF = p[P_LF], wb = lR + lF;
+  const double tw = p[P_TRACKW];
+  const double Fdown = 0.5 * p[P_CDOWN] * vx * vx;
+  const double stat = 0.5 * m * g * lF / wb;
+  const double lonT = 0.5 * m * ax * p[P_ZCG] / wb;
+  const double latT = 0.5 * m * ay * p[P_ZCG] / tw;
+  const double FzFL = -(stat - lonT + latT + 0.25 * Fdown);
+  const double FzFR = -(stat - lonT - latT + 0.25 * Fdown);
+  const double FzRL = -(stat + lonT + latT + 0.25 * Fdown);
+  const double FzRR = -(stat + lonT - latT + 0.25 * Fdown);
+  const double cd = std::cos(dl), sd = std::sin(dl);
+  const double vxFL = vx - 0.5 * tw * r, vxFR = vx + 0.5 * tw * r;
+  const double vyF = vy + lF * r;
+  const double vlonFL = cd * vxFL + sd * vyF, vlonFR = cd * vxFR + sd * vyF;
+  const double vlatFL = -sd * vxFL + cd * vyF, vlatFR = -sd * vxFR + cd * vyF;
+  const double vlonRL = vx - 0.5 * tw * r, vlonRR = vx + 0.5 * tw * r;
+  const double vlatR = vy - lR * r;
+  const double aFL = std::atan2(vlatFL, smooth_abs_nonzero(vlonFL));
+  const double aFR = std::atan2(vlatFR, smooth_abs_nonzero(vlonFR));
+  const double aRL = std::atan2(vlatR, smooth_abs_nonzero(vlonRL));
+  const double aRR = std::atan2(vlatR, smooth_abs_nonzero(vlonRR));
+  const bool cross = p[P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
+  const double FlatFL = FzFL * lat_pacejka(p, cross ? aRR : aFL);
+  const double FlatFR = FzFR * lat_pacejka(p, cross ? aRL : aFR);
+  const double FlatRL = FzRL * lat_pacejka(p, cross ? aFR : aRL);
+  const double FlatRR = FzRR * lat_pacejka(p, cross ? aFL : aRR);
+  const double th = std::tanh(10.0 * vx);
+  const double Fdrag = -(p[P_CR0] + p[P_CR1] * vx + p[P_CR2] * vx * vx) * th;
+  const double C = lR / wb;
+  const double beta = std::atan(C * std::tan(dl));
+  const double rkin = std::hypot(vx, vy) * std::sin(beta) / lR;
+  const double dtau = p[P_KTV] * (rkin - r);
+  const double dn = -m * g - 0.25 * Fdown;
+  const double FlonFL = p[P_CM0] * (T - dtau) * FzFL / dn;
+  const double FlonFR = p[P_CM0] * (T + dtau) * FzFR / dn;
+  const double FlonRL = p[P_CM0] * (T - dtau) * FzRL / dn;
+  const double FlonRR = p[P_CM0] * (T + dtau) * FzRR / dn;
+  FxFyMz[0] = (FlonFR + FlonFL) * cd - (FlatFR + FlatFL) * sd + FlonRR + FlonRL + Fdrag;
+  FxFyMz[1] = (FlonFR + FlonFL) * sd + (FlatFR + FlatFL) * cd + FlatRR + FlatRL;
+  FxFyMz[2] = (FlonFR * cd - FlatFR * sd) * tw / 2 + (FlonFR * sd + FlatFR * cd) * lF -
+              (FlonFL * cd - FlatFL * sd) * tw / 2 + (FlonFL * sd + FlatFL * cd) * lF +
+              FlonRR * tw / 2 - FlatRR * lR - FlonRL * tw / 2 - FlatRL * lR;
+}
+
+void fdyn6(const double* x, const double* u, const double* p, const Track& tr, double* f) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5];
+  const double m = p[P_M];
+  double F0[3], F1[3], F2[3];
+  fdyn6_forces(x, p, 0.0, 0.0, F0);
+  fdyn6_forces(x, p, 1.0, 0.0, F1);
+  fdyn6_forces(x, p, 0.0, 1.0, F2);
+  // m a = F0 + Gx a_x + Gy a_y  (first two rows)  ->  2x2 solve
+  const double a11 = m - (F1[0] - F0[0]), a12 = -(F2[0] - F0[0]);
+  const double a21 = -(F1[1] - F0[1]), a22 = m - (F2[1] - F0[1]);
+  const double det = a11 * a22 - a12 * a21;
+  const double ax = (F0[0] * a22 - a12 * F0[1]) / det;
+  const double ay = (a11 * F0[1] - a21 * F0[0]) / det;
+  const double Mz = F0[2] + (F1[2] - F0[2]) * ax + (F2[2] - F0[2]) * ay;
+  double kap, dkap;
+  kappa_lookup(tr, x[0], kap, dkap);
+  const double cp = std::cos(psi), sp = std::sin(psi);
+  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+  f[0] = sdot;
+  f[1] = vx * sp + vy * cp;
+  f[2] = r - kap * sdot;
+  f[3] = ax + vy * r;  // a_x = vxdot - vy r
+  f[4] = ay - vx * r;  // a_y = vydot + vx r
+  f[5] = Mz / p[P_IZ];
+  f[6] = (u[0] - x[6]) / p[P_TT];
+  f[7] = (u[1] - x[7]) / p[P_TD];
+}
+
+typedef void (*rhs_fn)(const double*, const double*, const double*, const Track&, double*);
+void fkin6_rhs(const double* x, const double* u, const double* p, const Track& tr, double* f) {
+  fkin6(x, u, p, tr, f, nullptr);
+}
+
+// ---------------------------------------------------------------------------------------
+// small dense linear algebra
+// ---------------------------------------------------------------------------------------
+// LU with partial pivoting, in place, n x n row-major.  Returns false if singular.
+bool lu_factor(int n, double* A, int* piv) {
+  for (int c = 0; c < n; c++) {
+    int pr = c;
+    double best = std::fabs(A[c * n + c]);
+    for (int r = c + 1; r < n; r++)
+      if (std::fabs(A[r * n + c]) > best) { best = std::fabs(A[r * n + c]); pr = r; }
+    piv[c] = pr;
+    if (!(best > 0.0)) return false;
+    if (pr != c)
+      for (int j = 0; j < n; j++) std::swap(A[c * n + j], A[pr * n + j]);
+    const double inv = 1.0 / A[c * n + c];
+    for (int r = c + 1; r < n; r++) {
+      const double l = A[r * n + c] * inv;
+      A[r * n + c] = l;
+      for (int j = c + 1; j < n; j++) A[r * n + j] -= l * A[c * n + j];
+    }
+  }
+  return true;
+}
+// solve for nrhs right-hand sides stored column-wise in Bm (n x nrhs row-major)
+void lu_solve(int n, const double* A, const int* piv, double* Bm, int nrhs) {
+  for (int c = 0; c < n; c++)
+    if (piv[c] != c)
+      for (int j = 0; j < nrhs; j++) std::swap(Bm[c * nrhs + j], Bm[piv[c] * nrhs + j]);
+  for (int r = 1; r < n; r++)
+    for (int c = 0; c < r; c++) {
+      const double l = A[r * n + c];
+      for (int j = 0; j < nrhs; j++) Bm[r * nrhs + j] -= l * Bm[c * nrhs + j];
+    }
+  for (int r = n - 1; r >= 0; r--) {
+    for (int c = r + 1; c < n; c++) {
+      const double a = A[r * n + c];
+      for (int j = 0; j < nrhs; j++) Bm[r * nrhs + j] -= a * Bm[c * nrhs + j];
+    }
+    const double inv = 1.0 / A[r * n + r];
+    for (int j = 0; j < nrhs; j++) Bm[r * nrhs + j] *= inv;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// integrators with forward sensitivities.  Output: xn[8], S[8][10] = d xn / d (x,u).
+// ---------------------------------------------------------------------------------------
+// classic RK4, one step (acados ERK, 4 stages, 1 step: old/generate.py:24-26)
+void erk4_sens(const double* x, const double* u, const double* p, const Track& tr, double h,
+               double* xn, double (*S)[NZ]) {
+  static const double a[4] = {0.0, 0.5, 0.5, 1.0}, bw[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+  double k[NX], kprev[NX] = {0}, xs[NX], J[NX][NZ];
+  double dk[NX][NZ], dkprev[NX][NZ] = {{0}}, dxs[NX][NZ];
+  double acc[NX] = {0}, dacc[NX][NZ] = {{0}};
+  for (int st = 0; st < 4; st++) {
+    for (int i = 0; i < NX; i++) {
+      xs[i] = x[i] + h * a[st] * kprev[i];
+      for (int j = 0; j < NZ; j++) dxs[i][j] = (i == j ? 1.0 : 0.0) + h * a[st] * dkprev[i][j];
+    }
+    fkin6(xs, u, p, tr, k, J);
+    for (int i = 0; i < NX; i++)
+      for (int j = 0; j < NZ; j++) {
+        double v = (j >= NX) ? J[i][j] : 0.0;  // direct dependence on u
+        for (int l = 0; l < NX; l++) v += J[i][l] * dxs[l][j];
+        dk[i][j] = v;
+      }
+    for (int i = 0; i < NX; i++) {
+      acc[i] += bw[st] * k[i];
+      kprev[i] = k[i];
+      for (int j = 0; j < NZ; j++) { dacc[i][j] += bw[st] * dk[i][j]; dkprev[i][j] = dk[i][j]; }
+    }
+  }
+  for (int i = 0; i < NX; i++) {
+    xn[i] = x[i] + h * acc[i];
+    if (S)
+      for (int j = 0; j < NZ; j++) S[i][j] = (i == j ? 1.0 : 0.0) + h * dacc[i][j];
+  }
+}
+
+struct Tableau { int ns; const double* A; const double* b; };  // A row-major ns x ns
+
+// Fully implicit RK (collocation) step, Newton on all ns*8 stage derivatives, converged
+// to round-off; sensitivities by the implicit-function theorem on the collocation system
+// (acados IRK: new_python/controller.py:305-307; sim: python/main.py:395-400).
+// If analytic == false the Newton matrix comes from central differences of `rhs` and no
+// sensitivities are produced (plant simulation only).  Returns Newton iterations, <0 on failure.
+int irk_step(rhs_fn rhs, bool analytic, const Tableau& tb, const double* x, const double* u,
+             const double* p, const Track& tr, double h, double* xn, double (*S)[NZ]) {
+  const int ns = tb.ns, n = ns * NX;
+  std::vector<double> K(n), M(n * n), R(n), Js(ns * NX * NZ);
+  std::vector<int> piv(n);
+  double f0[NX];
+  rhs(x, u, p, tr, f0);
+  for (int i = 0; i < ns; i++)
+    for (int a = 0; a < NX; a++) K[i * NX + a] = f0[a];
+  auto stage_state = [&](int i, double* xs) {
+    for (int a = 0; a < NX; a++) {
+      double v = x[a];
+      for (int j = 0; j < ns; j++) v += h * tb.A[i * ns + j] * K[j * NX + a];
+      xs[a] = v;
+    }
+  };
+  auto jac = [&](const double* xs, double* Jout) {  // Jout[8][10]
+    if (analytic) {
+      double ftmp[NX];
+      fkin6(xs, u, p, tr, ftmp, reinterpret_cast<double(*)[NZ]>(Jout));
+    } else {
+      double xp[NX], fp[NX], fm[NX];
+      for (int c = 0; c < NX; c++) {
+        const double e = 1e-6 * (1.0 + std::fabs(xs[c]));
+        std::memcpy(xp, xs, sizeof xp);
+        xp[c] = xs[c] + e; rhs(xp, u, p, tr, fp);
+        xp[c] = xs[c] - e; rhs(xp, u, p, tr, fm);
+        for (int a = 0; a < NX; a++) Jout[a * NZ + c] = (fp[a] - fm[a]) / (2 * e);
+      }
+      for (int a = 0; a < NX; a++) Jout[a * NZ + 8] = Jout[a * NZ + 9] = 0.0;
+    }
+  };
+  int it = 0;
+  bool ok = false;
+  double rprev = std::numeric_limits<double>::infinity();
+  for (; it < 60; it++) {
+    double rmax = 0.0, kmax = 0.0;
+    for (int i = 0; i < ns; i++) {
+      double xs[NX], fs[NX];
+      stage_state(i, xs);
+      rhs(xs, u, p, tr, fs);
+      jac(xs, &Js[i * NX * NZ]);
+      for (int a = 0; a < NX; a++) {
+        R[i * NX + a] = K[i * NX + a] - fs[a];
+        rmax = std::max(rmax, std::fabs(R[i * NX + a]));
+        kmax = std::max(kmax, std::fabs(K[i * NX + a]));
+      }
+    }
+    if (!(rmax == rmax)) return -1;
+    for (int i = 0; i < ns; i++)
+      for (int a = 0; a < NX; a++)
+        for (int j = 0; j < ns; j++)
+          for (int c = 0; c < NX; c++)
+            M[(i * NX + a) * n + j * NX + c] =
+                ((i == j && a == c) ? 1.0 : 0.0) - h * tb.A[i * ns + j] * Js[(i * NX + a) * NZ + c];
+    if (!lu_factor(n, M.data(), piv.data())) return -2;
+    // converged to round-off: tiny residual, or stagnation at the floor set by the stiff
+    // actuator rows (an error eps in T is amplified by 1/t_T in the residual)
+    if (rmax <= 4e-15 * (1.0 + kmax) || (it >= 2 && rmax >= 0.25 * rprev && rmax <= 1e-9 * (1.0 + kmax))) {
+      ok = true; break;
+    }
+    rprev = rmax;
+    lu_solve(n, M.data(), piv.data(), R.data(), 1);
+    for (int q = 0; q < n; q++) K[q] -= R[q];
+  }
+  if (!ok) return -3;
+  for (int a = 0; a < NX; a++) {
+    double v = x[a];
+    for (int i = 0; i < ns; i++) v += h * tb.b[i] * K[i * NX + a];
+    xn[a] = v;
+  }
+  if (S && analytic) {
+    // M dK/dw = [J_x(X_i) | J_u(X_i)]  (M factored at the converged point above)
+    std::vector<double> dK(n * NZ);
+    for (int i = 0; i < ns; i++)
+      for (int a = 0; a < NX; a++)
+        for (int c = 0; c < NZ; c++) dK[(i * NX + a) * NZ + c] = Js[(i * NX + a) * NZ + c];
+    lu_solve(n, M.data(), piv.data(), dK.data(), NZ);
+    for (int a = 0; a < NX; a++)
+      for (int c = 0; c < NZ; c++) {
+        double v = (a == c) ? 1.0 : 0.0;
+        for (int i = 0; i < ns; i++) v += h * tb.b[i] * dK[(i * NX + a) * NZ + c];
+        S[a][c] = v;
+      }
+  }
+  return it;
+}
+
+}  // namespace (model + integrators)
+
+#include "../include/ihm2b.h"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------
+// OCP -> QP (python/mpc.py:29-101, new_python/controller.py:320-385) in absolute variables
+// z_k = (u_k, x_k).  The LINEAR_LS cost is exactly quadratic and all path constraints are
+// linear, so only the dynamics are linearised.
+// ---------------------------------------------------------------------------------------
+struct Row { double c[NZ]; double lb, ub; };
+
+struct Qp {
+  int N;
+  std::vector<double> A, B, c;        // [N][8][8], [N][8][2], [N][8]: x+ = A x + B u + c
+  std::vector<double> H, g;           // [N+1][10][10], [N+1][10]
+  std::vector<std::vector<Row>> rows; // [N+1]
+  double x0[NX];
+};
+
+void build_cost(const ihm2b_config& cf, double s0, Qp& qp) {
+  const int N = cf.N;
+  qp.H.assign((N + 1) * NZ * NZ, 0.0);
+  qp.g.assign((N + 1) * NZ, 0.0);
+  for (int k = 0; k <= N; k++) {
+    double* H = &qp.H[k * NZ * NZ];
+    double* g = &qp.g[k * NZ];
+    if (k < N) {
+      // y = Vx x + Vu u : rows 0-7 x, rows 8-9 u, rows 10-11 (T - u_T, delta - u_delta)
+      double V[IHM2B_NY][NZ] = {{0}};
+      for (int i = 0; i < NX; i++) V[i][NU + i] = 1.0;
+      for (int i = 0; i < NU; i++) V[NX + i][i] = 1.0;
+      V[10][NU + 6] = 1.0; V[10][0] = -1.0;
+      V[11][NU + 7] = 1.0; V[11][1] = -1.0;
+      double yref[IHM2B_NY] = {0};
+      yref[0] = s0 + cf.s_target * k / N;  // controller.py:374-382
+      for (int r = 0; r < IHM2B_NY; r++) {
+        const double w = cf.cost_scale_stage * cf.W[r];
+        for (int a = 0; a < NZ; a++) {
+          g[a] -= w * V[r][a] * yref[r];
+          for (int b = 0; b < NZ; b++) H[a * NZ + b] += w * V[r][a] * V[r][b];
+        }
+      }
+    } else {
+      for (int i = 0; i < NX; i++) H[(NU + i) * NZ + NU + i] = cf.cost_scale_terminal * cf.W_e[i];
+      g[NU + 0] = -cf.cost_scale_terminal * cf.W_e[0] * (s0 + cf.s_target);  // controller.py:383-385
+      for (int i = 0; i < NU; i++) H[i * NZ + i] = 1.0;  // unused u_N, keeps H regular
+    }
+  }
+}
+
+void build_rows(const ihm2b_config& cf, Qp& qp) {
+  const int N = cf.N;
+  qp.rows.assign(N + 1, {});
+  auto unit = [](int idx, double lb, double ub) {
+    Row r; std::memset(&r, 0, sizeof r); r.c[idx] = 1.0; r.lb = lb; r.ub = ub; return r;
+  };
+  for (int k = 0; k <= N; k++) {
+    auto& R = qp.rows[k];
+    if (k < N) {
+      R.push_back(unit(0, -cf.T_max, cf.T_max));          // idxbu (mpc.py:86-89)
+      R.push_back(unit(1, -cf.delta_max, cf.delta_max));
+      Row g0; std::memset(&g0, 0, sizeof g0);             // C, D (mpc.py:91-99)
+      g0.c[0] = 1.0; g0.c[NU + 6] = -1.0; g0.lb = -cf.g_T_max; g0.ub = cf.g_T_max;
+      Row g1; std::memset(&g1, 0, sizeof g1);
+      g1.c[1] = 1.0; g1.c[NU + 7] = -1.0; g1.lb = -cf.g_delta_max; g1.ub = cf.g_delta_max;
+      R.push_back(g0); R.push_back(g1);
+      if (k > 0) {  // idxbx = [1,3,6,7] (mpc.py:78-80); stage 0 carries x0 instead
+        R.push_back(unit(NU + 1, -cf.n_max, cf.n_max));
+        R.push_back(unit(NU + 3, 0.0, cf.v_x_max));
+        R.push_back(unit(NU + 6, -cf.T_max, cf.T_max));
+        R.push_back(unit(NU + 7, -cf.delta_max, cf.delta_max));
+      }
+    } else {  // idxbx_e = [1,3,4,5] with the n / v_x / T / delta bounds (literal, mpc.py:81-83)
+      R.push_back(unit(NU + 1, -cf.n_max, cf.n_max));
+      R.push_back(unit(NU + 3, -cf.v_x_max, cf.v_x_max));
+      R.push_back(unit(NU + 4, -cf.T_max, cf.T_max));
+      R.push_back(unit(NU + 5, -cf.delta_max, cf.delta_max));
+    }
+  }
+}
+
+struct QpSol {
+  std::vector<double> z;     // [N+1][10]
+  std::vector<double> pi;    // [N+1][8]  (pi[0] unused)
+  std::vector<std::vector<double>> lamL, lamU, tL, tU;
+  int iters, status;         // status: 0 ok, 1 max iter, 2 min step, 3 nan
+  double mu, res_g, res_b, res_d, res_m, mag_g, mag_b, mag_d;
+};
+
+// Mehrotra predictor-corrector primal-dual IPM; KKT step by a Riccati recursion
+// (what HPIPM's d_ocp_qp_ipm_solve does: SURVEY App. C).  Works on the residual (delta)
+// form of the Newton system, x_0 is held fixed (stage 0 embeds the measured state).
+void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
+  const int N = qp.N;
+  const double tau = 0.995, thr0 = 0.1;
+  // ---- initialisation: primal from the caller (warm), slacks / multipliers cold ----
+  for (int a = 0; a < NX; a++) s.z[NU + a] = qp.x0[a];
+  s.pi.assign((N + 1) * NX, 0.0);
+  s.lamL.assign(N + 1, {}); s.lamU.assign(N + 1, {}); s.tL.assign(N + 1, {}); s.tU.assign(N + 1, {});
+  int nineq = 0;
+  for (int k = 0; k <= N; k++) {
+    const auto& R = qp.rows[k];
+    const int nr = (int)R.size();
+    s.lamL[k].resize(nr); s.lamU[k].resize(nr); s.tL[k].resize(nr); s.tU[k].resize(nr);
+    for (int r = 0; r < nr; r++) {
+      double cz = 0;
+      for (int a = 0; a < NZ; a++) cz += R[r].c[a] * s.z[k * NZ + a];
+      s.tL[k][r] = std::max(cz - R[r].lb, thr0);
+      s.tU[k][r] = std::max(R[r].ub - cz, thr0);
+      s.lamL[k][r] = cf.qp_mu0 / s.tL[k][r];
+      s.lamU[k][r] = cf.qp_mu0 / s.tU[k][r];
+      nineq += 2;
+    }
+  }
+  std::vector<double> rg((N + 1) * NZ), rb(N * NX);
+  std::vector<std::vector<double>> rdL(N + 1), rdU(N + 1), rmL(N + 1), rmU(N + 1);
+  std::vector<std::vector<double>> dlamL(N + 1), dlamU(N + 1), dtL(N + 1), dtU(N + 1);
+  for (int k = 0; k <= N; k++) {
+    const size_t nr = qp.rows[k].size();
+    rdL[k].resize(nr); rdU[k].resize(nr); rmL[k].resize(nr); rmU[k].resize(nr);
+    dlamL[k].resize(nr); dlamU[k].resize(nr); dtL[k].resize(nr); dtU[k].resize(nr);
+  }
+  std::vector<double> Ht((N + 1) * NZ * NZ), rgt((N + 1) * NZ);
+  std::vector<double> P((N + 1) * NX * NX), pv((N + 1) * NX), Kfb(N * NU * NX), kff(N * NU);
+  std::vector<double> Linv(N * 4), dz((N + 1) * NZ), dpi((N + 1) * NX);
+  s.status = 1;
+  int it = 0;
+  for (;; it++) {
+    // ---- residuals ----
+    double mg = 0, mb = 0, md = 0, res_g = 0, res_b = 0, res_d = 0, res_m = 0, mu = 0;
+    for (int k = 0; k <= N; k++) {
+      const double* z = &s.z[k * NZ];
+      for (int a = 0; a < NZ; a++) {
+        double v = qp.g[k * NZ + a];
+        mg = std::max(mg, std::fabs(v));
+        for (int b = 0; b < NZ; b++) v += qp.H[(k * NZ + a) * NZ + b] * z[b];
+        rg[k * NZ + a] = v;
+      }
+      if (k < N) {
+        const double* A = &qp.A[k * NX * NX]; const double* B = &qp.B[k * NX * NU];
+        const double* pin = &s.pi[(k + 1) * NX];
+        for (int a = 0; a < NU; a++)
+          for (int i = 0; i < NX; i++) rg[k * NZ + a] += B[i * NU + a] * pin[i];
+        for (int a = 0; a < NX; a++)
+          for (int i = 0; i < NX; i++) rg[k * NZ + NU + a] += A[i * NX + a] * pin[i];
+        for (int i = 0; i < NX; i++) {
+          double v = qp.c[k * NX + i];
+          mb = std::max(mb, std::fabs(v));
+          for (int a = 0; a < NX; a++) v += A[i * NX + a] * z[NU + a];
+          for (int a = 0; a < NU; a++) v += B[i * NU + a] * z[a];
+          rb[k * NX + i] = v - s.z[(k + 1) * NZ + NU + i];
+          res_b = std::max(res_b, std::fabs(rb[k * NX + i]));
+        }
+      }
+      for (int a = 0; a < NX; a++) rg[k * NZ + NU + a] -= s.pi[k * NX + a];
+      const auto& R = qp.rows[k];
+      for (size_t r = 0; r < R.size(); r++) {
+        double cz = 0;
+        for (int a = 0; a < NZ; a++) cz += R[r].c[a] * z[a];
+        for (int a = 0; a < NZ; a++) rg[k * NZ + a] -= R[r].c[a] * (s.lamL[k][r] - s.lamU[k][r]);
+        rdL[k][r] = cz - R[r].lb - s.tL[k][r];
+        rdU[k][r] = R[r].ub - cz - s.tU[k][r];
+        md = std::max(md, std::max(std::fabs(R[r].lb), std::fabs(R[r].ub)));
+        res_d = std::max(res_d, std::max(std::fabs(rdL[k][r]), std::fabs(rdU[k][r])));
+        rmL[k][r] = s.lamL[k][r] * s.tL[k][r];
+        rmU[k][r] = s.lamU[k][r] * s.tU[k][r];
+        res_m = std::max(res_m, std::max(rmL[k][r], rmU[k][r]));
+        mu += rmL[k][r] + rmU[k][r];
+      }
+      const int a0 = (k == 0) ? NU : NZ;  // x_0 is not a variable
+      for (int a = 0; a < (k == 0 ? NU : NZ); a++) res_g = std::max(res_g, std::fabs(rg[k * NZ + a]));
+      if (k == 0) for (int a = a0; a < NZ; a++) rg[a] = 0.0;
+    }
+    mu /= nineq;
+    s.mu = mu; s.res_g = res_g; s.res_b = res_b; s.res_d = res_d; s.res_m = res_m; s.iters = it;
+    s.mag_g = mg; s.mag_b = mb; s.mag_d = md;
+    if (!(res_g == res_g) || !(res_b == res_b) || !(mu == mu)) { s.status = 3; return; }
+    const double tol = cf.qp_tol;
+    if (res_g <= tol * (1 + mg) && res_b <= tol * (1 + mb) && res_d <= tol * (1 + md) && res_m <= cf.qp_tol_comp) {
+      s.status = 0; return;
+    }
+    if (it >= cf.qp_max_iter) { s.status = 1; return; }
+
+    auto kkt_solve = [&]() {
+      // modified Hessian / gradient
+      for (int k = 0; k <= N; k++) {
+        for (int q = 0; q < NZ * NZ; q++) Ht[k * NZ * NZ + q] = qp.H[k * NZ * NZ + q];
+        for (int a = 0; a < NZ; a++) rgt[k * NZ + a] = rg[k * NZ + a];
+        const auto& R = qp.rows[k];
+        for (size_t r = 0; r < R.size(); r++) {
+          const double gam = s.lamL[k][r] / s.tL[k][r] + s.lamU[k][r] / s.tU[k][r];
+          const double q = (rmL[k][r] + s.lamL[k][r] * rdL[k][r]) / s.tL[k][r] -
+                           (rmU[k][r] + s.lamU[k][r] * rdU[k][r]) / s.tU[k][r];
+          for (int a = 0; a < NZ; a++) {
+            rgt[k * NZ + a] += R[r].c[a] * q;
+            for (int b = 0; b < NZ; b++) Ht[(k * NZ + a) * NZ + b] += gam * R[r].c[a] * R[r].c[b];
+          }
+        }
+      }
+      // backward Riccati
+      for (int a = 0; a < NX; a++) {
+        pv[N * NX + a] = rgt[N * NZ + NU + a];
+        for (int b = 0; b < NX; b++) P[(N * NX + a) * NX + b] = Ht[(N * NZ + NU + a) * NZ + NU + b];
+      }
+      for (int k = N - 1; k >= 0; k--) {
+        const double* A = &qp.A[k * NX * NX]; const double* B = &qp.B[k * NX * NU];
+        const double* Pn = &P[(k + 1) * NX * NX];
+        double BA[NX][NZ], W[NX][NZ], v[NX], M[NZ][NZ], mv[NZ];
+        for (int i = 0; i < NX; i++) {
+          for (int a = 0; a < NU; a++) BA[i][a] = B[i * NU + a];
+          for (int a = 0; a < NX; a++) BA[i][NU + a] = A[i * NX + a];
+        }
+        for (int i = 0; i < NX; i++) {
+          double acc = pv[(k + 1) * NX + i];
+          for (int j = 0; j < NX; j++) acc += Pn[i * NX + j] * rb[k * NX + j];
+          v[i] = acc;
+          for (int a = 0; a < NZ; a++) {
+            double w = 0;
+            for (int j = 0; j < NX; j++) w += Pn[i * NX + j] * BA[j][a];
+            W[i][a] = w;
+          }
+        }
+        for (int a = 0; a < NZ; a++) {
+          double acc = rgt[k * NZ + a];
+          for (int i = 0; i < NX; i++) acc += BA[i][a] * v[i];
+          mv[a] = acc;
+          for (int b = 0; b < NZ; b++) {
+            double mm = Ht[(k * NZ + a) * NZ + b];
+            for (int i = 0; i < NX; i++) mm += BA[i][a] * W[i][b];
+            M[a][b] = mm;
+          }
+        }
+        // 2x2 inverse of M_uu
+        const double det = M[0][0] * M[1][1] - M[0][1] * M[1][0];
+        const double i00 = M[1][1] / det, i01 = -M[0][1] / det, i10 = -M[1][0] / det, i11 = M[0][0] / det;
+        Linv[k * 4 + 0] = i00; Linv[k * 4 + 1] = i01; Linv[k * 4 + 2] = i10; Linv[k * 4 + 3] = i11;
+        for (int b = 0; b < NX; b++) {
+          Kfb[(k * NU + 0) * NX + b] = -(i00 * M[0][NU + b] + i01 * M[1][NU + b]);
+          Kfb[(k * NU + 1) * NX + b] = -(i10 * M[0][NU + b] + i11 * M[1][NU + b]);
+        }
+        kff[k * NU + 0] = -(i00 * mv[0] + i01 * mv[1]);
+        kff[k * NU + 1] = -(i10 * mv[0] + i11 * mv[1]);
+        for (int a = 0; a < NX; a++) {
+          pv[k * NX + a] = mv[NU + a] + M[NU + a][0] * kff[k * NU] + M[NU + a][1] * kff[k * NU + 1];
+          for (int b = 0; b < NX; b++)
+            P[(k * NX + a) * NX + b] = M[NU + a][NU + b] + M[NU + a][0] * Kfb[(k * NU + 0) * NX + b] +
+                                       M[NU + a][1] * Kfb[(k * NU + 1) * NX + b];
+        }
+        for (int a = 0; a < NX; a++)
+          for (int b = a + 1; b < NX; b++) {
+            const double sym = 0.5 * (P[(k * NX + a) * NX + b] + P[(k * NX + b) * NX + a]);
+            P[(k * NX + a) * NX + b] = P[(k * NX + b) * NX + a] = sym;
+          }
+      }
+      // forward
+      for (int a = 0; a < NX; a++) dz[NU + a] = 0.0;  // x_0 fixed
+      for (int k = 0; k < N; k++) {
+        const double* A = &qp.A[k * NX * NX]; const double* B = &qp.B[k * NX * NU];
+        for (int a = 0; a < NU; a++) {
+          double acc = kff[k * NU + a];
+          for (int b = 0; b < NX; b++) acc += Kfb[(k * NU + a) * NX + b] * dz[k * NZ + NU + b];
+          dz[k * NZ + a] = acc;
+        }
+        for (int i = 0; i < NX; i++) {
+          double acc = rb[k * NX + i];
+          for (int a = 0; a < NX; a++) acc += A[i * NX + a] * dz[k * NZ + NU + a];
+          for (int a = 0; a < NU; a++) acc += B[i * NU + a] * dz[k * NZ + a];
+          dz[(k + 1) * NZ + NU + i] = acc;
+        }
+        for (int i = 0; i < NX; i++) {
+          double acc = pv[(k + 1) * NX + i];
+          for (int j = 0; j < NX; j++) acc += P[((k + 1) * NX + i) * NX + j] * dz[(k + 1) * NZ + NU + j];
+          dpi[(k + 1) * NX + i] = acc;  // costate of the delta problem = multiplier step
+        }
+      }
+      dz[N * NZ] = dz[N * NZ + 1] = 0.0;
+      // recover slack / multiplier steps
+      for (int k = 0; k <= N; k++) {
+        const auto& R = qp.rows[k];
+        for (size_t r = 0; r < R.size(); r++) {
+          double cdz = 0;
+          for (int a = 0; a < NZ; a++) cdz += R[r].c[a] * dz[k * NZ + a];
+          dtL[k][r] = cdz + rdL[k][r];
+          dtU[k][r] = -cdz + rdU[k][r];
+          dlamL[k][r] = -(rmL[k][r] + s.lamL[k][r] * dtL[k][r]) / s.tL[k][r];
+          dlamU[k][r] = -(rmU[k][r] + s.lamU[k][r] * dtU[k][r]) / s.tU[k][r];
+        }
+      }
+    };
+    auto max_step = [&]() {
+      double al = 1.0;
+      for (int k = 0; k <= N; k++)
+        for (size_t r = 0; r < qp.rows[k].size(); r++) {
+          if (dlamL[k][r] < 0) al = std::min(al, -s.lamL[k][r] / dlamL[k][r]);
+          if (dlamU[k][r] < 0) al = std::min(al, -s.lamU[k][r] / dlamU[k][r]);
+          if (dtL[k][r] < 0) al = std::min(al, -s.tL[k][r] / dtL[k][r]);
+          if (dtU[k][r] < 0) al = std::min(al, -s.tU[k][r] / dtU[k][r]);
+        }
+      return al;
+    };
+    // ---- predictor ----
+    kkt_solve();
+    const double al_aff = max_step();
+    double mu_aff = 0;
+    for (int k = 0; k <= N; k++)
+      for (size_t r = 0; r < qp.rows[k].size(); r++) {
+        mu_aff += (s.lamL[k][r] + al_aff * dlamL[k][r]) * (s.tL[k][r] + al_aff * dtL[k][r]);
+        mu_aff += (s.lamU[k][r] + al_aff * dlamU[k][r]) * (s.tU[k][r] + al_aff * dtU[k][r]);
+      }
+    mu_aff /= nineq;
+    const double sig = std::pow(mu_aff / mu, 3.0);
+    // centring target; floored so the iterates stay on the central path at mu ~ 0.1 tol_comp
+    // instead of diving to round-off, which wrecks the conditioning of the Riccati recursion
+    const double mu_t = std::max(sig * mu, 0.1 * cf.qp_tol_comp);
+    // ---- corrector ----
+    for (int k = 0; k <= N; k++)
+      for (size_t r = 0; r < qp.rows[k].size(); r++) {
+        rmL[k][r] += dlamL[k][r] * dtL[k][r] - mu_t;
+        rmU[k][r] += dlamU[k][r] * dtU[k][r] - mu_t;
+      }
+    kkt_solve();
+    const double al = std::min(1.0, tau * max_step());
+    if (al < 1e-12) { s.status = 2; return; }
+    for (int k = 0; k <= N; k++) {
+      for (int a = 0; a < NZ; a++) s.z[k * NZ + a] += al * dz[k * NZ + a];
+      if (k > 0) for (int a = 0; a < NX; a++) s.pi[k * NX + a] += al * dpi[k * NX + a];
+      for (size_t r = 0; r < qp.rows[k].size(); r++) {
+        s.lamL[k][r] += al * dlamL[k][r]; s.lamU[k][r] += al * dlamU[k][r];
+        s.tL[k][r] += al * dtL[k][r]; s.tU[k][r] += al * dtU[k][r];
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// SQP / SQP-RTI driver for one problem (acados ocp_nlp_sqp / ocp_nlp_sqp_rti restated:
+// SURVEY App. C; call site new_python/controller.py:396).
+// ---------------------------------------------------------------------------------------
+struct Problem {
+  const ihm2b_config* cf;
+  Track tr;
+  const double* p;
+};
+
+int integrate_ctrl(const Problem& pb, const double* x, const double* u, double* xn, double (*S)[NZ]) {
+  const ihm2b_config& cf = *pb.cf;
+  if (cf.integrator == IHM2B_ERK4) { erk4_sens(x, u, pb.p, pb.tr, cf.dt, xn, S); return 0; }
+  Tableau tb{4, cf.irk_A, cf.irk_b};
+  return irk_step(fkin6_rhs, true, tb, x, u, pb.p, pb.tr, cf.dt, xn, S);
+}
+
+// linearise the dynamics along (x, u); fills qp.A, qp.B, qp.c and phi. Returns false on NaN/failure.
+bool linearize(const Problem& pb, const double* x, const double* u, Qp& qp, double* phi) {
+  const int N = pb.cf->N;
+  qp.A.resize(N * NX * NX); qp.B.resize(N * NX * NU); qp.c.resize(N * NX);
+  bool ok = true;
+  for (int k = 0; k < N; k++) {
+    double S[NX][NZ], xn[NX];
+    if (integrate_ctrl(pb, &x[k * NX], &u[k * NU], xn, S) < 0) ok = false;
+    for (int i = 0; i < NX; i++) {
+      double c = xn[i];
+      for (int a = 0; a < NX; a++) { qp.A[(k * NX + i) * NX + a] = S[i][a]; c -= S[i][a] * x[k * NX + a]; }
+      for (int a = 0; a < NU; a++) { qp.B[(k * NX + i) * NU + a] = S[i][NX + a]; c -= S[i][NX + a] * u[k * NU + a]; }
+      qp.c[k * NX + i] = c;
+      phi[k * NX + i] = xn[i];
+      if (!(xn[i] == xn[i])) ok = false;
+    }
+  }
+  return ok;
+}
+
+struct SolveOut { int status, qp_iters, sqp_iters; double mu, res_stat, res_eq, res_ineq, res_comp, cost; };
+
+double ocp_cost(const ihm2b_config& cf, const Qp& qp, const double* z) {
+  double c = 0;
+  for (int k = 0; k <= cf.N; k++)
+    for (int a = 0; a < NZ; a++) {
+      double hz = 0;
+      for (int b = 0; b < NZ; b++) hz += qp.H[(k * NZ + a) * NZ + b] * z[k * NZ + b];
+      c += z[k * NZ + a] * (0.5 * hz + qp.g[k * NZ + a]);
+    }
+  return c;
+}
+
+void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveOut& out, QpSol* keep,
+               Qp* keep_qp) {
+  const ihm2b_config& cf = *pb.cf;
+  const int N = cf.N;
+  Qp qp; qp.N = N;
+  build_cost(cf, x0[0], qp);
+  build_rows(cf, qp);
+  std::memcpy(qp.x0, x0, sizeof qp.x0);
+  QpSol sol; sol.z.resize((N + 1) * NZ);
+  std::vector<double> phi(N * NX);
+  const int iters = (cf.nlp_solver == IHM2B_SQP_RTI) ? 1 : cf.nlp_max_iter;
+  out = SolveOut{IHM2B_MAXITER, 0, 0, 0, 0, 0, 0, 0, 0};
+  bool have_mult = false;
+  for (int it = 0; it < iters; it++) {
+    if (!linearize(pb, x, u, qp, phi.data())) { out.status = IHM2B_FAILURE; break; }
+    if (cf.nlp_solver == IHM2B_SQP) {
+      // NLP KKT residuals at the current iterate with the last QP multipliers
+      double rs = 0, re = 0, ri = 0, rc = 0;
+      for (int a = 0; a < NX; a++) re = std::max(re, std::fabs(x[a] - x0[a]));
+      for (int k = 0; k <= N; k++) {
+        double z[NZ] = {0};
+        if (k < N) { z[0] = u[k * NU]; z[1] = u[k * NU + 1]; }
+        for (int a = 0; a < NX; a++) z[NU + a] = x[k * NX + a];
+        if (k < N)
+          for (int i = 0; i < NX; i++) re = std::max(re, std::fabs(phi[k * NX + i] - x[(k + 1) * NX + i]));
+        double rg[NZ];
+        for (int a = 0; a < NZ; a++) {
+          double v = qp.g[k * NZ + a];
+          for (int b = 0; b < NZ; b++) v += qp.H[(k * NZ + a) * NZ + b] * z[b];
+          rg[a] = v;
+        }
+        if (have_mult) {
+          if (k < N)
+            for (int i = 0; i < NX; i++) {
+              for (int a = 0; a < NU; a++) rg[a] += qp.B[(k * NX + i) * NU + a] * sol.pi[(k + 1) * NX + i];
+              for (int a = 0; a < NX; a++) rg[NU + a] += qp.A[(k * NX + i) * NX + a] * sol.pi[(k + 1) * NX + i];
+            }
+          for (int a = 0; a < NX; a++) rg[NU + a] -= sol.pi[k * NX + a];
+        }
+        for (size_t r = 0; r < qp.rows[k].size(); r++) {
+          const Row& R = qp.rows[k][r];
+          double cz = 0;
+          for (int a = 0; a < NZ; a++) cz += R.c[a] * z[a];
+          ri = std::max(ri, std::max(R.lb - cz, cz - R.ub));
+          if (have_mult) {
+            for (int a = 0; a < NZ; a++) rg[a] -= R.c[a] * (sol.lamL[k][r] - sol.lamU[k][r]);
+            rc = std::max(rc, std::max(std::fabs(sol.lamL[k][r] * (cz - R.lb)), std::fabs(sol.lamU[k][r] * (R.ub - cz))));
+          }
+        }
+        for (int a = (k == 0 ? 0 : 0); a < (k == 0 ? NU : NZ); a++) rs = std::max(rs, std::fabs(rg[a]));
+        if (k == N) { /* u_N dummy */ }
+      }
+      ri = std::max(ri, 0.0);
+      if (!have_mult) rs = rc = std::numeric_limits<double>::infinity();
+      out.res_stat = rs; out.res_eq = re; out.res_ineq = ri; out.res_comp = rc;
+      if (have_mult && rs <= cf.nlp_tol && re <= cf.nlp_tol && ri <= cf.nlp_tol && rc <= cf.nlp_tol) {
+        out.status = IHM2B_SUCCESS; break;
+      }
+    }
+    for (int k = 0; k <= N; k++) {
+      sol.z[k * NZ] = (k < N) ? u[k * NU] : 0.0;
+      sol.z[k * NZ + 1] = (k < N) ? u[k * NU + 1] : 0.0;
+      for (int a = 0; a < NX; a++) sol.z[k * NZ + NU + a] = x[k * NX + a];
+    }
+    ipm_solve(cf, qp, sol);
+    out.qp_iters += sol.iters; out.sqp_iters = it + 1; out.mu = sol.mu;
+    if (sol.status == 3) { out.status = IHM2B_FAILURE; break; }
+    if (sol.status != 0) {
+      // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
+      const bool loose = sol.res_g <= 1e-6 * (1 + sol.mag_g) && sol.res_b <= 1e-6 * (1 + sol.mag_b) &&
+                         sol.res_d <= 1e-6 * (1 + sol.mag_d) && sol.res_m <= 1e-6;
+      if (!loose) { out.status = IHM2B_QP_FAILURE; break; }
+    }
+    have_mult = true;
+    const double alpha = 1.0;  // FIXED_STEP; (RTI always takes the full step)
+    for (int k = 0; k <= N; k++) {
+      if (k < N) for (int a = 0; a < NU; a++) u[k * NU + a] += alpha * (sol.z[k * NZ + a] - u[k * NU + a]);
+      for (int a = 0; a < NX; a++) x[k * NX + a] += alpha * (sol.z[k * NZ + NU + a] - x[k * NX + a]);
+    }
+    if (cf.nlp_solver == IHM2B_SQP_RTI) out.status = IHM2B_SUCCESS;
+  }
+  std::vector<double> z((N + 1) * NZ, 0.0);
+  for (int k = 0; k <= N; k++) {
+    if (k < N) { z[k * NZ] = u[k * NU]; z[k * NZ + 1] = u[k * NU + 1]; }
+    for (int a = 0; a < NX; a++) z[k * NZ + NU + a] = x[k * NX + a];
+  }
+  out.cost = ocp_cost(cf, qp, z.data());
+  if (keep) *keep = sol;
+  if (keep_qp) *keep_qp = qp;
+}
+
+// ---------------------------------------------------------------------------------------
+// plant step (python/main.py:395-400, 475-502): Radau-IIA collocation, sim_steps sub-steps,
+// model switch on the kinematic lateral acceleration.
+// ---------------------------------------------------------------------------------------
+int sim_step(const Problem& pb, const double* x, const double* u, double* xn) {
+  const ihm2b_config& cf = *pb.cf;
+  int model = cf.sim_model;
+  if (model == IHM2B_SIM_KIN6_DYN6) {
+    const double C = pb.p[P_LR] / (pb.p[P_LR] + pb.p[P_LF]);
+    const double beta = std::atan(C * std::tan(x[7]));
+    const double v2 = x[3] * x[3] + x[4] * x[4];
+    model = (v2 * std::sin(beta) / pb.p[P_LR] <= cf.sim_switch) ? IHM2B_SIM_FKIN6 : IHM2B_SIM_FDYN6;
+  }
+  Tableau tb{4, cf.sim_A, cf.sim_b};
+  const double h = cf.dt / cf.sim_steps;
+  double xc[NX], xt[NX];
+  std::memcpy(xc, x, sizeof xc);
+  for (int st = 0; st < cf.sim_steps; st++) {
+    int rc = (model == IHM2B_SIM_FKIN6)
+                 ? irk_step(fkin6_rhs, true, tb, xc, u, pb.p, pb.tr, h, xt, nullptr)
+                 : irk_step(fdyn6, false, tb, xc, u, pb.p, pb.tr, h, xt, nullptr);
+    if (rc < 0) {
+      for (int a = 0; a < NX; a++) xn[a] = std::numeric_limits<double>::quiet_NaN();
+      return model;
+    }
+    std::memcpy(xc, xt, sizeof xc);
+  }
+  std::memcpy(xn, xc, sizeof xc);
+  return model;
+}
+
+void shift_iterate(int N, double* x, double* u) {  // controller.py:388-393 (literal)
+  for (int j = 0; j < N - 1; j++) {
+    std::memcpy(&x[j * NX], &x[(j + 1) * NX], NX * sizeof(double));
+    std::memcpy(&u[j * NU], &u[(j + 1) * NU], NU * sizeof(double));
+  }
+  std::memcpy(&x[(N - 1) * NX], &x[N * NX], NX * sizeof(double));
+  u[(N - 1) * NU] = u[(N - 1) * NU + 1] = 0.0;
+}
+
+}  // namespace
+
+// =======================================================================================
+// C ABI (host memory, batch-major rows).  Mirrors include/ihm2b.h so one Python harness can
+// drive both sides of a parity test.
+// =======================================================================================
+extern "C" {
+
+int ihm2o_np(void) { return NP; }
+
+void ihm2o_fkin6(const double* x, const double* u, const double* p, const double* s_ref,
+                 const double* kappa_ref, int n_grid, double* f, double* J /* [8][10] or NULL */) {
+  Track tr{n_grid, s_ref, kappa_ref};
+  fkin6(x, u, p, tr, f, reinterpret_cast<double(*)[NZ]>(J));
+}
+
+void ihm2o_fdyn6(const double* x, const double* u, const double* p, const double* s_ref,
+                 const double* kappa_ref, int n_grid, double* f) {
+  Track tr{n_grid, s_ref, kappa_ref};
+  fdyn6(x, u, p, tr, f);
+}
+
+// kind 0: ERK4; 1: IRK with analytic Newton (fkin6); 2: IRK on fdyn6 (no sensitivities)
+int ihm2o_integrate(int kind, const double* tabA, const double* tabb, double h, const double* x,
+                    const double* u, const double* p, const double* s_ref, const double* kappa_ref,
+                    int n_grid, double* xn, double* S /* [8][10] or NULL */) {
+  Track tr{n_grid, s_ref, kappa_ref};
+  Tableau tb{4, tabA, tabb};
+  auto Sm = reinterpret_cast<double(*)[NZ]>(S);
+  if (kind == 0) { erk4_sens(x, u, p, tr, h, xn, Sm); return 0; }
+  if (kind == 1) return irk_step(fkin6_rhs, true, tb, x, u, p, tr, h, xn, Sm);
+  return irk_step(fdyn6, false, tb, x, u, p, tr, h, xn, nullptr);
+}
+
+static Problem make_problem(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                            const int32_t* track_index, const double* params, int i) {
+  const int t = track_index ? track_index[i] : 0;
+  Problem pb;
+  pb.cf = cf;
+  pb.tr = Track{cf->n_grid, s_ref + (size_t)t * cf->n_grid, kappa_ref + (size_t)t * cf->n_grid};
+  pb.p = params + (size_t)i * NP;
+  return pb;
+}
+
+// A [B][N][8][8], Bm [B][N][8][2], phi [B][N][8]
+int ihm2o_linearize(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                    const int32_t* track_index, const double* params, const double* x,
+                    const double* u, double* A, double* Bm, double* phi) {
+  const int N = cf->N;
+  int bad = 0;
+#pragma omp parallel for schedule(dynamic) reduction(+ : bad)
+  for (int i = 0; i < cf->batch; i++) {
+    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    Qp qp; qp.N = N;
+    std::vector<double> ph(N * NX);
+    if (!linearize(pb, x + (size_t)i * (N + 1) * NX, u + (size_t)i * N * NU, qp, ph.data())) bad++;
+    std::memcpy(A + (size_t)i * N * NX * NX, qp.A.data(), sizeof(double) * N * NX * NX);
+    std::memcpy(Bm + (size_t)i * N * NX * NU, qp.B.data(), sizeof(double) * N * NX * NU);
+    std::memcpy(phi + (size_t)i * N * NX, ph.data(), sizeof(double) * N * NX);
+  }
+  return bad;
+}
+
+// One controller call per instance: (optional literal shift) + SQP(-RTI) solve.
+// x [B][N+1][8], u [B][N][2] in/out; u0 [B][2]; status [B]; stats [B][8].
+int ihm2o_solve(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                const int32_t* track_index, const double* params, const double* x0, double* x,
+                double* u, double* u0, int32_t* status, double* stats, int do_shift) {
+  const int N = cf->N;
+#pragma omp parallel for schedule(dynamic)
+  for (int i = 0; i < cf->batch; i++) {
+    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    double* xi = x + (size_t)i * (N + 1) * NX;
+    double* ui = u + (size_t)i * N * NU;
+    if (do_shift) shift_iterate(N, xi, ui);
+    SolveOut so;
+    solve_one(pb, x0 + (size_t)i * NX, xi, ui, so, nullptr, nullptr);
+    status[i] = so.status;
+    u0[i * NU] = ui[0]; u0[i * NU + 1] = ui[1];
+    if (stats) {
+      double* st = stats + (size_t)i * 8;
+      st[0] = so.qp_iters; st[1] = so.sqp_iters; st[2] = so.mu; st[3] = so.res_stat;
+      st[4] = so.res_eq; st[5] = so.res_ineq; st[6] = so.res_comp; st[7] = so.cost;
+    }
+  }
+  return 0;
+}
+
+// Debug view of ONE problem's first QP and its IPM solution, for the KKT-certificate test.
+// Row storage padded to 8 rows per stage: Crow [N+1][8][10], lb/ub/lamL/lamU/tL/tU [N+1][8],
+// nrows [N+1].  z [N+1][10], pi [N+1][8].
+int ihm2o_qp_debug(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                   const double* params, const double* x0, const double* x, const double* u,
+                   double* A, double* Bm, double* c, double* H, double* g, double* Crow, double* lb,
+                   double* ub, int32_t* nrows, double* z, double* pi, double* lamL, double* lamU,
+                   double* tL, double* tU, double* info /* iters,status,mu,res_g,res_b,res_d,res_m */) {
+  const int N = cf->N;
+  ihm2b_config c1 = *cf;
+  c1.batch = 1; c1.nlp_solver = IHM2B_SQP_RTI;
+  Problem pb = make_problem(&c1, s_ref, kappa_ref, nullptr, params, 0);
+  std::vector<double> xi(x, x + (N + 1) * NX), ui(u, u + N * NU);
+  SolveOut so; QpSol sol; Qp qp;
+  solve_one(pb, x0, xi.data(), ui.data(), so, &sol, &qp);
+  std::memcpy(A, qp.A.data(), sizeof(double) * N * NX * NX);
+  std::memcpy(Bm, qp.B.data(), sizeof(double) * N * NX * NU);
+  std::memcpy(c, qp.c.data(), sizeof(double) * N * NX);
+  std::memcpy(H, qp.H.data(), sizeof(double) * (N + 1) * NZ * NZ);
+  std::memcpy(g, qp.g.data(), sizeof(double) * (N + 1) * NZ);
+  for (int k = 0; k <= N; k++) {
+    nrows[k] = (int)qp.rows[k].size();
+    for (int r = 0; r < nrows[k]; r++) {
+      std::memcpy(Crow + ((size_t)k * 8 + r) * NZ, qp.rows[k][r].c, sizeof(double) * NZ);
+      lb[k * 8 + r] = qp.rows[k][r].lb; ub[k * 8 + r] = qp.rows[k][r].ub;
+      lamL[k * 8 + r] = sol.lamL[k][r]; lamU[k * 8 + r] = sol.lamU[k][r];
+      tL[k * 8 + r] = sol.tL[k][r]; tU[k * 8 + r] = sol.tU[k][r];
+    }
+  }
+  std::memcpy(z, sol.z.data(), sizeof(double) * (N + 1) * NZ);
+  std::memcpy(pi, sol.pi.data(), sizeof(double) * (N + 1) * NX);
+  info[0] = sol.iters; info[1] = sol.status; info[2] = sol.mu; info[3] = sol.res_g;
+  info[4] = sol.res_b; info[5] = sol.res_d; info[6] = sol.res_m;
+  return so.status;
+}
+
+// x [B][8], u [B][2] -> xn [B][8], model [B]
+int ihm2o_sim_step(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                   const int32_t* track_index, const double* params, const double* x,
+                   const double* u, double* xn, int32_t* model) {
+#pragma omp parallel for schedule(dynamic)
+  for (int i = 0; i < cf->batch; i++) {
+    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    const int m = sim_step(pb, x + (size_t)i * NX, u + (size_t)i * NU, xn + (size_t)i * NX);
+    if (model) model[i] = m;
+  }
+  return 0;
+}
+
+// python/main.py:448-517 with the NMPC enabled.  xs [B][8] in/out; iterate x/u in/out;
+// xlog [n_steps+1][B][8], ulog [n_steps][B][2] (optional); done/fail [B] step index or -1.
+int ihm2o_closed_loop(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
+                      const int32_t* track_index, const double* params, const double* lap_length,
+                      int n_steps, double* xs, double* x, double* u, double* xlog, double* ulog,
+                      int32_t* done, int32_t* fail) {
+  const int N = cf->N, B = cf->batch;
+#pragma omp parallel for schedule(dynamic)
+  for (int i = 0; i < B; i++) {
+    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    const int t = track_index ? track_index[i] : 0;
+    double* xi = x + (size_t)i * (N + 1) * NX;
+    double* ui = u + (size_t)i * N * NU;
+    double* xc = xs + (size_t)i * NX;
+    done[i] = fail[i] = -1;
+    if (xlog) std::memcpy(xlog + (size_t)i * NX, xc, NX * sizeof(double));
+    for (int st = 0; st < n_steps; st++) {
+      bool active = done[i] < 0 && fail[i] < 0;
+      double uu[NU] = {0, 0};
+      if (active) {
+        shift_iterate(N, xi, ui);
+        SolveOut so;
+        solve_one(pb, xc, xi, ui, so, nullptr, nullptr);
+        if (so.status != IHM2B_SUCCESS && so.status != IHM2B_MAXITER) { fail[i] = st; active = false; }
+        else { uu[0] = ui[0]; uu[1] = ui[1]; }
+      }
+      if (active) {
+        double xn[NX];
+        sim_step(pb, xc, uu, xn);
+        bool nan = false;
+        for (int a = 0; a < NX; a++) nan |= !(xn[a] == xn[a]);
+        if (nan) fail[i] = st;  // main.py:503-512: keep the last state
+        else std::memcpy(xc, xn, sizeof xn);
+        if (!nan && xc[0] > lap_length[t] + 1.0) done[i] = st;  // main.py:515
+      }
+      if (ulog) { ulog[((size_t)st * B + i) * NU] = uu[0]; ulog[((size_t)st * B + i) * NU + 1] = uu[1]; }
+      if (xlog) std::memcpy(xlog + ((size_t)(st + 1) * B + i) * NX, xc, NX * sizeof(double));
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,142 @@
+"""ctypes driver of oracle/_build/libihm2_oracle.so (test infrastructure only)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libihm2_oracle.so")
+NX, NU, NZ, NP = 8, 2, 10, 20
+
+
+def build_oracle(force: bool = False) -> str:
+    src = os.path.join(_HERE, "ihm2_oracle.cpp")
+    hdr = os.path.join(_HERE, "..", "include", "ihm2b.h")
+    stale = (not os.path.exists(_SO)) or any(
+        os.path.exists(f) and os.path.getmtime(f) > os.path.getmtime(_SO) for f in (src, hdr)
+    )
+    if force or stale:
+        subprocess.run(["make", "-C", _HERE, "-B", "_build/libihm2_oracle.so"], check=True,
+                       capture_output=True)
+    return _SO
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Oracle:
+    """Holds one problem set (config + tracks + per-instance params) like an ihm2b handle."""
+
+    def __init__(self, cfg, s_ref, kappa_ref, track_index=None, params=None):
+        from ihm2_b200._abi import default_params
+
+        self.lib = C.CDLL(build_oracle())
+        assert self.lib.ihm2o_np() == NP
+        self.cfg = cfg
+        self.s_ref = _f(np.atleast_2d(s_ref))
+        self.kappa_ref = _f(np.atleast_2d(kappa_ref))
+        assert self.s_ref.shape == (cfg.n_tracks, cfg.n_grid)
+        B = cfg.batch
+        self.track_index = np.ascontiguousarray(
+            np.zeros(B, np.int32) if track_index is None else track_index, dtype=np.int32)
+        self.params = _f(np.tile(default_params(), (B, 1)) if params is None else params)
+        assert self.params.shape == (B, NP)
+
+    # ---- single-point model / integrator evaluations (track 0, instance 0 params) ----
+    def fkin6(self, x, u, jac=True):
+        f = np.zeros(NX)
+        J = np.zeros((NX, NZ)) if jac else None
+        self.lib.ihm2o_fkin6(_p(_f(x)), _p(_f(u)), _p(self.params[0]), _p(self.s_ref[0]),
+                             _p(self.kappa_ref[0]), C.c_int(self.cfg.n_grid), _p(f), _p(J))
+        return (f, J) if jac else f
+
+    def fdyn6(self, x, u):
+        f = np.zeros(NX)
+        self.lib.ihm2o_fdyn6(_p(_f(x)), _p(_f(u)), _p(self.params[0]), _p(self.s_ref[0]),
+                             _p(self.kappa_ref[0]), C.c_int(self.cfg.n_grid), _p(f))
+        return f
+
+    def integrate(self, kind, x, u, h, tableau=None, sens=True):
+        """kind: 0 ERK4, 1 IRK (fkin6, analytic Newton), 2 IRK on fdyn6."""
+        A = _f(tableau[0] if tableau else np.array(self.cfg.irk_A[:]))
+        b = _f(tableau[1] if tableau else np.array(self.cfg.irk_b[:]))
+        xn = np.zeros(NX)
+        S = np.zeros((NX, NZ)) if (sens and kind != 2) else None
+        rc = self.lib.ihm2o_integrate(C.c_int(kind), _p(A), _p(b), C.c_double(h), _p(_f(x)),
+                                      _p(_f(u)), _p(self.params[0]), _p(self.s_ref[0]),
+                                      _p(self.kappa_ref[0]), C.c_int(self.cfg.n_grid), _p(xn), _p(S))
+        assert rc >= 0, f"integrator failed rc={rc}"
+        return (xn, S) if S is not None else xn
+
+    # ---- batched path ----
+    def _common(self):
+        return (C.byref(self.cfg), _p(self.s_ref), _p(self.kappa_ref), _p(self.track_index),
+                _p(self.params))
+
+    def linearize(self, x, u):
+        B, N = self.cfg.batch, self.cfg.N
+        x, u = _f(x), _f(u)
+        A = np.zeros((B, N, NX, NX)); Bm = np.zeros((B, N, NX, NU)); phi = np.zeros((B, N, NX))
+        bad = self.lib.ihm2o_linearize(*self._common(), _p(x), _p(u), _p(A), _p(Bm), _p(phi))
+        return A, Bm, phi, bad
+
+    def solve(self, x0, x, u, do_shift=False):
+        """Returns u0 [B,2], status [B], stats [B,8]; x, u are updated copies."""
+        B = self.cfg.batch
+        x0 = _f(x0); x = _f(x).copy(); u = _f(u).copy()
+        u0 = np.zeros((B, NU)); status = np.zeros(B, np.int32); stats = np.zeros((B, 8))
+        self.lib.ihm2o_solve(*self._common(), _p(x0), _p(x), _p(u), _p(u0), _p(status), _p(stats),
+                             C.c_int(int(do_shift)))
+        return u0, status, stats, x, u
+
+    def qp_debug(self, x0, x, u):
+        N = self.cfg.N
+        out = dict(
+            A=np.zeros((N, NX, NX)), B=np.zeros((N, NX, NU)), c=np.zeros((N, NX)),
+            H=np.zeros((N + 1, NZ, NZ)), g=np.zeros((N + 1, NZ)), C=np.zeros((N + 1, 8, NZ)),
+            lb=np.zeros((N + 1, 8)), ub=np.zeros((N + 1, 8)), nrows=np.zeros(N + 1, np.int32),
+            z=np.zeros((N + 1, NZ)), pi=np.zeros((N + 1, NX)), lamL=np.zeros((N + 1, 8)),
+            lamU=np.zeros((N + 1, 8)), tL=np.zeros((N + 1, 8)), tU=np.zeros((N + 1, 8)),
+            info=np.zeros(7))
+        order = ["A", "B", "c", "H", "g", "C", "lb", "ub", "nrows", "z", "pi", "lamL", "lamU", "tL",
+                 "tU", "info"]
+        st = self.lib.ihm2o_qp_debug(C.byref(self.cfg), _p(self.s_ref), _p(self.kappa_ref),
+                                     _p(self.params), _p(_f(x0)), _p(_f(x)), _p(_f(u)),
+                                     *[_p(out[k]) for k in order])
+        out["status"] = st
+        return out
+
+    def sim_step(self, x, u):
+        B = self.cfg.batch
+        xn = np.zeros((B, NX)); model = np.zeros(B, np.int32)
+        self.lib.ihm2o_sim_step(*self._common(), _p(_f(x)), _p(_f(u)), _p(xn), _p(model))
+        return xn, model
+
+    def closed_loop(self, xs, x, u, lap_length, n_steps, log=True):
+        B = self.cfg.batch
+        xs = _f(xs).copy(); x = _f(x).copy(); u = _f(u).copy()
+        lap = _f(np.atleast_1d(lap_length))
+        xlog = np.zeros((n_steps + 1, B, NX)) if log else None
+        ulog = np.zeros((n_steps, B, NU)) if log else None
+        done = np.zeros(B, np.int32); fail = np.zeros(B, np.int32)
+        self.lib.ihm2o_closed_loop(*self._common(), _p(lap), C.c_int(n_steps), _p(xs), _p(x), _p(u),
+                                   _p(xlog), _p(ulog), _p(done), _p(fail))
+        return dict(x=xs, x_pred=x, u_pred=u, xlog=xlog, ulog=ulog, done=done, fail=fail)
+
+
+def initial_iterate(cfg, batch=None):
+    """controller.py:313-317."""
+    B = cfg.batch if batch is None else batch
+    N = cfg.N
+    x = np.zeros((B, N + 1, NX)); u = np.zeros((B, N, NU))
+    x[:, :, 0] = -6.0 + np.arange(N + 1) * cfg.dt
+    u[:, :, 0] = cfg.T_max
+    return x, u
