@@ -1,0 +1,357 @@
+// api.cu -- C ABI of libihm2b.so (include/ihm2b.h): handle life cycle, problem data,
+// iterate management and the solve / closed-loop entry points.
+//
+// The handle plays the role of the acados capsule (ihm2_fkin6_acados_create_capsule ...,
+// src/ihm2/src/mpc_control_node.cpp:274-304 in the reference): it owns every workspace
+// buffer; callers own the I/O buffers they pass in.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+namespace ihm2b {
+void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
+void launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
+                   cudaStream_t stream);
+void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
+                     const double* u, double* xn, int32_t* model, cudaStream_t stream);
+void launch_closed_loop_post(const KCfg& cf, const Work& w, int step, double* xs, const double* xn,
+                             const double* u0, const double* lap_len_dev, double* xlog, double* ulog,
+                             int32_t* done, int32_t* fail, cudaStream_t stream);
+}  // namespace ihm2b
+
+using namespace ihm2b;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return fail(IHM2B_ECUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct ihm2b_handle {
+  ihm2b_config cfg;
+  KCfg k;
+  Work w;
+  int device;
+  std::vector<void*> allocs;
+  double *s_ref, *kappa_ref, *params, *lap_len;
+  int32_t* track;
+  // scratch for the host entry point and the closed loop
+  double *x0_dev, *u0_dev, *xn_dev;
+  int32_t* status_dev;
+  double *x0_pin, *u0_pin;
+  int32_t* status_pin;
+  bool have_tracks, have_params;
+  int64_t launches;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(ihm2b_handle* h, T** p, size_t n) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, n * sizeof(T));
+  if (e != cudaSuccess) return fail(IHM2B_ENOMEM, "cudaMalloc(%zu bytes): %s", n * sizeof(T), cudaGetErrorString(e));
+  e = cudaMemset(q, 0, n * sizeof(T));
+  if (e != cudaSuccess) return fail(IHM2B_ECUDA, "cudaMemset: %s", cudaGetErrorString(e));
+  h->allocs.push_back(q);
+  *p = static_cast<T*>(q);
+  return IHM2B_OK;
+}
+
+__global__ void reset_iterate_kernel(int B, int N, double dt, double T_max, double* x, double* u) {
+  // controller.py:313-317: x_j = (-6 + j dt, 0, ...), u_j = (T_max, 0)
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= B * (N + 1)) return;
+  const int b = gid / (N + 1), j = gid - b * (N + 1);
+  double* xp = x + (size_t)gid * 8;
+  xp[0] = -6.0 + j * dt;
+  for (int i = 1; i < 8; i++) xp[i] = 0.0;
+  if (j < N) { u[((size_t)b * N + j) * 2] = T_max; u[((size_t)b * N + j) * 2 + 1] = 0.0; }
+}
+
+// controller.py:388-393 (literal): x_j <- x_{j+1}, u_j <- u_{j+1} for j < N-1;
+// x_{N-1} <- x_N, x_N unchanged, u_{N-1} <- 0.  One thread per (problem, component),
+// marching over the stages so the in-place shift needs no second buffer.
+__global__ void shift_iterate_kernel(int B, int N, double* x, double* u, const int32_t* frozen) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= B * 10) return;
+  const int b = gid / 10, c = gid - b * 10;
+  if (frozen && frozen[b]) return;
+  if (c < 8) {
+    double* xp = x + (size_t)b * (N + 1) * 8 + c;
+    for (int j = 0; j < N; j++) xp[j * 8] = xp[(j + 1) * 8];
+  } else {
+    double* up = u + (size_t)b * N * 2 + (c - 8);
+    for (int j = 0; j < N - 1; j++) up[j * 2] = up[(j + 1) * 2];
+    up[(N - 1) * 2] = 0.0;
+  }
+}
+
+void fill_kcfg(const ihm2b_config& c, KCfg& k) {
+  memset(&k, 0, sizeof k);
+  k.B = c.batch; k.N = c.N; k.n_grid = c.n_grid;
+  k.integrator = c.integrator; k.qp_max_iter = c.qp_max_iter;
+  k.dt = c.dt; k.s_target = c.s_target;
+  k.n_max = c.n_max; k.v_x_max = c.v_x_max; k.T_max = c.T_max; k.delta_max = c.delta_max;
+  k.g_T_max = c.g_T_max; k.g_delta_max = c.g_delta_max;
+  memcpy(k.W, c.W, sizeof k.W); memcpy(k.We, c.W_e, sizeof k.We);
+  k.cs = c.cost_scale_stage; k.ct = c.cost_scale_terminal;
+  k.mu0 = c.qp_mu0; k.tol = c.qp_tol; k.tol_comp = c.qp_tol_comp;
+  memcpy(k.irk_A, c.irk_A, sizeof k.irk_A); memcpy(k.irk_b, c.irk_b, sizeof k.irk_b);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ihm2b_last_error(void) { return g_err; }
+int ihm2b_version(void) { return 100; }
+
+int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
+  if (!cfg || !out) return fail(IHM2B_EINVAL, "null argument");
+  if (cfg->batch <= 0 || cfg->N < 2 || cfg->N > 512 || cfg->n_tracks <= 0 || cfg->n_grid < 2)
+    return fail(IHM2B_EINVAL, "bad dimensions: batch=%d N=%d n_tracks=%d n_grid=%d", cfg->batch, cfg->N,
+                cfg->n_tracks, cfg->n_grid);
+  if (cfg->integrator != IHM2B_ERK4 && cfg->integrator != IHM2B_IRK_GL4)
+    return fail(IHM2B_EINVAL, "unknown integrator %d", cfg->integrator);
+  if (cfg->nlp_solver != IHM2B_SQP_RTI && cfg->nlp_solver != IHM2B_SQP)
+    return fail(IHM2B_EINVAL, "unknown nlp_solver %d", cfg->nlp_solver);
+  if (cfg->nonlinear_constraints)
+    return fail(IHM2B_EINVAL, "nonlinear_constraints: not implemented in this build");
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
+  ihm2b_handle* h = new (std::nothrow) ihm2b_handle();
+  if (!h) return fail(IHM2B_ENOMEM, "host allocation failed");
+  h->cfg = *cfg;
+  fill_kcfg(*cfg, h->k);
+  h->launches = 0;
+  h->have_tracks = h->have_params = false;
+  CU(cudaGetDevice(&h->device));
+  const size_t B = cfg->batch, N = cfg->N;
+  Work& w = h->w;
+  memset(&w, 0, sizeof w);
+  int rc = IHM2B_OK;
+#define ALLOC(p, n) if (rc == IHM2B_OK) rc = dev_alloc(h, &(p), (n))
+  ALLOC(h->s_ref, (size_t)cfg->n_tracks * cfg->n_grid);
+  ALLOC(h->kappa_ref, (size_t)cfg->n_tracks * cfg->n_grid);
+  ALLOC(h->params, B * NP);
+  ALLOC(h->track, B);
+  ALLOC(h->lap_len, (size_t)cfg->n_tracks);
+  ALLOC(w.x, B * (N + 1) * 8);
+  ALLOC(w.u, B * N * 2);
+  ALLOC(w.BA, B * N * 80);
+  ALLOC(w.c, B * N * 8);
+  ALLOC(w.phi, B * N * 8);
+  ALLOC(w.LT, B * (N + 1) * 32);
+  ALLOC(w.K, B * N * 16);
+  ALLOC(w.kff, B * N * 2);
+  ALLOC(w.Minv, B * N * 4);
+  ALLOC(w.kfc, B * N * 2);
+  ALLOC(w.D, B * (N + 1) * 16);
+  ALLOC(w.xa, B * (N + 1) * 8);
+  ALLOC(w.ua, B * N * 2);
+  ALLOC(w.stats, B * 8);
+  ALLOC(w.status, B);
+  ALLOC(h->x0_dev, B * 8);
+  ALLOC(h->u0_dev, B * 2);
+  ALLOC(h->xn_dev, B * 8);
+  ALLOC(h->status_dev, B);
+#undef ALLOC
+  if (rc == IHM2B_OK) {
+    cudaError_t e = cudaMallocHost(&h->x0_pin, B * 8 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMallocHost(&h->u0_pin, B * 2 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMallocHost(&h->status_pin, B * sizeof(int32_t));
+    if (e != cudaSuccess) rc = fail(IHM2B_ENOMEM, "cudaMallocHost: %s", cudaGetErrorString(e));
+  }
+  if (rc != IHM2B_OK) { ihm2b_destroy(h); return rc; }
+  w.s_ref = h->s_ref; w.kappa_ref = h->kappa_ref; w.params = h->params; w.track = h->track;
+  *out = h;
+  return ihm2b_reset_iterate(h, nullptr);
+}
+
+int ihm2b_destroy(ihm2b_handle* h) {
+  if (!h) return IHM2B_OK;
+  for (void* p : h->allocs) cudaFree(p);
+  if (h->x0_pin) cudaFreeHost(h->x0_pin);
+  if (h->u0_pin) cudaFreeHost(h->u0_pin);
+  if (h->status_pin) cudaFreeHost(h->status_pin);
+  delete h;
+  return IHM2B_OK;
+}
+
+int ihm2b_set_tracks(ihm2b_handle* h, const double* s_ref, const double* kappa_ref, const double* rw,
+                     const double* lw) {
+  if (!h || !s_ref || !kappa_ref) return fail(IHM2B_EINVAL, "null argument");
+  (void)rw; (void)lw;  // widths only enter the nonlinear track constraint (not in this build)
+  const size_t n = (size_t)h->cfg.n_tracks * h->cfg.n_grid;
+  for (int t = 0; t < h->cfg.n_tracks; t++)
+    for (int i = 1; i < h->cfg.n_grid; i++)
+      if (!(s_ref[(size_t)t * h->cfg.n_grid + i] > s_ref[(size_t)t * h->cfg.n_grid + i - 1]))
+        return fail(IHM2B_EINVAL, "s_ref of track %d is not strictly increasing at %d", t, i);
+  CU(cudaMemcpy(h->s_ref, s_ref, n * sizeof(double), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->kappa_ref, kappa_ref, n * sizeof(double), cudaMemcpyHostToDevice));
+  h->have_tracks = true;
+  return IHM2B_OK;
+}
+
+int ihm2b_set_track_index(ihm2b_handle* h, const int32_t* idx) {
+  if (!h || !idx) return fail(IHM2B_EINVAL, "null argument");
+  for (int i = 0; i < h->cfg.batch; i++)
+    if (idx[i] < 0 || idx[i] >= h->cfg.n_tracks) return fail(IHM2B_EINVAL, "track_index[%d] = %d out of range", i, idx[i]);
+  CU(cudaMemcpy(h->track, idx, (size_t)h->cfg.batch * sizeof(int32_t), cudaMemcpyHostToDevice));
+  return IHM2B_OK;
+}
+
+int ihm2b_set_params(ihm2b_handle* h, const double* params) {
+  if (!h || !params) return fail(IHM2B_EINVAL, "null argument");
+  CU(cudaMemcpy(h->params, params, (size_t)h->cfg.batch * NP * sizeof(double), cudaMemcpyHostToDevice));
+  h->have_params = true;
+  return IHM2B_OK;
+}
+
+int ihm2b_set_iterate_dev(ihm2b_handle* h, const double* x, const double* u, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t B = h->cfg.batch, N = h->cfg.N;
+  if (x) CU(cudaMemcpyAsync(h->w.x, x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (u) CU(cudaMemcpyAsync(h->w.u, u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  return IHM2B_OK;
+}
+
+int ihm2b_get_iterate_dev(ihm2b_handle* h, double* x, double* u, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t B = h->cfg.batch, N = h->cfg.N;
+  if (x) CU(cudaMemcpyAsync(x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (u) CU(cudaMemcpyAsync(u, h->w.u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  return IHM2B_OK;
+}
+
+int ihm2b_reset_iterate(ihm2b_handle* h, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  const int total = h->cfg.batch * (h->cfg.N + 1);
+  reset_iterate_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      h->cfg.batch, h->cfg.N, h->cfg.dt, h->cfg.T_max, h->w.x, h->w.u);
+  h->launches++;
+  CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+int ihm2b_shift_iterate(ihm2b_handle* h, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  const int total = h->cfg.batch * 10;
+  shift_iterate_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      h->cfg.batch, h->cfg.N, h->w.x, h->w.u, nullptr);
+  h->launches++;
+  CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+static int check_ready(ihm2b_handle* h) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  if (!h->have_tracks) return fail(IHM2B_EINVAL, "ihm2b_set_tracks has not been called");
+  if (!h->have_params) return fail(IHM2B_EINVAL, "ihm2b_set_params has not been called");
+  return IHM2B_OK;
+}
+
+int ihm2b_linearize_dev(ihm2b_handle* h, double* A, double* Bm, double* phi, void* stream);
+
+int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* status, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!x0) return fail(IHM2B_EINVAL, "null x0");
+  if (h->cfg.integrator != IHM2B_ERK4) return fail(IHM2B_EINVAL, "integrator %d: not implemented in this build", h->cfg.integrator);
+  if (h->cfg.nlp_solver != IHM2B_SQP_RTI) return fail(IHM2B_EINVAL, "nlp_solver %d: not implemented in this build", h->cfg.nlp_solver);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
+  // enters the feedback phase, as the fixed x_0 of the QP.
+  launch_linearize(h->k, h->w, s);
+  launch_qp_rti(h->k, h->w, x0, u0, status, s);
+  h->launches += 2;
+  CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+int ihm2b_compute_control_host(ihm2b_handle* h, const double* x0, double* u0, int32_t* status, int do_shift) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!x0 || !u0) return fail(IHM2B_EINVAL, "null argument");
+  const size_t B = h->cfg.batch;
+  cudaStream_t s = nullptr;
+  memcpy(h->x0_pin, x0, B * 8 * sizeof(double));
+  CU(cudaMemcpyAsync(h->x0_dev, h->x0_pin, B * 8 * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (do_shift) { rc = ihm2b_shift_iterate(h, s); if (rc) return rc; }
+  rc = ihm2b_solve_dev(h, h->x0_dev, h->u0_dev, h->status_dev, s);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(h->u0_pin, h->u0_dev, B * 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(h->status_pin, h->status_dev, B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  memcpy(u0, h->u0_pin, B * 2 * sizeof(double));
+  if (status) memcpy(status, h->status_pin, B * sizeof(int32_t));
+  return IHM2B_OK;
+}
+
+namespace {
+// [B][N][8][10] (B | A) -> A [B][N][8][8], Bm [B][N][8][2]
+__global__ void split_ba_kernel(size_t rows, const double* BA, double* A, double* Bm) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= rows) return;
+  const double* r = BA + gid * 10;
+  if (Bm) { Bm[gid * 2] = r[0]; Bm[gid * 2 + 1] = r[1]; }
+  if (A) for (int j = 0; j < 8; j++) A[gid * 8 + j] = r[2 + j];
+}
+}  // namespace
+
+int ihm2b_linearize_dev(ihm2b_handle* h, double* A, double* Bm, double* phi, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (h->cfg.integrator != IHM2B_ERK4) return fail(IHM2B_EINVAL, "integrator %d: not implemented in this build", h->cfg.integrator);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  launch_linearize(h->k, h->w, s);
+  h->launches++;
+  const size_t rows = (size_t)h->cfg.batch * h->cfg.N * 8;
+  if (A || Bm) {
+    split_ba_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(rows, h->w.BA, A, Bm);
+    h->launches++;
+  }
+  if (phi) CU(cudaMemcpyAsync(phi, h->w.phi, rows * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats, void* stream) {
+  if (!h || !stats) return fail(IHM2B_EINVAL, "null argument");
+  CU(cudaMemcpyAsync(stats, h->w.stats, (size_t)h->cfg.batch * 8 * sizeof(double), cudaMemcpyDeviceToDevice,
+                     static_cast<cudaStream_t>(stream)));
+  return IHM2B_OK;
+}
+
+int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double* xn, int32_t* model, void* stream) {
+  (void)x; (void)u; (void)xn; (void)model; (void)stream;
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  return fail(IHM2B_EINVAL, "ihm2b_sim_step_dev: not implemented in this build");
+}
+
+int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const double* lap_length, double* xlog,
+                          double* ulog, int32_t* done, int32_t* failp, void* stream) {
+  (void)n_steps; (void)x; (void)lap_length; (void)xlog; (void)ulog; (void)done; (void)failp; (void)stream;
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  return fail(IHM2B_EINVAL, "ihm2b_closed_loop_dev: not implemented in this build");
+}
+
+int64_t ihm2b_launch_count(const ihm2b_handle* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,59 @@
+// common.cuh -- shared definitions of libihm2b.so (device side).
+//
+// Product code: nothing here includes, links or calls anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ihm2b.h"
+
+namespace ihm2b {
+
+constexpr int NX = IHM2B_NX, NU = IHM2B_NU, NZ = NX + NU, NP = IHM2B_NP;
+constexpr int NROW = 8;        // two-sided inequality rows per stage (padded)
+constexpr int GROUP = 8;       // lanes per problem in the QP kernel (lane = state row)
+
+// Kernel-side copy of the scalar options of ihm2b_config (passed by value).
+struct KCfg {
+  int B, N, n_grid;
+  int integrator, qp_max_iter;
+  double dt, s_target;
+  double n_max, v_x_max, T_max, delta_max, g_T_max, g_delta_max;
+  double W[IHM2B_NY], We[IHM2B_NYN];
+  double cs, ct;               // cost scaling: stage, terminal
+  double mu0, tol, tol_comp;
+  double irk_A[16], irk_b[4];
+};
+
+// Device workspace of one handle.  Batch-major, one contiguous block per problem and per
+// stage inside it, so that the 8 lanes that own a problem read 64..640 contiguous bytes.
+struct Work {
+  // problem data
+  const double* s_ref;      // [n_tracks][n_grid]
+  const double* kappa_ref;  // [n_tracks][n_grid]
+  const int32_t* track;     // [B]
+  const double* params;     // [B][NP]
+  // iterate (python: x_pred / u_pred), reference layout
+  double* x;                // [B][N+1][8]
+  double* u;                // [B][N][2]
+  // linearisation: BA[k][i][0..1] = B_k row i, BA[k][i][2..9] = A_k row i ; c_k = phi - A x - B u
+  double* BA;               // [B][N][8][10]
+  double* c;                // [B][N][8]
+  double* phi;              // [B][N][8]
+  // interior point state: lamL, lamU, tL, tU per row
+  double* LT;               // [B][N+1][4][8]
+  // Riccati factor of the current IPM iteration
+  double* K;                // [B][N][8][2]   K[k][a][:] = feedback column of state a
+  double* kff;              // [B][N][2]      predictor feed-forward
+  double* Minv;             // [B][N][4]      inverse of M_uu (i00,i01,i11,pad)
+  double* kfc;              // [B][N][2]      corrected feed-forward (kff + corrector part)
+  double* D;                // [B][N+1][2][8] second-order terms dlam_aff * dt_aff (L, U)
+  // candidate solution (affine, then corrected)
+  double* xa;               // [B][N+1][8]
+  double* ua;               // [B][N][2]
+  // outputs
+  double* stats;            // [B][8]
+  int32_t* status;          // [B]
+};
+
+}  // namespace ihm2b
