@@ -4,6 +4,7 @@
 // The handle plays the role of the acados capsule (ihm2_fkin6_acados_create_capsule ...,
 // src/ihm2/src/mpc_control_node.cpp:274-304 in the reference): it owns every workspace
 // buffer; callers own the I/O buffers they pass in.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -45,7 +46,7 @@ struct ihm2b_handle {
   Work w;
   int device;
   std::vector<void*> allocs;
-  double *s_ref, *kappa_ref, *params, *lap_len;
+  double *s_ref, *kappa_ref, *params, *lap_len, *actw, *actw_sim;
   int32_t* track;
   // scratch for the host entry point and the closed loop
   double *x0_dev, *u0_dev, *xn_dev;
@@ -148,6 +149,8 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->s_ref, (size_t)cfg->n_tracks * cfg->n_grid);
   ALLOC(h->kappa_ref, (size_t)cfg->n_tracks * cfg->n_grid);
   ALLOC(h->params, B * NP);
+  ALLOC(h->actw, B * 8);
+  ALLOC(h->actw_sim, B * 8);
   ALLOC(h->track, B);
   ALLOC(h->lap_len, (size_t)cfg->n_tracks);
   ALLOC(w.x, B * (N + 1) * 8);
@@ -178,6 +181,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   }
   if (rc != IHM2B_OK) { ihm2b_destroy(h); return rc; }
   w.s_ref = h->s_ref; w.kappa_ref = h->kappa_ref; w.params = h->params; w.track = h->track;
+  w.actw = h->actw; w.actw_sim = h->actw_sim;
   *out = h;
   return ihm2b_reset_iterate(h, nullptr);
 }
@@ -215,8 +219,47 @@ int ihm2b_set_track_index(ihm2b_handle* h, const int32_t* idx) {
   return IHM2B_OK;
 }
 
+// w = (I + z A)^-1 1 for a 4-stage tableau A (row-major): the collocation solution of the
+// first-order lag x' = (u - x) / t with z = h / t is K = w (u - x) / t.
+static bool lag_weights(const double* A, double z, double* w) {
+  double M[4][5];
+  for (int i = 0; i < 4; i++) {
+    for (int j = 0; j < 4; j++) M[i][j] = (i == j ? 1.0 : 0.0) + z * A[i * 4 + j];
+    M[i][4] = 1.0;
+  }
+  for (int c = 0; c < 4; c++) {
+    int pr = c;
+    for (int r = c + 1; r < 4; r++) if (fabs(M[r][c]) > fabs(M[pr][c])) pr = r;
+    if (!(fabs(M[pr][c]) > 0.0)) return false;
+    if (pr != c) for (int j = 0; j < 5; j++) { double t = M[c][j]; M[c][j] = M[pr][j]; M[pr][j] = t; }
+    for (int r = c + 1; r < 4; r++) {
+      const double l = M[r][c] / M[c][c];
+      for (int j = c; j < 5; j++) M[r][j] -= l * M[c][j];
+    }
+  }
+  for (int r = 3; r >= 0; r--) {
+    double v = M[r][4];
+    for (int c = r + 1; c < 4; c++) v -= M[r][c] * w[c];
+    w[r] = v / M[r][r];
+  }
+  return true;
+}
+
 int ihm2b_set_params(ihm2b_handle* h, const double* params) {
   if (!h || !params) return fail(IHM2B_EINVAL, "null argument");
+  const size_t B = h->cfg.batch;
+  std::vector<double> wc(B * 8), ws(B * 8);
+  const double hs = h->cfg.dt / (h->cfg.sim_steps > 0 ? h->cfg.sim_steps : 1);
+  for (size_t i = 0; i < B; i++) {
+    const double tT = params[i * NP + IHM2B_P_TT], tD = params[i * NP + IHM2B_P_TD];
+    if (!(tT > 0.0) || !(tD > 0.0) || !(params[i * NP + IHM2B_P_M] > 0.0))
+      return fail(IHM2B_EINVAL, "params[%zu]: t_T, t_delta and m must be positive", i);
+    if (!lag_weights(h->cfg.irk_A, h->cfg.dt / tT, &wc[i * 8]) || !lag_weights(h->cfg.irk_A, h->cfg.dt / tD, &wc[i * 8 + 4]) ||
+        !lag_weights(h->cfg.sim_A, hs / tT, &ws[i * 8]) || !lag_weights(h->cfg.sim_A, hs / tD, &ws[i * 8 + 4]))
+      return fail(IHM2B_EINVAL, "params[%zu]: singular collocation system for the actuator lags", i);
+  }
+  CU(cudaMemcpy(h->actw, wc.data(), B * 8 * sizeof(double), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->actw_sim, ws.data(), B * 8 * sizeof(double), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(h->params, params, (size_t)h->cfg.batch * NP * sizeof(double), cudaMemcpyHostToDevice));
   h->have_params = true;
   return IHM2B_OK;
@@ -273,7 +316,6 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   int rc = check_ready(h);
   if (rc) return rc;
   if (!x0) return fail(IHM2B_EINVAL, "null x0");
-  if (h->cfg.integrator != IHM2B_ERK4) return fail(IHM2B_EINVAL, "integrator %d: not implemented in this build", h->cfg.integrator);
   if (h->cfg.nlp_solver != IHM2B_SQP_RTI) return fail(IHM2B_EINVAL, "nlp_solver %d: not implemented in this build", h->cfg.nlp_solver);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
@@ -318,7 +360,6 @@ __global__ void split_ba_kernel(size_t rows, const double* BA, double* A, double
 int ihm2b_linearize_dev(ihm2b_handle* h, double* A, double* Bm, double* phi, void* stream) {
   int rc = check_ready(h);
   if (rc) return rc;
-  if (h->cfg.integrator != IHM2B_ERK4) return fail(IHM2B_EINVAL, "integrator %d: not implemented in this build", h->cfg.integrator);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   launch_linearize(h->k, h->w, s);
   h->launches++;

@@ -33,6 +33,8 @@ struct Work {
   const double* kappa_ref;  // [n_tracks][n_grid]
   const int32_t* track;     // [B]
   const double* params;     // [B][NP]
+  const double* actw;       // [B][8]  (I + h/t_T A)^-1 1, (I + h/t_delta A)^-1 1 (controller tableau)
+  const double* actw_sim;   // [B][8]  same for the plant tableau and sub-step
   // iterate (python: x_pred / u_pred), reference layout
   double* x;                // [B][N+1][8]
   double* u;                // [B][N][2]

@@ -109,7 +109,10 @@ __global__ void __launch_bounds__(128) linearize_erk4_kernel(const KCfg cf, cons
   }
 }
 
+void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream);
+
 void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream) {
+  if (cf.integrator == IHM2B_IRK_GL4) { launch_linearize_irk(cf, w, stream); return; }
   const int total = cf.B * cf.N;
   linearize_erk4_kernel<<<(total + 127) / 128, 128, 0, stream>>>(cf, w);
 }
