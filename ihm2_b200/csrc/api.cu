@@ -15,8 +15,9 @@
 
 namespace ihm2b {
 void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
-void launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
-                   cudaStream_t stream);
+int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
+                  cudaStream_t stream);
+int qp_smem_bytes(int N);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
 void launch_closed_loop_post(const KCfg& cf, const Work& w, int step, double* xs, const double* xn,
@@ -321,7 +322,9 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
   // enters the feedback phase, as the fixed x_0 of the QP.
   launch_linearize(h->k, h->w, s);
-  launch_qp_rti(h->k, h->w, x0, u0, status, s);
+  if (launch_qp_rti(h->k, h->w, x0, u0, status, s) != 0)
+    return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
+                qp_smem_bytes(h->cfg.N), h->cfg.N);
   h->launches += 2;
   CU(cudaGetLastError());
   return IHM2B_OK;

@@ -6,42 +6,68 @@
 // the reference tree) and the feedback phase of acados' ocp_nlp_sqp_rti for the OCP of
 // python/mpc.py:29-101 (LINEAR_LS cost, box bounds idxbx/idxbu, two rate rows C x + D u).
 //
-// Mapping: 8 lanes own one problem, lane a = row a of every 8-row object (state x_a, row a
-// of the cost-to-go matrix P, row a of [B A], inequality row a).  A warp carries 4 problems,
-// groups only ever synchronise among their own 8 lanes.  The stage data streams from global
-// memory (contiguous 640 B per stage and problem); what several lanes need goes through a
-// small per-group shared-memory scratch.
+// Mapping: ONE WARP PER PROBLEM, the whole horizon resident in shared memory (one record
+// of RS doubles per stage: [B A], c, multipliers/slacks, iterate, costate, Riccati gains,
+// candidate point), 3 problems per SM.  Lane l = (a = l & 7, q = l >> 3): a is the row of
+// every 8-row object (state x_a, row a of the cost-to-go matrix P, row a of [B A], inequality
+// row a); the four quarters q split the columns of the two dense products of the Riccati
+// step and otherwise compute redundantly, so that every reduction is a shuffle inside an
+// 8-lane segment and every hand-over goes through a few hundred bytes of scratch.
 //
-// Formulation (absolute variables z_k = (u_k, x_k), x_0 fixed to the measured state):
+// Formulation (variables z_k = (u_k, x_k), x_0 fixed to the measured state):
 //   min sum 1/2 z'Hz + g'z   s.t.  x_{k+1} = A x_k + B u_k + c_k,   lb <= C z <= ub
-// Per IPM iteration: one Riccati factorisation of H + C' diag(lam/t) C, predictor solve,
-// corrector solve with the same factor, one step length for primal and dual variables.
-// The Newton system is solved for the new point z+ directly ("absolute form"), so the linear
-// residuals contract exactly by (1 - alpha) per iteration; they are tracked through that
-// factor and are not recomputed.
+// Residual ("delta") form of the Newton system, as in the CPU oracle: each iteration
+// recomputes the stationarity / dynamics / slack residuals at the current point, factorises
+// H + C' diag(lam/t) C once by a backward Riccati sweep, and solves predictor and corrector
+// with that factor.  Equality multipliers are advanced through the costate recursion of the
+// full Newton step, which needs no stored cost-to-go matrices.
 #include "common.cuh"
 
 namespace ihm2b {
 
 namespace {
 
-constexpr int GS = 212;  // doubles of shared scratch per group (208 used; 212*2 = 8 mod 32 banks)
 constexpr double TAU = 0.995, THR0 = 0.1;
+constexpr unsigned FULL = 0xffffffffu;
 
-__device__ __forceinline__ double gsum(unsigned gm, double v) {
-  v += __shfl_xor_sync(gm, v, 1);
-  v += __shfl_xor_sync(gm, v, 2);
-  v += __shfl_xor_sync(gm, v, 4);
+// stage record (doubles)
+constexpr int R_BA = 0;     // [8][10]  (B | A) row-major
+constexpr int R_C = 80;     // [8]
+constexpr int R_LT = 88;    // lamL[8] lamU[8] tL[8] tU[8]
+constexpr int R_X = 120;    // [8]
+constexpr int R_U = 128;    // [2]
+constexpr int R_PI = 130;   // [8]
+constexpr int R_K = 138;    // [8][2]
+constexpr int R_KF = 154;   // kff[2] kfc[2]
+constexpr int R_MI = 158;   // i00 i01 i11 pad
+constexpr int R_D = 162;    // dlam_aff*dt_aff: L[8] U[8]
+constexpr int R_XA = 178;   // [8]
+constexpr int R_UA = 186;   // [2]
+constexpr int RS = 188;
+// scratch (doubles, after the N+1 records)
+constexpr int S_W = 0;      // [8][10]
+constexpr int S_M = 80;     // [8][10]  rows 2..9 of M
+constexpr int S_P = 160;    // [8][8]
+constexpr int S_V = 224;    // [8]
+constexpr int S_RB = 232;   // [8]
+constexpr int S_G = 240;    // gamma[8] psi[8] dl[8]
+constexpr int S_MU = 264;   // M00 M01 M11 mvu0 mvu1 pad[3]
+constexpr int S_TOT = 272;
+
+__device__ __forceinline__ double gsum(double v) {
+  v += __shfl_xor_sync(FULL, v, 1);
+  v += __shfl_xor_sync(FULL, v, 2);
+  v += __shfl_xor_sync(FULL, v, 4);
   return v;
 }
-__device__ __forceinline__ double gmaxr(unsigned gm, double v) {
-  v = fmax(v, __shfl_xor_sync(gm, v, 1));
-  v = fmax(v, __shfl_xor_sync(gm, v, 2));
-  v = fmax(v, __shfl_xor_sync(gm, v, 4));
-  return v;
-}
-// NaN-propagating max for residual tracking (fmax drops NaNs)
+// NaN-propagating max
 __device__ __forceinline__ double nmax(double a, double b) { return (b > a || b != b) ? b : a; }
+__device__ __forceinline__ double gmaxr(double v) {
+  v = nmax(v, __shfl_xor_sync(FULL, v, 1));
+  v = nmax(v, __shfl_xor_sync(FULL, v, 2));
+  v = nmax(v, __shfl_xor_sync(FULL, v, 4));
+  return v;
+}
 
 // Inequality row r of a stage of type ty (0: k = 0, 1: 0 < k < N, 2: k = N):
 //   v = (iu >= 0 ? u[iu] : 0) + sx * x[ix]   in [lb, ub]
@@ -76,17 +102,22 @@ __device__ __forceinline__ Row row_def(const KCfg& cf, int ty, int r) {
   return R;
 }
 
-__device__ __forceinline__ double row_value(unsigned gm, const Row& R, double xa, double u0, double u1) {
-  const double xs = __shfl_sync(gm, xa, R.ix < 0 ? 0 : R.ix, GROUP);
+// row value from a point held in memory (x[8], u[2])
+__device__ __forceinline__ double row_value_mem(const Row& R, const double* x, const double* u) {
+  double v = (R.iu >= 0) ? u[R.iu] : 0.0;
+  if (R.ix >= 0) v = fma(R.sx, x[R.ix], v);
+  return v;
+}
+// row value from a point held in registers (x_a per lane, u replicated)
+__device__ __forceinline__ double row_value_reg(const Row& R, double xa, double u0, double u1) {
+  const double xs = __shfl_sync(FULL, xa, R.ix < 0 ? 0 : R.ix, GROUP);
   double v = (R.iu == 0) ? u0 : (R.iu == 1) ? u1 : 0.0;
   if (R.ix >= 0) v = fma(R.sx, xs, v);
   return v;
 }
 
-// Scatter of per-row quantities q_r (in shared sq[0..7]) through C': what state lane a and
-// the two controls receive from C' q.
-//   ty < 2: rows (u_T, u_d, u_T - T, u_d - delta, n, v_x, T, delta)
-//   ty = 2: rows (n, v_x, v_y, r)
+// What state lane a receives from C' q (q_r in sq[0..7]).
+//   ty < 2: rows (u_T, u_d, u_T - T, u_d - delta, n, v_x, T, delta);  ty = 2: rows (n, v_x, v_y, r)
 __device__ __forceinline__ double ct_state(const double* sq, int ty, int a) {
   if (ty < 2) {
     switch (a) {
@@ -119,266 +150,277 @@ __device__ __forceinline__ double ctc_diag(const double* sq, int ty, int a) {
   return ct_state(sq, ty, a);
 }
 
-struct Ptrs {
-  const double* BA; const double* c;
-  double* x; double* u; double* LT; double* K; double* kff; double* Minv; double* kfc; double* D;
-  double* xa; double* ua;
-};
-
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
-// blockDim = 128 (16 problems per CTA), dynamic shared memory = 16 * GS doubles.
+// grid = B, block = 32, dynamic shared memory = ((N+1) * RS + S_TOT) doubles.
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) qp_rti_kernel(const KCfg cf, const Work w,
-                                                      const double* __restrict__ x0,
-                                                      double* __restrict__ u0_out,
-                                                      int32_t* __restrict__ status_out) {
+__global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
+                                                     const double* __restrict__ x0,
+                                                     double* __restrict__ u0_out,
+                                                     int32_t* __restrict__ status_out) {
   extern __shared__ double smem[];
-  const int tid = threadIdx.x;
-  const int a = tid & 7;
-  const int gl = tid >> 3;
-  const int b = blockIdx.x * (blockDim.x >> 3) + gl;
-  if (b >= cf.B) return;  // whole group leaves together; groups never sync across each other
-  const unsigned gm = 0xFFu << (tid & 24);
+  const int lane = threadIdx.x;
+  const int a = lane & 7, q = lane >> 3;
+  const int b = blockIdx.x;
   const int N = cf.N;
+  double* const sc = smem + (N + 1) * RS;
+  double* const sW = sc + S_W; double* const sM = sc + S_M; double* const sP = sc + S_P;
+  double* const sv = sc + S_V; double* const srb = sc + S_RB; double* const sG = sc + S_G;
+  double* const sMu = sc + S_MU;
+#define REC(k) (smem + (k) * RS)
 
-  double* sBA = smem + gl * GS;  // [8][10]
-  double* sW = sBA + 80;         // [8][10]
-  double* sv = sBA + 160;        // [8]
-  double* sc = sBA + 168;        // [8]
-  double* sK = sBA + 176;        // [8][2]
-  double* sG = sBA + 192;        // gamma[8], omega[8]
-
-  Ptrs P;
-  P.BA = w.BA + (size_t)b * N * 80;
-  P.c = w.c + (size_t)b * N * 8;
-  P.x = w.x + (size_t)b * (N + 1) * 8;
-  P.u = w.u + (size_t)b * N * 2;
-  P.LT = w.LT + (size_t)b * (N + 1) * 32;
-  P.K = w.K + (size_t)b * N * 16;
-  P.kff = w.kff + (size_t)b * N * 2;
-  P.Minv = w.Minv + (size_t)b * N * 4;
-  P.kfc = w.kfc + (size_t)b * N * 2;
-  P.D = w.D + (size_t)b * (N + 1) * 16;
-  P.xa = w.xa + (size_t)b * (N + 1) * 8;
-  P.ua = w.ua + (size_t)b * N * 2;
-
-  const double xh = x0[(size_t)b * 8 + a];                       // measured state, lane a
-  const double s0 = __shfl_sync(gm, xh, 0, GROUP);
+  // ------------------------------------------------------------------ load the problem
+  {
+    const double2* gBA = reinterpret_cast<const double2*>(w.BA + (size_t)b * N * 80);
+    for (int e = lane; e < N * 40; e += 32) {
+      const int k = e / 40, o = e - k * 40;
+      reinterpret_cast<double2*>(REC(k) + R_BA)[o] = gBA[e];
+    }
+    const double* gc = w.c + (size_t)b * N * 8;
+    for (int e = lane; e < N * 8; e += 32) REC(e >> 3)[R_C + (e & 7)] = gc[e];
+    const double* gx = w.x + (size_t)b * (N + 1) * 8;
+    for (int e = lane; e < (N + 1) * 8; e += 32) REC(e >> 3)[R_X + (e & 7)] = gx[e];
+    const double* gu = w.u + (size_t)b * N * 2;
+    for (int e = lane; e < N * 2; e += 32) REC(e >> 1)[R_U + (e & 1)] = gu[e];
+  }
+  const double xh = x0[(size_t)b * 8 + a];  // measured state, component a
+  const double s0 = __shfl_sync(FULL, xh, 0, GROUP);
+  __syncwarp();
+  if (q == 0) REC(0)[R_X + a] = xh;         // x_0 of the iterate is the measured state
+  if (lane < 2) REC(N)[R_U + lane] = 0.0;
   // cost (python/mpc.py:47-69, controller.py:320-385): constant near-diagonal GN Hessian
   const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
   const double hxN = cf.ct * cf.We[a];
   const double hu0 = cf.cs * (cf.W[8] + cf.W[10]), hu1 = cf.cs * (cf.W[9] + cf.W[11]);
-  const double hxu0 = (a == 6) ? -cf.cs * cf.W[10] : 0.0;  // H[x_a][u_T]
-  const double hxu1 = (a == 7) ? -cf.cs * cf.W[11] : 0.0;  // H[x_a][u_delta]
-  const double gs_scale = -cf.cs * cf.W[0];               // g[s]_k = gs_scale * yref_k
+  const double c10 = cf.cs * cf.W[10], c11 = cf.cs * cf.W[11];
+  const double hxu0 = (a == 6) ? -c10 : 0.0;  // H[x_a][u_T]
+  const double hxu1 = (a == 7) ? -c11 : 0.0;  // H[x_a][u_delta]
+  const double gs_scale = -cf.cs * cf.W[0];   // g[s]_k = gs_scale * yref_k
   const double gsN = -cf.ct * cf.We[0] * (s0 + cf.s_target);
+  __syncwarp();
 
   // ------------------------------------------------------------------ initialisation
-  double res_g0 = 0.0, res_b0 = 0.0, res_d0 = 0.0, mag_g = 0.0, mag_b = 0.0, mag_d = 0.0;
-  double S0 = 0.0;
-  int nineq = 0;
-  {
-    double xk = xh;
-    if (true) P.x[a] = xh;  // x_0 of the iterate is the measured state
-    for (int k = 0; k <= N; k++) {
-      const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
-      double u0 = 0.0, u1 = 0.0;
-      if (k < N) { const double2 uu = *reinterpret_cast<const double2*>(P.u + 2 * k); u0 = uu.x; u1 = uu.y; }
-      const Row R = row_def(cf, ty, a);
-      const double v = row_value(gm, R, xk, u0, u1);
-      double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0;
+  // slacks / multipliers cold (t = max(distance, thr0), lam = mu0 / t), pi = 0; 4 stages at a time
+  for (int k = q; k <= N; k += 4) {
+    const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
+    double* r = REC(k);
+    const Row R = row_def(cf, ty, a);
+    const double v = row_value_mem(R, r + R_X, r + R_U);
+    double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0;
+    if (R.act) {
+      tL = fmax(v - R.lb, THR0); tU = fmax(R.ub - v, THR0);
+      lamL = cf.mu0 / tL; lamU = cf.mu0 / tU;
+    }
+    r[R_LT + a] = lamL; r[R_LT + 8 + a] = lamU; r[R_LT + 16 + a] = tL; r[R_LT + 24 + a] = tU;
+    r[R_PI + a] = 0.0;
+  }
+  __syncwarp();
+  const double inv_n = 1.0 / (16.0 * N);  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4)
+  double mu = 0.0, res_g = 0.0, res_b = 0.0, res_d = 0.0, res_m = 0.0;
+  double mag_g = 0.0, mag_b = 0.0, mag_d = 0.0;
+  int it = 0, qp_status = 1;
+
+  // ------------------------------------------------------------------ IPM iterations
+  const int b0 = (q < 2) ? 3 * q : 2 * q + 2;              // first column of this quarter
+  const int c0 = b0, c1 = b0 + 1, c2 = (q < 2) ? b0 + 2 : b0 + 1;  // (q >= 2: third column is a duplicate)
+  while (true) {
+    // ================= backward sweep 1: residuals, Riccati factorisation, predictor rhs
+    double rg_m = 0.0, rb_m = 0.0, rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
+    double pa;
+    {
+      double* r = REC(N);
+      const Row R = row_def(cf, 2, a);
+      const double v = row_value_mem(R, r + R_X, r + R_U);
+      double gam = 0.0, psi = 0.0, dl = 0.0;
       if (R.act) {
-        tL = fmax(v - R.lb, THR0); tU = fmax(R.ub - v, THR0);
-        lamL = cf.mu0 / tL; lamU = cf.mu0 / tU;
-        res_d0 = nmax(res_d0, nmax(fabs(v - R.lb - tL), fabs(R.ub - v - tU)));
+        const double lamL = r[R_LT + a], lamU = r[R_LT + 8 + a], tL = r[R_LT + 16 + a], tU = r[R_LT + 24 + a];
+        const double itL = 1.0 / tL, itU = 1.0 / tU;
+        const double rdL = v - R.lb - tL, rdU = R.ub - v - tU;
+        gam = lamL * itL + lamU * itU;
+        psi = lamL * rdL * itL - lamU * rdU * itU;
+        dl = lamL - lamU;
+        rd_m = nmax(fabs(rdL), fabs(rdU));
+        rm_m = nmax(lamL * tL, lamU * tU);
+        S0 = lamL * tL + lamU * tU;
         mag_d = fmax(mag_d, fmax(fabs(R.lb), fabs(R.ub)));
-        S0 += lamL * tL + lamU * tU;
-        nineq += 2;
       }
-      double* lt = P.LT + k * 32;
-      lt[a] = lamL; lt[8 + a] = lamU; lt[16 + a] = tL; lt[24 + a] = tU;
-      // stationarity residual with pi = 0:  H z + g - C'(lamL - lamU)
-      sG[a] = lamL - lamU;
-      __syncwarp(gm);
-      const double gx = (a == 0) ? ((k < N) ? gs_scale * (s0 + cf.s_target * k / N) : gsN) : 0.0;
+      if (q == 0) { sG[a] = gam; sG[8 + a] = psi; sG[16 + a] = dl; }
+      __syncwarp();
+      const double gx = (a == 0) ? gsN : 0.0;
       mag_g = fmax(mag_g, fabs(gx));
-      if (k > 0) {
-        const double rgx = ((k < N) ? hx * xk + hxu0 * u0 + hxu1 * u1 : hxN * xk) + gx - ct_state(sG, ty, a);
-        res_g0 = nmax(res_g0, fabs(rgx));
+      const double base = hxN * r[R_X + a] + gx - r[R_PI + a];
+      rg_m = fabs(base - ct_state(sG + 16, 2, a));
+      pa = base + ct_state(sG + 8, 2, a);
+      const double pd = hxN + ctc_diag(sG, 2, a);
+      sP[a * 8 + 2 * q] = (2 * q == a) ? pd : 0.0;
+      sP[a * 8 + 2 * q + 1] = (2 * q + 1 == a) ? pd : 0.0;
+      __syncwarp();
+    }
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; k--) {
+      const int ty = (k == 0) ? 0 : 1;
+      double* r = REC(k);
+      const double* rn = REC(k + 1);
+      // ---- S1: residuals of this stage
+      {
+        const Row R = row_def(cf, ty, a);
+        const double v = row_value_mem(R, r + R_X, r + R_U);
+        double gam = 0.0, psi = 0.0, dl = 0.0;
+        if (R.act) {
+          const double lamL = r[R_LT + a], lamU = r[R_LT + 8 + a], tL = r[R_LT + 16 + a], tU = r[R_LT + 24 + a];
+          const double itL = 1.0 / tL, itU = 1.0 / tU;
+          const double rdL = v - R.lb - tL, rdU = R.ub - v - tU;
+          gam = lamL * itL + lamU * itU;
+          psi = lamL * rdL * itL - lamU * rdU * itU;
+          dl = lamL - lamU;
+          rd_m = nmax(rd_m, nmax(fabs(rdL), fabs(rdU)));
+          rm_m = nmax(rm_m, nmax(lamL * tL, lamU * tU));
+          S0 += lamL * tL + lamU * tU;
+          mag_d = fmax(mag_d, fmax(fabs(R.lb), fabs(R.ub)));
+        }
+        if (q == 0) { sG[a] = gam; sG[8 + a] = psi; sG[16 + a] = dl; }
       }
-      if (k < N) {
-        const double x6 = __shfl_sync(gm, xk, 6, GROUP), x7 = __shfl_sync(gm, xk, 7, GROUP);
-        const double rgu0 = hu0 * u0 - cf.cs * cf.W[10] * x6 - (sG[0] + sG[2]);
-        const double rgu1 = hu1 * u1 - cf.cs * cf.W[11] * x7 - (sG[1] + sG[3]);
-        res_g0 = nmax(res_g0, nmax(fabs(rgu0), fabs(rgu1)));
-        // dynamics residual  A x + B u + c - x_next
-        const double2* row = reinterpret_cast<const double2*>(P.BA + (size_t)k * 80 + a * 10);
-        const double2 bb = row[0];
-        double acc = P.c[k * 8 + a];
+      const double u0 = r[R_U], u1 = r[R_U + 1];
+      double atp = 0.0, btp0 = 0.0, btp1 = 0.0;
+      {
+        const double2* row = reinterpret_cast<const double2*>(r + R_BA + a * 10);
+        const double2* xx = reinterpret_cast<const double2*>(r + R_X);
+        double acc = r[R_C + a];
         mag_b = fmax(mag_b, fabs(acc));
+        const double2 bb = row[0];
         acc = fma(bb.x, u0, acc); acc = fma(bb.y, u1, acc);
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-          const double2 aa = row[1 + j];
-          acc = fma(aa.x, __shfl_sync(gm, xk, 2 * j, GROUP), acc);
-          acc = fma(aa.y, __shfl_sync(gm, xk, 2 * j + 1, GROUP), acc);
+          const double2 aa = row[1 + j], xj = xx[j];
+          acc = fma(aa.x, xj.x, acc); acc = fma(aa.y, xj.y, acc);
         }
-        const double xn = P.x[(k + 1) * 8 + a];
-        res_b0 = nmax(res_b0, fabs(acc - xn));
-        xk = xn;
-      }
-      __syncwarp(gm);
-    }
-    res_g0 = gmaxr(gm, res_g0); res_b0 = gmaxr(gm, res_b0); res_d0 = gmaxr(gm, res_d0);
-    mag_g = gmaxr(gm, mag_g); mag_b = gmaxr(gm, mag_b); mag_d = gmaxr(gm, mag_d);
-    S0 = gsum(gm, S0);
-    nineq = (int)(gsum(gm, (double)nineq) + 0.5);
-  }
-  const double inv_n = 1.0 / (double)nineq;
-  double mu = S0 * inv_n;
-  double res_m = cf.mu0;       // every product starts at mu0
-  double rho = 1.0;            // contraction factor of the linear residuals
-  int it = 0, qp_status = 1;
-  if (!(res_g0 == res_g0) || !(res_b0 == res_b0) || !(mu == mu)) { qp_status = 3; }
-
-  // ------------------------------------------------------------------ IPM iterations
-  while (qp_status == 1) {
-    const bool conv = rho * res_g0 <= cf.tol * (1.0 + mag_g) && rho * res_b0 <= cf.tol * (1.0 + mag_b) &&
-                      rho * res_d0 <= cf.tol * (1.0 + mag_d) && res_m <= cf.tol_comp;
-    if (conv) { qp_status = 0; break; }
-    if (it >= cf.qp_max_iter) break;
-
-    // ---------------- backward pass 1: Riccati factorisation + predictor gradient
-    double Pr[8], pa;
-    {
-      const Row R = row_def(cf, 2, a);
-      const double* lt = P.LT + N * 32;
-      const double lamL = lt[a], lamU = lt[8 + a], itL = 1.0 / lt[16 + a], itU = 1.0 / lt[24 + a];
-      sG[a] = R.act ? lamL * itL + lamU * itU : 0.0;
-      sG[8 + a] = R.act ? lamL * (1.0 + R.lb * itL) + lamU * (R.ub * itU - 1.0) : 0.0;
-      __syncwarp(gm);
-      const double dg = ctc_diag(sG, 2, a), dom = ct_state(sG + 8, 2, a);
-#pragma unroll
-      for (int j = 0; j < 8; j++) Pr[j] = (j == a) ? hxN + dg : 0.0;
-      pa = ((a == 0) ? gsN : 0.0) - dom;
-      __syncwarp(gm);
-    }
-    for (int k = N - 1; k >= 0; k--) {
-      const int ty = (k == 0) ? 0 : 1;
-      {  // stage data -> shared
-        const double2* row = reinterpret_cast<const double2*>(P.BA + (size_t)k * 80 + a * 10);
-        double2* dst = reinterpret_cast<double2*>(sBA + a * 10);
-#pragma unroll
-        for (int j = 0; j < 5; j++) dst[j] = row[j];
-        sc[a] = P.c[k * 8 + a];
-        const Row R = row_def(cf, ty, a);
-        const double* lt = P.LT + k * 32;
-        const double lamL = lt[a], lamU = lt[8 + a], itL = 1.0 / lt[16 + a], itU = 1.0 / lt[24 + a];
-        sG[a] = R.act ? lamL * itL + lamU * itU : 0.0;
-        sG[8 + a] = R.act ? lamL * (1.0 + R.lb * itL) + lamU * (R.ub * itU - 1.0) : 0.0;
-      }
-      __syncwarp(gm);
-      {  // W = P [B A],  v = P c + p
-        double Wr[10];
-#pragma unroll
-        for (int q = 0; q < 10; q++) Wr[q] = 0.0;
-        double va = pa;
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-          const double2* rj = reinterpret_cast<const double2*>(sBA + j * 10);
-#pragma unroll
-          for (int q = 0; q < 5; q++) {
-            const double2 e = rj[q];
-            Wr[2 * q] = fma(Pr[j], e.x, Wr[2 * q]);
-            Wr[2 * q + 1] = fma(Pr[j], e.y, Wr[2 * q + 1]);
-          }
-          va = fma(Pr[j], sc[j], va);
-        }
-        double2* dst = reinterpret_cast<double2*>(sW + a * 10);
-#pragma unroll
-        for (int q = 0; q < 5; q++) dst[q] = make_double2(Wr[2 * q], Wr[2 * q + 1]);
-        sv[a] = va;
-      }
-      __syncwarp(gm);
-      double Mr[10], mvx, M00 = 0.0, M01 = 0.0, M11 = 0.0, mvu0 = 0.0, mvu1 = 0.0;
-      {
-#pragma unroll
-        for (int q = 0; q < 10; q++) Mr[q] = 0.0;
-        mvx = 0.0;
+        const double rb = acc - rn[R_X + a];
+        rb_m = nmax(rb_m, fabs(rb));
+        if (q == 0) srb[a] = rb;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
-          const double col = sBA[i * 10 + 2 + a];
-          const double2 bi = *reinterpret_cast<const double2*>(sBA + i * 10);
-          const double2* wi = reinterpret_cast<const double2*>(sW + i * 10);
-          const double vi = sv[i];
-#pragma unroll
-          for (int q = 0; q < 5; q++) {
-            const double2 e = wi[q];
-            Mr[2 * q] = fma(col, e.x, Mr[2 * q]);
-            Mr[2 * q + 1] = fma(col, e.y, Mr[2 * q + 1]);
-            if (q == 0) {
-              M00 = fma(bi.x, e.x, M00); M01 = fma(bi.x, e.y, M01); M11 = fma(bi.y, e.y, M11);
-            }
-          }
-          mvx = fma(col, vi, mvx);
-          mvu0 = fma(bi.x, vi, mvu0); mvu1 = fma(bi.y, vi, mvu1);
+          const double pn = rn[R_PI + i];
+          const double2 b2 = *reinterpret_cast<const double2*>(r + R_BA + i * 10);
+          atp = fma(r[R_BA + i * 10 + 2 + a], pn, atp);
+          btp0 = fma(b2.x, pn, btp0); btp1 = fma(b2.y, pn, btp1);
         }
       }
-      {  // add H + C' Gamma C and the predictor gradient g - C' omega
-        const double g0 = sG[0], g1 = sG[1], g2 = sG[2], g3 = sG[3];
-        M00 += hu0 + g0 + g2; M11 += hu1 + g1 + g3;
-        mvu0 -= sG[8] + sG[10]; mvu1 -= sG[9] + sG[11];
-        Mr[0] += hxu0 - ((a == 6) ? g2 : 0.0);
-        Mr[1] += hxu1 - ((a == 7) ? g3 : 0.0);
-        const double dg = hx + ctc_diag(sG, ty, a);
+      const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
+      mag_g = fmax(mag_g, fabs(gx));
+      const double base_x = hx * r[R_X + a] + hxu0 * u0 + hxu1 * u1 + gx + atp - r[R_PI + a];
+      const double base_u0 = hu0 * u0 - c10 * r[R_X + 6] + btp0;
+      const double base_u1 = hu1 * u1 - c11 * r[R_X + 7] + btp1;
+      __syncwarp();  // (1) sG, srb, sP visible
+      if (k > 0) rg_m = nmax(rg_m, fabs(base_x - ct_state(sG + 16, ty, a)));
+      rg_m = nmax(rg_m, nmax(fabs(base_u0 - (sG[16] + sG[18])), fabs(base_u1 - (sG[17] + sG[19]))));
+      const double gx_t = base_x + ct_state(sG + 8, ty, a);
+      const double gu0_t = base_u0 + sG[8] + sG[10], gu1_t = base_u1 + sG[9] + sG[11];
+      const double gam0 = sG[0], gam1 = sG[1], gam2 = sG[2], gam3 = sG[3];
+      const double dgam = hx + ctc_diag(sG, ty, a);
+      // ---- S2: W = P [B A] (columns of this quarter), v = P rb + p
+      {
+        double Pr[8];
+        const double2* pr = reinterpret_cast<const double2*>(sP + a * 8);
 #pragma unroll
-        for (int q = 0; q < 8; q++) Mr[2 + q] += (q == a) ? dg : 0.0;
-        const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
-        mvx += gx - ct_state(sG + 8, ty, a);
-      }
-      const double idet = 1.0 / (M00 * M11 - M01 * M01);
-      const double i00 = M11 * idet, i01 = -M01 * idet, i11 = M00 * idet;
-      const double K0 = -(i00 * Mr[0] + i01 * Mr[1]), K1 = -(i01 * Mr[0] + i11 * Mr[1]);
-      const double kf0 = -(i00 * mvu0 + i01 * mvu1), kf1 = -(i01 * mvu0 + i11 * mvu1);
-      pa = mvx + K0 * mvu0 + K1 * mvu1;
-      *reinterpret_cast<double2*>(sK + 2 * a) = make_double2(K0, K1);
-      *reinterpret_cast<double2*>(P.K + k * 16 + 2 * a) = make_double2(K0, K1);
-      if (a == 0) {
-        *reinterpret_cast<double2*>(P.kff + 2 * k) = make_double2(kf0, kf1);
-        *reinterpret_cast<double2*>(P.Minv + 4 * k) = make_double2(i00, i01);
-        *reinterpret_cast<double2*>(P.Minv + 4 * k + 2) = make_double2(i11, 0.0);
-      }
-      __syncwarp(gm);
+        for (int j = 0; j < 4; j++) { const double2 t = pr[j]; Pr[2 * j] = t.x; Pr[2 * j + 1] = t.y; }
+        double W0 = 0.0, W1 = 0.0, W2 = 0.0, va = pa;
 #pragma unroll
-      for (int q = 0; q < 8; q++) {
-        const double2 kq = *reinterpret_cast<const double2*>(sK + 2 * q);
-        Pr[q] = fma(Mr[0], kq.x, fma(Mr[1], kq.y, Mr[2 + q]));
+        for (int j = 0; j < 8; j++) {
+          const double* bj = r + R_BA + j * 10;
+          W0 = fma(Pr[j], bj[c0], W0); W1 = fma(Pr[j], bj[c1], W1); W2 = fma(Pr[j], bj[c2], W2);
+          va = fma(Pr[j], srb[j], va);
+        }
+        sW[a * 10 + c0] = W0; sW[a * 10 + c1] = W1;
+        if (q < 2) sW[a * 10 + c2] = W2;
+        if (q == 0) sv[a] = va;
+      }
+      __syncwarp();  // (2)
+      // ---- S3: M = H~ + [B A]' W (rows 2.., columns of this quarter), uu block split by quarter
+      double mvx = gx_t;
+      {
+        double M0 = 0.0, M1 = 0.0, M2 = 0.0, e0 = 0.0, e1 = 0.0;
+        const int ub = (q == 2) ? 1 : 0;            // B column used by this quarter's uu entry
+        const int uw = (q == 0) ? 0 : 1;            // W column
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const double* bi = r + R_BA + i * 10;
+          const double* wi = sW + i * 10;
+          const double col = bi[2 + a], vi = sv[i];
+          M0 = fma(col, wi[c0], M0); M1 = fma(col, wi[c1], M1); M2 = fma(col, wi[c2], M2);
+          mvx = fma(col, vi, mvx);
+          if (q < 3) e0 = fma(bi[ub], wi[uw], e0);
+          else { e0 = fma(bi[0], vi, e0); e1 = fma(bi[1], vi, e1); }
+        }
+        // add H + C' Gamma C
+        if (c0 == 2 + a) M0 += dgam;
+        if (c1 == 2 + a) M1 += dgam;
+        if (c2 == 2 + a) M2 += dgam;
+        if (q == 0) { M0 += hxu0 - ((a == 6) ? gam2 : 0.0); M1 += hxu1 - ((a == 7) ? gam3 : 0.0); }
+        sM[a * 10 + c0] = M0; sM[a * 10 + c1] = M1;
+        if (q < 2) sM[a * 10 + c2] = M2;
+        if (a == 0) {
+          if (q < 3) sMu[q] = e0;
+          else { sMu[3] = e0; sMu[4] = e1; }
+        }
+      }
+      __syncwarp();  // (3)
+      // ---- S4: eliminate u, update P and p
+      {
+        const double M00 = sMu[0] + hu0 + gam0 + gam2, M01 = sMu[1], M11 = sMu[2] + hu1 + gam1 + gam3;
+        const double mvu0 = sMu[3] + gu0_t, mvu1 = sMu[4] + gu1_t;
+        const double idet = 1.0 / (M00 * M11 - M01 * M01);
+        const double i00 = M11 * idet, i01 = -M01 * idet, i11 = M00 * idet;
+        const double Mx0 = sM[a * 10], Mx1 = sM[a * 10 + 1];
+        const double K0 = -(i00 * Mx0 + i01 * Mx1), K1 = -(i01 * Mx0 + i11 * Mx1);
+        pa = mvx + K0 * mvu0 + K1 * mvu1;
+        if (q == 0) *reinterpret_cast<double2*>(r + R_K + 2 * a) = make_double2(K0, K1);
+        if (lane == 0) {
+          r[R_KF] = -(i00 * mvu0 + i01 * mvu1); r[R_KF + 1] = -(i01 * mvu0 + i11 * mvu1);
+          r[R_MI] = i00; r[R_MI + 1] = i01; r[R_MI + 2] = i11;
+        }
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+          const int j = 2 * q + t;
+          const double Mj0 = sM[j * 10], Mj1 = sM[j * 10 + 1];
+          const double K0j = -(i00 * Mj0 + i01 * Mj1), K1j = -(i01 * Mj0 + i11 * Mj1);
+          sP[a * 8 + j] = fma(Mx0, K0j, fma(Mx1, K1j, sM[a * 10 + 2 + j]));
+        }
       }
     }
+    __syncwarp();
+    res_g = gmaxr(rg_m); res_b = gmaxr(rb_m); res_d = gmaxr(rd_m); res_m = gmaxr(rm_m);
+    mag_g = gmaxr(mag_g); mag_b = gmaxr(mag_b); mag_d = gmaxr(mag_d);
+    S0 = gsum(S0);
+    mu = S0 * inv_n;
+    if (!(res_g == res_g) || !(res_b == res_b) || !(mu == mu)) { qp_status = 3; break; }
+    if (res_g <= cf.tol * (1.0 + mag_g) && res_b <= cf.tol * (1.0 + mag_b) && res_d <= cf.tol * (1.0 + mag_d) &&
+        res_m <= cf.tol_comp) { qp_status = 0; break; }
+    if (it >= cf.qp_max_iter) break;
 
-    // ---------------- forward passes (pred = 1: affine step; pred = 0: corrected step)
+    // ================= forward sweeps (pred = 1: affine step; pred = 0: corrected step)
     double alpha = 1.0, mu_t = 0.0;
+    bool bad = false;
     for (int pred = 1; pred >= 0; pred--) {
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
-      double xk = xh;
+      double xn = xh;  // component a of the new point
+#pragma unroll 1
       for (int k = 0; k <= N; k++) {
         const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
-        double u0 = 0.0, u1 = 0.0;
+        double* r = REC(k);
+        double u0n = 0.0, u1n = 0.0;
         if (k < N) {
-          const double2 Kc = *reinterpret_cast<const double2*>(P.K + k * 16 + 2 * a);
-          const double2 kf = *reinterpret_cast<const double2*>((pred ? P.kff : P.kfc) + 2 * k);
-          u0 = gsum(gm, Kc.x * xk) + kf.x;
-          u1 = gsum(gm, Kc.y * xk) + kf.y;
+          const double2 Kc = *reinterpret_cast<const double2*>(r + R_K + 2 * a);
+          const double dx = xn - r[R_X + a];
+          u0n = r[R_U] + gsum(Kc.x * dx) + r[R_KF + (pred ? 0 : 2)];
+          u1n = r[R_U + 1] + gsum(Kc.y * dx) + r[R_KF + (pred ? 1 : 3)];
         }
-        {  // inequality rows of this stage at the new point
+        {
           const Row R = row_def(cf, ty, a);
-          const double v = row_value(gm, R, xk, u0, u1);
+          const double v = row_value_reg(R, xn, u0n, u1n);
           if (R.act) {
-            const double* lt = P.LT + k * 32;
-            const double lamL = lt[a], lamU = lt[8 + a], tL = lt[16 + a], tU = lt[24 + a];
+            const double lamL = r[R_LT + a], lamU = r[R_LT + 8 + a], tL = r[R_LT + 16 + a], tU = r[R_LT + 24 + a];
             const double itL = 1.0 / tL, itU = 1.0 / tU;
             const double dtL = v - R.lb - tL, dtU = R.ub - v - tU;
             double dlL, dlU;
@@ -386,146 +428,167 @@ __global__ void __launch_bounds__(128) qp_rti_kernel(const KCfg cf, const Work w
               dlL = -lamL - lamL * dtL * itL; dlU = -lamU - lamU * dtU * itU;
               S1 += lamL * dtL + tL * dlL + lamU * dtU + tU * dlU;
               S2 += dlL * dtL + dlU * dtU;
-              P.D[k * 16 + a] = dlL * dtL; P.D[k * 16 + 8 + a] = dlU * dtU;
+              if (q == 0) { r[R_D + a] = dlL * dtL; r[R_D + 8 + a] = dlU * dtU; }
             } else {
-              const double DL = P.D[k * 16 + a], DU = P.D[k * 16 + 8 + a];
-              dlL = -lamL - (DL - mu_t + lamL * dtL) * itL;
-              dlU = -lamU - (DU - mu_t + lamU * dtU) * itU;
+              dlL = -lamL - (r[R_D + a] - mu_t + lamL * dtL) * itL;
+              dlU = -lamU - (r[R_D + 8 + a] - mu_t + lamU * dtU) * itU;
             }
             ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
           }
         }
-        P.xa[k * 8 + a] = xk;
+        if (q == 0) r[R_XA + a] = xn;
         if (k < N) {
-          if (a == 0) *reinterpret_cast<double2*>(P.ua + 2 * k) = make_double2(u0, u1);
-          const double2* row = reinterpret_cast<const double2*>(P.BA + (size_t)k * 80 + a * 10);
+          if (lane == 0) { r[R_UA] = u0n; r[R_UA + 1] = u1n; }
+          const double2* row = reinterpret_cast<const double2*>(r + R_BA + a * 10);
           const double2 bb = row[0];
-          double acc = P.c[k * 8 + a];
-          acc = fma(bb.x, u0, acc); acc = fma(bb.y, u1, acc);
+          double acc = r[R_C + a];
+          acc = fma(bb.x, u0n, acc); acc = fma(bb.y, u1n, acc);
 #pragma unroll
           for (int j = 0; j < 4; j++) {
             const double2 aa = row[1 + j];
-            acc = fma(aa.x, __shfl_sync(gm, xk, 2 * j, GROUP), acc);
-            acc = fma(aa.y, __shfl_sync(gm, xk, 2 * j + 1, GROUP), acc);
+            acc = fma(aa.x, __shfl_sync(FULL, xn, 2 * j, GROUP), acc);
+            acc = fma(aa.y, __shfl_sync(FULL, xn, 2 * j + 1, GROUP), acc);
           }
-          xk = acc;
+          xn = acc;
         }
       }
-      ratio = gmaxr(gm, ratio);
-      if (pred) {
-        const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0;
-        S1 = gsum(gm, S1); S2 = gsum(gm, S2);
-        const double mu_aff = (S0 + al_aff * (S1 + al_aff * S2)) * inv_n;
-        const double sr = mu_aff / mu;
-        mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
-        if (!(ratio == ratio)) { qp_status = 3; break; }
+      __syncwarp();
+      ratio = gmaxr(ratio);
+      if (!(ratio == ratio)) { bad = true; break; }
+      if (!pred) {
+        alpha = TAU * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
+        break;
+      }
+      const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0;
+      S1 = gsum(S1); S2 = gsum(S2);
+      const double mu_aff = (S0 + al_aff * (S1 + al_aff * S2)) * inv_n;
+      const double sr = mu_aff / mu;
+      // centring target, floored so the iterates stay on the central path at ~0.1 tol_comp
+      mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
 
-        // ---------------- backward pass 2: corrector gradient through the same factor
-        double dp;
-        {
-          const Row R = row_def(cf, 2, a);
-          const double* lt = P.LT + N * 32;
-          const double chi = R.act ? (P.D[N * 16 + a] - mu_t) / lt[16 + a] - (P.D[N * 16 + 8 + a] - mu_t) / lt[24 + a] : 0.0;
-          sG[a] = chi;
-          __syncwarp(gm);
-          dp = ct_state(sG, 2, a);
-          __syncwarp(gm);
-        }
-        for (int k = N - 1; k >= 0; k--) {
-          const int ty = (k == 0) ? 0 : 1;
-          const Row R = row_def(cf, ty, a);
-          const double* lt = P.LT + k * 32;
-          const double chi = R.act ? (P.D[k * 16 + a] - mu_t) / lt[16 + a] - (P.D[k * 16 + 8 + a] - mu_t) / lt[24 + a] : 0.0;
-          sG[a] = chi;
-          __syncwarp(gm);
-          double dmx = ct_state(sG, ty, a);
-          double dmu0 = sG[0] + sG[2], dmu1 = sG[1] + sG[3];
-          const double2 bb = *reinterpret_cast<const double2*>(P.BA + (size_t)k * 80 + a * 10);
-          dmu0 += gsum(gm, bb.x * dp);
-          dmu1 += gsum(gm, bb.y * dp);
+      // ================= backward sweep 2: corrector right-hand side through the same factor
+      double dp;
+      {
+        const double* r = REC(N);
+        const Row R = row_def(cf, 2, a);
+        const double chi = R.act ? (r[R_D + a] - mu_t) / r[R_LT + 16 + a] - (r[R_D + 8 + a] - mu_t) / r[R_LT + 24 + a] : 0.0;
+        if (q == 0) sG[a] = chi;
+        __syncwarp();
+        dp = ct_state(sG, 2, a);
+        __syncwarp();
+      }
+#pragma unroll 1
+      for (int k = N - 1; k >= 0; k--) {
+        const int ty = (k == 0) ? 0 : 1;
+        double* r = REC(k);
+        const Row R = row_def(cf, ty, a);
+        const double chi = R.act ? (r[R_D + a] - mu_t) / r[R_LT + 16 + a] - (r[R_D + 8 + a] - mu_t) / r[R_LT + 24 + a] : 0.0;
+        if (q == 0) sG[a] = chi;
+        __syncwarp();
+        double dmx = ct_state(sG, ty, a);
+        double dmu0 = sG[0] + sG[2], dmu1 = sG[1] + sG[3];
+        const double2 bb = *reinterpret_cast<const double2*>(r + R_BA + a * 10);
+        dmu0 += gsum(bb.x * dp);
+        dmu1 += gsum(bb.y * dp);
 #pragma unroll
-          for (int i = 0; i < 8; i++) dmx = fma(P.BA[(size_t)k * 80 + i * 10 + 2 + a], __shfl_sync(gm, dp, i, GROUP), dmx);
-          const double2 Kc = *reinterpret_cast<const double2*>(P.K + k * 16 + 2 * a);
-          const double2 m0 = *reinterpret_cast<const double2*>(P.Minv + 4 * k);
-          const double i11 = P.Minv[4 * k + 2];
-          const double2 kf = *reinterpret_cast<const double2*>(P.kff + 2 * k);
-          if (a == 0)
-            *reinterpret_cast<double2*>(P.kfc + 2 * k) =
-                make_double2(kf.x - (m0.x * dmu0 + m0.y * dmu1), kf.y - (m0.y * dmu0 + i11 * dmu1));
-          dp = dmx + Kc.x * dmu0 + Kc.y * dmu1;
-          __syncwarp(gm);
+        for (int i = 0; i < 8; i++) dmx = fma(r[R_BA + i * 10 + 2 + a], __shfl_sync(FULL, dp, i, GROUP), dmx);
+        const double2 Kc = *reinterpret_cast<const double2*>(r + R_K + 2 * a);
+        const double i00 = r[R_MI], i01 = r[R_MI + 1], i11 = r[R_MI + 2];
+        if (lane == 0) {
+          r[R_KF + 2] = r[R_KF] - (i00 * dmu0 + i01 * dmu1);
+          r[R_KF + 3] = r[R_KF + 1] - (i01 * dmu0 + i11 * dmu1);
         }
-      } else {
-        const double amax = (ratio > 0.0) ? 1.0 / ratio : 2.0;
-        alpha = fmin(1.0, TAU * amax);
-        if (!(ratio == ratio)) qp_status = 3;
+        dp = dmx + Kc.x * dmu0 + Kc.y * dmu1;
+        __syncwarp();
       }
     }
-    if (qp_status == 3) break;
+    if (bad) { qp_status = 3; break; }
     if (alpha < 1e-12) { qp_status = 2; break; }
 
-    // ---------------- update sweep
+    // ================= backward sweep 3: step; costate of the full Newton step -> pi
     {
-      double Sn = 0.0, rm = 0.0;
-      for (int k = 0; k <= N; k++) {
+      double pin = 0.0;  // pi+_{k+1}[a]
+#pragma unroll 1
+      for (int k = N; k >= 0; k--) {
         const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
-        const double xc = P.xa[k * 8 + a];
-        double u0 = 0.0, u1 = 0.0;
-        if (k < N) { const double2 uu = *reinterpret_cast<const double2*>(P.ua + 2 * k); u0 = uu.x; u1 = uu.y; }
+        double* r = REC(k);
         const Row R = row_def(cf, ty, a);
-        const double v = row_value(gm, R, xc, u0, u1);
+        const double v = row_value_mem(R, r + R_XA, r + R_UA);
+        double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0, dlp = 0.0;
         if (R.act) {
-          double* lt = P.LT + k * 32;
-          double lamL = lt[a], lamU = lt[8 + a], tL = lt[16 + a], tU = lt[24 + a];
+          lamL = r[R_LT + a]; lamU = r[R_LT + 8 + a]; tL = r[R_LT + 16 + a]; tU = r[R_LT + 24 + a];
           const double dtL = v - R.lb - tL, dtU = R.ub - v - tU;
-          const double dlL = -lamL - (P.D[k * 16 + a] - mu_t + lamL * dtL) / tL;
-          const double dlU = -lamU - (P.D[k * 16 + 8 + a] - mu_t + lamU * dtU) / tU;
+          const double dlL = -lamL - (r[R_D + a] - mu_t + lamL * dtL) / tL;
+          const double dlU = -lamU - (r[R_D + 8 + a] - mu_t + lamU * dtU) / tU;
+          dlp = (lamL + dlL) - (lamU + dlU);
           lamL = fma(alpha, dlL, lamL); lamU = fma(alpha, dlU, lamU);
           tL = fma(alpha, dtL, tL); tU = fma(alpha, dtU, tU);
-          lt[a] = lamL; lt[8 + a] = lamU; lt[16 + a] = tL; lt[24 + a] = tU;
-          Sn += lamL * tL + lamU * tU;
-          rm = nmax(rm, nmax(lamL * tL, lamU * tU));
         }
-        const double xo = P.x[k * 8 + a];
-        P.x[k * 8 + a] = fma(alpha, xc - xo, xo);
-        if (k < N && a < 2) {
-          const double uo = P.u[2 * k + a];
-          P.u[2 * k + a] = fma(alpha, ((a == 0) ? u0 : u1) - uo, uo);
+        const double xc = r[R_XA + a], xo = r[R_X + a], po = r[R_PI + a];
+        const double ua0 = (k < N) ? r[R_UA] : 0.0, ua1 = (k < N) ? r[R_UA + 1] : 0.0;
+        const double uo = (lane < 2) ? r[R_U + lane] : 0.0;
+        double atp = 0.0;
+        if (k < N) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) atp = fma(r[R_BA + i * 10 + 2 + a], __shfl_sync(FULL, pin, i, GROUP), atp);
         }
+        __syncwarp();
+        if (q == 0) {
+          sG[a] = dlp;
+          if (R.act) { r[R_LT + a] = lamL; r[R_LT + 8 + a] = lamU; r[R_LT + 16 + a] = tL; r[R_LT + 24 + a] = tU; }
+          r[R_X + a] = fma(alpha, xc - xo, xo);
+        }
+        if (lane < 2 && k < N) r[R_U + lane] = fma(alpha, ((lane == 0) ? ua0 : ua1) - uo, uo);
+        __syncwarp();
+        const double gx = (a == 0) ? ((k < N) ? gs_scale * (s0 + cf.s_target * k / N) : gsN) : 0.0;
+        pin = ((k < N) ? hx * xc + hxu0 * ua0 + hxu1 * ua1 : hxN * xc) + gx + atp - ct_state(sG, ty, a);
+        if (q == 0) r[R_PI + a] = fma(alpha, pin - po, po);
+        __syncwarp();
       }
-      S0 = gsum(gm, Sn);
-      res_m = gmaxr(gm, rm);
-      mu = S0 * inv_n;
-      rho *= (1.0 - alpha);
-      it++;
-      if (!(mu == mu)) { qp_status = 3; break; }
     }
+    it++;
   }
 
-  // ------------------------------------------------------------------ outputs
-  if (a == 0) {
+  // ------------------------------------------------------------------ outputs (RTI full step)
+  __syncwarp();
+  {
+    double* gx = w.x + (size_t)b * (N + 1) * 8;
+    for (int e = lane; e < (N + 1) * 8; e += 32) gx[e] = REC(e >> 3)[R_X + (e & 7)];
+    double* gu = w.u + (size_t)b * N * 2;
+    for (int e = lane; e < N * 2; e += 32) gu[e] = REC(e >> 1)[R_U + (e & 1)];
+  }
+  if (lane == 0) {
     int st;
     if (qp_status == 3) st = IHM2B_FAILURE;
     else if (qp_status == 0) st = IHM2B_SUCCESS;
     else {
-      const bool loose = rho * res_g0 <= 1e-6 * (1.0 + mag_g) && rho * res_b0 <= 1e-6 * (1.0 + mag_b) &&
-                         rho * res_d0 <= 1e-6 * (1.0 + mag_d) && res_m <= 1e-6;
+      // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
+      const bool loose = res_g <= 1e-6 * (1.0 + mag_g) && res_b <= 1e-6 * (1.0 + mag_b) &&
+                         res_d <= 1e-6 * (1.0 + mag_d) && res_m <= 1e-6;
       st = loose ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
     }
     w.status[b] = st;
     if (status_out) status_out[b] = st;
     double* sp = w.stats + (size_t)b * 8;
-    sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = rho * res_g0; sp[4] = rho * res_b0; sp[5] = rho * res_d0;
-    sp[6] = res_m; sp[7] = 0.0;
+    sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m; sp[7] = 0.0;
   }
-  if (u0_out && a < 2) u0_out[(size_t)b * 2 + a] = P.u[a];
+  if (u0_out && lane < 2) u0_out[(size_t)b * 2 + lane] = REC(0)[R_U + lane];
+#undef REC
 }
 
-void launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
-                   cudaStream_t stream) {
-  const int per_cta = 128 / GROUP;
-  const int grid = (cf.B + per_cta - 1) / per_cta;
-  qp_rti_kernel<<<grid, 128, per_cta * GS * sizeof(double), stream>>>(cf, w, x0, u0, status);
+int qp_smem_bytes(int N) { return ((N + 1) * RS + S_TOT) * (int)sizeof(double); }
+
+int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
+                  cudaStream_t stream) {
+  const int bytes = qp_smem_bytes(cf.N);
+  static int configured = 0;
+  if (configured < bytes) {
+    cudaError_t e = cudaFuncSetAttribute(qp_rti_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return (int)e;
+    configured = bytes;
+  }
+  qp_rti_kernel<<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
+  return 0;
 }
 
 }  // namespace ihm2b
