@@ -169,6 +169,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(w.ua, B * N * 2);
   ALLOC(w.stats, B * 8);
   ALLOC(w.status, B);
+  ALLOC(w.dbg, 64 * 8);
   ALLOC(h->x0_dev, B * 8);
   ALLOC(h->u0_dev, B * 2);
   ALLOC(h->xn_dev, B * 8);
@@ -394,6 +395,12 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
   (void)n_steps; (void)x; (void)lap_length; (void)xlog; (void)ulog; (void)done; (void)failp; (void)stream;
   if (!h) return fail(IHM2B_EINVAL, "null handle");
   return fail(IHM2B_EINVAL, "ihm2b_closed_loop_dev: not implemented in this build");
+}
+
+/* development aid (not part of the public header): per-iteration IPM trace of problem 0 */
+int ihm2b_debug_trace(ihm2b_handle* h, double* host64x8) {
+  if (!h || !host64x8) return IHM2B_EINVAL;
+  return cudaMemcpy(host64x8, h->w.dbg, 64 * 8 * sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess ? IHM2B_OK : IHM2B_ECUDA;
 }
 
 int64_t ihm2b_launch_count(const ihm2b_handle* h) { return h ? h->launches : 0; }

@@ -56,6 +56,7 @@ struct Work {
   // outputs
   double* stats;            // [B][8]
   int32_t* status;          // [B]
+  double* dbg;              // [64][8] per-iteration trace of problem 0 (development aid), may be NULL
 };
 
 }  // namespace ihm2b

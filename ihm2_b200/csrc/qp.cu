@@ -41,9 +41,11 @@ constexpr int R_K = 138;    // [8][2]
 constexpr int R_KF = 154;   // kff[2] kfc[2]
 constexpr int R_MI = 158;   // i00 i01 i11 pad
 constexpr int R_D = 162;    // dlam_aff*dt_aff: L[8] U[8]
-constexpr int R_XA = 178;   // [8]
-constexpr int R_UA = 186;   // [2]
-constexpr int RS = 188;
+constexpr int R_XA = 178;   // [8]  step dx of the current solve (affine, then corrected)
+constexpr int R_UA = 186;   // [2]  step du
+constexpr int R_RB = 188;   // [8]  dynamics residual  A x + B u + c - x_next
+constexpr int R_RG = 196;   // [8]  stationarity residual, state part
+constexpr int RS = 204;
 // scratch (doubles, after the N+1 records)
 constexpr int S_W = 0;      // [8][10]
 constexpr int S_M = 80;     // [8][10]  rows 2..9 of M
@@ -251,7 +253,9 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       const double gx = (a == 0) ? gsN : 0.0;
       mag_g = fmax(mag_g, fabs(gx));
       const double base = hxN * r[R_X + a] + gx - r[R_PI + a];
-      rg_m = fabs(base - ct_state(sG + 16, 2, a));
+      const double rgx = base - ct_state(sG + 16, 2, a);
+      rg_m = fabs(rgx);
+      if (q == 0) r[R_RG + a] = rgx;
       pa = base + ct_state(sG + 8, 2, a);
       const double pd = hxN + ctc_diag(sG, 2, a);
       sP[a * 8 + 2 * q] = (2 * q == a) ? pd : 0.0;
@@ -298,7 +302,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         }
         const double rb = acc - rn[R_X + a];
         rb_m = nmax(rb_m, fabs(rb));
-        if (q == 0) srb[a] = rb;
+        if (q == 0) { srb[a] = rb; r[R_RB + a] = rb; }
 #pragma unroll
         for (int i = 0; i < 8; i++) {
           const double pn = rn[R_PI + i];
@@ -313,7 +317,11 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       const double base_u0 = hu0 * u0 - c10 * r[R_X + 6] + btp0;
       const double base_u1 = hu1 * u1 - c11 * r[R_X + 7] + btp1;
       __syncwarp();  // (1) sG, srb, sP visible
-      if (k > 0) rg_m = nmax(rg_m, fabs(base_x - ct_state(sG + 16, ty, a)));
+      {
+        const double rgx = base_x - ct_state(sG + 16, ty, a);
+        if (k > 0) rg_m = nmax(rg_m, fabs(rgx));
+        if (q == 0) r[R_RG + a] = rgx;
+      }
       rg_m = nmax(rg_m, nmax(fabs(base_u0 - (sG[16] + sG[18])), fabs(base_u1 - (sG[17] + sG[19]))));
       const double gx_t = base_x + ct_state(sG + 8, ty, a);
       const double gu0_t = base_u0 + sG[8] + sG[10], gu1_t = base_u1 + sG[9] + sG[11];
@@ -394,6 +402,10 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     mag_g = gmaxr(mag_g); mag_b = gmaxr(mag_b); mag_d = gmaxr(mag_d);
     S0 = gsum(S0);
     mu = S0 * inv_n;
+    if (w.dbg && b == 0 && lane == 0 && it < 64) {
+      double* d = w.dbg + it * 8;
+      d[0] = res_g; d[1] = res_b; d[2] = res_d; d[3] = res_m; d[4] = mu;
+    }
     if (!(res_g == res_g) || !(res_b == res_b) || !(mu == mu)) { qp_status = 3; break; }
     if (res_g <= cf.tol * (1.0 + mag_g) && res_b <= cf.tol * (1.0 + mag_b) && res_d <= cf.tol * (1.0 + mag_d) &&
         res_m <= cf.tol_comp) { qp_status = 0; break; }
@@ -404,7 +416,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     bool bad = false;
     for (int pred = 1; pred >= 0; pred--) {
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
-      double xn = xh;  // component a of the new point
+      double dx = 0.0;  // component a of the state step (x_0 is fixed)
 #pragma unroll 1
       for (int k = 0; k <= N; k++) {
         const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
@@ -412,17 +424,17 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         double u0n = 0.0, u1n = 0.0;
         if (k < N) {
           const double2 Kc = *reinterpret_cast<const double2*>(r + R_K + 2 * a);
-          const double dx = xn - r[R_X + a];
-          u0n = r[R_U] + gsum(Kc.x * dx) + r[R_KF + (pred ? 0 : 2)];
-          u1n = r[R_U + 1] + gsum(Kc.y * dx) + r[R_KF + (pred ? 1 : 3)];
+          u0n = gsum(Kc.x * dx) + r[R_KF + (pred ? 0 : 2)];
+          u1n = gsum(Kc.y * dx) + r[R_KF + (pred ? 1 : 3)];
         }
         {
           const Row R = row_def(cf, ty, a);
-          const double v = row_value_reg(R, xn, u0n, u1n);
+          const double cdz = row_value_reg(R, dx, u0n, u1n);
           if (R.act) {
             const double lamL = r[R_LT + a], lamU = r[R_LT + 8 + a], tL = r[R_LT + 16 + a], tU = r[R_LT + 24 + a];
             const double itL = 1.0 / tL, itU = 1.0 / tU;
-            const double dtL = v - R.lb - tL, dtU = R.ub - v - tU;
+            const double v = row_value_mem(R, r + R_X, r + R_U);
+            const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
             double dlL, dlU;
             if (pred) {
               dlL = -lamL - lamL * dtL * itL; dlU = -lamU - lamU * dtU * itU;
@@ -436,20 +448,20 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
             ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
           }
         }
-        if (q == 0) r[R_XA + a] = xn;
+        if (q == 0) r[R_XA + a] = dx;
         if (k < N) {
           if (lane == 0) { r[R_UA] = u0n; r[R_UA + 1] = u1n; }
           const double2* row = reinterpret_cast<const double2*>(r + R_BA + a * 10);
           const double2 bb = row[0];
-          double acc = r[R_C + a];
+          double acc = r[R_RB + a];
           acc = fma(bb.x, u0n, acc); acc = fma(bb.y, u1n, acc);
 #pragma unroll
           for (int j = 0; j < 4; j++) {
             const double2 aa = row[1 + j];
-            acc = fma(aa.x, __shfl_sync(FULL, xn, 2 * j, GROUP), acc);
-            acc = fma(aa.y, __shfl_sync(FULL, xn, 2 * j + 1, GROUP), acc);
+            acc = fma(aa.x, __shfl_sync(FULL, dx, 2 * j, GROUP), acc);
+            acc = fma(aa.y, __shfl_sync(FULL, dx, 2 * j + 1, GROUP), acc);
           }
-          xn = acc;
+          dx = acc;
         }
       }
       __syncwarp();
@@ -502,47 +514,48 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         __syncwarp();
       }
     }
+    if (w.dbg && b == 0 && lane == 0 && it < 64) { w.dbg[it * 8 + 5] = alpha; w.dbg[it * 8 + 6] = mu_t; }
     if (bad) { qp_status = 3; break; }
     if (alpha < 1e-12) { qp_status = 2; break; }
 
-    // ================= backward sweep 3: step; costate of the full Newton step -> pi
+    // ================= backward sweep 3: step; costate recursion of the Newton step -> d pi
     {
-      double pin = 0.0;  // pi+_{k+1}[a]
+      double dpi = 0.0;  // d pi_{k+1}[a]
 #pragma unroll 1
       for (int k = N; k >= 0; k--) {
         const int ty = (k == 0) ? 0 : (k < N ? 1 : 2);
         double* r = REC(k);
         const Row R = row_def(cf, ty, a);
-        const double v = row_value_mem(R, r + R_XA, r + R_UA);
+        const double cdz = row_value_mem(R, r + R_XA, r + R_UA);
         double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0, dlp = 0.0;
         if (R.act) {
           lamL = r[R_LT + a]; lamU = r[R_LT + 8 + a]; tL = r[R_LT + 16 + a]; tU = r[R_LT + 24 + a];
-          const double dtL = v - R.lb - tL, dtU = R.ub - v - tU;
+          const double v = row_value_mem(R, r + R_X, r + R_U);
+          const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
           const double dlL = -lamL - (r[R_D + a] - mu_t + lamL * dtL) / tL;
           const double dlU = -lamU - (r[R_D + 8 + a] - mu_t + lamU * dtU) / tU;
-          dlp = (lamL + dlL) - (lamU + dlU);
+          dlp = dlL - dlU;
           lamL = fma(alpha, dlL, lamL); lamU = fma(alpha, dlU, lamU);
           tL = fma(alpha, dtL, tL); tU = fma(alpha, dtU, tU);
         }
-        const double xc = r[R_XA + a], xo = r[R_X + a], po = r[R_PI + a];
+        const double xc = r[R_XA + a], xo = r[R_X + a], po = r[R_PI + a], rgx = r[R_RG + a];
         const double ua0 = (k < N) ? r[R_UA] : 0.0, ua1 = (k < N) ? r[R_UA + 1] : 0.0;
         const double uo = (lane < 2) ? r[R_U + lane] : 0.0;
         double atp = 0.0;
         if (k < N) {
 #pragma unroll
-          for (int i = 0; i < 8; i++) atp = fma(r[R_BA + i * 10 + 2 + a], __shfl_sync(FULL, pin, i, GROUP), atp);
+          for (int i = 0; i < 8; i++) atp = fma(r[R_BA + i * 10 + 2 + a], __shfl_sync(FULL, dpi, i, GROUP), atp);
         }
         __syncwarp();
         if (q == 0) {
           sG[a] = dlp;
           if (R.act) { r[R_LT + a] = lamL; r[R_LT + 8 + a] = lamU; r[R_LT + 16 + a] = tL; r[R_LT + 24 + a] = tU; }
-          r[R_X + a] = fma(alpha, xc - xo, xo);
+          r[R_X + a] = fma(alpha, xc, xo);
         }
-        if (lane < 2 && k < N) r[R_U + lane] = fma(alpha, ((lane == 0) ? ua0 : ua1) - uo, uo);
+        if (lane < 2 && k < N) r[R_U + lane] = fma(alpha, (lane == 0) ? ua0 : ua1, uo);
         __syncwarp();
-        const double gx = (a == 0) ? ((k < N) ? gs_scale * (s0 + cf.s_target * k / N) : gsN) : 0.0;
-        pin = ((k < N) ? hx * xc + hxu0 * ua0 + hxu1 * ua1 : hxN * xc) + gx + atp - ct_state(sG, ty, a);
-        if (q == 0) r[R_PI + a] = fma(alpha, pin - po, po);
+        dpi = rgx + ((k < N) ? hx * xc + hxu0 * ua0 + hxu1 * ua1 : hxN * xc) + atp - ct_state(sG, ty, a);
+        if (q == 0) r[R_PI + a] = fma(alpha, dpi, po);
         __syncwarp();
       }
     }
