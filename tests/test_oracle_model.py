@@ -1,0 +1,161 @@
+"""Independent checks that pin the CPU oracle's model and integrators (the reference has no
+tests of its own): finite differences, a restatement of fkin6 in numpy written directly from
+python/models.py:232-307, scipy ODE solutions, and the committed golden vectors."""
+import os
+
+import numpy as np
+import pytest
+from scipy.integrate import solve_ivp
+
+from ihm2_b200 import _abi
+from oracle.lib import Oracle
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def fkin6_numpy(x, u, s_ref, kappa_ref, p):
+    """python/models.py:232-307 transcribed line by line (numpy instead of CasADi)."""
+    s, n, psi, v_x, v_y, r, T, delta = x
+    u_T, u_delta = u
+    m, l_R, l_F = p[_abi.P_M], p[_abi.P_LR], p[_abi.P_LF]
+    C = l_R / (l_R + l_F)
+    delta_dot = (u_delta - delta) / p[_abi.P_TD]
+    T_dot = (u_T - T) / p[_abi.P_TT]
+    F_motor = p[_abi.P_CM0] * T
+    F_drag = -(p[_abi.P_CR0] + p[_abi.P_CR1] * v_x + p[_abi.P_CR2] * v_x**2) * np.tanh(10 * v_x)
+    F_Rx = 0.5 * F_motor + F_drag
+    F_Fx = 0.5 * F_motor
+    beta = np.arctan(C * np.tan(delta))
+    v_dot = (F_Rx * np.cos(beta) + F_Fx * np.cos(delta - beta)) / m
+    beta_dot = C * (1 + np.tan(delta) ** 2) / (1 + C**2 * np.tan(delta) ** 2) * delta_dot
+    i = int(np.clip(np.searchsorted(s_ref, s, side="right") - 1, 0, len(s_ref) - 2))
+    kappa = kappa_ref[i] + (kappa_ref[i + 1] - kappa_ref[i]) / (s_ref[i + 1] - s_ref[i]) * (s - s_ref[i])
+    s_dot = (v_x * np.cos(psi) - v_y * np.sin(psi)) / (1 + kappa * n)
+    v_y_dot = v_dot * np.sin(beta) + beta_dot * v_x
+    return np.array([s_dot, v_x * np.sin(psi) + v_y * np.cos(psi), r - kappa * s_dot,
+                     v_dot * np.cos(beta) - beta_dot * v_y, v_y_dot, l_R * v_y_dot - beta_dot, T_dot, delta_dot])
+
+
+@pytest.fixture(scope="module")
+def orc(built, fsds):
+    cfg = _abi.make_config(batch=1, n_grid=len(fsds.s_ref))
+    return Oracle(cfg, fsds.s_ref, fsds.kappa_ref)
+
+
+def _points(n, seed=0):
+    rng = np.random.default_rng(seed)
+    X = np.stack([rng.uniform(0, 300, n), rng.uniform(-1, 1, n), rng.uniform(-0.3, 0.3, n), rng.uniform(0.5, 20, n),
+                  rng.uniform(-1, 1, n), rng.uniform(-1, 1, n), rng.uniform(-400, 400, n), rng.uniform(-0.4, 0.4, n)], 1)
+    U = np.stack([X[:, 6] + rng.uniform(-100, 100, n), X[:, 7] + rng.uniform(-0.02, 0.02, n)], 1)
+    return X, U
+
+
+def test_fkin6_matches_reference_transcription(orc, fsds):
+    X, U = _points(50)
+    p = _abi.default_params()
+    for x, u in zip(X, U):
+        f, _ = orc.fkin6(x, u)
+        np.testing.assert_allclose(f, fkin6_numpy(x, u, fsds.s_ref, fsds.kappa_ref, p), rtol=1e-12, atol=1e-10)
+
+
+def test_fkin6_jacobian_finite_differences(orc, fsds):
+    X, U = _points(20, 1)
+    for x, u in zip(X, U):
+        # stay inside one table segment so the piecewise-linear kappa is smooth
+        i = np.searchsorted(fsds.s_ref, x[0], side="right") - 1
+        x = x.copy(); x[0] = 0.5 * (fsds.s_ref[i] + fsds.s_ref[i + 1])
+        _, J = orc.fkin6(x, u)
+        z = np.concatenate([x, u])
+        for j in range(10):
+            e = 1e-6 * max(1.0, abs(z[j]))
+            if j == 0:
+                e = min(e, 0.2 * (fsds.s_ref[i + 1] - fsds.s_ref[i]))
+            zp, zm = z.copy(), z.copy(); zp[j] += e; zm[j] -= e
+            fd = (orc.fkin6(zp[:8], zp[8:], jac=False) - orc.fkin6(zm[:8], zm[8:], jac=False)) / (2 * e)
+            np.testing.assert_allclose(J[:, j], fd, rtol=2e-6, atol=2e-6 * max(1.0, np.abs(fd).max()))
+
+
+def test_kappa_lookup_extrapolates_linearly(orc, fsds):
+    s_ref, k_ref = fsds.s_ref, fsds.kappa_ref
+    x = np.array([s_ref[-1] + 3.0, 0.5, 0.0, 5.0, 0.0, 0.0, 0.0, 0.0]); u = np.zeros(2)
+    f = orc.fkin6(x, u, jac=False)
+    kap = k_ref[-2] + (k_ref[-1] - k_ref[-2]) / (s_ref[-1] - s_ref[-2]) * (x[0] - s_ref[-2])
+    assert abs(f[0] - 5.0 / (1 + kap * 0.5)) < 1e-12
+    x[0] = s_ref[0] - 2.0
+    f = orc.fkin6(x, u, jac=False)
+    kap = k_ref[0] + (k_ref[1] - k_ref[0]) / (s_ref[1] - s_ref[0]) * (x[0] - s_ref[0])
+    assert abs(f[0] - 5.0 / (1 + kap * 0.5)) < 1e-12
+
+
+def _slow_lag_oracle(fsds):
+    """Actuator lags slowed to 0.5 s so that explicit RK4 and a scipy reference are meaningful."""
+    p = _abi.default_params(); p[_abi.P_TT] = 0.5; p[_abi.P_TD] = 0.5
+    cfg = _abi.make_config(batch=1, n_grid=len(fsds.s_ref))
+    return Oracle(cfg, fsds.s_ref, fsds.kappa_ref, params=p[None]), p
+
+
+def test_integrators_against_scipy(built, fsds):
+    o, p = _slow_lag_oracle(fsds)
+    X, U = _points(5, 2)
+    for x, u in zip(X, U):
+        sol = solve_ivp(lambda t, y: fkin6_numpy(y, u, fsds.s_ref, fsds.kappa_ref, p), (0, 0.05), x, rtol=1e-12,
+                        atol=1e-12, method="DOP853")
+        ref = sol.y[:, -1]
+        xe, _ = o.integrate(0, x, u, 0.05)
+        xi, _ = o.integrate(1, x, u, 0.05)
+        # kappa' jumps at the table knots limit the observable order; both must still be accurate
+        assert np.max(np.abs(xe - ref) / np.maximum(1, np.abs(ref))) < 2e-5
+        assert np.max(np.abs(xi - ref) / np.maximum(1, np.abs(ref))) < 2e-6
+
+
+def test_erk4_is_fourth_order_and_irk_is_more_accurate(built, fsds):
+    o, p = _slow_lag_oracle(fsds)
+    # constant-curvature stretch: put the state where kappa is locally linear (inside a segment)
+    x = np.array([100.3, 0.2, 0.05, 8.0, 0.1, 0.2, 100.0, 0.05]); u = np.array([150.0, 0.06])
+    h = 0.02
+    def rollout(kind, h, n):
+        y = x.copy()
+        for _ in range(n):
+            y = o.integrate(kind, y, u, h, sens=False) if kind == 2 else o.integrate(kind, y, u, h)[0]
+        return y
+    ref = rollout(1, h / 8, 8)
+    e1 = np.abs(rollout(0, h, 1) - ref).max(); e2 = np.abs(rollout(0, h / 2, 2) - ref).max()
+    assert 8 < e1 / e2 < 40, (e1, e2)  # ~16 for order 4 (local 5)
+    assert np.abs(rollout(1, h, 1) - ref).max() < 1e-3 * e1 + 1e-12
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_integrator_sensitivities_finite_differences(built, fsds, kind):
+    o, _ = _slow_lag_oracle(fsds)
+    x = np.array([100.3, 0.2, 0.05, 8.0, 0.1, 0.2, 100.0, 0.05]); u = np.array([150.0, 0.06])
+    _, S = o.integrate(kind, x, u, 0.05)
+    z = np.concatenate([x, u])
+    for j in range(10):
+        e = 1e-6 * max(1.0, abs(z[j])) if j else 1e-4
+        zp, zm = z.copy(), z.copy(); zp[j] += e; zm[j] -= e
+        fd = (o.integrate(kind, zp[:8], zp[8:], 0.05)[0] - o.integrate(kind, zm[:8], zm[8:], 0.05)[0]) / (2 * e)
+        np.testing.assert_allclose(S[:, j], fd, rtol=1e-6, atol=1e-7)
+
+
+def test_irk_stiff_lag_matches_pade(orc):
+    """T' = (u_T - T)/t_T with h/t_T = 50: Gauss-Legendre-4 gives the (4,4) Pade value of exp(-50)."""
+    z = -50.0
+    R = (1 + z / 2 + 3 * z**2 / 28 + z**3 / 84 + z**4 / 1680) / (1 - z / 2 + 3 * z**2 / 28 - z**3 / 84 + z**4 / 1680)
+    x = np.array([10.0, 0, 0, 5.0, 0, 0, 100.0, 0.0]); u = np.array([300.0, 0.0])
+    xn, S = orc.integrate(1, x, u, 0.05)
+    assert abs(xn[6] - (R * 100.0 + (1 - R) * 300.0)) < 1e-9
+    assert abs(S[6, 6] - R) < 1e-12 and abs(S[6, 8] - (1 - R)) < 1e-12
+
+
+def test_golden_model_vectors(orc):
+    g = np.load(os.path.join(GOLD, "model.npz"))
+    for i in range(len(g["x"])):
+        f, J = orc.fkin6(g["x"][i], g["u"][i])
+        np.testing.assert_allclose(f, g["f"][i], rtol=1e-13, atol=1e-13)
+        np.testing.assert_allclose(J, g["J"][i], rtol=1e-13, atol=1e-13)
+        np.testing.assert_allclose(orc.fdyn6(g["x"][i], g["u"][i]), g["fdyn6"][i], rtol=1e-12, atol=1e-12)
+        xe, Se = orc.integrate(0, g["x"][i], g["u"][i], 0.05)
+        np.testing.assert_allclose(xe, g["erk4_x"][i], rtol=1e-12, atol=1e-9)
+        xi, Si = orc.integrate(1, g["x"][i], g["u"][i], 0.05)
+        np.testing.assert_allclose(xi, g["irk_x"][i], rtol=1e-12, atol=1e-11)
+        np.testing.assert_allclose(Si, g["irk_S"][i], rtol=1e-10, atol=1e-11)
