@@ -55,6 +55,10 @@ struct ihm2b_handle {
   double *x0_pin, *u0_pin;
   int32_t* status_pin;
   bool have_tracks, have_params;
+  bool profile;
+  cudaEvent_t ev[3];
+  double prof_ms[2];   // accumulated linearise / QP kernel time
+  int64_t prof_n;
   int64_t launches;
 };
 
@@ -141,6 +145,8 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   fill_kcfg(*cfg, h->k);
   h->launches = 0;
   h->have_tracks = h->have_params = false;
+  h->profile = false; h->prof_ms[0] = h->prof_ms[1] = 0.0; h->prof_n = 0;
+  for (int i = 0; i < 3; i++) h->ev[i] = nullptr;
   CU(cudaGetDevice(&h->device));
   const size_t B = cfg->batch, N = cfg->N;
   Work& w = h->w;
@@ -191,6 +197,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
 int ihm2b_destroy(ihm2b_handle* h) {
   if (!h) return IHM2B_OK;
   for (void* p : h->allocs) cudaFree(p);
+  for (int i = 0; i < 3; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->x0_pin) cudaFreeHost(h->x0_pin);
   if (h->u0_pin) cudaFreeHost(h->u0_pin);
   if (h->status_pin) cudaFreeHost(h->status_pin);
@@ -322,10 +329,20 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
   // enters the feedback phase, as the fixed x_0 of the QP.
+  if (h->profile) cudaEventRecord(h->ev[0], s);
   launch_linearize(h->k, h->w, s);
+  if (h->profile) cudaEventRecord(h->ev[1], s);
   if (launch_qp_rti(h->k, h->w, x0, u0, status, s) != 0)
     return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
                 qp_smem_bytes(h->cfg.N), h->cfg.N);
+  if (h->profile) {
+    cudaEventRecord(h->ev[2], s);
+    cudaEventSynchronize(h->ev[2]);
+    float a = 0.f, b = 0.f;
+    cudaEventElapsedTime(&a, h->ev[0], h->ev[1]);
+    cudaEventElapsedTime(&b, h->ev[1], h->ev[2]);
+    h->prof_ms[0] += a; h->prof_ms[1] += b; h->prof_n++;
+  }
   h->launches += 2;
   CU(cudaGetLastError());
   return IHM2B_OK;
@@ -401,6 +418,62 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
 int ihm2b_debug_trace(ihm2b_handle* h, double* host64x8) {
   if (!h || !host64x8) return IHM2B_EINVAL;
   return cudaMemcpy(host64x8, h->w.dbg, 64 * 8 * sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess ? IHM2B_OK : IHM2B_ECUDA;
+}
+
+/* development / measurement aids (not part of the public header) ----------------------
+ * per-kernel device times of ihm2b_solve_dev: when enabled every solve synchronises on its
+ * own events; ihm2b_profile_read returns the mean linearise / QP kernel time in ms. */
+int ihm2b_profile_enable(ihm2b_handle* h, int on) {
+  if (!h) return IHM2B_EINVAL;
+  if (on && !h->ev[0]) for (int i = 0; i < 3; i++) if (cudaEventCreate(&h->ev[i]) != cudaSuccess) return IHM2B_ECUDA;
+  h->profile = on != 0; h->prof_ms[0] = h->prof_ms[1] = 0.0; h->prof_n = 0;
+  return IHM2B_OK;
+}
+int ihm2b_profile_read(ihm2b_handle* h, double* ms2) {
+  if (!h || !ms2) return IHM2B_EINVAL;
+  const double n = h->prof_n > 0 ? (double)h->prof_n : 1.0;
+  ms2[0] = h->prof_ms[0] / n; ms2[1] = h->prof_ms[1] / n;
+  return IHM2B_OK;
+}
+
+namespace {
+__global__ void dfma_peak_kernel(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 1.0000001, c = 1e-9;
+  for (int i = 0; i < iters; i++) {
+    a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+  }
+  if (a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 == 12345.678) out[0] = a0;
+}
+}  // namespace
+/* FP64 CUDA-core (DFMA) throughput of the current device in TFLOP/s: the roofline denominator
+ * that MEASURED_PEAKS.json does not carry. */
+int ihm2b_measure_fp64_tflops(double* tflops) {
+  if (!tflops) return IHM2B_EINVAL;
+  cudaDeviceProp prop;
+  int dev = 0;
+  CU(cudaGetDevice(&dev));
+  CU(cudaGetDeviceProperties(&prop, dev));
+  double* d = nullptr;
+  CU(cudaMalloc(&d, 8));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+  double best = 0.0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(e0);
+    dfma_peak_kernel<<<blocks, threads>>>(d, iters);
+    cudaEventRecord(e1);
+    CU(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) * 1e-12;
+    if (rep > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops = best;
+  return IHM2B_OK;
 }
 
 int64_t ihm2b_launch_count(const ihm2b_handle* h) { return h ? h->launches : 0; }

@@ -65,6 +65,16 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def measure_fp64_tflops() -> float:
+    """DFMA-chain microbenchmark on the current device (FP64 CUDA-core roofline denominator)."""
+    lib = load_library()
+    out = C.c_double(0.0)
+    rc = lib.ihm2b_measure_fp64_tflops(C.byref(out))
+    if rc != 0:
+        raise Ihm2bError(f"libihm2b error {rc}: {lib.ihm2b_last_error().decode()}")
+    return float(out.value)
+
+
 class Engine:
     """One ihm2b handle: B independent NMPC problems on the current CUDA device."""
 
@@ -184,6 +194,16 @@ class Engine:
         self._check(self.lib.ihm2b_closed_loop_dev(self._h, C.c_int32(n_steps), _dptr(x), _hptr(self.lap_length),
                                                    _dptr(xlog), _dptr(ulog), _dptr(done), _dptr(fail), _stream()))
         return dict(x=x, xlog=xlog, ulog=ulog, done=done, fail=fail)
+
+    # ---- measurement aids ----
+    def profile(self, on: bool = True):
+        self._check(self.lib.ihm2b_profile_enable(self._h, C.c_int(int(on))))
+
+    def profile_read(self):
+        """Mean device time (ms) of the linearisation and QP kernels since profile(True)."""
+        ms = (C.c_double * 2)()
+        self._check(self.lib.ihm2b_profile_read(self._h, ms))
+        return float(ms[0]), float(ms[1])
 
     @property
     def launch_count(self) -> int:

@@ -1,0 +1,185 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (ctypes), against the CPU oracle
+on the same seeded inputs and against the committed golden fixtures.  Run on the B200 box."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+REL_TOL = 1e-6   # north_star: <= 1e-6 relative in fp64 per SQP-RTI step
+
+
+def rel(a, b):
+    return float(np.max(np.abs(a - b)) / max(1.0, np.max(np.abs(b))))
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(built):
+    import torch
+    assert torch.cuda.is_available(), "these tests need the B200"
+    return torch
+
+
+def _engine(cfg, mp, **kw):
+    from ihm2_b200.engine import Engine
+    return Engine(cfg, mp.s_ref, mp.kappa_ref, **kw)
+
+
+def _random_iterate(B, N, seed):
+    rng = np.random.default_rng(seed)
+    x = np.zeros((B, N + 1, 8)); u = np.zeros((B, N, 2))
+    lo = [0, -1.5, -0.4, 0.2, -1, -1, -300, -0.4]; hi = [300, 1.5, 0.4, 18, 1, 1, 300, 0.4]
+    for c in range(8):
+        x[..., c] = rng.uniform(lo[c], hi[c], (B, N + 1))
+    u[..., 0] = x[:, :-1, 6] + rng.uniform(-50, 50, (B, N)); u[..., 1] = x[:, :-1, 7] + rng.uniform(-0.02, 0.02, (B, N))
+    return x, u
+
+
+@pytest.mark.parametrize("integrator", ["ERK4", "IRK_GL4"])
+def test_linearize_matches_oracle(torch_cuda, fsds, integrator):
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B = 128
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), integrator=getattr(_abi, integrator))
+    x, u = _random_iterate(B, cfg.N, 11)
+    eng = _engine(cfg, fsds); eng.set_iterate(x, u)
+    A, Bm, phi = [t.cpu().numpy() for t in eng.linearize()]
+    Ao, Bo, po, bad = Oracle(cfg, fsds.s_ref, fsds.kappa_ref).linearize(x, u)
+    assert bad == 0
+    # state rows are O(1): absolute 1e-10; the explicit-RK torque row carries R(-50) ~ 2.4e5: relative
+    assert np.abs(phi - po).max() / max(1.0, np.abs(po).max()) < 1e-11
+    assert rel(A, Ao) < 1e-11 and rel(Bm, Bo) < 1e-11
+    assert np.abs(A - Ao)[:, :, :6].max() < 1e-9 and np.abs(Bm - Bo)[:, :, :6].max() < 1e-9
+    eng.close()
+
+
+def test_linearize_and_rti_match_golden(torch_cuda, fsds):
+    """No oracle at run time: inputs and outputs from tests/golden/rti.npz."""
+    from ihm2_b200 import _abi
+    g = np.load(os.path.join(GOLD, "rti.npz"))
+    B = len(g["x0"])
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref))
+    eng = _engine(cfg, fsds)
+    eng.set_iterate(g["x_in"], g["u_in"])
+    A, Bm, phi = [t.cpu().numpy() for t in eng.linearize()]
+    assert rel(A, g["A"]) < 1e-11 and rel(Bm, g["B"]) < 1e-11 and rel(phi, g["phi"]) < 1e-11
+    eng.shift_iterate()
+    u0, status = eng.solve(torch_cuda.as_tensor(g["x0"], device="cuda"))
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    assert (status.cpu().numpy() == g["status"]).all()
+    assert rel(u0.cpu().numpy(), g["u0"]) < REL_TOL and rel(xg, g["x_out"]) < REL_TOL and rel(ug, g["u_out"]) < REL_TOL
+    np.testing.assert_array_equal(eng.stats().cpu().numpy()[:, 0], g["qp_iters"])   # same IPM path
+    eng.close()
+
+
+def test_shift_is_literal(torch_cuda, fsds):
+    from ihm2_b200 import _abi
+    from ihm2_b200.workloads import shift_np
+    cfg = _abi.make_config(batch=5, n_grid=len(fsds.s_ref))
+    x, u = _random_iterate(5, cfg.N, 3)
+    eng = _engine(cfg, fsds); eng.set_iterate(x, u); eng.shift_iterate()
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    xs, us = shift_np(x, u)
+    np.testing.assert_array_equal(xg, xs); np.testing.assert_array_equal(ug, us)
+    eng.reset_iterate()
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    np.testing.assert_allclose(xg[0, :, 0], -6 + np.arange(41) * 0.05); assert (ug[..., 0] == 500).all()
+    eng.close()
+
+
+@pytest.fixture(scope="module")
+def config2(torch_cuda, skidpad):
+    """BASELINE.json configs[1]: 4096 perturbed initial states, one SQP-RTI step, data/skidpad."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.workloads import nominal_iterate, perturbed_batch
+    from oracle.lib import Oracle
+    B = 4096
+    x_nom, xp, up = nominal_iterate("skidpad", 20)
+    cfg = _abi.make_config(batch=B, n_grid=len(skidpad.s_ref))
+    x0, x, u = perturbed_batch(x_nom, xp, up, B, seed=0, cfg=cfg)
+    eng = _engine(cfg, skidpad); eng.set_iterate(x, u)
+    A, Bm, phi = [t.cpu().numpy() for t in eng.linearize()]
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    out = dict(x0=x0, x_in=x, u_in=u, A=A, B=Bm, phi=phi, u0=u0.cpu().numpy(), status=status.cpu().numpy(), x=xg, u=ug,
+               stats=eng.stats().cpu().numpy(), cfg=cfg)
+    out["oracle"] = Oracle(cfg, skidpad.s_ref, skidpad.kappa_ref).solve(x0, x, u)
+    eng.close()
+    return out
+
+
+def test_config2_rti_matches_oracle(config2):
+    u0o, so, sto, xo, uo = config2["oracle"]
+    sg = config2["status"]
+    assert np.mean(sg == so) > 0.99                      # borderline-infeasible QPs may flip
+    ok = (sg == 0) & (so == 0)
+    assert ok.sum() > 0.6 * len(sg)
+    assert rel(config2["u0"][ok], u0o[ok]) < REL_TOL
+    assert rel(config2["x"][ok], xo[ok]) < REL_TOL and rel(config2["u"][ok], uo[ok]) < REL_TOL
+    for c in range(8):                                   # per field, as the tolerance is stated
+        assert rel(config2["x"][ok][..., c], xo[ok][..., c]) < REL_TOL
+    same_iters = np.mean(config2["stats"][ok, 0] == sto[ok, 0])
+    assert same_iters > 0.98
+
+
+def test_config2_solution_properties(config2):
+    """Size-independent checks at the full batch: the accepted solutions satisfy the linearised
+    dynamics of their own QP, the measured state is embedded, and all bounds hold."""
+    ok = config2["status"] == 0
+    x, u, x_in, u_in = config2["x"][ok], config2["u"][ok], config2["x_in"][ok], config2["u_in"][ok]
+    A, Bm, phi = config2["A"][ok], config2["B"][ok], config2["phi"][ok]
+    np.testing.assert_array_equal(x[:, 0], config2["x0"][ok])
+    pred = phi + np.einsum("bkij,bkj->bki", A, x[:, :-1] - x_in[:, :-1]) + np.einsum("bkij,bkj->bki", Bm, u - u_in)
+    assert np.abs(pred - x[:, 1:]).max() < 1e-7
+    cfg = config2["cfg"]
+    e = 1e-7
+    assert (np.abs(u[..., 0]) <= cfg.T_max + e).all() and (np.abs(u[..., 1]) <= cfg.delta_max + e).all()
+    assert (np.abs(u[..., 1] - x[:, :-1, 7]) <= cfg.g_delta_max + e).all()
+    assert (np.abs(x[:, 1:, 1]) <= cfg.n_max + e).all() and (x[:, 1:-1, 3] >= -e).all()
+    assert (np.abs(x[:, 1:-1, 7]) <= cfg.delta_max + e).all() and (np.abs(x[:, -1, 5]) <= cfg.delta_max + e).all()
+
+
+def test_host_entry_point_equals_device_path(torch_cuda, fsds):
+    from ihm2_b200 import _abi
+    g = np.load(os.path.join(GOLD, "rti.npz"))
+    cfg = _abi.make_config(batch=len(g["x0"]), n_grid=len(fsds.s_ref))
+    eng = _engine(cfg, fsds); eng.set_iterate(g["x_in"], g["u_in"])
+    u0, status = eng.compute_control_host(g["x0"], do_shift=True)
+    assert (status == g["status"]).all() and rel(u0, g["u0"]) < REL_TOL
+    eng.close()
+
+
+def test_erk4_rti_with_slow_actuators(torch_cuda, fsds):
+    """ERK4 variant (old/generate.py:24-26).  With the reference's t_T = 1 ms the explicit map has
+    dT+/dT ~ 2.4e5 and the QP is unusable, so parity is checked with the lags slowed to 0.1 s."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    g = np.load(os.path.join(GOLD, "rti.npz"))
+    B = len(g["x0"])
+    p = np.tile(_abi.default_params(), (B, 1)); p[:, _abi.P_TT] = 0.1; p[:, _abi.P_TD] = 0.1
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), integrator=_abi.ERK4)
+    eng = _engine(cfg, fsds, params=p); eng.set_iterate(g["x_in"], g["u_in"])
+    u0, status = eng.solve(torch_cuda.as_tensor(g["x0"], device="cuda"))
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    u0o, so, _, xo, uo = Oracle(cfg, fsds.s_ref, fsds.kappa_ref, params=p).solve(g["x0"], g["x_in"], g["u_in"])
+    sg = status.cpu().numpy()
+    assert (sg == so).all()
+    ok = sg == 0
+    assert ok.any() and rel(xg[ok], xo[ok]) < REL_TOL and rel(ug[ok], uo[ok]) < REL_TOL
+    eng.close()
+
+
+def test_api_misuse_is_reported(torch_cuda, fsds):
+    from ihm2_b200 import _abi
+    from ihm2_b200.engine import Engine, Ihm2bError
+    cfg = _abi.make_config(batch=4, n_grid=len(fsds.s_ref))
+    with pytest.raises(Ihm2bError):
+        Engine(cfg, fsds.s_ref, fsds.kappa_ref, track_index=np.array([0, 1, 0, 0]))      # only one track
+    with pytest.raises(Ihm2bError):
+        Engine(cfg, fsds.s_ref[::-1].copy(), fsds.kappa_ref)                             # s_ref not increasing
+    big = _abi.make_config(batch=4, n_grid=len(fsds.s_ref), Nf=400)                      # does not fit on chip
+    eng = Engine(big, fsds.s_ref, fsds.kappa_ref)
+    with pytest.raises(Ihm2bError):
+        eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
+    eng.close()
