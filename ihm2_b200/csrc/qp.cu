@@ -36,9 +36,9 @@ constexpr int PER_STAGE = 212;  // doubles of shared memory per stage
 constexpr int S_W = 0;          // scratch: W [8][10]
 constexpr int S_M = 80;         //          rows 2..9 of M [8][10]
 constexpr int S_P = 160;        //          P [8][8]
-constexpr int S_V = 224;        //          v [8]
-constexpr int S_MU = 232;       //          M00 M01 M11 mvu0 mvu1 pad[3]
-constexpr int S_TOT = 240;
+constexpr int S_V = 224;        //          v [8]  (v of the Riccati step; 2 x [8] exchange buffer elsewhere)
+constexpr int S_MU = 240;       //          M00 M01 M11 mvu0 mvu1 pad[3]
+constexpr int S_TOT = 248;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -109,6 +109,7 @@ __device__ __forceinline__ double ctc_apply(const CtDef& d, const double* q) { r
 // grid = B, block = 32, dynamic shared memory = ((N+1) * PER_STAGE + S_TOT) doubles.
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
+template <int NT>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
 __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
                                                      const double* __restrict__ x0,
                                                      double* __restrict__ u0_out,
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   const int lane = threadIdx.x;
   const int a = lane & 7, q = lane >> 3;
   const int b = blockIdx.x;
-  const int N = cf.N, N1 = N + 1;
+  const int N = (NT > 0) ? NT : cf.N, N1 = N + 1;
   // structure of arrays, stage-major
   double* const pBA = smem;              // [N1][8][10]  (B | A) row-major
   double* const pC = pBA + N1 * 80;      // [N1][8]
@@ -203,6 +204,12 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   const int b0 = (q < 2) ? 3 * q : 2 * q + 2;              // first [B A] column of this quarter
   const int c0 = b0, c1 = b0 + 1, c2 = (q < 2) ? b0 + 2 : b0 + 1;  // (q >= 2: third column is a duplicate)
 
+#ifdef IHM2B_PHASE_TIMERS
+  long long tph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+#define TICK(i) { const long long t_ = clock64(); tph[i] += t_ - tlast; tlast = t_; }
+#else
+#define TICK(i)
+#endif
   while (true) {
     // ================= A: inequality rows of all stages (stage-parallel)
     double rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
@@ -228,6 +235,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       pGAM[k * 8 + a] = gam; pD1[k * 8 + a] = psi; pD2[k * 8 + a] = dl;
     }
     __syncwarp();
+    TICK(0)
     // ================= B: stationarity and dynamics residuals of all stages (stage-parallel)
     double rg_m = 0.0, rb_m = 0.0;
     for (int i = 0; i < rounds; i++) {
@@ -287,6 +295,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         res_m <= cf.tol_comp) { qp_status = 0; break; }
     if (it >= cf.qp_max_iter) break;
     __syncwarp();
+    TICK(1)
 
     // ================= C: backward Riccati sweep (factorisation + predictor right-hand side)
     double pa = pGX[N * 8 + a];
@@ -374,6 +383,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       __syncwarp();
     }
 
+    TICK(2)
     // ================= D..H: predictor (pred = 1), corrector (pred = 0)
     double alpha = 1.0, mu_t = 0.0;
     bool bad = false;
@@ -384,27 +394,30 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         const int kfo = pred ? 0 : 2;
 #pragma unroll 1
         for (int k = 0; k < N; k++) {
-          const double2 Kc = *reinterpret_cast<const double2*>(pK + k * 16 + 2 * a);
-          const double du0 = gsum(Kc.x * dx) + pKF[k * 4 + kfo];
-          const double du1 = gsum(Kc.y * dx) + pKF[k * 4 + kfo + 1];
-          if (q == 0) pDX[k * 8 + a] = dx;
-          if (lane == 0) { pDU[k * 2] = du0; pDU[k * 2 + 1] = du1; }
+          if (q == 0) pDX[k * 8 + a] = dx;       // the stored step doubles as the exchange buffer
+          __syncwarp();
+          const double2* dxv = reinterpret_cast<const double2*>(pDX + k * 8);
+          const double2* Kv = reinterpret_cast<const double2*>(pK + k * 16);
           const double2* row = reinterpret_cast<const double2*>(pBA + k * 80 + a * 10);
-          const double2 bb = row[0];
-          double acc = pRB[k * 8 + a];
-          acc = fma(bb.x, du0, acc); acc = fma(bb.y, du1, acc);
+          double u0a = pKF[k * 4 + kfo], u1a = pKF[k * 4 + kfo + 1], u0b = 0.0, u1b = 0.0;
+          double xa0 = pRB[k * 8 + a], xa1 = 0.0;
 #pragma unroll
           for (int j = 0; j < 4; j++) {
-            const double2 aa = row[1 + j];
-            acc = fma(aa.x, __shfl_sync(FULL, dx, 2 * j, GROUP), acc);
-            acc = fma(aa.y, __shfl_sync(FULL, dx, 2 * j + 1, GROUP), acc);
+            const double2 d = dxv[j], ka = Kv[2 * j], kb = Kv[2 * j + 1], aa = row[1 + j];
+            u0a = fma(ka.x, d.x, u0a); u1a = fma(ka.y, d.x, u1a);
+            u0b = fma(kb.x, d.y, u0b); u1b = fma(kb.y, d.y, u1b);
+            xa0 = fma(aa.x, d.x, xa0); xa1 = fma(aa.y, d.y, xa1);
           }
-          dx = acc;
+          const double du0 = u0a + u0b, du1 = u1a + u1b;
+          if (lane == 0) { pDU[k * 2] = du0; pDU[k * 2 + 1] = du1; }
+          const double2 bb = row[0];
+          dx = fma(bb.x, du0, fma(bb.y, du1, xa0 + xa1));
         }
         if (q == 0) pDX[N * 8 + a] = dx;
         if (lane < 2) pDU[N * 2 + lane] = 0.0;
       }
       __syncwarp();
+      TICK(3)
       // ---- inequality rows at the step (stage-parallel): slack / multiplier steps, step length
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
       for (int i = 0; i < rounds; i++) {
@@ -452,20 +465,29 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         pGAM[k * 8 + a] = act ? (pD1[k * 8 + a] - mu_t) / pTL[k * 8 + a] - (pD2[k * 8 + a] - mu_t) / pTU[k * 8 + a] : 0.0;
       }
       __syncwarp();
+      TICK(4)
       // ---- backward substitution of the corrector right-hand side C' chi through the same factor
       {
         double dp = ct_apply(ctT, pGAM + N * 8);
 #pragma unroll 1
         for (int k = N - 1; k >= 0; k--) {
+          double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of dp
+          if (q == 0) xb[a] = dp;
+          __syncwarp();
           const double* chi = pGAM + k * 8;
           const double* BAk = pBA + k * 80;
-          double dmx = ct_apply(ctP, chi);
-          double dmu0 = chi[0] + chi[2], dmu1 = chi[1] + chi[3];
-          const double2 bb = *reinterpret_cast<const double2*>(BAk + a * 10);
-          dmu0 += gsum(bb.x * dp);
-          dmu1 += gsum(bb.y * dp);
+          double dmx = ct_apply(ctP, chi), dmy = 0.0;
+          double dmu0 = chi[0] + chi[2], dmu1 = chi[1] + chi[3], dmv0 = 0.0, dmv1 = 0.0;
 #pragma unroll
-          for (int i = 0; i < 8; i++) dmx = fma(BAk[i * 10 + 2 + a], __shfl_sync(FULL, dp, i, GROUP), dmx);
+          for (int i = 0; i < 8; i += 2) {
+            const double p0 = xb[i], p1 = xb[i + 1];
+            const double2 b0v = *reinterpret_cast<const double2*>(BAk + i * 10);
+            const double2 b1v = *reinterpret_cast<const double2*>(BAk + i * 10 + 10);
+            dmx = fma(BAk[i * 10 + 2 + a], p0, dmx); dmy = fma(BAk[i * 10 + 12 + a], p1, dmy);
+            dmu0 = fma(b0v.x, p0, dmu0); dmu1 = fma(b0v.y, p0, dmu1);
+            dmv0 = fma(b1v.x, p1, dmv0); dmv1 = fma(b1v.y, p1, dmv1);
+          }
+          dmx += dmy; dmu0 += dmv0; dmu1 += dmv1;
           const double2 Kc = *reinterpret_cast<const double2*>(pK + k * 16 + 2 * a);
           const double i00 = pMI[k * 4], i01 = pMI[k * 4 + 1], i11 = pMI[k * 4 + 2];
           if (lane == 0) {
@@ -476,7 +498,9 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         }
       }
       __syncwarp();
+      TICK(5)
     }
+    TICK(4)
     if (w.dbg && b == 0 && lane == 0 && it < 64) { w.dbg[it * 8 + 5] = alpha; w.dbg[it * 8 + 6] = mu_t; }
     if (bad) { qp_status = 3; break; }
     if (alpha < 1e-12) { qp_status = 2; break; }
@@ -492,10 +516,18 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         const double dxa = pDX[k * 8 + a];
         double acc = pRG[k * 8 + a] - (ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8));
         if (!term) {
+          double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of d pi_{k+1}
+          if (q == 0) xb[a] = dpi;
+          __syncwarp();
           const double* BAk = pBA + k * 80;
+          double acc2 = 0.0;
           acc += hx * dxa + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
 #pragma unroll
-          for (int i = 0; i < 8; i++) acc = fma(BAk[i * 10 + 2 + a], __shfl_sync(FULL, dpi, i, GROUP), acc);
+          for (int i = 0; i < 8; i += 2) {
+            acc = fma(BAk[i * 10 + 2 + a], xb[i], acc);
+            acc2 = fma(BAk[i * 10 + 12 + a], xb[i + 1], acc2);
+          }
+          acc += acc2;
         } else {
           acc += hxN * dxa;
         }
@@ -503,6 +535,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         if (q == 0) pPI[k * 8 + a] = fma(alpha, dpi, pPI[k * 8 + a]);
       }
     }
+    TICK(6)
     // ================= J: step of multipliers / slacks (stage-parallel), then of the primal point
     for (int i = 0; i < rounds; i++) {
       const int k = q + 4 * i;
@@ -523,8 +556,12 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     for (int e = lane; e < N1 * 8; e += 32) pX[e] = fma(alpha, pDX[e], pX[e]);
     for (int e = lane; e < N * 2; e += 32) pU[e] = fma(alpha, pDU[e], pU[e]);
     __syncwarp();
+    TICK(7)
     it++;
   }
+#ifdef IHM2B_PHASE_TIMERS
+  if (w.dbg && b == 0 && lane == 0) for (int i = 0; i < 8; i++) w.dbg[63 * 8 + i] = (double)tph[i] / (it > 0 ? it : 1);
+#endif
 
   // ------------------------------------------------------------------ outputs (RTI full step)
   __syncwarp();
@@ -557,13 +594,20 @@ int qp_smem_bytes(int N) { return ((N + 1) * PER_STAGE + S_TOT) * (int)sizeof(do
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream) {
   const int bytes = qp_smem_bytes(cf.N);
-  static int configured = 0;
+  static int configured40 = 0, configured = 0;
+  if (cf.N == 40) {
+    if (!configured40) {
+      if (cudaFuncSetAttribute(qp_rti_kernel<40>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return 1;
+      configured40 = 1;
+    }
+    qp_rti_kernel<40><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
+    return 0;
+  }
   if (configured < bytes) {
-    cudaError_t e = cudaFuncSetAttribute(qp_rti_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return (int)e;
+    if (cudaFuncSetAttribute(qp_rti_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return 1;
     configured = bytes;
   }
-  qp_rti_kernel<<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
+  qp_rti_kernel<0><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
   return 0;
 }
 

@@ -20,3 +20,7 @@ for _ in range(reps):
     e0.record(); eng.solve(x0d); e1.record(); torch.cuda.synchronize()
     print(f"B={B} solve {e0.elapsed_time(e1):.3f} ms", flush=True)
 print("ipm iters mean", eng.stats()[:, 0].mean().item())
+import ctypes as C
+tr = np.zeros((64, 8)); eng.lib.ihm2b_debug_trace(eng._h, tr.ctypes.data_as(C.c_void_p))
+names = ["A rows", "B residuals", "C riccati", "D/G fwd", "E/H rows(+chi)", "F bwd2", "I costate", "J update"]
+print("phase cycles per iteration (problem 0):", {n: int(v) for n, v in zip(names, tr[63])}, "sum", int(tr[63].sum()))
