@@ -20,9 +20,9 @@ int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, i
 int qp_smem_bytes(int N);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
-void launch_closed_loop_post(const KCfg& cf, const Work& w, int step, double* xs, const double* xn,
-                             const double* u0, const double* lap_len_dev, double* xlog, double* ulog,
-                             int32_t* done, int32_t* fail, cudaStream_t stream);
+void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
+                             const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
+                             int32_t* fail, cudaStream_t stream);
 }  // namespace ihm2b
 
 using namespace ihm2b;
@@ -402,16 +402,39 @@ int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats, void* stream) {
 }
 
 int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double* xn, int32_t* model, void* stream) {
-  (void)x; (void)u; (void)xn; (void)model; (void)stream;
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
-  return fail(IHM2B_EINVAL, "ihm2b_sim_step_dev: not implemented in this build");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
+  if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6_DYN6) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
+  launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, static_cast<cudaStream_t>(stream));
+  h->launches++;
+  CU(cudaGetLastError());
+  return IHM2B_OK;
 }
 
 int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const double* lap_length, double* xlog,
                           double* ulog, int32_t* done, int32_t* failp, void* stream) {
-  (void)n_steps; (void)x; (void)lap_length; (void)xlog; (void)ulog; (void)done; (void)failp; (void)stream;
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
-  return fail(IHM2B_EINVAL, "ihm2b_closed_loop_dev: not implemented in this build");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!x || !lap_length || !done || !failp || n_steps < 0) return fail(IHM2B_EINVAL, "bad argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t B = h->cfg.batch;
+  CU(cudaMemcpyAsync(h->lap_len, lap_length, (size_t)h->cfg.n_tracks * sizeof(double), cudaMemcpyHostToDevice, s));
+  CU(cudaMemsetAsync(done, 0xFF, B * sizeof(int32_t), s));   // -1
+  CU(cudaMemsetAsync(failp, 0xFF, B * sizeof(int32_t), s));
+  if (xlog) CU(cudaMemcpyAsync(xlog, x, B * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  for (int step = 0; step < n_steps; step++) {
+    rc = ihm2b_shift_iterate(h, stream);
+    if (rc) return rc;
+    rc = ihm2b_solve_dev(h, x, h->u0_dev, h->status_dev, stream);
+    if (rc) return rc;
+    launch_sim_step(h->cfg, h->k, h->w, x, h->u0_dev, h->xn_dev, nullptr, s);
+    launch_closed_loop_post((int)B, step, h->track, h->lap_len, h->status_dev, h->u0_dev, h->xn_dev, x, xlog, ulog, done,
+                            failp, s);
+    h->launches += 2;
+  }
+  CU(cudaGetLastError());
+  return IHM2B_OK;
 }
 
 /* development aid (not part of the public header): per-iteration IPM trace of problem 0 */

@@ -597,14 +597,14 @@ int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, i
   static int configured40 = 0, configured = 0;
   if (cf.N == 40) {
     if (!configured40) {
-      if (cudaFuncSetAttribute(qp_rti_kernel<40>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return 1;
+      if (cudaFuncSetAttribute(qp_rti_kernel<40>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
       configured40 = 1;
     }
     qp_rti_kernel<40><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
     return 0;
   }
   if (configured < bytes) {
-    if (cudaFuncSetAttribute(qp_rti_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return 1;
+    if (cudaFuncSetAttribute(qp_rti_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
     configured = bytes;
   }
   qp_rti_kernel<0><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);

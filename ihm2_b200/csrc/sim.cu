@@ -1,0 +1,222 @@
+// sim.cu -- plant step of the closed loop (python/main.py:395-400, 475-502 of the reference):
+// AcadosSimSolver with IRK, collocation_type GAUSS_RADAU_IIA, 4 stages, `sim_steps` sub-steps over
+// dt, model fkin6 (python/models.py:232-307) or fdyn6 (:455-606) chosen per step by the kinematic
+// lateral acceleration v^2 sin(beta) / l_R (main.py:482-489).
+//
+// Mapping: 4 lanes per problem, lane i evaluates the model at collocation point i, so the four
+// model evaluations of a sub-step run side by side; stage derivatives are exchanged with
+// shuffles inside the 4-lane group.  With h = dt/100 the collocation equations are far from
+// stiff (h |J| <~ 0.1) once the two actuator lags are taken out in closed form, so they are
+// solved by fixed-point iteration to round-off, warm-started from the previous sub-step, which
+// converges to the same point as acados' Newton iteration.
+//
+// fdyn6 is stated implicitly in the reference (accelerations feed the vertical loads); the
+// force balance is affine in (a_x, a_y), so the tyre terms are evaluated once per point and a
+// 2 x 2 linear solve yields the explicit right-hand side.
+#include "model.cuh"
+
+namespace ihm2b {
+
+namespace {
+
+__device__ __forceinline__ double smooth_abs_nonzero(double v) {  // python/utils.py:27-32
+  return tanh(10.0 * v) * v + 1e-6 * exp(-v * v);
+}
+__device__ __forceinline__ double lat_pacejka(const double* p, double al) {  // python/models.py:69-74
+  const double Ba = p[IHM2B_P_BA] * al;
+  return p[IHM2B_P_DA] * sin(p[IHM2B_P_CA] * atan(Ba - p[IHM2B_P_EA] * (Ba - atan(Ba))));
+}
+
+// rows 0..5 of the fdyn6 right-hand side (rows 6, 7 are the actuator lags, handled in closed form)
+__device__ void fdyn6_rhs(const double* __restrict__ x, const double* __restrict__ p, const TrackView& tr,
+                          double* __restrict__ f) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
+  const double m = p[IHM2B_P_M], g = p[IHM2B_P_G], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF], wb = lR + lF;
+  const double tw = p[IHM2B_P_TRACKW];
+  const double Fdown = 0.5 * p[IHM2B_P_CDOWN] * vx * vx;
+  const double stat = 0.5 * m * g * lF / wb;
+  const double cl = 0.5 * m * p[IHM2B_P_ZCG] / wb;   // d(lonT)/d a_x
+  const double ct = 0.5 * m * p[IHM2B_P_ZCG] / tw;   // d(latT)/d a_y
+  double sd, cd;
+  sincos(dl, &sd, &cd);
+  const double vxL = vx - 0.5 * tw * r, vxR = vx + 0.5 * tw * r;
+  const double vyF = vy + lF * r, vlatR = vy - lR * r;
+  const double aFL = atan2(-sd * vxL + cd * vyF, smooth_abs_nonzero(cd * vxL + sd * vyF));
+  const double aFR = atan2(-sd * vxR + cd * vyF, smooth_abs_nonzero(cd * vxR + sd * vyF));
+  const double aRL = atan2(vlatR, smooth_abs_nonzero(vxL));
+  const double aRR = atan2(vlatR, smooth_abs_nonzero(vxR));
+  const bool cross = p[IHM2B_P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
+  const double muFL = lat_pacejka(p, cross ? aRR : aFL), muFR = lat_pacejka(p, cross ? aRL : aFR);
+  const double muRL = lat_pacejka(p, cross ? aFR : aRL), muRR = lat_pacejka(p, cross ? aFL : aRR);
+  const double Fdrag = -(p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx) * tanh(10.0 * vx);
+  const double C = lR / wb;
+  const double td = sd / cd, Ctd = C * td;
+  const double sbeta = Ctd * rsqrt(1.0 + Ctd * Ctd);
+  const double dtau = p[IHM2B_P_KTV] * (hypot(vx, vy) * sbeta / lR - r);
+  const double idn = 1.0 / (-m * g - 0.25 * Fdown);
+  const double lonL = p[IHM2B_P_CM0] * (T - dtau) * idn, lonR = p[IHM2B_P_CM0] * (T + dtau) * idn;
+  // body-frame force per unit vertical load of each wheel, and its yaw arm
+  const double fxFL = lonL * cd - muFL * sd, fyFL = lonL * sd + muFL * cd;
+  const double fxFR = lonR * cd - muFR * sd, fyFR = lonR * sd + muFR * cd;
+  const double fxRL = lonL, fyRL = muRL, fxRR = lonR, fyRR = muRR;
+  const double mzFL = -0.5 * tw * fxFL + lF * fyFL, mzFR = 0.5 * tw * fxFR + lF * fyFR;
+  const double mzRL = -0.5 * tw * fxRL - lR * fyRL, mzRR = 0.5 * tw * fxRR - lR * fyRR;
+  // Fz_i = z0 + cx_i a_x + cy_i a_y   with (cx, cy) = FL (+cl,-ct) FR (+cl,+ct) RL (-cl,-ct) RR (-cl,+ct)
+  const double z0 = -(stat + 0.25 * Fdown);
+  const double Fx0 = z0 * (fxFL + fxFR + fxRL + fxRR) + Fdrag, Fy0 = z0 * (fyFL + fyFR + fyRL + fyRR);
+  const double Mz0 = z0 * (mzFL + mzFR + mzRL + mzRR);
+  const double gxx = cl * (fxFL + fxFR - fxRL - fxRR), gxy = ct * (-fxFL + fxFR - fxRL + fxRR);
+  const double gyx = cl * (fyFL + fyFR - fyRL - fyRR), gyy = ct * (-fyFL + fyFR - fyRL + fyRR);
+  const double gzx = cl * (mzFL + mzFR - mzRL - mzRR), gzy = ct * (-mzFL + mzFR - mzRL + mzRR);
+  const double a11 = m - gxx, a12 = -gxy, a21 = -gyx, a22 = m - gyy;
+  const double idet = 1.0 / (a11 * a22 - a12 * a21);
+  const double ax = (Fx0 * a22 - a12 * Fy0) * idet, ay = (a11 * Fy0 - a21 * Fx0) * idet;
+  const double Mz = Mz0 + gzx * ax + gzy * ay;
+  double kap, dkap, sp, cp;
+  kappa_lookup(tr, x[0], kap, dkap);
+  sincos(psi, &sp, &cp);
+  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+  f[0] = sdot;
+  f[1] = vx * sp + vy * cp;
+  f[2] = r - kap * sdot;
+  f[3] = ax + vy * r;
+  f[4] = ay - vx * r;
+  f[5] = Mz / p[IHM2B_P_IZ];
+}
+
+constexpr int MAX_FP = 80;
+
+}  // namespace
+
+struct SimCfg {
+  int B, n_grid, model, n_sub;
+  double h, sw;
+  double A[16], b[4];
+};
+
+// blockDim 128 = 32 problems; lane group of 4 = one problem
+__global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Work w, const double* __restrict__ xin,
+                                                        const double* __restrict__ uin, double* __restrict__ xout,
+                                                        int32_t* __restrict__ model_out) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = gid >> 2, i = gid & 3;
+  if (b >= sc.B) return;  // whole 4-lane groups leave together
+  const unsigned gm = 0xFu << (threadIdx.x & 28);
+  const int t = w.track[b];
+  TrackView tr{sc.n_grid, w.s_ref + (size_t)t * sc.n_grid, w.kappa_ref + (size_t)t * sc.n_grid};
+  double p[NP], x[NX];
+  for (int j = 0; j < NP; j++) p[j] = __ldg(w.params + (size_t)b * NP + j);
+  for (int j = 0; j < NX; j++) x[j] = xin[(size_t)b * NX + j];
+  const double u0 = uin[(size_t)b * 2], u1 = uin[(size_t)b * 2 + 1];
+  double wT[4], wD[4];
+  for (int j = 0; j < 4; j++) { wT[j] = __ldg(w.actw_sim + (size_t)b * 8 + j); wD[j] = __ldg(w.actw_sim + (size_t)b * 8 + 4 + j); }
+  int model = sc.model;
+  if (model == IHM2B_SIM_KIN6_DYN6) {  // python/main.py:482-489
+    const double C = p[IHM2B_P_LR] / (p[IHM2B_P_LR] + p[IHM2B_P_LF]);
+    const double beta = atan(C * tan(x[7]));
+    model = ((x[3] * x[3] + x[4] * x[4]) * sin(beta) / p[IHM2B_P_LR] <= sc.sw) ? IHM2B_SIM_FKIN6 : IHM2B_SIM_FDYN6;
+  }
+  const double h = sc.h, itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
+  double Ai[4], bw[4];
+  for (int j = 0; j < 4; j++) { Ai[j] = h * sc.A[i * 4 + j]; bw[j] = h * sc.b[j]; }
+  double K[6];  // rows 0..5 of this lane's stage derivative
+  bool ok = true, first = true;
+#pragma unroll 1
+  for (int sub = 0; sub < sc.n_sub; sub++) {
+    // actuator lags in closed form: K_j = w_j (u - x) / t
+    const double cT = (u0 - x[6]) * itT, cD = (u1 - x[7]) * itD;
+    double xs[NX];
+    xs[6] = x[6]; xs[7] = x[7];
+    double dT = 0.0, dD = 0.0;
+    for (int j = 0; j < 4; j++) { xs[6] = fma(Ai[j], wT[j] * cT, xs[6]); xs[7] = fma(Ai[j], wD[j] * cD, xs[7]); dT = fma(bw[j], wT[j] * cT, dT); dD = fma(bw[j], wD[j] * cD, dD); }
+    if (first) {  // first sub-step: start from f(x); afterwards from the previous sub-step's stages
+      double xx[NX], f[NX];
+      for (int r = 0; r < NX; r++) xx[r] = x[r];
+      if (model == IHM2B_SIM_FKIN6) fkin6<false>(xx, u0, u1, p, tr, f, nullptr); else fdyn6_rhs(xx, p, tr, f);
+      for (int r = 0; r < 6; r++) K[r] = f[r];
+      first = false;
+    }
+    int it = 0;
+    double dprev = 1e300;
+#pragma unroll 1
+    for (;; it++) {
+      for (int r = 0; r < 6; r++) {
+        double v = x[r];
+#pragma unroll
+        for (int j = 0; j < 4; j++) v = fma(Ai[j], __shfl_sync(gm, K[r], j, 4), v);
+        xs[r] = v;
+      }
+      double f[NX];
+      if (model == IHM2B_SIM_FKIN6) fkin6<false>(xs, u0, u1, p, tr, f, nullptr); else fdyn6_rhs(xs, p, tr, f);
+      double dmax = 0.0, kmax = 0.0;
+      for (int r = 0; r < 6; r++) { dmax = fmax(dmax, fabs(f[r] - K[r])); kmax = fmax(kmax, fabs(f[r])); K[r] = f[r]; }
+      if (!(dmax == dmax)) dmax = 1e300;
+      dmax = fmax(dmax, __shfl_xor_sync(gm, dmax, 1)); dmax = fmax(dmax, __shfl_xor_sync(gm, dmax, 2));
+      kmax = fmax(kmax, __shfl_xor_sync(gm, kmax, 1)); kmax = fmax(kmax, __shfl_xor_sync(gm, kmax, 2));
+      // converged to round-off: tiny update, or stagnation at the noise floor of the model evaluation
+      if (dmax <= 4e-15 * (1.0 + kmax) || (it >= 3 && dmax >= 0.5 * dprev && dmax <= 1e-11 * (1.0 + kmax))) break;
+      dprev = dmax;
+      if (it >= MAX_FP || dmax >= 1e300) { ok = false; break; }
+    }
+    for (int r = 0; r < 6; r++) {
+      double v = x[r];
+#pragma unroll
+      for (int j = 0; j < 4; j++) v = fma(bw[j], __shfl_sync(gm, K[r], j, 4), v);
+      x[r] = v;
+    }
+    x[6] += dT; x[7] += dD;
+    if (!ok) break;
+  }
+  if (i == 0) {
+    for (int r = 0; r < NX; r++) xout[(size_t)b * NX + r] = ok ? x[r] : nan("");
+    if (model_out) model_out[b] = model;
+  }
+}
+
+void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u,
+                     double* xn, int32_t* model, cudaStream_t stream) {
+  SimCfg sc;
+  sc.B = cf.B; sc.n_grid = cf.n_grid; sc.model = cfg.sim_model; sc.n_sub = cfg.sim_steps > 0 ? cfg.sim_steps : 1;
+  sc.h = cfg.dt / sc.n_sub; sc.sw = cfg.sim_switch;
+  for (int i = 0; i < 16; i++) sc.A[i] = cfg.sim_A[i];
+  for (int i = 0; i < 4; i++) sc.b[i] = cfg.sim_b[i];
+  const int threads = 128, total = cf.B * 4;
+  sim_step_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn, model);
+}
+
+// closed-loop bookkeeping after solve + plant step (python/main.py:503-517): an instance stops at
+// its first solver failure (status not in {0, 2}) or NaN in the plant (state kept), and is done
+// when s > lap_length + 1.
+__global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restrict__ track, const double* __restrict__ lap,
+                                        const int32_t* __restrict__ status, const double* __restrict__ u0,
+                                        const double* __restrict__ xn, double* __restrict__ xs, double* __restrict__ xlog,
+                                        double* __restrict__ ulog, int32_t* __restrict__ done, int32_t* __restrict__ fail) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  bool active = done[b] < 0 && fail[b] < 0;
+  double uu0 = 0.0, uu1 = 0.0;
+  if (active) {
+    const int st = status[b];
+    if (st != IHM2B_SUCCESS && st != IHM2B_MAXITER) { fail[b] = step; active = false; }
+    else { uu0 = u0[b * 2]; uu1 = u0[b * 2 + 1]; }
+  }
+  if (active) {
+    bool isnan_ = false;
+    for (int r = 0; r < 8; r++) isnan_ |= !(xn[b * 8 + r] == xn[b * 8 + r]);
+    if (isnan_) fail[b] = step;
+    else {
+      for (int r = 0; r < 8; r++) xs[b * 8 + r] = xn[b * 8 + r];
+      if (xn[b * 8] > lap[track[b]] + 1.0) done[b] = step;
+    }
+  }
+  if (ulog) { ulog[((size_t)step * B + b) * 2] = uu0; ulog[((size_t)step * B + b) * 2 + 1] = uu1; }
+  if (xlog) for (int r = 0; r < 8; r++) xlog[((size_t)(step + 1) * B + b) * 8 + r] = xs[b * 8 + r];
+}
+
+void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
+                             const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
+                             int32_t* fail, cudaStream_t stream) {
+  closed_loop_post_kernel<<<(B + 127) / 128, 128, 0, stream>>>(B, step, track, lap, status, u0, xn, xs, xlog, ulog, done, fail);
+}
+
+}  // namespace ihm2b

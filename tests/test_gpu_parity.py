@@ -183,3 +183,59 @@ def test_api_misuse_is_reported(torch_cuda, fsds):
     with pytest.raises(Ihm2bError):
         eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
     eng.close()
+
+
+@pytest.mark.parametrize("name", ["fkin6", "fdyn6", "switch"])
+def test_sim_step_matches_golden(torch_cuda, fsds, name):
+    """Plant step (Radau-IIA, 100 sub-steps; python/main.py:395-400, 475-502) vs the oracle's fixture."""
+    from ihm2_b200 import _abi
+    g = np.load(os.path.join(GOLD, "sim.npz"))
+    B = len(g["x"])
+    model = {"fkin6": _abi.SIM_FKIN6, "fdyn6": _abi.SIM_FDYN6, "switch": _abi.SIM_KIN6_DYN6}[name]
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), sim_model=model)
+    eng = _engine(cfg, fsds)
+    xn, md = eng.sim_step(torch_cuda.as_tensor(g["x"], device="cuda"), torch_cuda.as_tensor(g["u"], device="cuda"))
+    np.testing.assert_array_equal(md.cpu().numpy(), g[f"sim_{name}_model"])
+    ref = g[f"sim_{name}_x"]
+    err = np.abs(xn.cpu().numpy() - ref) / np.maximum(1.0, np.abs(ref))
+    assert err.max() < 1e-9, err.max(axis=0)
+    eng.close()
+
+
+def test_sim_step_matches_oracle_random(torch_cuda, fsds):
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B = 256
+    rng = np.random.default_rng(5)
+    x = np.stack([rng.uniform(0, 300, B), rng.uniform(-1, 1, B), rng.uniform(-0.2, 0.2, B), rng.uniform(0.5, 20, B),
+                  rng.uniform(-0.5, 0.5, B), rng.uniform(-0.5, 0.5, B), rng.uniform(-300, 300, B), rng.uniform(-0.3, 0.3, B)], 1)
+    u = np.stack([x[:, 6] + rng.uniform(-50, 50, B), x[:, 7] + rng.uniform(-0.02, 0.02, B)], 1)
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref))
+    eng = _engine(cfg, fsds)
+    xn, md = eng.sim_step(torch_cuda.as_tensor(x, device="cuda"), torch_cuda.as_tensor(u, device="cuda"))
+    xo, mo = Oracle(cfg, fsds.s_ref, fsds.kappa_ref).sim_step(x, u)
+    np.testing.assert_array_equal(md.cpu().numpy(), mo)
+    assert (mo == 1).sum() > 10 and (mo == 0).sum() > 10      # both plants exercised
+    good = ~np.isnan(xo).any(axis=1)
+    err = np.abs(xn.cpu().numpy()[good] - xo[good]) / np.maximum(1.0, np.abs(xo[good]))
+    assert good.sum() > 0.9 * B and err.max() < 1e-8, err.max(axis=0)
+    eng.close()
+
+
+def test_closed_loop_matches_golden(torch_cuda, fsds):
+    """python/main.py:448-517 with the NMPC enabled: shift -> solve -> plant step, 40 steps on the device."""
+    from ihm2_b200 import _abi
+    g = np.load(os.path.join(GOLD, "closed_loop.npz"))
+    B, n_steps = len(g["x_start"]), int(g["n_steps"])
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref))
+    eng = _engine(cfg, fsds, lap_length=[fsds.lap_length])
+    x = torch_cuda.as_tensor(g["x_start"], device="cuda").contiguous()
+    res = eng.closed_loop(x, n_steps, log=True)
+    np.testing.assert_array_equal(res["fail"].cpu().numpy(), g["fail"])
+    np.testing.assert_array_equal(res["done"].cpu().numpy(), g["done"])
+    xl, ul = res["xlog"].cpu().numpy(), res["ulog"].cpu().numpy()
+    for c in range(8):
+        assert rel(xl[..., c], g["xlog"][..., c]) < REL_TOL, c
+    for c in range(2):
+        assert rel(ul[..., c], g["ulog"][..., c]) < REL_TOL, c
+    eng.close()
