@@ -241,13 +241,11 @@ def main():
     eng.profile(False)
 
     # final gather of controls / status over NCCL (the path's only collective), after the timed loop
-    if world > 1:
-        gu = torch.empty(world * B, 2, dtype=torch.float64, device=dev); gs = torch.empty(world * B, dtype=torch.int32, device=dev)
-        dist.all_gather_into_tensor(gu, u0_d); dist.all_gather_into_tensor(gs, st_d)
-        torch.cuda.synchronize()
-        status_all = gs.cpu().numpy()
-    else:
-        status_all = status
+    from ihm2_b200.dist import gather_results
+    gu, gs, gst = gather_results(u0_d, [B] * world), gather_results(st_d, [B] * world), gather_results(stats, [B] * world)
+    torch.cuda.synchronize()
+    status_all = gs.cpu().numpy()
+    assert gu.shape[0] == world * B and gst.shape[0] == world * B
 
     if rank == 0:
         fl = flops_per_solve(n_ipm)

@@ -239,3 +239,26 @@ def test_closed_loop_matches_golden(torch_cuda, fsds):
     for c in range(2):
         assert rel(ul[..., c], g["ulog"][..., c]) < REL_TOL, c
     eng.close()
+
+
+def test_boundary_classes_reproduce_the_closed_loop(torch_cuda, fsds):
+    """IHM2Controller.compute_control + MultiModelSimulator.simulate driven from Python, as the
+    reference's loop would (python/main.py:448-517), against the oracle's golden log."""
+    from ihm2_b200.controller import IHM2Controller
+    from ihm2_b200.simulator import MultiModelSimulator
+    g = np.load(os.path.join(GOLD, "closed_loop.npz"))
+    B = len(g["x_start"])
+    ctl = IHM2Controller(fsds.s_ref, fsds.kappa_ref, batch=B)
+    sim = MultiModelSimulator(fsds.s_ref, fsds.kappa_ref, batch=B)
+    x = torch_cuda.as_tensor(g["x_start"], device="cuda")
+    assert tuple(ctl.x_pred.shape) == (B, 41, 8) and tuple(ctl.u_pred.shape) == (B, 40, 2)
+    for t in range(20):
+        u, status = ctl.compute_control(x, return_status=True)
+        assert (status == 0).all()
+        assert rel(u.cpu().numpy(), g["ulog"][t]) < REL_TOL
+        x = sim.simulate(x, u)
+        assert rel(x.cpu().numpy(), g["xlog"][t + 1]) < REL_TOL
+    # scalar numpy call keeps the reference's convention (controller.py:397-405)
+    one = IHM2Controller(fsds.s_ref, fsds.kappa_ref)
+    u = one.compute_control(g["x_start"][0])
+    assert u.shape == (2,) and rel(u, g["ulog"][0][0]) < REL_TOL
