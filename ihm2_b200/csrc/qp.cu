@@ -6,16 +6,17 @@
 // the reference tree) and the feedback phase of acados' ocp_nlp_sqp_rti for the OCP of
 // python/mpc.py:29-101 (LINEAR_LS cost, box bounds idxbx/idxbu, two rate rows C x + D u).
 //
-// Mapping: ONE WARP PER PROBLEM, the whole horizon resident in shared memory (structure of
-// arrays, stage-major: [B A], c, iterate, costate, multipliers/slacks, residuals, Riccati
-// gains, steps: 212 doubles per stage), 3 problems per SM.  Lane l = (a = l & 7, q = l >> 3).
+// Mapping: ONE WARP PER PROBLEM, 8 problems per SM.  Lane l = (a = l & 7, q = l >> 3).
 //  * serial sweeps (Riccati factorisation, forward / backward substitutions, costate): a is the
 //    row of every 8-row object (state x_a, row a of the cost-to-go matrix P, row a of [B A]);
 //    the four quarters q split the columns of the two dense products of the Riccati step;
-//    reductions are shuffles inside an 8-lane segment.
+//    hand-overs go through shared memory.  What these sweeps touch (gains, residuals, steps:
+//    58 doubles per stage) stays in shared memory for the whole solve; [B A] is streamed from
+//    L2 through a small cp.async ring a few stages ahead of its use.
 //  * everything that is independent across stages (inequality rows, residuals, step lengths,
 //    updates) runs stage-parallel: lane (a, q) handles row / state a of stages q, q+4, q+8, ...
-//    so the divisions and the row logic stay off the serial chains.
+//    directly on global memory (256 contiguous bytes per warp instruction, L2-resident while
+//    the problem is in flight), so the divisions and the row logic stay off the serial chains.
 //
 // Formulation (variables z_k = (u_k, x_k), x_0 fixed to the measured state):
 //   min sum 1/2 z'Hz + g'z   s.t.  x_{k+1} = A x_k + B u_k + c_k,   lb <= C z <= ub
@@ -24,6 +25,8 @@
 // H + C' diag(lam/t) C once by a backward Riccati sweep, and solves predictor and corrector
 // with that factor.  Equality multipliers are advanced through the costate recursion of the
 // full Newton step, which needs no stored cost-to-go matrices.
+#include <cuda_pipeline.h>
+
 #include "common.cuh"
 
 namespace ihm2b {
@@ -32,13 +35,25 @@ namespace {
 
 constexpr double TAU = 0.995, THR0 = 0.1;
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int PER_STAGE = 212;  // doubles of shared memory per stage
+constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
+#ifndef RING_P_
+#define RING_P_ 3
+#endif
+#ifndef PAR_UNROLL
+#define PAR_UNROLL 2
+#endif
+#define PAR_STR_(x) #x
+#define PAR_STR(x) PAR_STR_(x)
+#define PAR_LOOP _Pragma(PAR_STR(unroll PAR_UNROLL))
+constexpr int RING_P = RING_P_;  // [B A] prefetch distance (stages) of the serial sweeps
+constexpr int RING_R = RING_P + 1;
 constexpr int S_W = 0;          // scratch: W [8][10]
 constexpr int S_M = 80;         //          rows 2..9 of M [8][10]
 constexpr int S_P = 160;        //          P [8][8]
 constexpr int S_V = 224;        //          v [8]  (v of the Riccati step; 2 x [8] exchange buffer elsewhere)
 constexpr int S_MU = 240;       //          M00 M01 M11 mvu0 mvu1 pad[3]
-constexpr int S_TOT = 248;
+constexpr int S_RING = 248;      //          [B A] ring, RING_R x [8][10]
+constexpr int S_TOT = 248 + RING_R * 80;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -119,17 +134,8 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   const int a = lane & 7, q = lane >> 3;
   const int b = blockIdx.x;
   const int N = (NT > 0) ? NT : cf.N, N1 = N + 1;
-  // structure of arrays, stage-major
-  double* const pBA = smem;              // [N1][8][10]  (B | A) row-major
-  double* const pC = pBA + N1 * 80;      // [N1][8]
-  double* const pX = pC + N1 * 8;        // [N1][8]   iterate
-  double* const pU = pX + N1 * 8;        // [N1][2]
-  double* const pPI = pU + N1 * 2;       // [N1][8]   costate
-  double* const pLL = pPI + N1 * 8;      // [N1][8]   lamL, lamU, tL, tU
-  double* const pLU = pLL + N1 * 8;
-  double* const pTL = pLU + N1 * 8;
-  double* const pTU = pTL + N1 * 8;
-  double* const pGAM = pTU + N1 * 8;     // [N1][8]   gamma, later chi
+  // Shared memory (structure of arrays, stage-major): what the serial sweeps touch.
+  double* const pGAM = smem;             // [N1][8]   gamma -> chi -> C'(dlamL - dlamU) per state
   double* const pGX = pGAM + N1 * 8;     // [N1][8]   Newton gradient (state part), later dx
   double* const pGU = pGX + N1 * 8;      // [N1][2]   Newton gradient (control part), later du
   double* const pRG = pGU + N1 * 2;      // [N1][8]   stationarity residual (state part)
@@ -137,9 +143,45 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   double* const pK = pRB + N1 * 8;       // [N1][8][2]
   double* const pKF = pK + N1 * 16;      // [N1][4]   kff[2], kfc[2]
   double* const pMI = pKF + N1 * 4;      // [N1][4]   i00 i01 i11 pad
-  double* const pD1 = pMI + N1 * 4;      // [N1][8]   psi -> dlam_aff*dt_aff (L) -> dlamL
-  double* const pD2 = pD1 + N1 * 8;      // [N1][8]   dl  -> dlam_aff*dt_aff (U) -> dlamU
-  double* const sc = pD2 + N1 * 8;
+  double* const sc = pMI + N1 * 4;
+  // Global memory (L2-resident while the problem is in flight): what only the stage-parallel
+  // phases touch, accessed as 256 contiguous bytes per warp instruction; and [B A], which the
+  // serial sweeps stream through a small cp.async ring RING_P stages ahead of their use.
+  const double* __restrict__ const gBA = w.BA + (size_t)b * N * 80;   // [N][8][10]  (B | A) row-major
+  double* const ring = sc + S_RING;
+  // stage k -> ring slot; issue the asynchronous copy of one stage (40 chunks of 16 bytes)
+  auto ba_prefetch = [&](int k) {
+#ifdef BA_DIRECT
+    return;
+#endif
+    if (k >= 0 && k < N) {
+      double* dst = ring + (k % RING_R) * 80;
+      const double* src = gBA + k * 80;
+      __pipeline_memcpy_async(dst + 2 * lane, src + 2 * lane, 16);
+      if (lane < 8) __pipeline_memcpy_async(dst + 64 + 2 * lane, src + 64 + 2 * lane, 16);
+    }
+    __pipeline_commit();
+  };
+  // wait for stage k (the oldest outstanding copy), make it visible to the warp
+  auto ba_acquire = [&](int k) -> const double* {
+#ifdef BA_DIRECT
+    __syncwarp();
+    return gBA + k * 80;
+#endif
+    __pipeline_wait_prior(RING_P - 1);
+    __syncwarp();
+    return ring + (k % RING_R) * 80;
+  };
+  const double* __restrict__ const pC = w.c + (size_t)b * N * 8;      // [N][8]
+  double* __restrict__ const pX = w.x + (size_t)b * N1 * 8;           // [N1][8]   iterate, updated in place
+  double* __restrict__ const pU = w.u + (size_t)b * N * 2;            // [N][2]
+  double* __restrict__ const pPI = w.xa + (size_t)b * N1 * 8;         // [N1][8]   costate
+  double* __restrict__ const pLL = w.LT + (size_t)b * N1 * 32;        // [N1][8]   lamL, lamU, tL, tU
+  double* __restrict__ const pLU = pLL + N1 * 8;
+  double* __restrict__ const pTL = pLU + N1 * 8;
+  double* __restrict__ const pTU = pTL + N1 * 8;
+  double* __restrict__ const pD1 = w.D + (size_t)b * N1 * 16;         // [N1][8]   psi -> dlam_aff*dt_aff (L) -> dlamL
+  double* __restrict__ const pD2 = pD1 + N1 * 8;                      // [N1][8]   dl  -> dlam_aff*dt_aff (U) -> dlamU
   double* const sW = sc + S_W; double* const sM = sc + S_M; double* const sP = sc + S_P;
   double* const sv = sc + S_V; double* const sMu = sc + S_MU;
   double* const pDX = pGX; double* const pDU = pGU;
@@ -147,16 +189,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   // ------------------------------------------------------------------ load the problem
   double mag_b = 0.0;
   {
-    const double2* gBA = reinterpret_cast<const double2*>(w.BA + (size_t)b * N * 80);
-    double2* sBA2 = reinterpret_cast<double2*>(pBA);
-    for (int e = lane; e < N * 40; e += 32) sBA2[e] = gBA[e];
-    const double* gc = w.c + (size_t)b * N * 8;
-    for (int e = lane; e < N * 8; e += 32) { const double v = gc[e]; pC[e] = v; mag_b = fmax(mag_b, fabs(v)); }
-    const double* gx = w.x + (size_t)b * N1 * 8;
-    for (int e = lane; e < N1 * 8; e += 32) pX[e] = gx[e];
-    const double* gu = w.u + (size_t)b * N * 2;
-    for (int e = lane; e < N * 2; e += 32) pU[e] = gu[e];
-    if (lane < 2) pU[N * 2 + lane] = 0.0;
+    for (int e = lane; e < N * 8; e += 32) mag_b = fmax(mag_b, fabs(pC[e]));
     mag_b = wmax(mag_b);
   }
   const double xh = x0[(size_t)b * 8 + a];  // measured state, component a
@@ -182,13 +215,13 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
 
   // ------------------------------------------------------------------ initialisation
   // slacks / multipliers cold (t = max(distance, thr0), lam = mu0 / t), pi = 0
-  for (int i = 0; i < rounds; i++) {
+  PAR_LOOP for (int i = 0; i < rounds; i++) {
     const int k = q + 4 * i;
     if (k > N) break;
     const bool term = (k == N);
     const RowDef& R = term ? Rt : Rp;
     const bool act = term ? (a < 4) : (a < 4 || k > 0);
-    const double v = R.cu * pU[k * 2 + R.iu] + R.cx * pX[k * 8 + R.ix];
+    const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
     double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0;
     if (act) {
       tL = fmax(v - R.lb, THR0); tU = fmax(R.ub - v, THR0);
@@ -213,13 +246,13 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   while (true) {
     // ================= A: inequality rows of all stages (stage-parallel)
     double rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
-    for (int i = 0; i < rounds; i++) {
+    PAR_LOOP for (int i = 0; i < rounds; i++) {
       const int k = q + 4 * i;
       if (k > N) break;
       const bool term = (k == N);
       const RowDef& R = term ? Rt : Rp;
       const bool act = term ? (a < 4) : (a < 4 || k > 0);
-      const double v = R.cu * pU[k * 2 + R.iu] + R.cx * pX[k * 8 + R.ix];
+      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
       double gam = 0.0, psi = 0.0, dl = 0.0;
       if (act) {
         const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
@@ -238,7 +271,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     TICK(0)
     // ================= B: stationarity and dynamics residuals of all stages (stage-parallel)
     double rg_m = 0.0, rb_m = 0.0;
-    for (int i = 0; i < rounds; i++) {
+    PAR_LOOP for (int i = 0; i < rounds; i++) {
       const int k = q + 4 * i;
       if (k > N) break;
       const bool term = (k == N);
@@ -248,7 +281,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       double base_x;
       if (!term) {
         const double u0 = pU[k * 2], u1 = pU[k * 2 + 1];
-        const double2* row = reinterpret_cast<const double2*>(pBA + k * 80 + a * 10);
+        const double2* row = reinterpret_cast<const double2*>(gBA + k * 80 + a * 10);
         const double2* xx = reinterpret_cast<const double2*>(pX + k * 8);
         double acc = pC[k * 8 + a];
         const double2 bb = row[0];
@@ -266,8 +299,8 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
 #pragma unroll
         for (int r = 0; r < 8; r++) {
           const double pn = pPI[(k + 1) * 8 + r];
-          atp = fma(pBA[k * 80 + r * 10 + 2 + a], pn, atp);
-          btp = fma(pBA[k * 80 + r * 10 + j], pn, btp);
+          atp = fma(gBA[k * 80 + r * 10 + 2 + a], pn, atp);
+          btp = fma(gBA[k * 80 + r * 10 + j], pn, btp);
         }
         const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
         base_x = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - pia;
@@ -304,10 +337,12 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       sP[a * 8 + 2 * q] = (2 * q == a) ? pd : 0.0;
       sP[a * 8 + 2 * q + 1] = (2 * q + 1 == a) ? pd : 0.0;
     }
-    __syncwarp();
+#pragma unroll
+    for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
     for (int k = N - 1; k >= 0; k--) {
-      const double* BAk = pBA + k * 80;
+      const double* BAk = ba_acquire(k);   // includes the warp barrier that publishes P
+      ba_prefetch(k - RING_P);
       const double* gk = pGAM + k * 8;
       const double gam0 = gk[0], gam1 = gk[1], gam2 = gk[2], gam3 = gk[3];
       const double dgam = hx + ctc_apply(ctP, gk);
@@ -392,13 +427,16 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       {
         double dx = 0.0;  // x_0 is fixed
         const int kfo = pred ? 0 : 2;
+#pragma unroll
+        for (int d = 0; d < RING_P; d++) ba_prefetch(d);
 #pragma unroll 1
         for (int k = 0; k < N; k++) {
           if (q == 0) pDX[k * 8 + a] = dx;       // the stored step doubles as the exchange buffer
-          __syncwarp();
+          const double* BAk = ba_acquire(k);     // (warp barrier inside)
+          ba_prefetch(k + RING_P);
           const double2* dxv = reinterpret_cast<const double2*>(pDX + k * 8);
           const double2* Kv = reinterpret_cast<const double2*>(pK + k * 16);
-          const double2* row = reinterpret_cast<const double2*>(pBA + k * 80 + a * 10);
+          const double2* row = reinterpret_cast<const double2*>(BAk + a * 10);
           double u0a = pKF[k * 4 + kfo], u1a = pKF[k * 4 + kfo + 1], u0b = 0.0, u1b = 0.0;
           double xa0 = pRB[k * 8 + a], xa1 = 0.0;
 #pragma unroll
@@ -420,7 +458,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       TICK(3)
       // ---- inequality rows at the step (stage-parallel): slack / multiplier steps, step length
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
-      for (int i = 0; i < rounds; i++) {
+      PAR_LOOP for (int i = 0; i < rounds; i++) {
         const int k = q + 4 * i;
         if (k > N) break;
         const bool term = (k == N);
@@ -428,7 +466,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         const bool act = term ? (a < 4) : (a < 4 || k > 0);
         if (!act) continue;
         const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-        const double v = R.cu * pU[k * 2 + R.iu] + R.cx * pX[k * 8 + R.ix];
+        const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
         const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
         const double itL = 1.0 / tL, itU = 1.0 / tU;
         const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
@@ -449,6 +487,14 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       if (!(ratio == ratio)) { bad = true; break; }
       if (!pred) {
         alpha = TAU * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
+        // C'(dlamL - dlamU) seen by every state (stage-parallel), for the costate recursion
+        __syncwarp();
+        PAR_LOOP for (int i = 0; i < rounds; i++) {
+          const int k = q + 4 * i;
+          if (k > N) break;
+          const CtDef& ct = (k == N) ? ctT : ctP;
+          pGAM[k * 8 + a] = ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8);
+        }
         break;
       }
       const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0;
@@ -458,7 +504,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       // centring target, floored so the iterates stay on the central path at ~0.1 tol_comp
       mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
       // ---- corrector term chi of every row (stage-parallel), stored over gamma
-      for (int i = 0; i < rounds; i++) {
+      PAR_LOOP for (int i = 0; i < rounds; i++) {
         const int k = q + 4 * i;
         if (k > N) break;
         const bool act = (k == N) ? (a < 4) : (a < 4 || k > 0);
@@ -469,13 +515,15 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       // ---- backward substitution of the corrector right-hand side C' chi through the same factor
       {
         double dp = ct_apply(ctT, pGAM + N * 8);
+#pragma unroll
+        for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
         for (int k = N - 1; k >= 0; k--) {
           double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of dp
           if (q == 0) xb[a] = dp;
-          __syncwarp();
+          const double* BAk = ba_acquire(k);       // (warp barrier inside)
+          ba_prefetch(k - RING_P);
           const double* chi = pGAM + k * 8;
-          const double* BAk = pBA + k * 80;
           double dmx = ct_apply(ctP, chi), dmy = 0.0;
           double dmu0 = chi[0] + chi[2], dmu1 = chi[1] + chi[3], dmv0 = 0.0, dmv1 = 0.0;
 #pragma unroll
@@ -506,20 +554,21 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     if (alpha < 1e-12) { qp_status = 2; break; }
     __syncwarp();
 
-    // ================= I: costate recursion of the Newton step -> d pi, pi += alpha d pi
+    // ================= I: costate recursion of the Newton step -> d pi (kept in the rg slot)
     {
       double dpi = 0.0;
+#pragma unroll
+      for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
       for (int k = N; k >= 0; k--) {
         const bool term = (k == N);
-        const CtDef& ct = term ? ctT : ctP;
         const double dxa = pDX[k * 8 + a];
-        double acc = pRG[k * 8 + a] - (ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8));
+        double acc = pRG[k * 8 + a] - pGAM[k * 8 + a];
         if (!term) {
           double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of d pi_{k+1}
           if (q == 0) xb[a] = dpi;
-          __syncwarp();
-          const double* BAk = pBA + k * 80;
+          const double* BAk = ba_acquire(k);       // (warp barrier inside)
+          ba_prefetch(k - RING_P);
           double acc2 = 0.0;
           acc += hx * dxa + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
 #pragma unroll
@@ -532,12 +581,12 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
           acc += hxN * dxa;
         }
         dpi = acc;
-        if (q == 0) pPI[k * 8 + a] = fma(alpha, dpi, pPI[k * 8 + a]);
+        if (q == 0) pRG[k * 8 + a] = dpi;   // applied to pi in the update phase
       }
     }
     TICK(6)
     // ================= J: step of multipliers / slacks (stage-parallel), then of the primal point
-    for (int i = 0; i < rounds; i++) {
+    PAR_LOOP for (int i = 0; i < rounds; i++) {
       const int k = q + 4 * i;
       if (k > N) break;
       const bool term = (k == N);
@@ -545,7 +594,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       const bool act = term ? (a < 4) : (a < 4 || k > 0);
       if (!act) continue;
       const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-      const double v = R.cu * pU[k * 2 + R.iu] + R.cx * pX[k * 8 + R.ix];
+      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
       const double tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
       const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
       pLL[k * 8 + a] = fma(alpha, pD1[k * 8 + a], pLL[k * 8 + a]);
@@ -553,7 +602,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       pTL[k * 8 + a] = fma(alpha, dtL, tL); pTU[k * 8 + a] = fma(alpha, dtU, tU);
     }
     __syncwarp();
-    for (int e = lane; e < N1 * 8; e += 32) pX[e] = fma(alpha, pDX[e], pX[e]);
+    for (int e = lane; e < N1 * 8; e += 32) { pX[e] = fma(alpha, pDX[e], pX[e]); pPI[e] = fma(alpha, pRG[e], pPI[e]); }
     for (int e = lane; e < N * 2; e += 32) pU[e] = fma(alpha, pDU[e], pU[e]);
     __syncwarp();
     TICK(7)
@@ -565,12 +614,6 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
 
   // ------------------------------------------------------------------ outputs (RTI full step)
   __syncwarp();
-  {
-    double* gx = w.x + (size_t)b * N1 * 8;
-    for (int e = lane; e < N1 * 8; e += 32) gx[e] = pX[e];
-    double* gu = w.u + (size_t)b * N * 2;
-    for (int e = lane; e < N * 2; e += 32) gu[e] = pU[e];
-  }
   if (lane == 0) {
     int st;
     if (qp_status == 3) st = IHM2B_FAILURE;

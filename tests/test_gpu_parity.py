@@ -178,7 +178,7 @@ def test_api_misuse_is_reported(torch_cuda, fsds):
         Engine(cfg, fsds.s_ref, fsds.kappa_ref, track_index=np.array([0, 1, 0, 0]))      # only one track
     with pytest.raises(Ihm2bError):
         Engine(cfg, fsds.s_ref[::-1].copy(), fsds.kappa_ref)                             # s_ref not increasing
-    big = _abi.make_config(batch=4, n_grid=len(fsds.s_ref), Nf=400)                      # does not fit on chip
+    big = _abi.make_config(batch=4, n_grid=len(fsds.s_ref), Nf=500)                      # does not fit on chip
     eng = Engine(big, fsds.s_ref, fsds.kappa_ref)
     with pytest.raises(Ihm2bError):
         eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
