@@ -75,6 +75,9 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
+CPU_THREADS = 1
+
+
 def host_cores() -> int:
     return len(os.sched_getaffinity(0))
 
@@ -86,6 +89,8 @@ def cpu_oracle_rate(x0, x, u, mp, n_sample: int, repeats: int = 1):
 
     cfg = _abi.make_config(batch=n_sample, n_grid=len(mp.s_ref))
     o = Oracle(cfg, mp.s_ref, mp.kappa_ref)
+    global CPU_THREADS
+    CPU_THREADS = int(o.lib.ihm2o_set_threads(host_cores()))   # torchrun exports OMP_NUM_THREADS=1
     best = float("inf")
     for _ in range(repeats):
         t0 = time.perf_counter()
@@ -132,7 +137,7 @@ def reference_arm(args, rank: int):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": "configs[1]: 4096 perturbed initial states, single SQP-RTI step, data/skidpad, N=40, IRK-GL4",
                    "note": "acados/HPIPM not installable here: CPU restatement (oracle/ihm2_oracle.cpp), not acados"},
-        "cpu_baseline": {"value": val, "unit": "solves/s", "cores": host_cores(), "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "solves/s", "cores": CPU_THREADS, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -166,6 +171,8 @@ def main():
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+        os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
         dist.barrier()
@@ -274,7 +281,7 @@ def main():
                          "peak_source": "DFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)",
                          "flops_per_solve": fl["total"], "flops_per_launch": B * fl["qp"],
                          "hbm_secondary": {"algorithmic_bytes_per_solve": 6800, "achieved_gbs": value / world * 6800 * 1e-9, "peak_gbs": hbm}},
-            "cpu_baseline": {"value": cpu_val, "unit": "solves/s", "cores": host_cores(), "kind": "port",
+            "cpu_baseline": {"value": cpu_val, "unit": "solves/s", "cores": CPU_THREADS, "kind": "port",
                              "sample": f"first {n_cpu} of the {B} problems of one step, OpenMP over problems, {cpu_t:.2f} s"},
         }
         print(json.dumps(out))

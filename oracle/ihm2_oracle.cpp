@@ -34,6 +34,9 @@
 #include <cstring>
 #include <limits>
 #include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace {
 
@@ -951,6 +954,17 @@ void shift_iterate(int N, double* x, double* u) {  // controller.py:388-393 (lit
 extern "C" {
 
 int ihm2o_np(void) { return NP; }
+
+// OpenMP team size used by the batched entry points (torchrun exports OMP_NUM_THREADS=1)
+int ihm2o_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
 
 void ihm2o_fkin6(const double* x, const double* u, const double* p, const double* s_ref,
                  const double* kappa_ref, int n_grid, double* f, double* J /* [8][10] or NULL */) {
