@@ -47,13 +47,9 @@ constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
 #define PAR_LOOP _Pragma(PAR_STR(unroll PAR_UNROLL))
 constexpr int RING_P = RING_P_;  // [B A] prefetch distance (stages) of the serial sweeps
 constexpr int RING_R = RING_P + 1;
-constexpr int S_W = 0;          // scratch: W [8][10]
-constexpr int S_M = 80;         //          rows 2..9 of M [8][10]
-constexpr int S_P = 160;        //          P [8][8]
-constexpr int S_V = 224;        //          v [8]  (v of the Riccati step; 2 x [8] exchange buffer elsewhere)
-constexpr int S_MU = 240;       //          M00 M01 M11 mvu0 mvu1 pad[3]
-constexpr int S_RING = 248;      //          [B A] ring, RING_R x [8][10]
-constexpr int S_TOT = 248 + RING_R * 80;
+constexpr int S_V = 0;          // scratch: 2 x [8] exchange buffer of the substitution sweeps
+constexpr int S_RING = 16;      //          [B A] ring, RING_R x [8][10]
+constexpr int S_TOT = S_RING + RING_R * 80;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -66,6 +62,11 @@ __device__ __forceinline__ double wsum(double v) {   // over the warp
   v += __shfl_xor_sync(FULL, v, 8);
   v += __shfl_xor_sync(FULL, v, 16);
   return v;
+}
+// D = A (8x4, row) * B (4x8, col) + D on the FP64 tensor cores.  Lane l holds a = A[l>>2][l&3],
+// b = B[l&3][l>>2], (c0, c1) = D[l>>2][2(l&3)], D[l>>2][2(l&3)+1].
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 // NaN-propagating max
 __device__ __forceinline__ double nmax(double a, double b) { return (b > a || b != b) ? b : a; }
@@ -182,8 +183,7 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   double* __restrict__ const pTU = pTL + N1 * 8;
   double* __restrict__ const pD1 = w.D + (size_t)b * N1 * 16;         // [N1][8]   psi -> dlam_aff*dt_aff (L) -> dlamL
   double* __restrict__ const pD2 = pD1 + N1 * 8;                      // [N1][8]   dl  -> dlam_aff*dt_aff (U) -> dlamU
-  double* const sW = sc + S_W; double* const sM = sc + S_M; double* const sP = sc + S_P;
-  double* const sv = sc + S_V; double* const sMu = sc + S_MU;
+  double* const sv = sc + S_V;
   double* const pDX = pGX; double* const pDU = pGU;
 
   // ------------------------------------------------------------------ load the problem
@@ -234,8 +234,6 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
   const double inv_n = 1.0 / (16.0 * N);  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4)
   double mu = 0.0, res_g = 0.0, res_b = 0.0, res_d = 0.0, res_m = 0.0;
   int it = 0, qp_status = 1;
-  const int b0 = (q < 2) ? 3 * q : 2 * q + 2;              // first [B A] column of this quarter
-  const int c0 = b0, c1 = b0 + 1, c2 = (q < 2) ? b0 + 2 : b0 + 1;  // (q >= 2: third column is a duplicate)
 
 #ifdef IHM2B_PHASE_TIMERS
   long long tph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -245,14 +243,17 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
 #endif
   while (true) {
     // ================= A: inequality rows of all stages (stage-parallel)
+    // Also leaves what the Riccati sweep adds to M, ready to load: pGAM[k][j] = diagonal of H~_xx,
+    // pMI[k] = (M_uu diagonal addends, M_xu addends of rows T and delta).
     double rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
     PAR_LOOP for (int i = 0; i < rounds; i++) {
-      const int k = q + 4 * i;
-      if (k > N) break;
+      const int kk = q + 4 * i;
+      const bool on = (kk <= N);
+      const int k = on ? kk : N;
       const bool term = (k == N);
       const RowDef& R = term ? Rt : Rp;
-      const bool act = term ? (a < 4) : (a < 4 || k > 0);
-      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
+      const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
+      const double v = (term ? 0.0 : R.cu * pU[(term ? 0 : k) * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
       double gam = 0.0, psi = 0.0, dl = 0.0;
       if (act) {
         const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
@@ -265,7 +266,14 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         rm_m = nmax(rm_m, nmax(lamL * tL, lamU * tU));
         S0 += lamL * tL + lamU * tU;
       }
-      pGAM[k * 8 + a] = gam; pD1[k * 8 + a] = psi; pD2[k * 8 + a] = dl;
+      const CtDef& ct = term ? ctT : ctP;
+      const double g1 = __shfl_sync(FULL, gam, ct.i1, GROUP), g2 = __shfl_sync(FULL, gam, ct.i2, GROUP);
+      const double gp2 = __shfl_sync(FULL, gam, (a + 2) & 7, GROUP);
+      if (on) {
+        pGAM[k * 8 + a] = (term ? hxN : hx) + ct.c1 * g1 + fabs(ct.c2) * g2;
+        pD1[k * 8 + a] = psi; pD2[k * 8 + a] = dl;
+        if (a < 4 && !term) pMI[k * 4 + a] = (a < 2) ? ((a == 0 ? hu0 : hu1) + gam + gp2) : (-(a == 2 ? c10 : c11) - gam);
+      }
     }
     __syncwarp();
     TICK(0)
@@ -331,88 +339,74 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     TICK(1)
 
     // ================= C: backward Riccati sweep (factorisation + predictor right-hand side)
-    double pa = pGX[N * 8 + a];
+    // FP64 tensor-core form.  Lane l = (g = l >> 2, t = l & 3) owns the m8n8k4 fragments; z is
+    // ordered (x, u) here, so the extended stage matrix is E = [A | B | rb | 0] (8 x 16) and
+    //   W' = E' P           (step 1, P symmetric: its accumulator tile is its own operand)
+    //   M  = H~ + E' W      (step 2: tile 00 = M_xx, tile 01 = [M_xu | A' v], tile 11 = [M_uu | B' v])
+    // The contraction index is permuted (slot t <-> rows 2t of the first, 2t+1 of the second
+    // DMMA), which makes every accumulator pair (c0, c1) directly the operand pair of the next
+    // product: no transposition between the two steps, P never leaves registers.
     {
-      const double pd = hxN + ctc_apply(ctT, pGAM + N * 8);
-      sP[a * 8 + 2 * q] = (2 * q == a) ? pd : 0.0;
-      sP[a * 8 + 2 * q + 1] = (2 * q + 1 == a) ? pd : 0.0;
-    }
+      const int g = lane >> 2, t = lane & 3;
+      const bool dgA = (g == 2 * t), dgB = (g == 2 * t + 1);       // this lane's accumulator sits on the diagonal
+      const double pdg = pGAM[N * 8 + g];
+      double P0 = dgA ? pdg : 0.0, P1 = dgB ? pdg : 0.0;             // P[g][2t], P[g][2t+1]
+      double pp0 = pGX[N * 8 + 2 * t], pp1 = pGX[N * 8 + 2 * t + 1]; // p[2t], p[2t+1]
+      const int ra = (2 * t) * 10;
+      // per-lane sources of the accumulator initialisers (offsets in doubles from smem, stage stride added below)
+      const bool e1ring = (g < 2), e1on = (g <= 2);
+      const int o01 = (t == 1) ? (int)(pGX - smem) + g : (int)(pMI - smem) + 2 + (g & 1);
+      const int s01 = (t == 1) ? 8 : 4;
+      const bool k01a = (t == 1) || (t == 0 && g == 6), k01b = (t == 0 && g == 7);
+      const int o11 = (t == 1) ? (int)(pGU - smem) + (g & 1) : (int)(pMI - smem) + (g & 1);
+      const int s11 = (t == 1) ? 2 : 4;
+      const bool k11a = (t == 1 && g < 2) || (lane == 0), k11b = (lane == 4);
 #pragma unroll
-    for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
+      for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
-    for (int k = N - 1; k >= 0; k--) {
-      const double* BAk = ba_acquire(k);   // includes the warp barrier that publishes P
-      ba_prefetch(k - RING_P);
-      const double* gk = pGAM + k * 8;
-      const double gam0 = gk[0], gam1 = gk[1], gam2 = gk[2], gam3 = gk[3];
-      const double dgam = hx + ctc_apply(ctP, gk);
-      // ---- W = P [B A] (columns of this quarter), v = P rb + p
-      {
-        double Pr[8];
-        const double2* pr = reinterpret_cast<const double2*>(sP + a * 8);
-#pragma unroll
-        for (int j = 0; j < 4; j++) { const double2 t = pr[j]; Pr[2 * j] = t.x; Pr[2 * j + 1] = t.y; }
-        const double* rbk = pRB + k * 8;
-        double W0 = 0.0, W1 = 0.0, W2 = 0.0, va = pa;
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-          const double* bj = BAk + j * 10;
-          W0 = fma(Pr[j], bj[c0], W0); W1 = fma(Pr[j], bj[c1], W1); W2 = fma(Pr[j], bj[c2], W2);
-          va = fma(Pr[j], rbk[j], va);
-        }
-        sW[a * 10 + c0] = W0; sW[a * 10 + c1] = W1;
-        if (q < 2) sW[a * 10 + c2] = W2;
-        if (q == 0) sv[a] = va;
-      }
-      __syncwarp();
-      // ---- M = H~ + [B A]' W (rows 2.., columns of this quarter), uu block split by quarter
-      double mvx = pGX[k * 8 + a];
-      {
-        double M0 = 0.0, M1 = 0.0, M2 = 0.0, e0 = 0.0, e1 = 0.0;
-        const int ub = (q == 2) ? 1 : 0;            // B column of this quarter's uu entry
-        const int uw = (q == 0) ? 0 : 1;            // W column
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          const double* bi = BAk + i * 10;
-          const double* wi = sW + i * 10;
-          const double col = bi[2 + a], vi = sv[i];
-          M0 = fma(col, wi[c0], M0); M1 = fma(col, wi[c1], M1); M2 = fma(col, wi[c2], M2);
-          mvx = fma(col, vi, mvx);
-          if (q < 3) e0 = fma(bi[ub], wi[uw], e0);
-          else { e0 = fma(bi[0], vi, e0); e1 = fma(bi[1], vi, e1); }
-        }
-        if (c0 == 2 + a) M0 += dgam;
-        if (c1 == 2 + a) M1 += dgam;
-        if (c2 == 2 + a) M2 += dgam;
-        if (q == 0) { M0 += hxu0 - ((a == 6) ? gam2 : 0.0); M1 += hxu1 - ((a == 7) ? gam3 : 0.0); }
-        sM[a * 10 + c0] = M0; sM[a * 10 + c1] = M1;
-        if (q < 2) sM[a * 10 + c2] = M2;
-        if (a == 0) {
-          if (q < 3) sMu[q] = e0;
-          else { sMu[3] = e0; sMu[4] = e1; }
-        }
-      }
-      __syncwarp();
-      // ---- eliminate u, update P and p
-      {
-        const double M00 = sMu[0] + hu0 + gam0 + gam2, M01 = sMu[1], M11 = sMu[2] + hu1 + gam1 + gam3;
-        const double mvu0 = sMu[3] + pGU[k * 2], mvu1 = sMu[4] + pGU[k * 2 + 1];
+      for (int k = N - 1; k >= 0; k--) {
+        const double* BAk = ba_acquire(k);
+        ba_prefetch(k - RING_P);
+        // operand fragments of E and accumulator initialisers (independent of P: ahead of the chain)
+        const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];
+        const double* e1p = e1ring ? (BAk + ra + g) : (pRB + k * 8 + 2 * t);
+        double E1a = e1p[0], E1b = e1p[e1ring ? 10 : 1];
+        if (!e1on) { E1a = 0.0; E1b = 0.0; }
+        const double dgv = pGAM[k * 8 + g], v01 = smem[o01 + k * s01], v11 = smem[o11 + k * s11];
+        double T00a = dgA ? dgv : 0.0, T00b = dgB ? dgv : 0.0;
+        double T01a = k01a ? v01 : 0.0, T01b = k01b ? v01 : 0.0;
+        double T11a = k11a ? v11 : 0.0, T11b = k11b ? v11 : 0.0;
+        // ---- step 1: W' tiles (rows = columns of E, columns = rows of P)
+        double W0a = 0.0, W0b = 0.0;
+        double W1a = (g == 2) ? pp0 : 0.0, W1b = (g == 2) ? pp1 : 0.0;     // column 10: v = P rb + p
+        dmma(W1a, W1b, E1a, P0); dmma(W0a, W0b, E0a, P0);
+        dmma(W1a, W1b, E1b, P1); dmma(W0a, W0b, E0b, P1);
+        // ---- step 2: M tiles, the uu / gradient tile first (the reciprocal chain hangs on it)
+        dmma(T11a, T11b, E1a, W1a); dmma(T01a, T01b, E0a, W1a);
+        dmma(T11a, T11b, E1b, W1b); dmma(T01a, T01b, E0b, W1b);
+        dmma(T00a, T00b, E0a, W0a); dmma(T00a, T00b, E0b, W0b);
+        // ---- eliminate u
+        const double M00 = __shfl_sync(FULL, T11a, 0), M01 = __shfl_sync(FULL, T11b, 0), M11 = __shfl_sync(FULL, T11b, 4);
+        const double mvu0 = __shfl_sync(FULL, T11a, 1), mvu1 = __shfl_sync(FULL, T11a, 5);
+        const double xg0 = __shfl_sync(FULL, T01a, g << 2), xg1 = __shfl_sync(FULL, T01b, g << 2);        // M_xu row g
+        const double xa0 = __shfl_sync(FULL, T01a, t << 3), xa1 = __shfl_sync(FULL, T01b, t << 3);        // row 2t
+        const double xb0 = __shfl_sync(FULL, T01a, (t << 3) + 4), xb1 = __shfl_sync(FULL, T01b, (t << 3) + 4);  // row 2t+1
+        const double mva = __shfl_sync(FULL, T01a, (t << 3) + 1), mvb = __shfl_sync(FULL, T01a, (t << 3) + 5);  // mv_x[2t], [2t+1]
         const double idet = 1.0 / (M00 * M11 - M01 * M01);
         const double i00 = M11 * idet, i01 = -M01 * idet, i11 = M00 * idet;
-        const double Mx0 = sM[a * 10], Mx1 = sM[a * 10 + 1];
-        const double K0 = -(i00 * Mx0 + i01 * Mx1), K1 = -(i01 * Mx0 + i11 * Mx1);
-        pa = mvx + K0 * mvu0 + K1 * mvu1;
-        if (q == 0) *reinterpret_cast<double2*>(pK + k * 16 + 2 * a) = make_double2(K0, K1);
+        const double Ka0 = -(i00 * xa0 + i01 * xa1), Ka1 = -(i01 * xa0 + i11 * xa1);   // K[:, 2t]
+        const double Kb0 = -(i00 * xb0 + i01 * xb1), Kb1 = -(i01 * xb0 + i11 * xb1);   // K[:, 2t+1]
+        P0 = fma(xg0, Ka0, fma(xg1, Ka1, T00a));
+        P1 = fma(xg0, Kb0, fma(xg1, Kb1, T00b));
+        pp0 = fma(Ka0, mvu0, fma(Ka1, mvu1, mva));
+        pp1 = fma(Kb0, mvu0, fma(Kb1, mvu1, mvb));
+        if (g == 0) {
+          *reinterpret_cast<double2*>(pK + k * 16 + 4 * t) = make_double2(Ka0, Ka1);
+          *reinterpret_cast<double2*>(pK + k * 16 + 4 * t + 2) = make_double2(Kb0, Kb1);
+        }
         if (lane == 0) {
           pKF[k * 4] = -(i00 * mvu0 + i01 * mvu1); pKF[k * 4 + 1] = -(i01 * mvu0 + i11 * mvu1);
           pMI[k * 4] = i00; pMI[k * 4 + 1] = i01; pMI[k * 4 + 2] = i11;
-        }
-#pragma unroll
-        for (int t = 0; t < 2; t++) {
-          const int j = 2 * q + t;
-          const double Mj0 = sM[j * 10], Mj1 = sM[j * 10 + 1];
-          const double K0j = -(i00 * Mj0 + i01 * Mj1), K1j = -(i01 * Mj0 + i11 * Mj1);
-          sP[a * 8 + j] = fma(Mx0, K0j, fma(Mx1, K1j, sM[a * 10 + 2 + j]));
         }
       }
       __syncwarp();
