@@ -39,6 +39,9 @@ constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
 #ifndef RING_P_
 #define RING_P_ 3
 #endif
+#ifndef QP_MIN_BLOCKS
+#define QP_MIN_BLOCKS 10   // problems (warps) per SM the register allocation is held to
+#endif
 #ifndef PAR_UNROLL
 #define PAR_UNROLL 2
 #endif
@@ -67,6 +70,15 @@ __device__ __forceinline__ double wsum(double v) {   // over the warp
 // b = B[l&3][l>>2], (c0, c1) = D[l>>2][2(l&3)], D[l>>2][2(l&3)+1].
 __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+// Predicated shared-memory stores (one lane of the warp writes; no divergent branch on the serial chains)
+__device__ __forceinline__ void sts_if(bool p, double* ptr, double v) {
+  asm volatile("{.reg .pred p; setp.ne.b32 p, %0, 0; @p st.shared.f64 [%1], %2;}"
+               :: "r"((int)p), "r"((unsigned)__cvta_generic_to_shared(ptr)), "d"(v) : "memory");
+}
+__device__ __forceinline__ void sts2_if(bool p, double* ptr, double v0, double v1) {
+  asm volatile("{.reg .pred p; setp.ne.b32 p, %0, 0; @p st.shared.v2.f64 [%1], {%2, %3};}"
+               :: "r"((int)p), "r"((unsigned)__cvta_generic_to_shared(ptr)), "d"(v0), "d"(v1) : "memory");
 }
 // NaN-propagating max
 __device__ __forceinline__ double nmax(double a, double b) { return (b > a || b != b) ? b : a; }
@@ -126,7 +138,7 @@ __device__ __forceinline__ double ctc_apply(const CtDef& d, const double* q) { r
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
 template <int NT>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
-__global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
+__global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf, const Work w,
                                                      const double* __restrict__ x0,
                                                      double* __restrict__ u0_out,
                                                      int32_t* __restrict__ status_out) {
@@ -155,12 +167,13 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
 #ifdef BA_DIRECT
     return;
 #endif
-    if (k >= 0 && k < N) {
-      double* dst = ring + (k % RING_R) * 80;
-      const double* src = gBA + k * 80;
-      __pipeline_memcpy_async(dst + 2 * lane, src + 2 * lane, 16);
-      if (lane < 8) __pipeline_memcpy_async(dst + 64 + 2 * lane, src + 64 + 2 * lane, 16);
-    }
+    // out-of-range requests re-copy the first / last stage into the slot that already holds it
+    k = max(0, min(k, N - 1));
+    double* dst = ring + (k % RING_R) * 80;
+    const double* src = gBA + k * 80;
+    __pipeline_memcpy_async(dst + 2 * lane, src + 2 * lane, 16);                                   // bytes 0..511
+    __pipeline_memcpy_async(reinterpret_cast<float*>(dst + 64) + lane,
+                            reinterpret_cast<const float*>(src + 64) + lane, 4);                  // bytes 512..639
     __pipeline_commit();
   };
   // wait for stage k (the oldest outstanding copy), make it visible to the warp
@@ -400,14 +413,11 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
         P1 = fma(xg0, Kb0, fma(xg1, Kb1, T00b));
         pp0 = fma(Ka0, mvu0, fma(Ka1, mvu1, mva));
         pp1 = fma(Kb0, mvu0, fma(Kb1, mvu1, mvb));
-        if (g == 0) {
-          *reinterpret_cast<double2*>(pK + k * 16 + 4 * t) = make_double2(Ka0, Ka1);
-          *reinterpret_cast<double2*>(pK + k * 16 + 4 * t + 2) = make_double2(Kb0, Kb1);
-        }
-        if (lane == 0) {
-          pKF[k * 4] = -(i00 * mvu0 + i01 * mvu1); pKF[k * 4 + 1] = -(i01 * mvu0 + i11 * mvu1);
-          pMI[k * 4] = i00; pMI[k * 4 + 1] = i01; pMI[k * 4 + 2] = i11;
-        }
+        sts2_if(g == 0, pK + k * 16 + 4 * t, Ka0, Ka1);
+        sts2_if(g == 0, pK + k * 16 + 4 * t + 2, Kb0, Kb1);
+        sts2_if(lane == 0, pKF + k * 4, -(i00 * mvu0 + i01 * mvu1), -(i01 * mvu0 + i11 * mvu1));
+        sts2_if(lane == 0, pMI + k * 4, i00, i01);
+        sts_if(lane == 0, pMI + k * 4 + 2, i11);
       }
       __syncwarp();
     }
@@ -418,34 +428,37 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     bool bad = false;
     for (int pred = 1; pred >= 0; pred--) {
       // ---- forward substitution: du = K dx + kf, dx+ = A dx + B du + rb
+      // Matrix-vector products as DMMAs whose right operand repeats the vector in all 8 columns:
+      // lane (g, t) holds (dx[2t], dx[2t+1]) going in and receives row g of the result.
       {
-        double dx = 0.0;  // x_0 is fixed
+        const int g = lane >> 2, t = lane & 3;
+        double dxa = 0.0, dxb = 0.0;  // x_0 is fixed
         const int kfo = pred ? 0 : 2;
+        const bool lo = (g < 2), tlo = (t < 2);
 #pragma unroll
         for (int d = 0; d < RING_P; d++) ba_prefetch(d);
 #pragma unroll 1
         for (int k = 0; k < N; k++) {
-          if (q == 0) pDX[k * 8 + a] = dx;       // the stored step doubles as the exchange buffer
           const double* BAk = ba_acquire(k);     // (warp barrier inside)
           ba_prefetch(k + RING_P);
-          const double2* dxv = reinterpret_cast<const double2*>(pDX + k * 8);
-          const double2* Kv = reinterpret_cast<const double2*>(pK + k * 16);
-          const double2* row = reinterpret_cast<const double2*>(BAk + a * 10);
-          double u0a = pKF[k * 4 + kfo], u1a = pKF[k * 4 + kfo + 1], u0b = 0.0, u1b = 0.0;
-          double xa0 = pRB[k * 8 + a], xa1 = 0.0;
-#pragma unroll
-          for (int j = 0; j < 4; j++) {
-            const double2 d = dxv[j], ka = Kv[2 * j], kb = Kv[2 * j + 1], aa = row[1 + j];
-            u0a = fma(ka.x, d.x, u0a); u1a = fma(ka.y, d.x, u1a);
-            u0b = fma(kb.x, d.y, u0b); u1b = fma(kb.y, d.y, u1b);
-            xa0 = fma(aa.x, d.x, xa0); xa1 = fma(aa.y, d.y, xa1);
-          }
-          const double du0 = u0a + u0b, du1 = u1a + u1b;
-          if (lane == 0) { pDU[k * 2] = du0; pDU[k * 2 + 1] = du1; }
-          const double2 bb = row[0];
-          dx = fma(bb.x, du0, fma(bb.y, du1, xa0 + xa1));
+          sts2_if(g == 0, pDX + k * 8 + 2 * t, dxa, dxb);
+          const double2 Af = *reinterpret_cast<const double2*>(BAk + g * 10 + 2 + 2 * t);   // A[g][2t], A[g][2t+1]
+          double Ka = pK[k * 16 + 4 * t + (g & 1)], Kb = pK[k * 16 + 4 * t + 2 + (g & 1)];  // K[g][2t], K[g][2t+1]
+          double Bf = BAk[g * 10 + (t & 1)];                                               // B[g][t]
+          double kf = pKF[k * 4 + kfo + (g & 1)];
+          const double rbg = pRB[k * 8 + g];
+          if (!lo) { Ka = 0.0; Kb = 0.0; kf = 0.0; }
+          if (!tlo) Bf = 0.0;
+          double U0 = kf, U1 = kf, X0 = rbg, X1 = rbg;
+          dmma(U0, U1, Ka, dxa); dmma(X0, X1, Af.x, dxa);
+          dmma(U0, U1, Kb, dxb); dmma(X0, X1, Af.y, dxb);
+          double duf = __shfl_sync(FULL, U0, (t & 1) << 2);      // du[t] for the k-slots 0, 1
+          if (!tlo) duf = 0.0;
+          dmma(X0, X1, Bf, duf);
+          sts_if((lane & ~4) == 0, pDU + k * 2 + (lane >> 2), U0);
+          dxa = __shfl_sync(FULL, X0, t << 3); dxb = __shfl_sync(FULL, X0, (t << 3) + 4);
         }
-        if (q == 0) pDX[N * 8 + a] = dx;
+        if (g == 0) *reinterpret_cast<double2*>(pDX + N * 8 + 2 * t) = make_double2(dxa, dxb);
         if (lane < 2) pDU[N * 2 + lane] = 0.0;
       }
       __syncwarp();
@@ -481,13 +494,17 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       if (!(ratio == ratio)) { bad = true; break; }
       if (!pred) {
         alpha = TAU * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
-        // C'(dlamL - dlamU) seen by every state (stage-parallel), for the costate recursion
+        // right-hand side of the costate recursion per state (stage-parallel):
+        // rg - C'(dlamL - dlamU) + (H dz)_x, left in the gamma slot
         __syncwarp();
         PAR_LOOP for (int i = 0; i < rounds; i++) {
           const int k = q + 4 * i;
           if (k > N) break;
-          const CtDef& ct = (k == N) ? ctT : ctP;
-          pGAM[k * 8 + a] = ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8);
+          const bool term = (k == N);
+          const CtDef& ct = term ? ctT : ctP;
+          const double cdl = ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8);
+          const double hdz = term ? hxN * pDX[k * 8 + a] : hx * pDX[k * 8 + a] + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
+          pGAM[k * 8 + a] = pRG[k * 8 + a] - cdl + hdz;
         }
         break;
       }
@@ -497,46 +514,56 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
       const double sr = mu_aff / mu;
       // centring target, floored so the iterates stay on the central path at ~0.1 tol_comp
       mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
-      // ---- corrector term chi of every row (stage-parallel), stored over gamma
+      // ---- corrector term chi of every row (stage-parallel); what the backward sweep adds per state
+      // (C' chi) goes to the gamma slot, the two control entries to the kfc slot
       PAR_LOOP for (int i = 0; i < rounds; i++) {
-        const int k = q + 4 * i;
-        if (k > N) break;
-        const bool act = (k == N) ? (a < 4) : (a < 4 || k > 0);
-        pGAM[k * 8 + a] = act ? (pD1[k * 8 + a] - mu_t) / pTL[k * 8 + a] - (pD2[k * 8 + a] - mu_t) / pTU[k * 8 + a] : 0.0;
+        const int kk = q + 4 * i;
+        const bool on = (kk <= N);
+        const int k = on ? kk : N;
+        const bool term = (k == N);
+        const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
+        double chi = 0.0;
+        if (act) chi = (pD1[k * 8 + a] - mu_t) / pTL[k * 8 + a] - (pD2[k * 8 + a] - mu_t) / pTU[k * 8 + a];
+        const CtDef& ct = term ? ctT : ctP;
+        const double c1v = __shfl_sync(FULL, chi, ct.i1, GROUP), c2v = __shfl_sync(FULL, chi, ct.i2, GROUP);
+        const double cp2 = __shfl_sync(FULL, chi, (a + 2) & 7, GROUP);
+        if (on) {
+          pGAM[k * 8 + a] = ct.c1 * c1v + ct.c2 * c2v;
+          if (a < 2 && !term) pKF[k * 4 + 2 + a] = chi + cp2;
+        }
       }
       __syncwarp();
       TICK(4)
       // ---- backward substitution of the corrector right-hand side C' chi through the same factor
+      //   dmu = chi_u + B' dp+,  kfc = kff - M_uu^-1 dmu,  dp = (C' chi)_x + A' dp+ + K' dmu      (DMMA form)
       {
-        double dp = ct_apply(ctT, pGAM + N * 8);
+        const int g = lane >> 2, t = lane & 3;
+        const bool lo = (g < 2), tlo = (t < 2);
+        const int ra = (2 * t) * 10;
+        double dpa = pGAM[N * 8 + 2 * t], dpb = pGAM[N * 8 + 2 * t + 1];
 #pragma unroll
         for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
         for (int k = N - 1; k >= 0; k--) {
-          double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of dp
-          if (q == 0) xb[a] = dp;
           const double* BAk = ba_acquire(k);       // (warp barrier inside)
           ba_prefetch(k - RING_P);
-          const double* chi = pGAM + k * 8;
-          double dmx = ct_apply(ctP, chi), dmy = 0.0;
-          double dmu0 = chi[0] + chi[2], dmu1 = chi[1] + chi[3], dmv0 = 0.0, dmv1 = 0.0;
-#pragma unroll
-          for (int i = 0; i < 8; i += 2) {
-            const double p0 = xb[i], p1 = xb[i + 1];
-            const double2 b0v = *reinterpret_cast<const double2*>(BAk + i * 10);
-            const double2 b1v = *reinterpret_cast<const double2*>(BAk + i * 10 + 10);
-            dmx = fma(BAk[i * 10 + 2 + a], p0, dmx); dmy = fma(BAk[i * 10 + 12 + a], p1, dmy);
-            dmu0 = fma(b0v.x, p0, dmu0); dmu1 = fma(b0v.y, p0, dmu1);
-            dmv0 = fma(b1v.x, p1, dmv0); dmv1 = fma(b1v.y, p1, dmv1);
-          }
-          dmx += dmy; dmu0 += dmv0; dmu1 += dmv1;
-          const double2 Kc = *reinterpret_cast<const double2*>(pK + k * 16 + 2 * a);
+          const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];        // A[2t][g], A[2t+1][g]
+          double E1a = BAk[ra + (g & 1)], E1b = BAk[ra + 10 + (g & 1)];      // B[2t][g], B[2t+1][g]
+          double Ui = pKF[k * 4 + 2 + (g & 1)];
+          double Kf = pK[k * 16 + 2 * g + (t & 1)];                          // K[t][g]
+          const double Xi = pGAM[k * 8 + g];
+          const double kf0 = pKF[k * 4], kf1 = pKF[k * 4 + 1];
           const double i00 = pMI[k * 4], i01 = pMI[k * 4 + 1], i11 = pMI[k * 4 + 2];
-          if (lane == 0) {
-            pKF[k * 4 + 2] = pKF[k * 4] - (i00 * dmu0 + i01 * dmu1);
-            pKF[k * 4 + 3] = pKF[k * 4 + 1] - (i01 * dmu0 + i11 * dmu1);
-          }
-          dp = dmx + Kc.x * dmu0 + Kc.y * dmu1;
+          if (!lo) { E1a = 0.0; E1b = 0.0; Ui = 0.0; }
+          if (!tlo) Kf = 0.0;
+          double U0 = Ui, U1 = Ui, X0 = Xi, X1 = Xi;
+          dmma(U0, U1, E1a, dpa); dmma(X0, X1, E0a, dpa);
+          dmma(U0, U1, E1b, dpb); dmma(X0, X1, E0b, dpb);
+          const double d0 = __shfl_sync(FULL, U0, 0), d1 = __shfl_sync(FULL, U0, 4);
+          const double dmuf = tlo ? ((t == 0) ? d0 : d1) : 0.0;
+          dmma(X0, X1, Kf, dmuf);
+          sts2_if(lane == 0, pKF + k * 4 + 2, kf0 - (i00 * d0 + i01 * d1), kf1 - (i01 * d0 + i11 * d1));
+          dpa = __shfl_sync(FULL, X0, t << 3); dpb = __shfl_sync(FULL, X0, (t << 3) + 4);
         }
       }
       __syncwarp();
@@ -549,34 +576,26 @@ __global__ void __launch_bounds__(32) qp_rti_kernel(const KCfg cf, const Work w,
     __syncwarp();
 
     // ================= I: costate recursion of the Newton step -> d pi (kept in the rg slot)
+    //   dpi_k = [rg - C' dlam + H dz]_k + A_k' dpi_{k+1}                                   (DMMA form)
     {
-      double dpi = 0.0;
+      const int g = lane >> 2, t = lane & 3;
+      const int ra = (2 * t) * 10;
+      double da = pGAM[N * 8 + 2 * t], db = pGAM[N * 8 + 2 * t + 1];
+      sts2_if(g == 0, pRG + N * 8 + 2 * t, da, db);
 #pragma unroll
       for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
 #pragma unroll 1
-      for (int k = N; k >= 0; k--) {
-        const bool term = (k == N);
-        const double dxa = pDX[k * 8 + a];
-        double acc = pRG[k * 8 + a] - pGAM[k * 8 + a];
-        if (!term) {
-          double* xb = sv + ((k & 1) << 3);        // double-buffered exchange of d pi_{k+1}
-          if (q == 0) xb[a] = dpi;
-          const double* BAk = ba_acquire(k);       // (warp barrier inside)
-          ba_prefetch(k - RING_P);
-          double acc2 = 0.0;
-          acc += hx * dxa + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
-#pragma unroll
-          for (int i = 0; i < 8; i += 2) {
-            acc = fma(BAk[i * 10 + 2 + a], xb[i], acc);
-            acc2 = fma(BAk[i * 10 + 12 + a], xb[i + 1], acc2);
-          }
-          acc += acc2;
-        } else {
-          acc += hxN * dxa;
-        }
-        dpi = acc;
-        if (q == 0) pRG[k * 8 + a] = dpi;   // applied to pi in the update phase
+      for (int k = N - 1; k >= 0; k--) {
+        const double* BAk = ba_acquire(k);         // (warp barrier inside)
+        ba_prefetch(k - RING_P);
+        const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];
+        const double Xi = pGAM[k * 8 + g];
+        double X0 = Xi, X1 = Xi;
+        dmma(X0, X1, E0a, da); dmma(X0, X1, E0b, db);
+        sts_if(t == 0, pRG + k * 8 + g, X0);       // applied to pi in the update phase
+        da = __shfl_sync(FULL, X0, t << 3); db = __shfl_sync(FULL, X0, (t << 3) + 4);
       }
+      __syncwarp();
     }
     TICK(6)
     // ================= J: step of multipliers / slacks (stage-parallel), then of the primal point
