@@ -170,7 +170,8 @@ class IHM2Controller(Controller):
                  q_v_x_f: float = 1.0, q_v_y_f: float = 1.0, q_r_f: float = 1.0, q_T_f: float = 1.0,
                  q_delta_f: float = 100.0, q_T_dot: float = 0.0, q_delta_dot: float = 500.0, *, batch: int = 1,
                  car_params: CarParams | None = None, params=None, track_index=None, lap_length=None,
-                 integrator: str = "IRK", sim_model: int = _abi.SIM_KIN6_DYN6) -> None:
+                 integrator: str = "IRK", sim_model: int = _abi.SIM_KIN6_DYN6, nlp_solver_type: str = "SQP_RTI",
+                 nlp_solver_max_iter: int = 2) -> None:
         super().__init__(car_params)
         self.Nf, self.dt, self.s_target = Nf, dt, s_target
         self.config = Controller.Config(horizon_size=Nf, sampling_time=dt)
@@ -183,7 +184,12 @@ class IHM2Controller(Controller):
                                s_target=s_target, n_max=n_max, v_x_max=v_x_max, T_max=T_max, delta_max=delta_max,
                                T_dot_max=T_dot_max, delta_dot_max=delta_dot_max, a_lat_max=a_lat_max, W=W, W_e=W_e,
                                integrator=_abi.IRK_GL4 if integrator.upper().startswith("IRK") else _abi.ERK4,
-                               sim_model=sim_model)
+                               sim_model=sim_model,
+                               # controller.py:301-302 hard-codes "SQP" with 2 iterations and MERIT_BACKTRACKING; the
+                               # default here is the RTI step BASELINE.json's metric is quoted on.  "SQP" runs the full-step
+                               # loop with the KKT test (the merit line search is not implemented).
+                               nlp_solver=_abi.SQP if nlp_solver_type.upper() == "SQP" else _abi.SQP_RTI,
+                               nlp_max_iter=nlp_solver_max_iter, globalization=_abi.FIXED_STEP)
         if params is None:
             params = np.tile(self.car_params.to_vector(), (batch, 1))
         self.solver = Engine(cfg, s_ref, kappa_ref, track_index=track_index, params=params, lap_length=lap_length)

@@ -18,6 +18,8 @@ void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream);
 int qp_smem_bytes(int N);
+void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
+                         int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
@@ -52,6 +54,7 @@ struct ihm2b_handle {
   // scratch for the host entry point and the closed loop
   double *x0_dev, *u0_dev, *xn_dev;
   int32_t* status_dev;
+  int32_t* active_dev;   // SQP mode: instances still iterating
   double *x0_pin, *u0_pin;
   int32_t* status_pin;
   bool have_tracks, have_params;
@@ -103,6 +106,11 @@ __global__ void shift_iterate_kernel(int B, int N, double* x, double* u, const i
     for (int j = 0; j < N - 1; j++) up[j * 2] = up[(j + 1) * 2];
     up[(N - 1) * 2] = 0.0;
   }
+}
+
+__global__ void fill_i32_kernel(int n, int32_t* p, int32_t v) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid < n) p[gid] = v;
 }
 
 void fill_kcfg(const ihm2b_config& c, KCfg& k) {
@@ -180,7 +188,9 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->u0_dev, B * 2);
   ALLOC(h->xn_dev, B * 8);
   ALLOC(h->status_dev, B);
+  ALLOC(h->active_dev, B);
 #undef ALLOC
+  w.active = nullptr; w.sqp_it = -1;
   if (rc == IHM2B_OK) {
     cudaError_t e = cudaMallocHost(&h->x0_pin, B * 8 * sizeof(double));
     if (e == cudaSuccess) e = cudaMallocHost(&h->u0_pin, B * 2 * sizeof(double));
@@ -325,8 +335,35 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   int rc = check_ready(h);
   if (rc) return rc;
   if (!x0) return fail(IHM2B_EINVAL, "null x0");
-  if (h->cfg.nlp_solver != IHM2B_SQP_RTI) return fail(IHM2B_EINVAL, "nlp_solver %d: not implemented in this build", h->cfg.nlp_solver);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (h->cfg.nlp_solver == IHM2B_SQP) {
+    // acados ocp_nlp_sqp restated (configured by new_python/controller.py:301-302):
+    // repeat { linearise; KKT residual test with the multipliers of the last QP; QP; full step }.
+    // Instances that converged (status 0) or whose QP failed (status 1 / 4) drop out through
+    // the `active` mask; the others end with status 2 (ACADOS_MAXITER), which the reference
+    // tolerates (mpc_control_node.cpp:190-197).  Step length: fixed 1.0.
+    if (h->cfg.globalization != IHM2B_FIXED_STEP)
+      return fail(IHM2B_EINVAL, "globalization %d: the merit-function line search is not implemented, use IHM2B_FIXED_STEP",
+                  h->cfg.globalization);
+    if (h->cfg.nlp_max_iter < 1) return fail(IHM2B_EINVAL, "nlp_max_iter %d < 1", h->cfg.nlp_max_iter);
+    fill_i32_kernel<<<(h->cfg.batch + 255) / 256, 256, 0, s>>>(h->cfg.batch, h->active_dev, 1);
+    fill_i32_kernel<<<(h->cfg.batch + 255) / 256, 256, 0, s>>>(h->cfg.batch, h->w.status, IHM2B_MAXITER);
+    if (status) fill_i32_kernel<<<(h->cfg.batch + 255) / 256, 256, 0, s>>>(h->cfg.batch, status, IHM2B_MAXITER);
+    h->launches += status ? 3 : 2;
+    Work w = h->w;
+    w.active = h->active_dev;
+    for (int it = 0; it < h->cfg.nlp_max_iter; it++) {
+      w.sqp_it = it;
+      launch_linearize(h->k, w, s);
+      launch_nlp_residual(h->k, w, x0, h->cfg.nlp_tol, it > 0, status, s);
+      if (launch_qp_rti(h->k, w, x0, u0, status, s) != 0)
+        return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
+                    qp_smem_bytes(h->cfg.N), h->cfg.N);
+      h->launches += 3;
+    }
+    CU(cudaGetLastError());
+    return IHM2B_OK;
+  }
   // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
   // enters the feedback phase, as the fixed x_0 of the QP.
   if (h->profile) cudaEventRecord(h->ev[0], s);

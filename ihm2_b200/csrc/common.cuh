@@ -57,6 +57,9 @@ struct Work {
   double* stats;            // [B][8]
   int32_t* status;          // [B]
   double* dbg;              // [64][8] per-iteration trace of problem 0 (development aid), may be NULL
+  // SQP mode (nlp_solver = SQP): instances still iterating, index of the current SQP iteration
+  int32_t* active;          // [B], NULL in RTI mode (all instances run)
+  int sqp_it;               // -1 in RTI mode
 };
 
 }  // namespace ihm2b

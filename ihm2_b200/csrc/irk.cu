@@ -266,6 +266,7 @@ __global__ void __launch_bounds__(128) linearize_irk_kernel(const KCfg cf, const
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= cf.B * cf.N) return;
   const int b = gid / cf.N, k = gid - b * cf.N;
+  if (w.active && !w.active[b]) return;   // SQP mode: instance already converged or failed
   const int t = w.track[b];
   TrackView tr{cf.n_grid, w.s_ref + (size_t)t * cf.n_grid, w.kappa_ref + (size_t)t * cf.n_grid};
   double p[NP], x[NX], wa[8];

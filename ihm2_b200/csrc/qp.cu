@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   const int lane = threadIdx.x;
   const int a = lane & 7, q = lane >> 3;
   const int b = blockIdx.x;
+  if (w.active && !w.active[b]) return;      // SQP mode: instance already converged or failed
   const int N = (NT > 0) ? NT : cf.N, N1 = N + 1;
   // Shared memory (structure of arrays, stage-major): what the serial sweeps touch.
   double* const pGAM = smem;             // [N1][8]   gamma -> chi -> C'(dlamL - dlamU) per state
@@ -637,12 +638,111 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
                          res_d <= 1e-6 * (1.0 + mag_d) && res_m <= 1e-6;
       st = loose ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
     }
+    double* sp = w.stats + (size_t)b * 8;
+    if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics
+      sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m; sp[7] = 0.0;
+    } else {                     // SQP: the NLP residuals (sp[3..6]) are written by nlp_residual_kernel
+      sp[0] = (w.sqp_it > 0 ? sp[0] : 0.0) + it; sp[1] = w.sqp_it + 1; sp[2] = mu; sp[7] = 0.0;
+      if (st != IHM2B_SUCCESS) w.active[b] = 0;   // the iteration stops at a failed QP (status 1 / 4)
+      else st = IHM2B_MAXITER;                    // until the residual test of a later iteration says converged
+    }
     w.status[b] = st;
     if (status_out) status_out[b] = st;
-    double* sp = w.stats + (size_t)b * 8;
-    sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m; sp[7] = 0.0;
   }
   if (u0_out && lane < 2) u0_out[(size_t)b * 2 + lane] = pU[lane];
+}
+
+// ---------------------------------------------------------------------------------------
+// SQP mode: KKT residuals of the NLP at the current iterate with the multipliers of the last
+// QP (acados ocp_nlp_sqp, SURVEY App. C: res_stat, res_eq, res_ineq, res_comp in the
+// infinity norm; all <= nlp_tol stops the instance with status 0).  Uses the fresh
+// linearisation (phi, [B A]).  One warp per problem, lane (a, q) = state / row a of the
+// stages q, q+4, ...  grid = B, block = 32.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const Work w, const double* __restrict__ x0,
+                                                          const double nlp_tol, const int have_mult,
+                                                          int32_t* __restrict__ status_out) {
+  const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
+  if (w.active && !w.active[b]) return;
+  const int N = cf.N, N1 = N + 1;
+  const double* gBA = w.BA + (size_t)b * N * 80;
+  const double* phi = w.phi + (size_t)b * N * 8;
+  const double* pX = w.x + (size_t)b * N1 * 8;
+  const double* pU = w.u + (size_t)b * N * 2;
+  const double* pPI = w.xa + (size_t)b * N1 * 8;
+  const double* pLL = w.LT + (size_t)b * N1 * 32;
+  const double* pLU = pLL + N1 * 8;
+  const double s0 = x0[(size_t)b * 8];
+  const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
+  const double hxN = cf.ct * cf.We[a];
+  const double hu0 = cf.cs * (cf.W[8] + cf.W[10]), hu1 = cf.cs * (cf.W[9] + cf.W[11]);
+  const double c10 = cf.cs * cf.W[10], c11 = cf.cs * cf.W[11];
+  const double hxu0 = (a == 6) ? -c10 : 0.0, hxu1 = (a == 7) ? -c11 : 0.0;
+  const double gs_scale = -cf.cs * cf.W[0], gsN = -cf.ct * cf.We[0] * (s0 + cf.s_target);
+  const RowDef Rp = row_path(cf, a), Rt = row_term(cf, a);
+  const CtDef ctP = ct_path(a), ctT = ct_term(a);
+  double rs = 0.0, re = fabs(pX[a] - x0[(size_t)b * 8 + a]), ri = 0.0, rc = 0.0;
+  const unsigned seg = 0xffu << (8 * q);   // the segments run different trip counts
+  for (int k = q; k <= N; k += 4) {
+    const bool term = (k == N);
+    const double xa_ = pX[k * 8 + a];
+    // inequality row a of this stage
+    const RowDef& R = term ? Rt : Rp;
+    const bool act = term ? (a < 4) : (a < 4 || k > 0);
+    double dl = 0.0;
+    if (act) {
+      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
+      ri = nmax(ri, nmax(R.lb - v, v - R.ub));
+      if (have_mult) {
+        const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a];
+        dl = lamL - lamU;
+        rc = nmax(rc, nmax(fabs(lamL * (v - R.lb)), fabs(lamU * (R.ub - v))));
+      }
+    }
+    // C'(lamL - lamU): the rows of this stage live in the 8 lanes of this segment
+    const CtDef& ct = term ? ctT : ctP;
+    const double d1 = __shfl_sync(seg, dl, ct.i1, GROUP), d2 = __shfl_sync(seg, dl, ct.i2, GROUP);
+    const double dj = __shfl_sync(seg, dl, a & 1, GROUP), dj2 = __shfl_sync(seg, dl, 2 + (a & 1), GROUP);
+    const double cdl = ct.c1 * d1 + ct.c2 * d2;
+    double rgx;
+    if (!term) {
+      const double u0 = pU[k * 2], u1 = pU[k * 2 + 1];
+      re = nmax(re, fabs(phi[k * 8 + a] - pX[(k + 1) * 8 + a]));
+      double atp = 0.0, btp = 0.0;
+      const int j = a & 1;
+      if (have_mult) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+          const double pn = pPI[(k + 1) * 8 + r];
+          atp = fma(gBA[k * 80 + r * 10 + 2 + a], pn, atp);
+          btp = fma(gBA[k * 80 + r * 10 + j], pn, btp);
+        }
+      }
+      const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
+      rgx = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - (have_mult ? pPI[k * 8 + a] : 0.0) - cdl;
+      const double rgu = (j == 0 ? hu0 * u0 - c10 * pX[k * 8 + 6] : hu1 * u1 - c11 * pX[k * 8 + 7]) + btp - (dj + dj2);
+      if (a < 2) rs = nmax(rs, fabs(rgu));
+    } else {
+      rgx = hxN * xa_ + ((a == 0) ? gsN : 0.0) - (have_mult ? pPI[k * 8 + a] : 0.0) - cdl;
+    }
+    if (k > 0) rs = nmax(rs, fabs(rgx));
+  }
+  rs = wmax(rs); re = wmax(re); ri = fmax(wmax(ri), 0.0); rc = wmax(rc);
+  if (!have_mult) { rs = __longlong_as_double(0x7ff0000000000000LL); rc = rs; }
+  if (lane == 0) {
+    double* sp = w.stats + (size_t)b * 8;
+    sp[3] = rs; sp[4] = re; sp[5] = ri; sp[6] = rc;
+    if (have_mult && rs <= nlp_tol && re <= nlp_tol && ri <= nlp_tol && rc <= nlp_tol) {
+      w.status[b] = IHM2B_SUCCESS;
+      if (status_out) status_out[b] = IHM2B_SUCCESS;
+      w.active[b] = 0;
+    }
+  }
+}
+
+void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
+                         int32_t* status, cudaStream_t stream) {
+  nlp_residual_kernel<<<cf.B, 32, 0, stream>>>(cf, w, x0, nlp_tol, have_mult, status);
 }
 
 int qp_smem_bytes(int N) { return ((N + 1) * PER_STAGE + S_TOT) * (int)sizeof(double); }

@@ -121,7 +121,15 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream);
  * replaces the body of IHM2Controller.compute_control after the shift
  * (controller.py:370-385 x0 embedding + yref, :396 solver.solve(), :405 get(0,"u");
  * ihm2_fkin6_acados_solve, mpc_control_node.cpp:177-206).
- * x0_dev [B][8] in; u0_dev [B][2], status_dev [B] out. */
+ * x0_dev [B][8] in; u0_dev [B][2], status_dev [B] out.
+ * nlp_solver = IHM2B_SQP_RTI: one linearisation + one QP + full step (status 0 / 1 / 4).
+ * nlp_solver = IHM2B_SQP (acados ocp_nlp_sqp as configured by controller.py:301-302): up to
+ * nlp_max_iter rounds of { linearise, KKT residual test against nlp_tol with the multipliers
+ * of the last QP, QP, full step }; instances drop out as they converge (status 0) or their QP
+ * fails (1 / 4), the rest end with status 2 (ACADOS_MAXITER, tolerated by the reference,
+ * mpc_control_node.cpp:190-197).  stats: [qp iterations (sum), sqp iterations, mu, res_stat,
+ * res_eq, res_ineq, res_comp, -].  globalization must be IHM2B_FIXED_STEP in this build
+ * (IHM2B_EINVAL otherwise: the merit-function line search is not implemented). */
 int ihm2b_solve_dev(ihm2b_handle* h, const double* x0_dev, double* u0_dev, int32_t* status_dev,
                     void* stream);
 /* Same call with HOST buffers: H2D of x0, shift (if do_shift), solve, D2H of u0/status,

@@ -262,3 +262,67 @@ def test_boundary_classes_reproduce_the_closed_loop(torch_cuda, fsds):
     one = IHM2Controller(fsds.s_ref, fsds.kappa_ref)
     u = one.compute_control(g["x_start"][0])
     assert u.shape == (2,) and rel(u, g["ulog"][0][0]) < REL_TOL
+
+
+def _sqp_inputs(skidpad, fsds, Nf, B):
+    """N = 40: the config-2 inputs (perturbed states around the skidpad nominal).  N = 80: a slow,
+    straight warm start on fsds_default (the hard-bounded OCP has no feasible full-throttle
+    start over 4 s), perturbed measured states."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.workloads import nominal_iterate, perturbed_batch
+    if Nf == 40:
+        x_nom, xp, up = nominal_iterate("skidpad", 20)
+        return skidpad, dict(), perturbed_batch(x_nom, xp, up, B, seed=2)
+    rng = np.random.default_rng(5)
+    v0, dt = 5.0, 1 / 20
+    x = np.zeros((B, Nf + 1, 8)); u = np.zeros((B, Nf, 2))
+    x[:, :, 0] = -6 + v0 * dt * np.arange(Nf + 1)[None, :]; x[:, :, 3] = v0; x[:, :, 6] = 30.0; u[:, :, 0] = 30.0
+    x0 = x[:, 0, :] + rng.uniform(-1, 1, (B, 8)) * np.array([0.5, 0.3, 0.05, 1.0, 0.1, 0.1, 20, 0.02])
+    return fsds, dict(Nf=Nf, s_target=40.0), (x0, x, u)
+
+
+@pytest.mark.parametrize("Nf,B,iters", [(40, 512, 25), (80, 128, 6)])
+def test_sqp_mode_matches_oracle(torch_cuda, skidpad, fsds, Nf, B, iters):
+    """nlp_solver = SQP (new_python/controller.py:301-302 uses SQP with 2 iterations; BASELINE
+    configs[3] asks for N = 80): linearise / KKT test / QP / full step repeated on the device,
+    instances dropping out as they converge or fail.  Same statuses, SQP iteration counts and
+    iterates as the oracle's SQP loop."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    mp, kw, (x0, x, u) = _sqp_inputs(skidpad, fsds, Nf, B)
+    cfg = _abi.make_config(batch=B, n_grid=len(mp.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=iters,
+                           globalization=_abi.FIXED_STEP, **kw)
+    eng = _engine(cfg, mp); eng.set_iterate(x, u)
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    sg = status.cpu().numpy()
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    stg = eng.stats().cpu().numpy()
+    eng.close()
+    u0o, so, sto, xo, uo = Oracle(cfg, mp.s_ref, mp.kappa_ref).solve(x0, x, u)
+    assert set(np.unique(sg)) <= {0, 1, 2, 4}
+    assert np.mean(sg == so) > 0.97
+    conv = (sg == 0) & (so == 0)
+    if Nf == 40:
+        assert conv.sum() > 0.25 * B                     # a good share reaches the KKT tolerance
+        assert np.mean(stg[conv, 1] == sto[conv, 1]) > 0.95  # after the same number of SQP iterations
+        assert (stg[conv, 3:7].max(axis=1) <= cfg.nlp_tol).all()
+    same = conv & (stg[:, 1] == sto[:, 1])
+    if same.sum():
+        assert rel(u0.cpu().numpy()[same], u0o[same]) < REL_TOL
+        assert rel(xg[same], xo[same]) < REL_TOL and rel(ug[same], uo[same]) < REL_TOL
+    run = (sg == 2) & (so == 2)                          # still iterating at the cap: same iterate too
+    assert same.sum() + run.sum() > 0.5 * B
+    if run.sum():
+        assert rel(xg[run], xo[run]) < 1e-5 and rel(ug[run], uo[run]) < 1e-5
+        assert np.mean(stg[run, 1] == iters) == 1.0
+
+
+def test_sqp_rejects_unimplemented_line_search(torch_cuda, skidpad):
+    from ihm2_b200 import _abi
+    from ihm2_b200.engine import Ihm2bError
+    cfg = _abi.make_config(batch=4, n_grid=len(skidpad.s_ref), nlp_solver=_abi.SQP,
+                           globalization=_abi.MERIT_BACKTRACKING)
+    eng = _engine(cfg, skidpad)
+    with pytest.raises(Ihm2bError, match="line search"):
+        eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
+    eng.close()
