@@ -260,6 +260,17 @@ def main():
         ach = B * fl["qp"] / (qp_ms * 1e-3) * 1e-12
         n_cpu = 1024
         cpu_val, cpu_t = cpu_oracle_rate(x0_h, x_h, u_h, mp, n_cpu)
+        traffic, traffic_src = None, None   # dram bytes of the QP launch from the committed ncu --set full summary
+        prof = os.path.join(ROOT, "profiles", "r01_qp_rti_kernel_ncu_summary.csv")
+        if os.path.exists(prof) and B == B_PER_GPU:
+            unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            tb = 0.0
+            for line in open(prof):
+                f = line.strip().split(",")
+                if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tb += float(f[2]) * unit.get(f[1], 1.0)
+            if tb > 0:
+                traffic, traffic_src = tb, "profiles/r01_qp_rti_kernel_ncu_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         hbm = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
         out = {
@@ -277,7 +288,7 @@ def main():
             "gpu_launches": int(launches),
             "kernels_ms": {"linearize_irk": lin_ms, "qp_rti": qp_ms},
             "roofline": {"bound": "fp64", "kernel": "qp_rti_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-                         "frac": ach / peak if peak else None, "traffic": None,
+                         "frac": ach / peak if peak else None, "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src,
                          "peak_source": "DFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)",
                          "flops_per_solve": fl["total"], "flops_per_launch": B * fl["qp"],
                          "hbm_secondary": {"algorithmic_bytes_per_solve": 6800, "achieved_gbs": value / world * 6800 * 1e-9, "peak_gbs": hbm}},
