@@ -114,6 +114,13 @@ __device__ __forceinline__ RowDef row_term(const KCfg& cf, int r) {
   return R;
 }
 
+// Value of a row at (u, x).  Every pass evaluates rows through this one expression: the slack residuals
+// v - lb - t are differences of nearly equal numbers near convergence, and the passes must agree on v
+// to the last bit (a row value carried along as v + alpha C dz instead stalls the IPM).
+__device__ __forceinline__ double row_value(const RowDef& R, bool term, double u, double x) {
+  return fma(R.cx, x, term ? 0.0 : R.cu * u);
+}
+
 // C' q seen by state a:  c1 * q[i1] + c2 * q[i2]   (diagonal of C' diag(q) C: c1 q[i1] + |c2| q[i2])
 struct CtDef { int i1, i2; double c1, c2; };
 __device__ __forceinline__ CtDef ct_path(int a) {
@@ -228,21 +235,52 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   __syncwarp();
 
   // ------------------------------------------------------------------ initialisation
+  // Row pass "A" of one (stage, row): barrier Hessian weight gamma, first-order terms psi / dl for the
+  // residuals, residual norms; leaves what the Riccati sweep adds to M ready to load:
+  // pGAM[k][j] = diagonal of H~_xx, pMI[k] = (M_uu diagonal addends, M_xu addends of rows T and delta).
+  // Called by all 32 lanes (segment shuffles inside).
+  double rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
+  auto rows_A = [&](int k, bool on, bool term, bool act, const RowDef& R, double v, double lamL, double lamU,
+                    double tL, double tU) {
+    double gam = 0.0, psi = 0.0, dl = 0.0;
+    if (act) {
+      const double itL = 1.0 / tL, itU = 1.0 / tU;
+      const double rdL = v - R.lb - tL, rdU = R.ub - v - tU;
+      gam = lamL * itL + lamU * itU;
+      psi = lamL * rdL * itL - lamU * rdU * itU;
+      dl = lamL - lamU;
+      rd_m = nmax(rd_m, nmax(fabs(rdL), fabs(rdU)));
+      rm_m = nmax(rm_m, nmax(lamL * tL, lamU * tU));
+      S0 += lamL * tL + lamU * tU;
+    }
+    const CtDef& ct = term ? ctT : ctP;
+    const double g1 = __shfl_sync(FULL, gam, ct.i1, GROUP), g2 = __shfl_sync(FULL, gam, ct.i2, GROUP);
+    const double gp2 = __shfl_sync(FULL, gam, (a + 2) & 7, GROUP);
+    if (on) {
+      pGAM[k * 8 + a] = (term ? hxN : hx) + ct.c1 * g1 + fabs(ct.c2) * g2;
+      pD1[k * 8 + a] = psi; pD2[k * 8 + a] = dl;
+      if (a < 4 && !term) pMI[k * 4 + a] = (a < 2) ? ((a == 0 ? hu0 : hu1) + gam + gp2) : (-(a == 2 ? c10 : c11) - gam);
+    }
+  };
   // slacks / multipliers cold (t = max(distance, thr0), lam = mu0 / t), pi = 0
   PAR_LOOP for (int i = 0; i < rounds; i++) {
-    const int k = q + 4 * i;
-    if (k > N) break;
+    const int kk = q + 4 * i;
+    const bool on = (kk <= N);
+    const int k = on ? kk : N;
     const bool term = (k == N);
     const RowDef& R = term ? Rt : Rp;
-    const bool act = term ? (a < 4) : (a < 4 || k > 0);
-    const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
+    const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
+    const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
     double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0;
     if (act) {
       tL = fmax(v - R.lb, THR0); tU = fmax(R.ub - v, THR0);
       lamL = cf.mu0 / tL; lamU = cf.mu0 / tU;
     }
-    pLL[k * 8 + a] = lamL; pLU[k * 8 + a] = lamU; pTL[k * 8 + a] = tL; pTU[k * 8 + a] = tU;
-    pPI[k * 8 + a] = 0.0;
+    if (on) {
+      pLL[k * 8 + a] = lamL; pLU[k * 8 + a] = lamU; pTL[k * 8 + a] = tL; pTU[k * 8 + a] = tU;
+      pPI[k * 8 + a] = 0.0;
+    }
+    rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
   }
   __syncwarp();
   const double inv_n = 1.0 / (16.0 * N);  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4)
@@ -256,39 +294,6 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
 #define TICK(i)
 #endif
   while (true) {
-    // ================= A: inequality rows of all stages (stage-parallel)
-    // Also leaves what the Riccati sweep adds to M, ready to load: pGAM[k][j] = diagonal of H~_xx,
-    // pMI[k] = (M_uu diagonal addends, M_xu addends of rows T and delta).
-    double rd_m = 0.0, rm_m = 0.0, S0 = 0.0;
-    PAR_LOOP for (int i = 0; i < rounds; i++) {
-      const int kk = q + 4 * i;
-      const bool on = (kk <= N);
-      const int k = on ? kk : N;
-      const bool term = (k == N);
-      const RowDef& R = term ? Rt : Rp;
-      const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
-      const double v = (term ? 0.0 : R.cu * pU[(term ? 0 : k) * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
-      double gam = 0.0, psi = 0.0, dl = 0.0;
-      if (act) {
-        const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
-        const double itL = 1.0 / tL, itU = 1.0 / tU;
-        const double rdL = v - R.lb - tL, rdU = R.ub - v - tU;
-        gam = lamL * itL + lamU * itU;
-        psi = lamL * rdL * itL - lamU * rdU * itU;
-        dl = lamL - lamU;
-        rd_m = nmax(rd_m, nmax(fabs(rdL), fabs(rdU)));
-        rm_m = nmax(rm_m, nmax(lamL * tL, lamU * tU));
-        S0 += lamL * tL + lamU * tU;
-      }
-      const CtDef& ct = term ? ctT : ctP;
-      const double g1 = __shfl_sync(FULL, gam, ct.i1, GROUP), g2 = __shfl_sync(FULL, gam, ct.i2, GROUP);
-      const double gp2 = __shfl_sync(FULL, gam, (a + 2) & 7, GROUP);
-      if (on) {
-        pGAM[k * 8 + a] = (term ? hxN : hx) + ct.c1 * g1 + fabs(ct.c2) * g2;
-        pD1[k * 8 + a] = psi; pD2[k * 8 + a] = dl;
-        if (a < 4 && !term) pMI[k * 4 + a] = (a < 2) ? ((a == 0 ? hu0 : hu1) + gam + gp2) : (-(a == 2 ? c10 : c11) - gam);
-      }
-    }
     __syncwarp();
     TICK(0)
     // ================= B: stationarity and dynamics residuals of all stages (stage-parallel)
@@ -467,46 +472,48 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       // ---- inequality rows at the step (stage-parallel): slack / multiplier steps, step length
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
       PAR_LOOP for (int i = 0; i < rounds; i++) {
-        const int k = q + 4 * i;
-        if (k > N) break;
+        const int kk = q + 4 * i;
+        const bool on = (kk <= N);
+        const int k = on ? kk : N;
         const bool term = (k == N);
         const RowDef& R = term ? Rt : Rp;
-        const bool act = term ? (a < 4) : (a < 4 || k > 0);
-        if (!act) continue;
-        const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-        const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
-        const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
-        const double itL = 1.0 / tL, itU = 1.0 / tU;
-        const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
-        if (pred) {
-          const double dlL = -lamL - lamL * dtL * itL, dlU = -lamU - lamU * dtU * itU;
-          S1 += lamL * dtL + tL * dlL + lamU * dtU + tU * dlU;
-          S2 += dlL * dtL + dlU * dtU;
-          pD1[k * 8 + a] = dlL * dtL; pD2[k * 8 + a] = dlU * dtU;
-          ratio = nmax(ratio, nmax(nmax(1.0 + dtL * itL, 1.0 + dtU * itU), nmax(-dtL * itL, -dtU * itU)));
-        } else {
-          const double dlL = -lamL - (pD1[k * 8 + a] - mu_t + lamL * dtL) * itL;
-          const double dlU = -lamU - (pD2[k * 8 + a] - mu_t + lamU * dtU) * itU;
-          pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
-          ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
+        const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
+        double ddl = 0.0;   // dlamL - dlamU of this row (corrector pass)
+        if (act) {
+          const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
+          const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
+          const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
+          const double itL = 1.0 / tL, itU = 1.0 / tU;
+          const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
+          if (pred) {
+            const double dlL = -lamL - lamL * dtL * itL, dlU = -lamU - lamU * dtU * itU;
+            S1 += lamL * dtL + tL * dlL + lamU * dtU + tU * dlU;
+            S2 += dlL * dtL + dlU * dtU;
+            pD1[k * 8 + a] = dlL * dtL; pD2[k * 8 + a] = dlU * dtU;
+            ratio = nmax(ratio, nmax(nmax(1.0 + dtL * itL, 1.0 + dtU * itU), nmax(-dtL * itL, -dtU * itU)));
+          } else {
+            const double dlL = -lamL - (pD1[k * 8 + a] - mu_t + lamL * dtL) * itL;
+            const double dlU = -lamU - (pD2[k * 8 + a] - mu_t + lamU * dtU) * itU;
+            pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
+            ddl = dlL - dlU;
+            ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
+          }
+        }
+        if (!pred) {
+          // right-hand side of the costate recursion per state: rg - C'(dlamL - dlamU) + (H dz)_x,
+          // left in the gamma slot (the rows of a stage sit in the 8 lanes of this segment)
+          const CtDef& ct = term ? ctT : ctP;
+          const double d1 = __shfl_sync(FULL, ddl, ct.i1, GROUP), d2 = __shfl_sync(FULL, ddl, ct.i2, GROUP);
+          if (on) {
+            const double hdz = term ? hxN * pDX[k * 8 + a] : hx * pDX[k * 8 + a] + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
+            pGAM[k * 8 + a] = pRG[k * 8 + a] - (ct.c1 * d1 + ct.c2 * d2) + hdz;
+          }
         }
       }
       ratio = wmax(ratio);
       if (!(ratio == ratio)) { bad = true; break; }
       if (!pred) {
         alpha = TAU * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
-        // right-hand side of the costate recursion per state (stage-parallel):
-        // rg - C'(dlamL - dlamU) + (H dz)_x, left in the gamma slot
-        __syncwarp();
-        PAR_LOOP for (int i = 0; i < rounds; i++) {
-          const int k = q + 4 * i;
-          if (k > N) break;
-          const bool term = (k == N);
-          const CtDef& ct = term ? ctT : ctP;
-          const double cdl = ct_apply(ct, pD1 + k * 8) - ct_apply(ct, pD2 + k * 8);
-          const double hdz = term ? hxN * pDX[k * 8 + a] : hx * pDX[k * 8 + a] + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
-          pGAM[k * 8 + a] = pRG[k * 8 + a] - cdl + hdz;
-        }
         break;
       }
       const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0;
@@ -599,21 +606,31 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       __syncwarp();
     }
     TICK(6)
-    // ================= J: step of multipliers / slacks (stage-parallel), then of the primal point
+    // ================= J + A: step of multipliers / slacks, and the row pass of the NEXT iteration on the
+    // updated values while they are in registers (stage-parallel); then the step of the primal point
+    rd_m = 0.0; rm_m = 0.0; S0 = 0.0;
     PAR_LOOP for (int i = 0; i < rounds; i++) {
-      const int k = q + 4 * i;
-      if (k > N) break;
+      const int kk = q + 4 * i;
+      const bool on = (kk <= N);
+      const int k = on ? kk : N;
       const bool term = (k == N);
       const RowDef& R = term ? Rt : Rp;
-      const bool act = term ? (a < 4) : (a < 4 || k > 0);
-      if (!act) continue;
-      const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
-      const double tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
-      const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
-      pLL[k * 8 + a] = fma(alpha, pD1[k * 8 + a], pLL[k * 8 + a]);
-      pLU[k * 8 + a] = fma(alpha, pD2[k * 8 + a], pLU[k * 8 + a]);
-      pTL[k * 8 + a] = fma(alpha, dtL, tL); pTU[k * 8 + a] = fma(alpha, dtU, tU);
+      const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
+      double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0, v = 0.0;
+      if (act) {
+        const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
+        v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
+        tL = pTL[k * 8 + a]; tU = pTU[k * 8 + a];
+        const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
+        lamL = fma(alpha, pD1[k * 8 + a], pLL[k * 8 + a]);
+        lamU = fma(alpha, pD2[k * 8 + a], pLU[k * 8 + a]);
+        tL = fma(alpha, dtL, tL); tU = fma(alpha, dtU, tU);
+        // the row at the updated point, from the values the primal update below will store
+        v = row_value(R, term, fma(alpha, pDU[(term ? 0 : k) * 2 + R.iu], pU[(term ? 0 : k) * 2 + R.iu]),
+                      fma(alpha, pDX[k * 8 + R.ix], pX[k * 8 + R.ix]));
+        pLL[k * 8 + a] = lamL; pLU[k * 8 + a] = lamU; pTL[k * 8 + a] = tL; pTU[k * 8 + a] = tU;
+      }
+      rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
     }
     __syncwarp();
     for (int e = lane; e < N1 * 8; e += 32) { pX[e] = fma(alpha, pDX[e], pX[e]); pPI[e] = fma(alpha, pRG[e], pPI[e]); }
@@ -691,7 +708,7 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
     const bool act = term ? (a < 4) : (a < 4 || k > 0);
     double dl = 0.0;
     if (act) {
-      const double v = (term ? 0.0 : R.cu * pU[k * 2 + R.iu]) + R.cx * pX[k * 8 + R.ix];
+      const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
       ri = nmax(ri, nmax(R.lb - v, v - R.ub));
       if (have_mult) {
         const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a];
