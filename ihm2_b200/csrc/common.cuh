@@ -45,7 +45,7 @@ struct Work {
   // interior point state: lamL, lamU, tL, tU per row
   double* LT;               // [B][N+1][4][8]
   // Riccati factor of the current IPM iteration
-  double* K;                // [B][N][8][2]   K[k][a][:] = feedback column of state a
+  double* K;                // [B][N][8][2]   (unused by the current QP kernel: the gains live in shared memory)
   double* kff;              // [B][N][2]      predictor feed-forward
   double* Minv;             // [B][N][4]      inverse of M_uu (i00,i01,i11,pad)
   double* kfc;              // [B][N][2]      corrected feed-forward (kff + corrector part)

@@ -6,17 +6,22 @@
 // the reference tree) and the feedback phase of acados' ocp_nlp_sqp_rti for the OCP of
 // python/mpc.py:29-101 (LINEAR_LS cost, box bounds idxbx/idxbu, two rate rows C x + D u).
 //
-// Mapping: ONE WARP PER PROBLEM, 8 problems per SM.  Lane l = (a = l & 7, q = l >> 3).
-//  * serial sweeps (Riccati factorisation, forward / backward substitutions, costate): a is the
-//    row of every 8-row object (state x_a, row a of the cost-to-go matrix P, row a of [B A]);
-//    the four quarters q split the columns of the two dense products of the Riccati step;
-//    hand-overs go through shared memory.  What these sweeps touch (gains, residuals, steps:
-//    58 doubles per stage) stays in shared memory for the whole solve; [B A] is streamed from
-//    L2 through a small cp.async ring a few stages ahead of its use.
+// Mapping: ONE WARP PER PROBLEM, 11 problems per SM (19.2 KB of shared memory, 168 registers).
+//  * serial sweeps (Riccati factorisation, forward / backward substitutions, costate recursion) run on
+//    the FP64 tensor cores: every 8x8 (x 8 | 10 | 16) product of a stage is one or a few
+//    mma.sync.m8n8k4.f64 (DMMA), lane l = (g = l >> 2, t = l & 3) owning the fragments.  The
+//    cost-to-go matrix P never leaves its accumulator registers; matrix-vector products repeat the
+//    vector in the 8 columns of the right operand.  A dependent DFMA costs 23 cycles on B200, a
+//    DMMA 26 (scripts/micro/dmma_lat.cu), so a length-8 contraction drops from ~190 to ~50 cycles
+//    and the per-lane operand traffic from 36 shared-memory loads per stage to 4-6.
+//    What these sweeps hand over between stages and sweeps (gains, residuals, steps: 58 doubles per
+//    stage) stays in shared memory for the whole solve; the [B A] operand fragments are read
+//    straight from L2 into registers PF stages ahead of their use.
 //  * everything that is independent across stages (inequality rows, residuals, step lengths,
-//    updates) runs stage-parallel: lane (a, q) handles row / state a of stages q, q+4, q+8, ...
-//    directly on global memory (256 contiguous bytes per warp instruction, L2-resident while
-//    the problem is in flight), so the divisions and the row logic stay off the serial chains.
+//    updates) runs stage-parallel with lane l = (a = l & 7, q = l >> 3): row / state a of stages
+//    q, q+4, q+8, ... directly on global memory (256 contiguous bytes per warp instruction,
+//    L2-resident while the problem is in flight), so the divisions and the row logic stay off the
+//    serial chains.  Values a pass needs from the other rows of its stage come by 8-lane shuffles.
 //
 // Formulation (variables z_k = (u_k, x_k), x_0 fixed to the measured state):
 //   min sum 1/2 z'Hz + g'z   s.t.  x_{k+1} = A x_k + B u_k + c_k,   lb <= C z <= ub
@@ -25,8 +30,6 @@
 // H + C' diag(lam/t) C once by a backward Riccati sweep, and solves predictor and corrector
 // with that factor.  Equality multipliers are advanced through the costate recursion of the
 // full Newton step, which needs no stored cost-to-go matrices.
-#include <cuda_pipeline.h>
-
 #include "common.cuh"
 
 namespace ihm2b {
@@ -36,23 +39,21 @@ namespace {
 constexpr double TAU = 0.995, THR0 = 0.1;
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
-#ifndef RING_P_
-#define RING_P_ 3
+#ifndef PF_
+#define PF_ 2
 #endif
 #ifndef QP_MIN_BLOCKS
-#define QP_MIN_BLOCKS 10   // problems (warps) per SM the register allocation is held to
+#define QP_MIN_BLOCKS 11   // problems (warps) per SM the register allocation is held to
 #endif
 #ifndef PAR_UNROLL
-#define PAR_UNROLL 2
+#define PAR_UNROLL 1
 #endif
 #define PAR_STR_(x) #x
 #define PAR_STR(x) PAR_STR_(x)
 #define PAR_LOOP _Pragma(PAR_STR(unroll PAR_UNROLL))
-constexpr int RING_P = RING_P_;  // [B A] prefetch distance (stages) of the serial sweeps
-constexpr int RING_R = RING_P + 1;
+constexpr int PF = PF_;         // [B A] prefetch distance (stages) of the serial sweeps
 constexpr int S_V = 0;          // scratch: 2 x [8] exchange buffer of the substitution sweeps
-constexpr int S_RING = 16;      //          [B A] ring, RING_R x [8][10]
-constexpr int S_TOT = S_RING + RING_R * 80;
+constexpr int S_TOT = 16;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -80,6 +81,34 @@ __device__ __forceinline__ void sts2_if(bool p, double* ptr, double v0, double v
   asm volatile("{.reg .pred p; setp.ne.b32 p, %0, 0; @p st.shared.v2.f64 [%1], {%2, %3};}"
                :: "r"((int)p), "r"((unsigned)__cvta_generic_to_shared(ptr)), "d"(v0), "d"(v1) : "memory");
 }
+// Serial sweep over the stages with the per-lane [B A] operand fragments fetched from global memory (L2)
+// PF stages ahead into a rotating register file: DIR = -1 walks k = N-1 .. 0, DIR = +1 walks k = 0 .. N-1.
+// NT > 0 with NT % PF == 0 drops the remainder code at compile time.
+template <int NT, int PF, int DIR, class Frag, class Load, class Body>
+__device__ __forceinline__ void sweep(const int N, Load load, Body body) {
+  Frag f[PF];
+  const int k0 = (DIR > 0) ? 0 : N - 1;
+#pragma unroll
+  for (int d = 0; d < PF; d++) f[d] = load(max(0, min(N - 1, k0 + DIR * d)));
+  int k = k0, left = N;
+#pragma unroll 1
+  for (; left >= PF; left -= PF, k += DIR * PF) {
+#pragma unroll
+    for (int d = 0; d < PF; d++) {
+      const Frag cur = f[d];
+      f[d] = load(max(0, min(N - 1, k + DIR * (d + PF))));
+      body(k + DIR * d, cur);
+    }
+  }
+  if (NT <= 0 || NT % PF != 0) {
+#pragma unroll
+    for (int d = 0; d < PF; d++)
+      if (d < left) body(k + DIR * d, f[d]);
+  }
+}
+struct Frag4 { double a, b, c, d; };
+struct Frag3 { double a, b, c; };
+struct Frag2 { double a, b; };
 // NaN-propagating max
 __device__ __forceinline__ double nmax(double a, double b) { return (b > a || b != b) ? b : a; }
 __device__ __forceinline__ double wmax(double v) {
@@ -159,41 +188,16 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   double* const pGAM = smem;             // [N1][8]   gamma -> chi -> C'(dlamL - dlamU) per state
   double* const pGX = pGAM + N1 * 8;     // [N1][8]   Newton gradient (state part), later dx
   double* const pGU = pGX + N1 * 8;      // [N1][2]   Newton gradient (control part), later du
-  double* const pRG = pGU + N1 * 2;      // [N1][8]   stationarity residual (state part)
+  double* const pRG = pGU + N1 * 2;      // [N1][8]   stationarity residual (state part), later d pi
   double* const pRB = pRG + N1 * 8;      // [N1][8]   dynamics residual
   double* const pK = pRB + N1 * 8;       // [N1][8][2]
   double* const pKF = pK + N1 * 16;      // [N1][4]   kff[2], kfc[2]
   double* const pMI = pKF + N1 * 4;      // [N1][4]   i00 i01 i11 pad
   double* const sc = pMI + N1 * 4;
   // Global memory (L2-resident while the problem is in flight): what only the stage-parallel
-  // phases touch, accessed as 256 contiguous bytes per warp instruction; and [B A], which the
-  // serial sweeps stream through a small cp.async ring RING_P stages ahead of their use.
+  // phases touch, accessed as 256 contiguous bytes per warp instruction; and [B A], whose operand
+  // fragments the serial sweeps load into registers PF stages ahead of their use.
   const double* __restrict__ const gBA = w.BA + (size_t)b * N * 80;   // [N][8][10]  (B | A) row-major
-  double* const ring = sc + S_RING;
-  // stage k -> ring slot; issue the asynchronous copy of one stage (40 chunks of 16 bytes)
-  auto ba_prefetch = [&](int k) {
-#ifdef BA_DIRECT
-    return;
-#endif
-    // out-of-range requests re-copy the first / last stage into the slot that already holds it
-    k = max(0, min(k, N - 1));
-    double* dst = ring + (k % RING_R) * 80;
-    const double* src = gBA + k * 80;
-    __pipeline_memcpy_async(dst + 2 * lane, src + 2 * lane, 16);                                   // bytes 0..511
-    __pipeline_memcpy_async(reinterpret_cast<float*>(dst + 64) + lane,
-                            reinterpret_cast<const float*>(src + 64) + lane, 4);                  // bytes 512..639
-    __pipeline_commit();
-  };
-  // wait for stage k (the oldest outstanding copy), make it visible to the warp
-  auto ba_acquire = [&](int k) -> const double* {
-#ifdef BA_DIRECT
-    __syncwarp();
-    return gBA + k * 80;
-#endif
-    __pipeline_wait_prior(RING_P - 1);
-    __syncwarp();
-    return ring + (k % RING_R) * 80;
-  };
   const double* __restrict__ const pC = w.c + (size_t)b * N * 8;      // [N][8]
   double* __restrict__ const pX = w.x + (size_t)b * N1 * 8;           // [N1][8]   iterate, updated in place
   double* __restrict__ const pU = w.u + (size_t)b * N * 2;            // [N][2]
@@ -373,23 +377,22 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       double pp0 = pGX[N * 8 + 2 * t], pp1 = pGX[N * 8 + 2 * t + 1]; // p[2t], p[2t+1]
       const int ra = (2 * t) * 10;
       // per-lane sources of the accumulator initialisers (offsets in doubles from smem, stage stride added below)
-      const bool e1ring = (g < 2), e1on = (g <= 2);
+      const bool e1on = (g <= 2);
       const int o01 = (t == 1) ? (int)(pGX - smem) + g : (int)(pMI - smem) + 2 + (g & 1);
       const int s01 = (t == 1) ? 8 : 4;
       const bool k01a = (t == 1) || (t == 0 && g == 6), k01b = (t == 0 && g == 7);
       const int o11 = (t == 1) ? (int)(pGU - smem) + (g & 1) : (int)(pMI - smem) + (g & 1);
       const int s11 = (t == 1) ? 2 : 4;
       const bool k11a = (t == 1 && g < 2) || (lane == 0), k11b = (lane == 4);
-#pragma unroll
-      for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
-#pragma unroll 1
-      for (int k = N - 1; k >= 0; k--) {
-        const double* BAk = ba_acquire(k);
-        ba_prefetch(k - RING_P);
+      auto load_E = [&](int k) {
+        const double* p = gBA + k * 80 + ra;
+        return Frag4{p[2 + g], p[12 + g], p[g & 1], p[10 + (g & 1)]};   // A[2t][g], A[2t+1][g], B[2t][g&1], B[2t+1][g&1]
+      };
+      auto riccati_stage = [&](const int k, const Frag4 f) {
         // operand fragments of E and accumulator initialisers (independent of P: ahead of the chain)
-        const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];
-        const double* e1p = e1ring ? (BAk + ra + g) : (pRB + k * 8 + 2 * t);
-        double E1a = e1p[0], E1b = e1p[e1ring ? 10 : 1];
+        const double E0a = f.a, E0b = f.b;
+        double E1a = f.c, E1b = f.d;
+        if (g == 2) { E1a = pRB[k * 8 + 2 * t]; E1b = pRB[k * 8 + 2 * t + 1]; }
         if (!e1on) { E1a = 0.0; E1b = 0.0; }
         const double dgv = pGAM[k * 8 + g], v01 = smem[o01 + k * s01], v11 = smem[o11 + k * s11];
         double T00a = dgA ? dgv : 0.0, T00b = dgB ? dgv : 0.0;
@@ -424,7 +427,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         sts2_if(lane == 0, pKF + k * 4, -(i00 * mvu0 + i01 * mvu1), -(i01 * mvu0 + i11 * mvu1));
         sts2_if(lane == 0, pMI + k * 4, i00, i01);
         sts_if(lane == 0, pMI + k * 4 + 2, i11);
-      }
+      };
+      sweep<NT, PF, -1, Frag4>(N, load_E, riccati_stage);
       __syncwarp();
     }
 
@@ -441,30 +445,30 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         double dxa = 0.0, dxb = 0.0;  // x_0 is fixed
         const int kfo = pred ? 0 : 2;
         const bool lo = (g < 2), tlo = (t < 2);
-#pragma unroll
-        for (int d = 0; d < RING_P; d++) ba_prefetch(d);
-#pragma unroll 1
-        for (int k = 0; k < N; k++) {
-          const double* BAk = ba_acquire(k);     // (warp barrier inside)
-          ba_prefetch(k + RING_P);
+        auto load_F = [&](int k) {
+          const double* p = gBA + k * 80 + g * 10;
+          const double2 af = *reinterpret_cast<const double2*>(p + 2 + 2 * t);
+          return Frag3{af.x, af.y, p[t & 1]};                      // A[g][2t], A[g][2t+1], B[g][t&1]
+        };
+        auto forward_stage = [&](const int k, const Frag3 f) {
           sts2_if(g == 0, pDX + k * 8 + 2 * t, dxa, dxb);
-          const double2 Af = *reinterpret_cast<const double2*>(BAk + g * 10 + 2 + 2 * t);   // A[g][2t], A[g][2t+1]
           double Ka = pK[k * 16 + 4 * t + (g & 1)], Kb = pK[k * 16 + 4 * t + 2 + (g & 1)];  // K[g][2t], K[g][2t+1]
-          double Bf = BAk[g * 10 + (t & 1)];                                               // B[g][t]
+          double Bf = f.c;                                                                 // B[g][t]
           double kf = pKF[k * 4 + kfo + (g & 1)];
           const double rbg = pRB[k * 8 + g];
           if (!lo) { Ka = 0.0; Kb = 0.0; kf = 0.0; }
           if (!tlo) Bf = 0.0;
           double U0 = kf, U1 = kf, X0 = rbg, X1 = rbg;
-          dmma(U0, U1, Ka, dxa); dmma(X0, X1, Af.x, dxa);
-          dmma(U0, U1, Kb, dxb); dmma(X0, X1, Af.y, dxb);
+          dmma(U0, U1, Ka, dxa); dmma(X0, X1, f.a, dxa);
+          dmma(U0, U1, Kb, dxb); dmma(X0, X1, f.b, dxb);
           double duf = __shfl_sync(FULL, U0, (t & 1) << 2);      // du[t] for the k-slots 0, 1
           if (!tlo) duf = 0.0;
           dmma(X0, X1, Bf, duf);
           sts_if((lane & ~4) == 0, pDU + k * 2 + (lane >> 2), U0);
           dxa = __shfl_sync(FULL, X0, t << 3); dxb = __shfl_sync(FULL, X0, (t << 3) + 4);
-        }
-        if (g == 0) *reinterpret_cast<double2*>(pDX + N * 8 + 2 * t) = make_double2(dxa, dxb);
+        };
+        sweep<NT, PF, +1, Frag3>(N, load_F, forward_stage);
+        sts2_if(g == 0, pDX + N * 8 + 2 * t, dxa, dxb);
         if (lane < 2) pDU[N * 2 + lane] = 0.0;
       }
       __syncwarp();
@@ -549,14 +553,13 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         const bool lo = (g < 2), tlo = (t < 2);
         const int ra = (2 * t) * 10;
         double dpa = pGAM[N * 8 + 2 * t], dpb = pGAM[N * 8 + 2 * t + 1];
-#pragma unroll
-        for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
-#pragma unroll 1
-        for (int k = N - 1; k >= 0; k--) {
-          const double* BAk = ba_acquire(k);       // (warp barrier inside)
-          ba_prefetch(k - RING_P);
-          const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];        // A[2t][g], A[2t+1][g]
-          double E1a = BAk[ra + (g & 1)], E1b = BAk[ra + 10 + (g & 1)];      // B[2t][g], B[2t+1][g]
+        auto load_E = [&](int k) {
+          const double* p = gBA + k * 80 + ra;
+          return Frag4{p[2 + g], p[12 + g], p[g & 1], p[10 + (g & 1)]};   // A[2t][g], A[2t+1][g], B[2t][g&1], B[2t+1][g&1]
+        };
+        auto backward_stage = [&](const int k, const Frag4 f) {
+          const double E0a = f.a, E0b = f.b;
+          double E1a = f.c, E1b = f.d;
           double Ui = pKF[k * 4 + 2 + (g & 1)];
           double Kf = pK[k * 16 + 2 * g + (t & 1)];                          // K[t][g]
           const double Xi = pGAM[k * 8 + g];
@@ -572,7 +575,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
           dmma(X0, X1, Kf, dmuf);
           sts2_if(lane == 0, pKF + k * 4 + 2, kf0 - (i00 * d0 + i01 * d1), kf1 - (i01 * d0 + i11 * d1));
           dpa = __shfl_sync(FULL, X0, t << 3); dpb = __shfl_sync(FULL, X0, (t << 3) + 4);
-        }
+        };
+        sweep<NT, PF, -1, Frag4>(N, load_E, backward_stage);
       }
       __syncwarp();
       TICK(5)
@@ -590,19 +594,19 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       const int ra = (2 * t) * 10;
       double da = pGAM[N * 8 + 2 * t], db = pGAM[N * 8 + 2 * t + 1];
       sts2_if(g == 0, pRG + N * 8 + 2 * t, da, db);
-#pragma unroll
-      for (int d = 0; d < RING_P; d++) ba_prefetch(N - 1 - d);
-#pragma unroll 1
-      for (int k = N - 1; k >= 0; k--) {
-        const double* BAk = ba_acquire(k);         // (warp barrier inside)
-        ba_prefetch(k - RING_P);
-        const double E0a = BAk[ra + 2 + g], E0b = BAk[ra + 12 + g];
+      auto load_A = [&](int k) {
+        const double* p = gBA + k * 80 + ra;
+        return Frag2{p[2 + g], p[12 + g]};                                  // A[2t][g], A[2t+1][g]
+      };
+      auto costate_stage = [&](const int k, const Frag2 f) {
+        const double E0a = f.a, E0b = f.b;
         const double Xi = pGAM[k * 8 + g];
         double X0 = Xi, X1 = Xi;
         dmma(X0, X1, E0a, da); dmma(X0, X1, E0b, db);
         sts_if(t == 0, pRG + k * 8 + g, X0);       // applied to pi in the update phase
         da = __shfl_sync(FULL, X0, t << 3); db = __shfl_sync(FULL, X0, (t << 3) + 4);
-      }
+      };
+      sweep<NT, PF, -1, Frag2>(N, load_A, costate_stage);
       __syncwarp();
     }
     TICK(6)
