@@ -262,7 +262,10 @@ __device__ void irk_gl4_sens(const double* __restrict__ x, double u0, double u1,
 }
 
 // grid: ceil(B*N / 128), one thread per (problem, interval)
-__global__ void __launch_bounds__(128) linearize_irk_kernel(const KCfg cf, const Work w) {
+#ifndef LIN_MIN_BLOCKS
+#define LIN_MIN_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(128, LIN_MIN_BLOCKS) linearize_irk_kernel(const KCfg cf, const Work w) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= cf.B * cf.N) return;
   const int b = gid / cf.N, k = gid - b * cf.N;
