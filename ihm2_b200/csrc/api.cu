@@ -24,7 +24,7 @@ void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, con
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
                              const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
-                             int32_t* fail, cudaStream_t stream);
+                             int32_t* fail, int32_t* active_mask, cudaStream_t stream);
 }  // namespace ihm2b
 
 using namespace ihm2b;
@@ -93,11 +93,11 @@ __global__ void reset_iterate_kernel(int B, int N, double dt, double T_max, doub
 // controller.py:388-393 (literal): x_j <- x_{j+1}, u_j <- u_{j+1} for j < N-1;
 // x_{N-1} <- x_N, x_N unchanged, u_{N-1} <- 0.  One thread per (problem, component),
 // marching over the stages so the in-place shift needs no second buffer.
-__global__ void shift_iterate_kernel(int B, int N, double* x, double* u, const int32_t* frozen) {
+__global__ void shift_iterate_kernel(int B, int N, double* x, double* u, const int32_t* active) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= B * 10) return;
   const int b = gid / 10, c = gid - b * 10;
-  if (frozen && frozen[b]) return;
+  if (active && !active[b]) return;
   if (c < 8) {
     double* xp = x + (size_t)b * (N + 1) * 8 + c;
     for (int j = 0; j < N; j++) xp[j * 8] = xp[(j + 1) * 8];
@@ -316,7 +316,7 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream) {
   if (!h) return fail(IHM2B_EINVAL, "null handle");
   const int total = h->cfg.batch * 10;
   shift_iterate_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      h->cfg.batch, h->cfg.N, h->w.x, h->w.u, nullptr);
+      h->cfg.batch, h->cfg.N, h->w.x, h->w.u, h->w.active);
   h->launches++;
   CU(cudaGetLastError());
   return IHM2B_OK;
@@ -460,16 +460,24 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
   CU(cudaMemsetAsync(done, 0xFF, B * sizeof(int32_t), s));   // -1
   CU(cudaMemsetAsync(failp, 0xFF, B * sizeof(int32_t), s));
   if (xlog) CU(cudaMemcpyAsync(xlog, x, B * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  // instances that finished their lap or stopped on a solver failure cost nothing in later steps: every
+  // kernel of the step honours the mask (RTI mode only; the SQP loop owns the mask during a solve)
+  const bool masked = (h->cfg.nlp_solver == IHM2B_SQP_RTI);
+  if (masked) {
+    fill_i32_kernel<<<(unsigned)((B + 255) / 256), 256, 0, s>>>((int)B, h->active_dev, 1);
+    h->w.active = h->active_dev;
+    h->launches++;
+  }
   for (int step = 0; step < n_steps; step++) {
     rc = ihm2b_shift_iterate(h, stream);
-    if (rc) return rc;
-    rc = ihm2b_solve_dev(h, x, h->u0_dev, h->status_dev, stream);
-    if (rc) return rc;
+    if (!rc) rc = ihm2b_solve_dev(h, x, h->u0_dev, h->status_dev, stream);
+    if (rc) { h->w.active = nullptr; return rc; }
     launch_sim_step(h->cfg, h->k, h->w, x, h->u0_dev, h->xn_dev, nullptr, s);
     launch_closed_loop_post((int)B, step, h->track, h->lap_len, h->status_dev, h->u0_dev, h->xn_dev, x, xlog, ulog, done,
-                            failp, s);
+                            failp, masked ? h->active_dev : nullptr, s);
     h->launches += 2;
   }
+  h->w.active = nullptr;
   CU(cudaGetLastError());
   return IHM2B_OK;
 }

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   const int b = gid >> 2, i = gid & 3;
   if (b >= sc.B) return;  // whole 4-lane groups leave together
+  if (w.active && !w.active[b]) return;   // closed loop: instance finished its lap or stopped
   const unsigned gm = 0xFu << (threadIdx.x & 28);
   const int t = w.track[b];
   TrackView tr{sc.n_grid, w.s_ref + (size_t)t * sc.n_grid, w.kappa_ref + (size_t)t * sc.n_grid};
@@ -190,7 +191,8 @@ void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, con
 __global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restrict__ track, const double* __restrict__ lap,
                                         const int32_t* __restrict__ status, const double* __restrict__ u0,
                                         const double* __restrict__ xn, double* __restrict__ xs, double* __restrict__ xlog,
-                                        double* __restrict__ ulog, int32_t* __restrict__ done, int32_t* __restrict__ fail) {
+                                        double* __restrict__ ulog, int32_t* __restrict__ done, int32_t* __restrict__ fail,
+                                        int32_t* __restrict__ active_mask) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   bool active = done[b] < 0 && fail[b] < 0;
@@ -209,14 +211,15 @@ __global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restri
       if (xn[b * 8] > lap[track[b]] + 1.0) done[b] = step;
     }
   }
+  if (active_mask && (done[b] >= 0 || fail[b] >= 0)) active_mask[b] = 0;   // later steps skip this instance
   if (ulog) { ulog[((size_t)step * B + b) * 2] = uu0; ulog[((size_t)step * B + b) * 2 + 1] = uu1; }
   if (xlog) for (int r = 0; r < 8; r++) xlog[((size_t)(step + 1) * B + b) * 8 + r] = xs[b * 8 + r];
 }
 
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
                              const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
-                             int32_t* fail, cudaStream_t stream) {
-  closed_loop_post_kernel<<<(B + 127) / 128, 128, 0, stream>>>(B, step, track, lap, status, u0, xn, xs, xlog, ulog, done, fail);
+                             int32_t* fail, int32_t* active_mask, cudaStream_t stream) {
+  closed_loop_post_kernel<<<(B + 127) / 128, 128, 0, stream>>>(B, step, track, lap, status, u0, xn, xs, xlog, ulog, done, fail, active_mask);
 }
 
 }  // namespace ihm2b
