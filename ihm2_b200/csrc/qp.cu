@@ -106,6 +106,7 @@ __device__ __forceinline__ void sweep(const int N, Load load, Body body) {
       if (d < left) body(k + DIR * d, f[d]);
   }
 }
+struct FragB { double a0, a1, b0, b1, e0a, e0b, e1a, e1b, xa, xb, pa, pb, u0, u1; };
 struct Frag4 { double a, b, c, d; };
 struct Frag3 { double a, b, c; };
 struct Frag2 { double a, b; };
@@ -300,7 +301,37 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   while (true) {
     __syncwarp();
     TICK(0)
-    // ================= B: stationarity and dynamics residuals of all stages (stage-parallel)
+    // ================= B: stationarity and dynamics residuals of all stages
+    // B1: the three [B A] products of every stage, A x + B u, A' pi+, B' pi+, as DMMA matrix-vector
+    // products (no dependence between stages: the tensor pipe runs back to back); results parked in the
+    // rb / rg / kfc slots.
+    {
+      const int g = lane >> 2, t = lane & 3;
+      const int ra = (2 * t) * 10;
+      const bool lo = (g < 2);
+      auto load_B = [&](int k) {
+        const double* p = gBA + k * 80;
+        const double2 af = *reinterpret_cast<const double2*>(p + g * 10 + 2 + 2 * t);
+        const double2 bd = *reinterpret_cast<const double2*>(p + g * 10);
+        const double2 xf = *reinterpret_cast<const double2*>(pX + k * 8 + 2 * t);
+        const double2 pf = *reinterpret_cast<const double2*>(pPI + (k + 1) * 8 + 2 * t);
+        const double2 uf = *reinterpret_cast<const double2*>(pU + k * 2);
+        return FragB{af.x, af.y, bd.x, bd.y, p[ra + 2 + g], p[ra + 12 + g], p[ra + (g & 1)], p[ra + 10 + (g & 1)],
+                     xf.x, xf.y, pf.x, pf.y, uf.x, uf.y};
+      };
+      auto products = [&](const int k, const FragB f) {
+        double R0 = fma(f.b0, f.u0, f.b1 * f.u1), R1 = R0, T0 = 0.0, T1 = 0.0, V0 = 0.0, V1 = 0.0;
+        const double e1a = lo ? f.e1a : 0.0, e1b = lo ? f.e1b : 0.0;
+        dmma(R0, R1, f.a0, f.xa); dmma(T0, T1, f.e0a, f.pa); dmma(V0, V1, e1a, f.pa);
+        dmma(R0, R1, f.a1, f.xb); dmma(T0, T1, f.e0b, f.pb); dmma(V0, V1, e1b, f.pb);
+        sts_if(t == 0, pRB + k * 8 + g, R0);                 // (A x + B u)[g]
+        sts_if(t == 1, pRG + k * 8 + g, T0);                 // (A' pi+)[g]
+        sts_if(t == 2 && lo, pKF + k * 4 + 2 + g, V0);       // (B' pi+)[g]
+      };
+      sweep<NT, PF, +1, FragB>(N, load_B, products);
+      __syncwarp();
+    }
+    // B2: the rest per state / row (stage-parallel)
     double rg_m = 0.0, rb_m = 0.0;
     PAR_LOOP for (int i = 0; i < rounds; i++) {
       const int k = q + 4 * i;
@@ -312,27 +343,11 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       double base_x;
       if (!term) {
         const double u0 = pU[k * 2], u1 = pU[k * 2 + 1];
-        const double2* row = reinterpret_cast<const double2*>(gBA + k * 80 + a * 10);
-        const double2* xx = reinterpret_cast<const double2*>(pX + k * 8);
-        double acc = pC[k * 8 + a];
-        const double2 bb = row[0];
-        acc = fma(bb.x, u0, acc); acc = fma(bb.y, u1, acc);
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const double2 aa = row[1 + j], xj = xx[j];
-          acc = fma(aa.x, xj.x, acc); acc = fma(aa.y, xj.y, acc);
-        }
-        const double rb = acc - pX[(k + 1) * 8 + a];
+        const double rb = pRB[k * 8 + a] + pC[k * 8 + a] - pX[(k + 1) * 8 + a];
         rb_m = nmax(rb_m, fabs(rb));
         pRB[k * 8 + a] = rb;
         const int j = a & 1;
-        double atp = 0.0, btp = 0.0;
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-          const double pn = pPI[(k + 1) * 8 + r];
-          atp = fma(gBA[k * 80 + r * 10 + 2 + a], pn, atp);
-          btp = fma(gBA[k * 80 + r * 10 + j], pn, btp);
-        }
+        const double atp = pRG[k * 8 + a], btp = pKF[k * 4 + 2 + j];
         const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
         base_x = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - pia;
         const double base_u = (j == 0 ? hu0 * u0 - c10 * pX[k * 8 + 6] : hu1 * u1 - c11 * pX[k * 8 + 7]) + btp;
