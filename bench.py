@@ -131,7 +131,7 @@ def reference_arm(args, rank: int):
     ms = 1e3 * sum(times) / len(times)
     val = n_sample / (ms * 1e-3)
     sample = f"first {n_sample} of the {B_PER_GPU} problems per step, OpenMP over problems"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "solves/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
@@ -139,7 +139,28 @@ def reference_arm(args, rank: int):
                    "note": "acados/HPIPM not installable here: CPU restatement (oracle/ihm2_oracle.cpp), not acados"},
         "cpu_baseline": {"value": val, "unit": "solves/s", "cores": CPU_THREADS, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL prints its version line) write to fd 1; the contract is ONE JSON line on stdout.
+    Point fd 1 at stderr for the rest of the process and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
 
 
 def main():
@@ -151,6 +172,7 @@ def main():
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="problems per GPU (default: the config's 4096)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -295,7 +317,7 @@ def main():
             "cpu_baseline": {"value": cpu_val, "unit": "solves/s", "cores": CPU_THREADS, "kind": "port",
                              "sample": f"first {n_cpu} of the {B} problems of one step, OpenMP over problems, {cpu_t:.2f} s"},
         }
-        print(json.dumps(out))
+        emit(out)
     eng.close()
     if world > 1:
         dist.barrier()
