@@ -11,7 +11,15 @@
 //   r           explicit in the others
 //   (s, n, psi) depend on all of the above     -> Newton on 12 unknowns
 // The block-triangular Newton matrix gives the same converged point as the dense iteration.
-// One thread per (problem, shooting interval); the small dense factors live in local memory.
+//
+// Mapping: a block owns NI = 32 shooting intervals and keeps their LU factors, stage slopes and
+// Jacobians in SHARED memory (372 doubles per interval, interval-interleaved so every access is
+// conflict-free).  Phase 1: one thread per interval runs the two Newton solves.  Phase 2: one
+// thread per (interval, 2-3 columns of d/d(x,u)) -- 128 threads, the column is warp-uniform -- runs
+// the block forward substitution of its column through the shared factors and writes its
+// column of [B A].  Phase 3: one thread per interval forms c and phi.  (A thread-per-interval
+// version with the factors in a 5.4 KB local-memory frame was bound by local-memory misses:
+// 5.3 GB of DRAM traffic per launch against 126 MB algorithmic.)
 #include "model.cuh"
 
 namespace ihm2b {
@@ -21,34 +29,62 @@ namespace {
 constexpr int NS = 4;
 constexpr int MAX_NEWTON = 12;
 
-// in-place LU without pivoting (the matrices are I - h A (x) J, close to the identity)
+constexpr int NI = 32;     // intervals per block; shared arrays are [entry][NI]
+
+// in-place LU without pivoting (the matrices are I - h A (x) J, close to the identity);
+// element (r, c) at M[(r * n + c) * NI]; L below the diagonal (unit), U above, reciprocal pivots on it
 template <int n>
 __device__ __forceinline__ void lu_factor(double* M) {
-#pragma unroll 1
-  for (int c = 0; c < n; c++) {
-    const double inv = 1.0 / M[c * n + c];
-    M[c * n + c] = inv;  // store the reciprocal pivot
-    for (int r = c + 1; r < n; r++) {
-      const double l = M[r * n + c] * inv;
-      M[r * n + c] = l;
-      for (int j = c + 1; j < n; j++) M[r * n + j] = fma(-l, M[c * n + j], M[r * n + j]);
+  // left-looking, one row at a time in registers: row r is reduced against the finished rows c < r, so the
+  // shared-memory loads never wait on a store of the same sweep (the right-looking form is a chain of
+  // load - fma - store round trips through shared memory, ~10x slower here)
+#pragma unroll
+  for (int r = 0; r < n; r++) {
+    double row[n];
+#pragma unroll
+    for (int j = 0; j < n; j++) row[j] = M[(r * n + j) * NI];
+#pragma unroll
+    for (int c = 0; c < r; c++) {
+      const double l = row[c] * M[(c * n + c) * NI];   // reciprocal pivot of row c
+      row[c] = l;
+#pragma unroll
+      for (int j = c + 1; j < n; j++) row[j] = fma(-l, M[(c * n + j) * NI], row[j]);
     }
+    row[r] = 1.0 / row[r];  // store the reciprocal pivot
+#pragma unroll
+    for (int j = 0; j < n; j++) M[(r * n + j) * NI] = row[j];
   }
 }
 template <int n>
 __device__ __forceinline__ void lu_solve(const double* M, double* b) {
-#pragma unroll 1
+#pragma unroll
   for (int r = 1; r < n; r++) {
     double v = b[r];
-    for (int c = 0; c < r; c++) v = fma(-M[r * n + c], b[c], v);
+#pragma unroll
+    for (int c = 0; c < r; c++) v = fma(-M[(r * n + c) * NI], b[c], v);
     b[r] = v;
   }
-#pragma unroll 1
+#pragma unroll
   for (int r = n - 1; r >= 0; r--) {
     double v = b[r];
-    for (int c = r + 1; c < n; c++) v = fma(-M[r * n + c], b[c], v);
-    b[r] = v * M[r * n + r];
+#pragma unroll
+    for (int c = r + 1; c < n; c++) v = fma(-M[(r * n + c) * NI], b[c], v);
+    b[r] = v * M[(r * n + r) * NI];
   }
+}
+
+// shared-memory record of one interval (offsets in entries)
+constexpr int OFF_MV = 0;            // LU of the (v_x, v_y) Newton matrix [8][8]
+constexpr int OFF_MP = 64;           // LU of the (s, n, psi) Newton matrix [12][12]
+constexpr int OFF_K = 208;           // converged stage slopes K[4][8]
+constexpr int OFF_J = 240;           // Jacobians at the 4 collocation points, 33 kept entries each
+constexpr int OFF_XN = 372;          // x_next [8]
+constexpr int PER_INT = 380;
+// kept entries of J (JMASK): rows 0..2 x columns 0..5, rows 3..5 x columns {3,4,6,7,9}
+__device__ __forceinline__ constexpr int jslot(int row, int col) {
+  return row < 3 ? (col < 6 ? row * 6 + col : -1)
+                 : (col == 3 ? 18 + (row - 3) * 5 : col == 4 ? 19 + (row - 3) * 5 : col == 6 ? 20 + (row - 3) * 5
+                    : col == 7 ? 21 + (row - 3) * 5 : col == 9 ? 22 + (row - 3) * 5 : -1);
 }
 
 // quantities of a collocation point that depend only on (T_i, delta_i, d delta_i / dt)
@@ -58,100 +94,118 @@ struct VPoint {
 
 }  // namespace
 
-// x[8], u -> xn[8], S[8][10].  wT / wD: (I + (h / t) A)^-1 1 for the two actuator lags.
-__device__ void irk_gl4_sens(const double* __restrict__ x, double u0, double u1,
-                             const double* __restrict__ p, const TrackView& tr, double h,
-                             const double* __restrict__ A4, const double* __restrict__ b4,
-                             const double* __restrict__ wT, const double* __restrict__ wD,
-                             double* __restrict__ xn, double (*S)[NZ], bool& ok) {
+
+// ---- phase 1: Newton solves of one interval; factors, slopes, Jacobians -> shared memory (sm already offset by the
+// interval's lane: entry e at sm[e * NI]).  Returns false on NaN.
+__device__ bool irk_newton(const double* __restrict__ x, double u0, double u1, const double* __restrict__ p,
+                           const TrackView& tr, double h, const double* __restrict__ A4, const double* __restrict__ b4,
+                           const double* __restrict__ wT, const double* __restrict__ wD, double* __restrict__ sm) {
+#define KS(i, a) sm[(OFF_K + (i) * 8 + (a)) * NI]
+  double* const Mv = sm + OFF_MV * NI;
+  double* const Mp = sm + OFF_MP * NI;
   const double m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
   const double C = lR / (lR + lF), im = 1.0 / m;
   const double itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
-  double K[NS][NX];
   // ---- actuators: K = w (u - x) / t
   double Ti[NS], Di[NS];
-  for (int i = 0; i < NS; i++) { K[i][6] = wT[i] * (u0 - x[6]) * itT; K[i][7] = wD[i] * (u1 - x[7]) * itD; }
+#pragma unroll
+  for (int i = 0; i < NS; i++) { KS(i, 6) = wT[i] * (u0 - x[6]) * itT; KS(i, 7) = wD[i] * (u1 - x[7]) * itD; }
+#pragma unroll
   for (int i = 0; i < NS; i++) {
     double a = x[6], d = x[7];
-    for (int j = 0; j < NS; j++) { a = fma(h * A4[i * NS + j], K[j][6], a); d = fma(h * A4[i * NS + j], K[j][7], d); }
+#pragma unroll
+    for (int j = 0; j < NS; j++) { a = fma(h * A4[i * NS + j], KS(j, 6), a); d = fma(h * A4[i * NS + j], KS(j, 7), d); }
     Ti[i] = a; Di[i] = d;
   }
   // ---- (v_x, v_y): Newton on 8 unknowns
   VPoint vp[NS];
+#pragma unroll
   for (int i = 0; i < NS; i++) {
     double sd, cd;
     sincos(Di[i], &sd, &cd);
     const double td = sd / cd, Ctd = C * td, den = 1.0 + Ctd * Ctd;
     vp[i].cb = rsqrt(den); vp[i].sb = Ctd * vp[i].cb;
-    vp[i].bdot = C * (1.0 + td * td) / den * K[i][7];
+    vp[i].bdot = C * (1.0 + td * td) / den * KS(i, 7);
     vp[i].cdb = cd * vp[i].cb + sd * vp[i].sb;
     vp[i].Fm = p[IHM2B_P_CM0] * Ti[i];
   }
-  double Mv[8 * 8], Rv[8];
-  auto veval = [&](int i, double vx, double vy, double& f3, double& f4, double& dvd) {
+  double Rv[8];
+  auto veval = [&](const VPoint& v, double vx, double vy, double& f3, double& f4, double& dvd) {
     const double th = tanh(10.0 * vx);
     const double poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
-    const double FRx = 0.5 * vp[i].Fm - poly * th;
-    const double vdot = (FRx * vp[i].cb + 0.5 * vp[i].Fm * vp[i].cdb) * im;
-    f3 = vdot * vp[i].cb - vp[i].bdot * vy;
-    f4 = vdot * vp[i].sb + vp[i].bdot * vx;
-    dvd = (-(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th)) * vp[i].cb * im;
+    const double FRx = 0.5 * v.Fm - poly * th;
+    const double vdot = (FRx * v.cb + 0.5 * v.Fm * v.cdb) * im;
+    f3 = vdot * v.cb - v.bdot * vy;
+    f4 = vdot * v.sb + v.bdot * vx;
+    dvd = (-(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th)) * v.cb * im;
   };
-  for (int i = 0; i < NS; i++) { double d; veval(i, x[3], x[4], K[i][3], K[i][4], d); }
-  ok = true;
+#pragma unroll
+  for (int i = 0; i < NS; i++) { double d, f3, f4; veval(vp[i], x[3], x[4], f3, f4, d); KS(i, 3) = f3; KS(i, 4) = f4; }
+  bool ok = true;
 #pragma unroll 1
   for (int it = 0;; it++) {
+#pragma unroll
     for (int i = 0; i < NS; i++) {
       double vx = x[3], vy = x[4];
-      for (int j = 0; j < NS; j++) { vx = fma(h * A4[i * NS + j], K[j][3], vx); vy = fma(h * A4[i * NS + j], K[j][4], vy); }
+#pragma unroll
+      for (int j = 0; j < NS; j++) { vx = fma(h * A4[i * NS + j], KS(j, 3), vx); vy = fma(h * A4[i * NS + j], KS(j, 4), vy); }
       double f3, f4, dvd;
-      veval(i, vx, vy, f3, f4, dvd);
-      Rv[2 * i] = K[i][3] - f3; Rv[2 * i + 1] = K[i][4] - f4;
+      veval(vp[i], vx, vy, f3, f4, dvd);
+      Rv[2 * i] = KS(i, 3) - f3; Rv[2 * i + 1] = KS(i, 4) - f4;
       const double J33 = dvd * vp[i].cb, J34 = -vp[i].bdot, J43 = dvd * vp[i].sb + vp[i].bdot;
+#pragma unroll
       for (int j = 0; j < NS; j++) {
         const double ha = h * A4[i * NS + j], e = (i == j) ? 1.0 : 0.0;
-        Mv[(2 * i) * 8 + 2 * j] = e - ha * J33;      Mv[(2 * i) * 8 + 2 * j + 1] = -ha * J34;
-        Mv[(2 * i + 1) * 8 + 2 * j] = -ha * J43;     Mv[(2 * i + 1) * 8 + 2 * j + 1] = e;
+        Mv[((2 * i) * 8 + 2 * j) * NI] = e - ha * J33;      Mv[((2 * i) * 8 + 2 * j + 1) * NI] = -ha * J34;
+        Mv[((2 * i + 1) * 8 + 2 * j) * NI] = -ha * J43;     Mv[((2 * i + 1) * 8 + 2 * j + 1) * NI] = e;
       }
     }
     lu_factor<8>(Mv);
     lu_solve<8>(Mv, Rv);
     double dmax = 0.0, kmax = 0.0;
+#pragma unroll
     for (int i = 0; i < NS; i++) {
-      K[i][3] -= Rv[2 * i]; K[i][4] -= Rv[2 * i + 1];
+      const double k3 = KS(i, 3) - Rv[2 * i], k4 = KS(i, 4) - Rv[2 * i + 1];
+      KS(i, 3) = k3; KS(i, 4) = k4;
       dmax = fmax(dmax, fmax(fabs(Rv[2 * i]), fabs(Rv[2 * i + 1])));
-      kmax = fmax(kmax, fmax(fabs(K[i][3]), fabs(K[i][4])));
+      kmax = fmax(kmax, fmax(fabs(k3), fabs(k4)));
     }
     if (!(dmax == dmax)) { ok = false; break; }
     if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) break;
   }
   // ---- r: explicit, r' = l_R v_y' - beta'   (python/models.py:304)
   double vxi[NS], vyi[NS], ri[NS];
-  for (int i = 0; i < NS; i++) K[i][5] = lR * K[i][4] - vp[i].bdot;
+#pragma unroll
+  for (int i = 0; i < NS; i++) KS(i, 5) = lR * KS(i, 4) - vp[i].bdot;
+#pragma unroll
   for (int i = 0; i < NS; i++) {
     double a = x[3], b = x[4], c = x[5];
+#pragma unroll
     for (int j = 0; j < NS; j++) {
       const double ha = h * A4[i * NS + j];
-      a = fma(ha, K[j][3], a); b = fma(ha, K[j][4], b); c = fma(ha, K[j][5], c);
+      a = fma(ha, KS(j, 3), a); b = fma(ha, KS(j, 4), b); c = fma(ha, KS(j, 5), c);
     }
     vxi[i] = a; vyi[i] = b; ri[i] = c;
   }
   // ---- (s, n, psi): Newton on 12 unknowns
-  double Mp[12 * 12], Rp[12];
+  double Rp[12];
   {
     double kap, dkap, sp, cp;
     kappa_lookup(tr, x[0], kap, dkap);
     sincos(x[2], &sp, &cp);
     const double sdot = (x[3] * cp - x[4] * sp) / (1.0 + kap * x[1]);
-    for (int i = 0; i < NS; i++) { K[i][0] = sdot; K[i][1] = x[3] * sp + x[4] * cp; K[i][2] = x[5] - kap * sdot; }
+#pragma unroll
+    for (int i = 0; i < NS; i++) { KS(i, 0) = sdot; KS(i, 1) = x[3] * sp + x[4] * cp; KS(i, 2) = x[5] - kap * sdot; }
   }
 #pragma unroll 1
   for (int it = 0;; it++) {
+#pragma unroll
     for (int i = 0; i < NS; i++) {
       double s = x[0], n = x[1], psi = x[2];
+#pragma unroll
       for (int j = 0; j < NS; j++) {
         const double ha = h * A4[i * NS + j];
-        s = fma(ha, K[j][0], s); n = fma(ha, K[j][1], n); psi = fma(ha, K[j][2], psi);
+        s = fma(ha, KS(j, 0), s); n = fma(ha, KS(j, 1), n); psi = fma(ha, KS(j, 2), psi);
       }
       double kap, dkap, sp, cp;
       kappa_lookup(tr, s, kap, dkap);
@@ -159,142 +213,240 @@ __device__ void irk_gl4_sens(const double* __restrict__ x, double u0, double u1,
       const double iD = 1.0 / (1.0 + kap * n);
       const double num = vxi[i] * cp - vyi[i] * sp;
       const double sdot = num * iD;
-      Rp[3 * i] = K[i][0] - sdot;
-      Rp[3 * i + 1] = K[i][1] - (vxi[i] * sp + vyi[i] * cp);
-      Rp[3 * i + 2] = K[i][2] - (ri[i] - kap * sdot);
+      Rp[3 * i] = KS(i, 0) - sdot;
+      Rp[3 * i + 1] = KS(i, 1) - (vxi[i] * sp + vyi[i] * cp);
+      Rp[3 * i + 2] = KS(i, 2) - (ri[i] - kap * sdot);
       double J[3][3];
       J[0][0] = -sdot * dkap * n * iD; J[0][1] = -sdot * kap * iD; J[0][2] = -(vxi[i] * sp + vyi[i] * cp) * iD;
       J[1][0] = 0.0; J[1][1] = 0.0; J[1][2] = num;
       J[2][0] = -dkap * sdot - kap * J[0][0]; J[2][1] = -kap * J[0][1]; J[2][2] = -kap * J[0][2];
+#pragma unroll
       for (int j = 0; j < NS; j++) {
         const double ha = h * A4[i * NS + j];
+#pragma unroll
         for (int a = 0; a < 3; a++)
+#pragma unroll
           for (int c = 0; c < 3; c++)
-            Mp[(3 * i + a) * 12 + 3 * j + c] = ((i == j && a == c) ? 1.0 : 0.0) - ha * J[a][c];
+            Mp[((3 * i + a) * 12 + 3 * j + c) * NI] = ((i == j && a == c) ? 1.0 : 0.0) - ha * J[a][c];
       }
     }
     lu_factor<12>(Mp);
     lu_solve<12>(Mp, Rp);
     double dmax = 0.0, kmax = 0.0;
+#pragma unroll
     for (int i = 0; i < NS; i++)
+#pragma unroll
       for (int a = 0; a < 3; a++) {
-        K[i][a] -= Rp[3 * i + a];
+        const double kk = KS(i, a) - Rp[3 * i + a];
+        KS(i, a) = kk;
         dmax = fmax(dmax, fabs(Rp[3 * i + a]));
-        kmax = fmax(kmax, fabs(K[i][a]));
+        kmax = fmax(kmax, fabs(kk));
       }
     if (!(dmax == dmax)) { ok = false; break; }
     if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) break;
   }
+#pragma unroll
   for (int a = 0; a < NX; a++) {
     double v = x[a];
-    for (int i = 0; i < NS; i++) v = fma(h * b4[i], K[i][a], v);
-    xn[a] = v;
+#pragma unroll
+    for (int i = 0; i < NS; i++) v = fma(h * b4[i], KS(i, a), v);
+    sm[(OFF_XN + a) * NI] = v;
   }
-  if (!S) return;
-
-  // ---- sensitivities: (I - h A (x) J) dK = J_x E + J_u, block forward substitution,
-  //      one column of d / d(x,u) at a time.  J at the converged collocation points.
-  double J4[NS][NX][NZ];
+  // ---- Jacobians at the converged collocation points (kept entries only)
+#pragma unroll 1
   for (int i = 0; i < NS; i++) {
-    double xs[NX], f[NX];
+    double xs[NX], f[NX], J[NX][NZ];
+#pragma unroll
     for (int a = 0; a < NX; a++) {
       double v = x[a];
-      for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], K[j][a], v);
+#pragma unroll
+      for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], KS(j, a), v);
       xs[a] = v;
     }
-    fkin6<true>(xs, u0, u1, p, tr, f, J4[i]);
+    fkin6<true>(xs, u0, u1, p, tr, f, J);
+#pragma unroll
+    for (int r = 0; r < 6; r++)
+#pragma unroll
+      for (int c = 0; c < NZ; c++)
+        if (jslot(r, c) >= 0) sm[(OFF_J + i * 33 + jslot(r, c)) * NI] = ((JMASK[r] >> c) & 1u) ? J[r][c] : 0.0;
   }
-#pragma unroll 1
-  for (int col = 0; col < NZ; col++) {
-    double dK[NS][NX], dX[NS][NX];  // dX excludes the identity part
-    for (int i = 0; i < NS; i++) {
-      dK[i][6] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : 0.0;
-      dK[i][7] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : 0.0;
-    }
-    auto stage_sum = [&](int a) {
-      for (int i = 0; i < NS; i++) {
-        double v = 0.0;
-        for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], dK[j][a], v);
-        dX[i][a] = v;
-      }
-    };
-    stage_sum(6); stage_sum(7);
-    const bool vcol = (SMASK[3] >> col) & 1u;
-    if (vcol) {
-      for (int i = 0; i < NS; i++)
-        for (int a = 0; a < 2; a++) {
-          double v = ((JMASK[3 + a] >> col) & 1u) ? J4[i][3 + a][col] : 0.0;
-          v = fma(J4[i][3 + a][6], dX[i][6], v);
-          v = fma(J4[i][3 + a][7], dX[i][7], v);
-          Rv[2 * i + a] = v;
-        }
-      lu_solve<8>(Mv, Rv);
-      for (int i = 0; i < NS; i++) { dK[i][3] = Rv[2 * i]; dK[i][4] = Rv[2 * i + 1]; }
-    } else {
-      for (int i = 0; i < NS; i++) dK[i][3] = dK[i][4] = 0.0;
-    }
-    stage_sum(3); stage_sum(4);
-    for (int i = 0; i < NS; i++) {
-      double v = ((JMASK[5] >> col) & 1u) ? J4[i][5][col] : 0.0;
-      v = fma(J4[i][5][3], dX[i][3], v);
-      v = fma(J4[i][5][6], dX[i][6], v);
-      v = fma(J4[i][5][7], dX[i][7], v);
-      dK[i][5] = vcol ? v : 0.0;
-    }
-    stage_sum(5);
-    for (int i = 0; i < NS; i++)
-      for (int a = 0; a < 3; a++) {
-        double v = ((JMASK[a] >> col) & 1u) ? J4[i][a][col] : 0.0;
-        if ((JMASK[a] >> 3) & 1u) v = fma(J4[i][a][3], dX[i][3], v);
-        if ((JMASK[a] >> 4) & 1u) v = fma(J4[i][a][4], dX[i][4], v);
-        if ((JMASK[a] >> 5) & 1u) v = fma(J4[i][a][5], dX[i][5], v);
-        Rp[3 * i + a] = v;
-      }
-    lu_solve<12>(Mp, Rp);
-    for (int i = 0; i < NS; i++)
-      for (int a = 0; a < 3; a++) dK[i][a] = Rp[3 * i + a];
-    for (int a = 0; a < NX; a++) {
-      double v = (a == col) ? 1.0 : 0.0;
-      for (int i = 0; i < NS; i++) v = fma(h * b4[i], dK[i][a], v);
-      S[a][col] = v;
-    }
-  }
+  return ok;
+#undef KS
 }
 
-// grid: ceil(B*N / 128), one thread per (problem, interval)
+// ---- phase 2: one column of d x_next / d (x, u):  (I - h A (x) J) dK = J_x E + J_u by block forward
+// substitution through the shared factors.  `col` is uniform over the warp.
+__device__ void irk_sens_column(const int col, const double* __restrict__ sm, double h, const double* __restrict__ A4,
+                                const double* __restrict__ b4, const double* __restrict__ wT,
+                                const double* __restrict__ wD, double itT, double itD, double* __restrict__ Scol) {
+  const double* const Mv = sm + OFF_MV * NI;
+  const double* const Mp = sm + OFF_MP * NI;
+#define JC(i, r, c) sm[(OFF_J + (i) * 33 + jslot(r, c)) * NI]
+  double dK[NS], dX6[NS], dX7[NS], dX3[NS], dX4[NS], dX5[NS];
+  auto stage_sum = [&](const double* dk, double* dx) {
+#pragma unroll
+    for (int i = 0; i < NS; i++) {
+      double v = 0.0;
+#pragma unroll
+      for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], dk[j], v);
+      dx[i] = v;
+    }
+  };
+  auto out_row = [&](int a, const double* dk) {
+    double v = (a == col) ? 1.0 : 0.0;
+#pragma unroll
+    for (int i = 0; i < NS; i++) v = fma(h * b4[i], dk[i], v);
+    Scol[a] = v;
+  };
+  // actuators (closed form)
+#pragma unroll
+  for (int i = 0; i < NS; i++) dK[i] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : 0.0;
+  stage_sum(dK, dX6); out_row(6, dK);
+#pragma unroll
+  for (int i = 0; i < NS; i++) dK[i] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : 0.0;
+  stage_sum(dK, dX7); out_row(7, dK);
+  // (v_x, v_y)
+  const bool vcol = (SMASK[3] >> col) & 1u;
+  double dK3[NS], dK4[NS];
+  if (vcol) {
+    double Rv[8];
+#pragma unroll
+    for (int i = 0; i < NS; i++)
+#pragma unroll
+      for (int a = 0; a < 2; a++) {
+        double v = 0.0;
+        if (col == 3) v = JC(i, 3 + a, 3);
+        else if (col == 4) v = JC(i, 3 + a, 4);
+        else if (col == 6) v = JC(i, 3 + a, 6);
+        else if (col == 7) v = JC(i, 3 + a, 7);
+        else if (col == 9) v = JC(i, 3 + a, 9);
+        v = fma(JC(i, 3 + a, 6), dX6[i], v);
+        v = fma(JC(i, 3 + a, 7), dX7[i], v);
+        Rv[2 * i + a] = v;
+      }
+    lu_solve<8>(Mv, Rv);
+#pragma unroll
+    for (int i = 0; i < NS; i++) { dK3[i] = Rv[2 * i]; dK4[i] = Rv[2 * i + 1]; }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NS; i++) dK3[i] = dK4[i] = 0.0;
+  }
+  stage_sum(dK3, dX3); stage_sum(dK4, dX4);
+  out_row(3, dK3); out_row(4, dK4);
+  // r
+#pragma unroll
+  for (int i = 0; i < NS; i++) {
+    double v = 0.0;
+    if (col == 3) v = JC(i, 5, 3);
+    else if (col == 4) v = JC(i, 5, 4);
+    else if (col == 6) v = JC(i, 5, 6);
+    else if (col == 7) v = JC(i, 5, 7);
+    else if (col == 9) v = JC(i, 5, 9);
+    v = fma(JC(i, 5, 3), dX3[i], v);
+    v = fma(JC(i, 5, 6), dX6[i], v);
+    v = fma(JC(i, 5, 7), dX7[i], v);
+    dK[i] = vcol ? v : 0.0;
+  }
+  stage_sum(dK, dX5); out_row(5, dK);
+  // (s, n, psi)
+  double Rp[12];
+#pragma unroll
+  for (int i = 0; i < NS; i++)
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      double v = 0.0;
+      if (col == 0) v = JC(i, a, 0);
+      else if (col == 1) v = JC(i, a, 1);
+      else if (col == 2) v = JC(i, a, 2);
+      else if (col == 3) v = JC(i, a, 3);
+      else if (col == 4) v = JC(i, a, 4);
+      else if (col == 5) v = JC(i, a, 5);
+      v = fma(JC(i, a, 3), dX3[i], v);
+      v = fma(JC(i, a, 4), dX4[i], v);
+      v = fma(JC(i, a, 5), dX5[i], v);
+      Rp[3 * i + a] = v;
+    }
+  lu_solve<12>(Mp, Rp);
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    double dk[NS];
+#pragma unroll
+    for (int i = 0; i < NS; i++) dk[i] = Rp[3 * i + a];
+    out_row(a, dk);
+  }
+#undef JC
+}
+
 #ifndef LIN_MIN_BLOCKS
 #define LIN_MIN_BLOCKS 2
 #endif
-__global__ void __launch_bounds__(128, LIN_MIN_BLOCKS) linearize_irk_kernel(const KCfg cf, const Work w) {
-  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= cf.B * cf.N) return;
-  const int b = gid / cf.N, k = gid - b * cf.N;
-  if (w.active && !w.active[b]) return;   // SQP mode: instance already converged or failed
-  const int t = w.track[b];
-  TrackView tr{cf.n_grid, w.s_ref + (size_t)t * cf.n_grid, w.kappa_ref + (size_t)t * cf.n_grid};
-  double p[NP], x[NX], wa[8];
-  for (int i = 0; i < NP; i++) p[i] = __ldg(w.params + (size_t)b * NP + i);
+constexpr int NCG = 4;     // column groups: a thread of phase 2 handles the columns cg, cg + 4, (cg + 8)
+// grid: ceil(B*N / NI) blocks of NI * NCG threads; dynamic shared memory PER_INT * NI doubles.
+// 2 blocks per SM by shared memory; 8 warps per SM leave phase 1 its registers.
+__global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel(const KCfg cf, const Work w) {
+  extern __shared__ double smem[];
+  __shared__ int s_ok[NI];
+  const int tid = threadIdx.x;
+  const int j = tid & (NI - 1), cg = tid / NI;           // interval of the block, column group (warp-uniform)
+  const int gid = blockIdx.x * NI + j;
+  const bool in_range = gid < cf.B * cf.N;
+  const int b = in_range ? gid / cf.N : 0, k = in_range ? gid - b * cf.N : 0;
+  const bool live = in_range && !(w.active && !w.active[b]);   // SQP mode: instance already converged or failed
+  double* const sm = smem + j;
+  double wa[8];
   for (int i = 0; i < 8; i++) wa[i] = __ldg(w.actw + (size_t)b * 8 + i);
-  for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
-  const double u0 = w.u[((size_t)b * cf.N + k) * NU], u1 = w.u[((size_t)b * cf.N + k) * NU + 1];
-  double xn[NX], S[NX][NZ];
-  bool ok;
-  irk_gl4_sens(x, u0, u1, p, tr, cf.dt, cf.irk_A, cf.irk_b, wa, wa + 4, xn, S, ok);
+  const double itT = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TT), itD = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TD);
   const size_t sk = (size_t)b * cf.N + k;
+  if (tid < NI) {
+    bool ok = false;
+    if (live) {
+      const int t = w.track[b];
+      TrackView tr{cf.n_grid, w.s_ref + (size_t)t * cf.n_grid, w.kappa_ref + (size_t)t * cf.n_grid};
+      double p[NP], x[NX];
+      for (int i = 0; i < NP; i++) p[i] = __ldg(w.params + (size_t)b * NP + i);
+      for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
+      const double u0 = w.u[sk * NU], u1 = w.u[sk * NU + 1];
+      ok = irk_newton(x, u0, u1, p, tr, cf.dt, cf.irk_A, cf.irk_b, wa, wa + 4, sm);
+    }
+    s_ok[j] = ok;
+  }
+  __syncthreads();
   double* ba = w.BA + sk * NX * NZ;
-  for (int i = 0; i < NX; i++) {
-    double ci = ok ? xn[i] - S[i][8] * u0 - S[i][9] * u1 : nan("");
-    for (int j = 0; j < NX; j++) ci = fma(-S[i][j], x[j], ci);
-    w.c[sk * NX + i] = ci;
-    w.phi[sk * NX + i] = ok ? xn[i] : nan("");
-    ba[i * NZ] = S[i][8]; ba[i * NZ + 1] = S[i][9];
-    for (int j = 0; j < NX; j++) ba[i * NZ + 2 + j] = S[i][j];
+  if (live) {
+#pragma unroll 1
+    for (int col = cg; col < NZ; col += NCG) {
+      double Scol[NX];
+      irk_sens_column(col, sm, cf.dt, cf.irk_A, cf.irk_b, wa, wa + 4, itT, itD, Scol);
+      const int oc = (col < NX) ? 2 + col : col - NX;     // [B A] column of d/d(x,u) column `col`
+#pragma unroll
+      for (int a = 0; a < NX; a++) ba[a * NZ + oc] = Scol[a];
+    }
+  }
+  __syncthreads();
+  if (tid < NI && live) {
+    const bool ok = s_ok[j] != 0;
+    double x[NX];
+    for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
+    const double u0 = w.u[sk * NU], u1 = w.u[sk * NU + 1];
+    for (int i = 0; i < NX; i++) {
+      const double xn = sm[(OFF_XN + i) * NI];
+      double ci = ok ? xn - ba[i * NZ] * u0 - ba[i * NZ + 1] * u1 : nan("");
+      for (int c = 0; c < NX; c++) ci = fma(-ba[i * NZ + 2 + c], x[c], ci);
+      w.c[sk * NX + i] = ci;
+      w.phi[sk * NX + i] = ok ? xn : nan("");
+    }
   }
 }
 
 void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream) {
   const int total = cf.B * cf.N;
-  linearize_irk_kernel<<<(total + 127) / 128, 128, 0, stream>>>(cf, w);
+  const int bytes = PER_INT * NI * (int)sizeof(double);
+  static int configured = 0;
+  if (!configured) {
+    cudaFuncSetAttribute(linearize_irk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    configured = 1;
+  }
+  linearize_irk_kernel<<<(total + NI - 1) / NI, NI * NCG, bytes, stream>>>(cf, w);
 }
 
 }  // namespace ihm2b
