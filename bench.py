@@ -261,6 +261,25 @@ def main():
     e2e_val = world * B / float(e2e_t.item())
     clocks = sampler.stop()
 
+    # the same steps on a handle WITHOUT launch-order history (what a first solve of fresh problems costs):
+    # the timed loop above runs with schedule_by_history, i.e. each step launches its problems longest first
+    # by the iteration counts of the previous step, as consecutive control steps of a closed loop do
+    cfg_nh = _abi.make_config(batch=B, n_grid=len(mp.s_ref), schedule_by_history=False)
+    eng_nh = Engine(cfg_nh, mp.s_ref, mp.kappa_ref)
+    t_nh = []
+    for i in range(3 + max(3, args.steps // 4)):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); eng_nh.set_iterate(x_ws, u_ws); eng_nh.solve(x0_d, u0_d, st_d); e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            t_nh.append(e0.elapsed_time(e1))
+    nh_t = torch.tensor([sum(t_nh) / len(t_nh)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(nh_t, op=dist.ReduceOp.MAX)
+    ms_no_history = float(nh_t.item())
+    eng_nh.close()
+
     # per-kernel device times (synchronising events inside the library; separate untimed pass)
     eng.profile(True)
     for _ in range(5):
@@ -302,6 +321,9 @@ def main():
             "config": {"workload": "configs[1]: 4096 perturbed initial states, single SQP-RTI step, data/skidpad, N=40",
                        "batch_per_gpu": B, "integrator": "IRK-GL4 (controller.py:305-307)", "qp": "IPM, tol 1e-9, <=50 iterations",
                        "l2": "flushed between timed steps (256 MiB write, outside the event pairs)",
+                       "launch_order": "longest first by the IPM iteration counts of the handle's previous solve (scheduling only, results bit-identical; "
+                                       "the previous solve here is the previous step on the same inputs, in a closed loop it is the previous control step)",
+                       "ms_per_step_without_history": ms_no_history, "value_without_history": world * B / (ms_no_history * 1e-3),
                        "parallelism": f"{world} rank(s), problems sharded by index, final NCCL gather after the timed loop",
                        "ipm_iterations_mean": n_ipm,
                        "status_counts": {str(k): int(v) for k, v in enumerate(np.bincount(status_all, minlength=5)) if v}},

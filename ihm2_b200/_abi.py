@@ -38,6 +38,8 @@ class Config(C.Structure):
         ("nonlinear_constraints", C.c_int32),
         ("sim_model", C.c_int32),
         ("sim_steps", C.c_int32),
+        ("schedule_by_history", C.c_int32),
+        ("reserved0", C.c_int32),
         ("dt", C.c_double),
         ("s_target", C.c_double),
         ("n_max", C.c_double),
@@ -145,6 +147,7 @@ def make_config(
     sim_model: int = SIM_KIN6_DYN6,
     sim_steps: int = 100,
     nonlinear_constraints: bool = False,
+    schedule_by_history: bool = True,
 ) -> Config:
     """Fill ihm2b_config from `IHM2Controller.__init__` style arguments
     (new_python/controller.py:250-309; python/mpc.py:77-99 for the bounds)."""
@@ -154,6 +157,7 @@ def make_config(
     cf.integrator, cf.nlp_solver, cf.nlp_max_iter = integrator, nlp_solver, nlp_max_iter
     cf.globalization, cf.qp_max_iter = globalization, qp_max_iter
     cf.nonlinear_constraints = int(nonlinear_constraints)
+    cf.schedule_by_history = int(schedule_by_history)
     cf.sim_model, cf.sim_steps = sim_model, sim_steps
     cf.dt, cf.s_target = dt, s_target
     cf.n_max, cf.v_x_max, cf.T_max, cf.delta_max = n_max, v_x_max, T_max, delta_max

@@ -18,6 +18,7 @@ void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream);
 int qp_smem_bytes(int N);
+void launch_build_order(int B, const double* stats, int32_t* order, cudaStream_t stream);
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
@@ -55,6 +56,8 @@ struct ihm2b_handle {
   double *x0_dev, *u0_dev, *xn_dev;
   int32_t* status_dev;
   int32_t* active_dev;   // SQP mode: instances still iterating
+  int32_t* order_dev;    // launch order of the QP kernel (longest first by the previous solve's iteration counts)
+  bool have_order;
   double *x0_pin, *u0_pin;
   int32_t* status_pin;
   bool have_tracks, have_params;
@@ -189,8 +192,10 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->xn_dev, B * 8);
   ALLOC(h->status_dev, B);
   ALLOC(h->active_dev, B);
+  ALLOC(h->order_dev, B);
 #undef ALLOC
-  w.active = nullptr; w.sqp_it = -1;
+  w.active = nullptr; w.sqp_it = -1; w.order = nullptr;
+  h->have_order = false;
   if (rc == IHM2B_OK) {
     cudaError_t e = cudaMallocHost(&h->x0_pin, B * 8 * sizeof(double));
     if (e == cudaSuccess) e = cudaMallocHost(&h->u0_pin, B * 2 * sizeof(double));
@@ -352,6 +357,7 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
     h->launches += status ? 3 : 2;
     Work w = h->w;
     w.active = h->active_dev;
+    w.order = nullptr;
     for (int it = 0; it < h->cfg.nlp_max_iter; it++) {
       w.sqp_it = it;
       launch_linearize(h->k, w, s);
@@ -369,11 +375,18 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   if (h->profile) cudaEventRecord(h->ev[0], s);
   launch_linearize(h->k, h->w, s);
   if (h->profile) cudaEventRecord(h->ev[1], s);
+  h->w.order = (h->have_order && h->cfg.schedule_by_history) ? h->order_dev : nullptr;
   if (launch_qp_rti(h->k, h->w, x0, u0, status, s) != 0)
     return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
                 qp_smem_bytes(h->cfg.N), h->cfg.N);
+  if (h->profile) cudaEventRecord(h->ev[2], s);
+  if (h->cfg.schedule_by_history) {
+    // next solve of this handle (closed loop: the next control step) launches its long problems first
+    launch_build_order(h->cfg.batch, h->w.stats, h->order_dev, s);
+    h->have_order = true;
+    h->launches++;
+  }
   if (h->profile) {
-    cudaEventRecord(h->ev[2], s);
     cudaEventSynchronize(h->ev[2]);
     float a = 0.f, b = 0.f;
     cudaEventElapsedTime(&a, h->ev[0], h->ev[1]);

@@ -60,6 +60,9 @@ struct Work {
   // SQP mode (nlp_solver = SQP): instances still iterating, index of the current SQP iteration
   int32_t* active;          // [B], NULL in RTI mode (all instances run)
   int sqp_it;               // -1 in RTI mode
+  // launch order of the QP kernel: block i solves problem order[i] (longest first by the iteration
+  // counts of the handle's previous solve), NULL = identity
+  const int32_t* order;
 };
 
 }  // namespace ihm2b

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   extern __shared__ double smem[];
   const int lane = threadIdx.x;
   const int a = lane & 7, q = lane >> 3;
-  const int b = blockIdx.x;
+  const int b = w.order ? w.order[blockIdx.x] : blockIdx.x;
   if (w.active && !w.active[b]) return;      // SQP mode: instance already converged or failed
   const int N = (NT > 0) ? NT : cf.N, N1 = N + 1;
   // Shared memory (structure of arrays, stage-major): what the serial sweeps touch.
@@ -779,6 +779,39 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream) {
   nlp_residual_kernel<<<cf.B, 32, 0, stream>>>(cf, w, x0, nlp_tol, have_mult, status);
+}
+
+// ---------------------------------------------------------------------------------------
+// Launch order for the next solve of this handle: problems sorted by decreasing IPM iteration count of
+// the solve just finished (counting sort, counts 0..63).  A solve is a serial chain whose length is its
+// iteration count (13 .. 50 here), and a batch is only 2-3 waves of resident warps: with the long problems
+// first the last wave is not left waiting for a 50-iteration straggler.  One block.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* __restrict__ stats, int32_t* __restrict__ order) {
+  __shared__ int cnt[64], start[64];
+  const int tid = threadIdx.x;
+  if (tid < 64) cnt[tid] = 0;
+  __syncthreads();
+  for (int b = tid; b < B; b += blockDim.x) {
+    const double it = stats[(size_t)b * 8];
+    const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
+    atomicAdd(&cnt[key], 1);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int acc = 0;
+    for (int k = 63; k >= 0; k--) { start[k] = acc; acc += cnt[k]; }
+  }
+  __syncthreads();
+  for (int b = tid; b < B; b += blockDim.x) {
+    const double it = stats[(size_t)b * 8];
+    const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
+    order[atomicAdd(&start[key], 1)] = b;
+  }
+}
+
+void launch_build_order(int B, const double* stats, int32_t* order, cudaStream_t stream) {
+  build_order_kernel<<<1, 1024, 0, stream>>>(B, stats, order);
 }
 
 int qp_smem_bytes(int N) { return ((N + 1) * PER_STAGE + S_TOT) * (int)sizeof(double); }

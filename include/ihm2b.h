@@ -66,6 +66,10 @@ typedef struct ihm2b_config {
   int32_t nonlinear_constraints; /* 1: add soft h(x,u) of old/generate_acaods_interface.py:190-212 */
   int32_t sim_model;      /* ihm2b_sim_model (python/main.py:346, 475-502) */
   int32_t sim_steps;      /* integrator sub-steps of the plant (python/main.py:398: 100) */
+  int32_t schedule_by_history; /* 1 (default of the Python layer): the QP kernel launches the problems of a solve
+                             longest first, by the IPM iteration counts of the handle's previous solve (in a
+                             closed loop: the previous control step).  Scheduling only; results are unchanged. */
+  int32_t reserved0;
   double dt;              /* sampling time (controller.py:255) */
   double s_target;        /* controller.py:256 */
   double n_max, v_x_max, T_max, delta_max; /* python/mpc.py:77-89 */

@@ -326,3 +326,26 @@ def test_sqp_rejects_unimplemented_line_search(torch_cuda, skidpad):
     with pytest.raises(Ihm2bError, match="line search"):
         eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
     eng.close()
+
+
+def test_history_scheduling_changes_nothing_but_the_order(torch_cuda, skidpad):
+    """schedule_by_history: the second solve of a handle launches its problems longest first (by the
+    iteration counts of the first).  Same inputs -> bit-identical outputs, with and without it."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.workloads import nominal_iterate, perturbed_batch
+    B = 1024
+    x_nom, xp, up = nominal_iterate("skidpad", 20)
+    outs = []
+    for flag in (True, False):
+        cfg = _abi.make_config(batch=B, n_grid=len(skidpad.s_ref), schedule_by_history=flag)
+        x0, x, u = perturbed_batch(x_nom, xp, up, B, seed=3, cfg=cfg)
+        eng = _engine(cfg, skidpad)
+        x0d = torch_cuda.as_tensor(x0, device="cuda")
+        for _ in range(2):                               # the second solve runs in history order
+            eng.set_iterate(x, u)
+            u0, status = eng.solve(x0d)
+        xg, ug = eng.get_iterate()
+        outs.append((u0.cpu().numpy(), status.cpu().numpy(), xg.cpu().numpy(), ug.cpu().numpy(), eng.stats().cpu().numpy()))
+        eng.close()
+    for a, b in zip(*outs):
+        np.testing.assert_array_equal(a, b)
