@@ -331,9 +331,9 @@ def main():
             "e2e": {"value": e2e_val, "unit": "solves/s", "h2d_bytes_per_step": B * 8 * 8, "d2h_bytes_per_step": B * (2 * 8 + 4)},
             "gpu_launches": int(launches),
             "kernels_ms": {"linearize_irk": lin_ms, "qp_rti": qp_ms},
-            "roofline": {"bound": "fp64", "kernel": "qp_rti_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "roofline": {"bound": "fp64", "bound_note": "FP64 CUDA-core / FP64 tensor-core (DMMA) throughput, SURVEY.md 8d: neither HBM nor the bf16 tensor peak bounds this path", "kernel": "qp_rti_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach / peak if peak else None, "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src,
-                         "peak_source": "DFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)",
+                         "peak_source": "larger of a DFMA-chain and a DMMA-chain (mma.m8n8k4.f64) microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)",
                          "flops_per_solve": fl["total"], "flops_per_launch": B * fl["qp"],
                          "hbm_secondary": {"algorithmic_bytes_per_solve": 6800, "achieved_gbs": value / world * 6800 * 1e-9, "peak_gbs": hbm}},
             "cpu_baseline": {"value": cpu_val, "unit": "solves/s", "cores": CPU_THREADS, "kind": "port",

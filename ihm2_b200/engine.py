@@ -66,7 +66,7 @@ def _stream():
 
 
 def measure_fp64_tflops() -> float:
-    """DFMA-chain microbenchmark on the current device (FP64 CUDA-core roofline denominator)."""
+    """DFMA- and DMMA-chain microbenchmarks on the current device (FP64 roofline denominator: the larger)."""
     lib = load_library()
     out = C.c_double(0.0)
     rc = lib.ihm2b_measure_fp64_tflops(C.byref(out))
