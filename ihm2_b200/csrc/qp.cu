@@ -626,7 +626,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     }
     TICK(6)
     // ================= J + A: step of multipliers / slacks, and the row pass of the NEXT iteration on the
-    // updated values while they are in registers (stage-parallel); then the step of the primal point
+    // updated values while they are in registers, and the step of the primal point / costate (stage-parallel)
     rd_m = 0.0; rm_m = 0.0; S0 = 0.0;
     PAR_LOOP for (int i = 0; i < rounds; i++) {
       const int kk = q + 4 * i;
@@ -650,10 +650,14 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         pLL[k * 8 + a] = lamL; pLU[k * 8 + a] = lamU; pTL[k * 8 + a] = tL; pTU[k * 8 + a] = tU;
       }
       rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
+      // step of the primal point and the costate: state a / control a of this stage.  The shuffles inside
+      // rows_A separate these stores from the row loads of the stage above.
+      if (on) {
+        pX[k * 8 + a] = fma(alpha, pDX[k * 8 + a], pX[k * 8 + a]);
+        pPI[k * 8 + a] = fma(alpha, pRG[k * 8 + a], pPI[k * 8 + a]);
+        if (a < 2 && !term) pU[k * 2 + a] = fma(alpha, pDU[k * 2 + a], pU[k * 2 + a]);
+      }
     }
-    __syncwarp();
-    for (int e = lane; e < N1 * 8; e += 32) { pX[e] = fma(alpha, pDX[e], pX[e]); pPI[e] = fma(alpha, pRG[e], pPI[e]); }
-    for (int e = lane; e < N * 2; e += 32) pU[e] = fma(alpha, pDU[e], pU[e]);
     __syncwarp();
     TICK(7)
     it++;
