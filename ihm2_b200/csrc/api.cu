@@ -18,7 +18,7 @@ void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream);
 int qp_smem_bytes(int N);
-void launch_build_order(int B, const double* stats, int32_t* order, cudaStream_t stream);
+void launch_build_order(int B, const double* stats, int col, int32_t* order, cudaStream_t stream);
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
@@ -366,6 +366,12 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
         return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
                     qp_smem_bytes(h->cfg.N), h->cfg.N);
       h->launches += 3;
+      if (h->cfg.schedule_by_history && it + 1 < h->cfg.nlp_max_iter) {
+        // the QP of the next SQP iteration needs about as many IPM iterations as this one: longest first
+        launch_build_order(h->cfg.batch, h->w.stats, 7, h->order_dev, s);
+        w.order = h->order_dev;
+        h->launches++;
+      }
     }
     CU(cudaGetLastError());
     return IHM2B_OK;
@@ -382,7 +388,7 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   if (h->profile) cudaEventRecord(h->ev[2], s);
   if (h->cfg.schedule_by_history) {
     // next solve of this handle (closed loop: the next control step) launches its long problems first
-    launch_build_order(h->cfg.batch, h->w.stats, h->order_dev, s);
+    launch_build_order(h->cfg.batch, h->w.stats, 0, h->order_dev, s);
     h->have_order = true;
     h->launches++;
   }

@@ -682,7 +682,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics
       sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m; sp[7] = 0.0;
     } else {                     // SQP: the NLP residuals (sp[3..6]) are written by nlp_residual_kernel
-      sp[0] = (w.sqp_it > 0 ? sp[0] : 0.0) + it; sp[1] = w.sqp_it + 1; sp[2] = mu; sp[7] = 0.0;
+      sp[0] = (w.sqp_it > 0 ? sp[0] : 0.0) + it; sp[1] = w.sqp_it + 1; sp[2] = mu; sp[7] = it;   // [7]: IPM iterations of this QP
       if (st != IHM2B_SUCCESS) w.active[b] = 0;   // the iteration stops at a failed QP (status 1 / 4)
       else st = IHM2B_MAXITER;                    // until the residual test of a later iteration says converged
     }
@@ -791,13 +791,13 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 // iteration count (13 .. 50 here), and a batch is only 2-3 waves of resident warps: with the long problems
 // first the last wave is not left waiting for a 50-iteration straggler.  One block.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* __restrict__ stats, int32_t* __restrict__ order) {
+__global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* __restrict__ stats, int col, int32_t* __restrict__ order) {
   __shared__ int cnt[64], start[64];
   const int tid = threadIdx.x;
   if (tid < 64) cnt[tid] = 0;
   __syncthreads();
   for (int b = tid; b < B; b += blockDim.x) {
-    const double it = stats[(size_t)b * 8];
+    const double it = stats[(size_t)b * 8 + col];
     const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
     atomicAdd(&cnt[key], 1);
   }
@@ -808,14 +808,14 @@ __global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* 
   }
   __syncthreads();
   for (int b = tid; b < B; b += blockDim.x) {
-    const double it = stats[(size_t)b * 8];
+    const double it = stats[(size_t)b * 8 + col];
     const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
     order[atomicAdd(&start[key], 1)] = b;
   }
 }
 
-void launch_build_order(int B, const double* stats, int32_t* order, cudaStream_t stream) {
-  build_order_kernel<<<1, 1024, 0, stream>>>(B, stats, order);
+void launch_build_order(int B, const double* stats, int col, int32_t* order, cudaStream_t stream) {
+  build_order_kernel<<<1, 1024, 0, stream>>>(B, stats, col, order);
 }
 
 int qp_smem_bytes(int N) { return ((N + 1) * PER_STAGE + S_TOT) * (int)sizeof(double); }
