@@ -107,6 +107,7 @@ __device__ __forceinline__ void sweep(const int N, Load load, Body body) {
   }
 }
 struct FragB { double a0, a1, b0, b1, e0a, e0b, e1a, e1b, xa, xb, pa, pb, u0, u1; };
+struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv; };
 struct Frag4 { double a, b, c, d; };
 struct Frag3 { double a, b, c; };
 struct Frag2 { double a, b; };
@@ -490,7 +491,23 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       TICK(3)
       // ---- inequality rows at the step (stage-parallel): slack / multiplier steps, step length
       double ratio = 0.0, S1 = 0.0, S2 = 0.0;
+      // the global-memory inputs of a round (L2) are fetched one round ahead of their use
+      auto load_rows = [&](int i) {
+        const int kk = q + 4 * i;
+        const int k = (kk <= N) ? kk : N;
+        const bool term = (k == N);
+        const RowDef& R = term ? Rt : Rp;
+        const int e = k * 8 + a;
+        RowIn in;
+        in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e];
+        in.d1 = pred ? 0.0 : pD1[e]; in.d2 = pred ? 0.0 : pD2[e];
+        in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
+        return in;
+      };
+      RowIn nxt = load_rows(0);
       PAR_LOOP for (int i = 0; i < rounds; i++) {
+        const RowIn cur = nxt;
+        if (i + 1 < rounds) nxt = load_rows(i + 1);
         const int kk = q + 4 * i;
         const bool on = (kk <= N);
         const int k = on ? kk : N;
@@ -500,8 +517,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         double ddl = 0.0;   // dlamL - dlamU of this row (corrector pass)
         if (act) {
           const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-          const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
-          const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a], tL = pTL[k * 8 + a], tU = pTU[k * 8 + a];
+          const double v = row_value(R, term, cur.uv, cur.xv);
+          const double lamL = cur.lamL, lamU = cur.lamU, tL = cur.tL, tU = cur.tU;
           const double itL = 1.0 / tL, itU = 1.0 / tU;
           const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
           if (pred) {
@@ -511,8 +528,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
             pD1[k * 8 + a] = dlL * dtL; pD2[k * 8 + a] = dlU * dtU;
             ratio = nmax(ratio, nmax(nmax(1.0 + dtL * itL, 1.0 + dtU * itU), nmax(-dtL * itL, -dtU * itU)));
           } else {
-            const double dlL = -lamL - (pD1[k * 8 + a] - mu_t + lamL * dtL) * itL;
-            const double dlU = -lamU - (pD2[k * 8 + a] - mu_t + lamU * dtU) * itU;
+            const double dlL = -lamL - (cur.d1 - mu_t + lamL * dtL) * itL;
+            const double dlU = -lamU - (cur.d2 - mu_t + lamU * dtU) * itU;
             pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
             ddl = dlL - dlU;
             ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
