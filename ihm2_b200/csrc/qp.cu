@@ -560,14 +560,22 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
       // ---- corrector term chi of every row (stage-parallel); what the backward sweep adds per state
       // (C' chi) goes to the gamma slot, the two control entries to the kfc slot
+      auto load_chi = [&](int i) {
+        const int kk = q + 4 * i;
+        const int e = ((kk <= N) ? kk : N) * 8 + a;
+        return Frag4{pD1[e], pD2[e], pTL[e], pTU[e]};
+      };
+      Frag4 cnx = load_chi(0);
       PAR_LOOP for (int i = 0; i < rounds; i++) {
+        const Frag4 cc = cnx;
+        if (i + 1 < rounds) cnx = load_chi(i + 1);
         const int kk = q + 4 * i;
         const bool on = (kk <= N);
         const int k = on ? kk : N;
         const bool term = (k == N);
         const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
         double chi = 0.0;
-        if (act) chi = (pD1[k * 8 + a] - mu_t) / pTL[k * 8 + a] - (pD2[k * 8 + a] - mu_t) / pTU[k * 8 + a];
+        if (act) chi = (cc.a - mu_t) / cc.c - (cc.b - mu_t) / cc.d;
         const CtDef& ct = term ? ctT : ctP;
         const double c1v = __shfl_sync(FULL, chi, ct.i1, GROUP), c2v = __shfl_sync(FULL, chi, ct.i2, GROUP);
         const double cp2 = __shfl_sync(FULL, chi, (a + 2) & 7, GROUP);
@@ -645,7 +653,21 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     // ================= J + A: step of multipliers / slacks, and the row pass of the NEXT iteration on the
     // updated values while they are in registers, and the step of the primal point / costate (stage-parallel)
     rd_m = 0.0; rm_m = 0.0; S0 = 0.0;
+    auto load_upd = [&](int i) {      // global-memory inputs of a round, fetched one round ahead
+      const int kk = q + 4 * i;
+      const int k = (kk <= N) ? kk : N;
+      const bool term = (k == N);
+      const RowDef& R = term ? Rt : Rp;
+      const int e = k * 8 + a;
+      RowIn in;
+      in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e]; in.d1 = pD1[e]; in.d2 = pD2[e];
+      in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
+      return in;
+    };
+    RowIn unx = load_upd(0);
     PAR_LOOP for (int i = 0; i < rounds; i++) {
+      const RowIn cur = unx;
+      if (i + 1 < rounds) unx = load_upd(i + 1);
       const int kk = q + 4 * i;
       const bool on = (kk <= N);
       const int k = on ? kk : N;
@@ -655,15 +677,14 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0, v = 0.0;
       if (act) {
         const double cdz = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
-        v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
-        tL = pTL[k * 8 + a]; tU = pTU[k * 8 + a];
+        v = row_value(R, term, cur.uv, cur.xv);
+        tL = cur.tL; tU = cur.tU;
         const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
-        lamL = fma(alpha, pD1[k * 8 + a], pLL[k * 8 + a]);
-        lamU = fma(alpha, pD2[k * 8 + a], pLU[k * 8 + a]);
+        lamL = fma(alpha, cur.d1, cur.lamL);
+        lamU = fma(alpha, cur.d2, cur.lamU);
         tL = fma(alpha, dtL, tL); tU = fma(alpha, dtU, tU);
         // the row at the updated point, from the values the primal update below will store
-        v = row_value(R, term, fma(alpha, pDU[(term ? 0 : k) * 2 + R.iu], pU[(term ? 0 : k) * 2 + R.iu]),
-                      fma(alpha, pDX[k * 8 + R.ix], pX[k * 8 + R.ix]));
+        v = row_value(R, term, fma(alpha, pDU[(term ? 0 : k) * 2 + R.iu], cur.uv), fma(alpha, pDX[k * 8 + R.ix], cur.xv));
         pLL[k * 8 + a] = lamL; pLU[k * 8 + a] = lamU; pTL[k * 8 + a] = tL; pTU[k * 8 + a] = tU;
       }
       rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
