@@ -107,6 +107,7 @@ __device__ __forceinline__ void sweep(const int N, Load load, Body body) {
   }
 }
 struct FragB { double a0, a1, b0, b1, e0a, e0b, e1a, e1b, xa, xb, pa, pb, u0, u1; };
+struct ResIn { double xa, pia, p1, p2, l1, l2, u0, u1, c, xn, xj, q0, q1, s0, s1; };
 struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv; };
 struct Frag4 { double a, b, c, d; };
 struct Frag3 { double a, b, c; };
@@ -332,36 +333,54 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       sweep<NT, PF, +1, FragB>(N, load_B, products);
       __syncwarp();
     }
-    // B2: the rest per state / row (stage-parallel)
+    // B2: the rest per state / row (stage-parallel); global-memory inputs fetched one round ahead
     double rg_m = 0.0, rb_m = 0.0;
-    PAR_LOOP for (int i = 0; i < rounds; i++) {
-      const int k = q + 4 * i;
-      if (k > N) break;
+    auto load_res = [&](int i) {
+      const int kk = q + 4 * i;
+      const int k = (kk <= N) ? kk : N;
       const bool term = (k == N);
       const CtDef& ct = term ? ctT : ctP;
-      const double xa_ = pX[k * 8 + a], pia = pPI[k * 8 + a];
-      const double psi_s = ct_apply(ct, pD1 + k * 8), dl_s = ct_apply(ct, pD2 + k * 8);
-      double base_x;
-      if (!term) {
-        const double u0 = pU[k * 2], u1 = pU[k * 2 + 1];
-        const double rb = pRB[k * 8 + a] + pC[k * 8 + a] - pX[(k + 1) * 8 + a];
-        rb_m = nmax(rb_m, fabs(rb));
-        pRB[k * 8 + a] = rb;
-        const int j = a & 1;
-        const double atp = pRG[k * 8 + a], btp = pKF[k * 4 + 2 + j];
-        const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
-        base_x = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - pia;
-        const double base_u = (j == 0 ? hu0 * u0 - c10 * pX[k * 8 + 6] : hu1 * u1 - c11 * pX[k * 8 + 7]) + btp;
-        const double rg_u = base_u - (pD2[k * 8 + j] + pD2[k * 8 + 2 + j]);
-        rg_m = nmax(rg_m, fabs(rg_u));
-        if (a < 2) pGU[k * 2 + a] = base_u + pD1[k * 8 + j] + pD1[k * 8 + 2 + j];
-      } else {
-        base_x = hxN * xa_ + ((a == 0) ? gsN : 0.0) - pia;
+      const int ku = term ? 0 : k, kn = term ? k : k + 1, j = a & 1;
+      ResIn in;
+      in.xa = pX[k * 8 + a]; in.pia = pPI[k * 8 + a];
+      in.p1 = pD1[k * 8 + ct.i1]; in.p2 = pD1[k * 8 + ct.i2]; in.l1 = pD2[k * 8 + ct.i1]; in.l2 = pD2[k * 8 + ct.i2];
+      in.u0 = pU[ku * 2]; in.u1 = pU[ku * 2 + 1];
+      in.c = pC[(term ? 0 : k) * 8 + a]; in.xn = pX[kn * 8 + a]; in.xj = pX[k * 8 + 6 + j];
+      in.q0 = pD2[k * 8 + j]; in.q1 = pD2[k * 8 + 2 + j]; in.s0 = pD1[k * 8 + j]; in.s1 = pD1[k * 8 + 2 + j];
+      return in;
+    };
+    ResIn rnx = load_res(0);
+    PAR_LOOP for (int i = 0; i < rounds; i++) {
+      const ResIn in = rnx;
+      if (i + 1 < rounds) rnx = load_res(i + 1);
+      const int k = q + 4 * i;
+      if (k <= N) {
+        const bool term = (k == N);
+        const CtDef& ct = term ? ctT : ctP;
+        const double xa_ = in.xa, pia = in.pia;
+        const double psi_s = ct.c1 * in.p1 + ct.c2 * in.p2, dl_s = ct.c1 * in.l1 + ct.c2 * in.l2;
+        double base_x;
+        if (!term) {
+          const double u0 = in.u0, u1 = in.u1;
+          const double rb = pRB[k * 8 + a] + in.c - in.xn;
+          rb_m = nmax(rb_m, fabs(rb));
+          pRB[k * 8 + a] = rb;
+          const int j = a & 1;
+          const double atp = pRG[k * 8 + a], btp = pKF[k * 4 + 2 + j];
+          const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
+          base_x = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - pia;
+          const double base_u = (j == 0 ? hu0 * u0 - c10 * in.xj : hu1 * u1 - c11 * in.xj) + btp;
+          const double rg_u = base_u - (in.q0 + in.q1);
+          rg_m = nmax(rg_m, fabs(rg_u));
+          if (a < 2) pGU[k * 2 + a] = base_u + in.s0 + in.s1;
+        } else {
+          base_x = hxN * xa_ + ((a == 0) ? gsN : 0.0) - pia;
+        }
+        const double rg_x = base_x - dl_s;
+        if (k > 0) rg_m = nmax(rg_m, fabs(rg_x));
+        pRG[k * 8 + a] = rg_x;
+        pGX[k * 8 + a] = base_x + psi_s;
       }
-      const double rg_x = base_x - dl_s;
-      if (k > 0) rg_m = nmax(rg_m, fabs(rg_x));
-      pRG[k * 8 + a] = rg_x;
-      pGX[k * 8 + a] = base_x + psi_s;
     }
     res_g = wmax(rg_m); res_b = wmax(rb_m); res_d = wmax(rd_m); res_m = wmax(rm_m);
     S0 = wsum(S0);
