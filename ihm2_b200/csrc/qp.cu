@@ -108,7 +108,7 @@ __device__ __forceinline__ void sweep(const int N, Load load, Body body) {
 }
 struct FragB { double a0, a1, b0, b1, e0a, e0b, e1a, e1b, xa, xb, pa, pb, u0, u1; };
 struct ResIn { double xa, pia, p1, p2, l1, l2, u0, u1, c, xn, xj, q0, q1, s0, s1; };
-struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv; };
+struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv, xa, pia; };
 struct Frag4 { double a, b, c, d; };
 struct Frag3 { double a, b, c; };
 struct Frag2 { double a, b; };
@@ -521,6 +521,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e];
         in.d1 = pred ? 0.0 : pD1[e]; in.d2 = pred ? 0.0 : pD2[e];
         in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
+        in.xa = 0.0; in.pia = 0.0;
         return in;
       };
       RowIn nxt = load_rows(0);
@@ -681,6 +682,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       RowIn in;
       in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e]; in.d1 = pD1[e]; in.d2 = pD2[e];
       in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
+      in.xa = pX[e]; in.pia = pPI[e];
       return in;
     };
     RowIn unx = load_upd(0);
@@ -710,8 +712,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       // step of the primal point and the costate: state a / control a of this stage.  The shuffles inside
       // rows_A separate these stores from the row loads of the stage above.
       if (on) {
-        pX[k * 8 + a] = fma(alpha, pDX[k * 8 + a], pX[k * 8 + a]);
-        pPI[k * 8 + a] = fma(alpha, pRG[k * 8 + a], pPI[k * 8 + a]);
+        pX[k * 8 + a] = fma(alpha, pDX[k * 8 + a], cur.xa);
+        pPI[k * 8 + a] = fma(alpha, pRG[k * 8 + a], cur.pia);
         if (a < 2 && !term) pU[k * 2 + a] = fma(alpha, pDU[k * 2 + a], pU[k * 2 + a]);
       }
     }
