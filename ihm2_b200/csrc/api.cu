@@ -21,6 +21,9 @@ int qp_smem_bytes(int N);
 void launch_build_order(int B, const double* stats, int col, int32_t* order, cudaStream_t stream);
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream);
+cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
+                                    const double* u, const double* ref, double* cost, double* grad, double* xtraj,
+                                    cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
@@ -584,6 +587,19 @@ int ihm2b_measure_fp64_tflops(double* tflops) {
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
   *tflops = best;
+  return IHM2B_OK;
+}
+
+int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const double* x0, const double* u,
+                               const double* ref, const double* weights, double* cost, double* grad, double* xtraj,
+                               void* stream) {
+  if (!x0 || !u || !ref || !weights || !cost || !grad) return fail(IHM2B_EINVAL, "null argument");
+  if (batch < 0 || !(dt > 0.0)) return fail(IHM2B_EINVAL, "bad batch %lld or dt %g", (long long)batch, dt);
+  if (Nf != 40 && Nf != 80) return fail(IHM2B_EINVAL, "Nf = %d: the rollout kernel is built for Nf = 40 and 80", Nf);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
+  if (batch == 0) return IHM2B_OK;
+  CU(launch_dpc_rollout_grad(batch, Nf, dt, weights, x0, u, ref, cost, grad, xtraj, static_cast<cudaStream_t>(stream)));
   return IHM2B_OK;
 }
 

@@ -1,0 +1,200 @@
+// dpc.cu -- DPC rollout of the kin4 bicycle model and the gradient of its tracking cost in the controls
+// (BASELINE.json configs[4]).
+//
+// Reference: dpc/main.py:56-84 (kin4 ODE), :87-97 (one RK4 step of dt = 1/20), :374-409 (IHM1.5 cost: tracking
+// terms on stages 1..Nf-1, control terms on stages 0..Nf-1, terminal terms with the _f weights; doc/dpc.typ:44-56),
+// constants dpc/main.py:23-37.  The reference leaves the policy itself undefined (DPCController is an empty class,
+// dpc/main.py:617-635); what it fixes is the rollout and the loss, so this kernel returns the loss and d loss / d u
+// for a batch of control sequences -- the quantity any policy trained through the rollout back-propagates.
+//
+// One thread per rollout.  Forward: RK4 over the horizon, the stage cost and its state gradient are formed on the
+// fly; per stage the thread keeps (phi, v, dJ/dX, dJ/dY, dJ/dphi, dJ/dv) in local memory (interleaved per thread by
+// the hardware, so coalesced).  Backward: the four RK4 stage points of a step are recomputed from (phi, v) -- X and Y
+// never enter the right-hand side -- and the adjoint is propagated through them by hand; the X / Y adjoints are plain
+// suffix sums.  Controls and gradients move as 32-byte pairs of stages so every sector touched is used in full.
+#include "common.cuh"
+
+namespace ihm2b {
+
+namespace {
+// dpc/main.py:23-29
+constexpr double DPC_M = 230.0, DPC_WHEELBASE = 1.5706, DPC_CM0 = 4.950, DPC_CR0 = 297.030, DPC_CR1 = 16.665,
+                 DPC_CR2 = 0.6784;
+constexpr double DPC_INV_M = 1.0 / DPC_M, DPC_INV_LR = 2.0 / DPC_WHEELBASE;
+
+struct DpcWeights {
+  double q[4], r[2], qf[4], dt;
+};
+
+// right-hand side at one RK4 stage point; only (phi, v) matter (dpc/main.py:69-83)
+struct Kin4Eval {
+  double s, c, dres;  // sin / cos of phi + beta, d(resistance)/d v_x
+  double k0, k1, k2, k3;
+};
+
+#ifndef DPC_NOINLINE
+#define DPC_NOINLINE 0
+#endif
+#ifndef DPC_UNROLL_H
+#define DPC_UNROLL_H 1
+#endif
+#ifndef DPC_MIN_BLOCKS
+#define DPC_MIN_BLOCKS 8
+#endif
+#if DPC_NOINLINE
+#define DPC_INLINE __noinline__
+#else
+#define DPC_INLINE __forceinline__
+#endif
+#define DPC_PRAGMA_(x) _Pragma(#x)
+#define DPC_PRAGMA(x) DPC_PRAGMA_(x)
+
+template <bool WITH_DERIV>
+__device__ DPC_INLINE Kin4Eval kin4(double phi, double v, double T, double beta, double sb, double cb) {
+  Kin4Eval e;
+  sincos(phi + beta, &e.s, &e.c);
+  const double vx = v * cb;
+  const double th = tanh(10.0 * vx);
+  const double poly = fma(vx, fma(vx, DPC_CR2, DPC_CR1), DPC_CR0);
+  e.k0 = v * e.c;
+  e.k1 = v * e.s;
+  e.k2 = v * sb * DPC_INV_LR;
+  e.k3 = (DPC_CM0 * T - poly * th) * DPC_INV_M;
+  if (WITH_DERIV) e.dres = fma(fma(2.0 * DPC_CR2, vx, DPC_CR1), th, poly * 10.0 * (1.0 - th * th));
+  return e;
+}
+
+// tracking term of one stage and its gradient in the state (dpc/main.py:377-388)
+__device__ __forceinline__ double track_term(const double x[4], const double4 r, const double* q, double g[4]) {
+  double sp, cp;
+  sincos(r.z, &sp, &cp);
+  const double dX = x[0] - r.x, dY = x[1] - r.y;
+  const double elon = cp * dX + sp * dY, elat = cp * dY - sp * dX;
+  const double ephi = x[2] - r.z, ev = x[3] - r.w;
+  const double wl = 2.0 * q[0] * elon, wt = 2.0 * q[1] * elat;
+  g[0] = wl * cp - wt * sp;
+  g[1] = wl * sp + wt * cp;
+  g[2] = 2.0 * q[2] * ephi;
+  g[3] = 2.0 * q[3] * ev;
+  return q[0] * elon * elon + q[1] * elat * elat + q[2] * ephi * ephi + q[3] * ev * ev;
+}
+
+template <int NF>
+__global__ void __launch_bounds__(128, DPC_MIN_BLOCKS) dpc_rollout_grad_kernel(long long B, DpcWeights w, const double* __restrict__ x0,
+                                                               const double* __restrict__ u,
+                                                               const double* __restrict__ ref,
+                                                               double* __restrict__ cost, double* __restrict__ grad,
+                                                               double* __restrict__ xtraj) {
+  static_assert(NF % 2 == 0, "stages move in pairs");
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const double dt = w.dt;
+  const double4* up = reinterpret_cast<const double4*>(u + i * (NF * 2));
+  const double4* rp = reinterpret_cast<const double4*>(ref + i * ((NF + 1) * 4));
+  double4* xo = xtraj ? reinterpret_cast<double4*>(xtraj + i * ((NF + 1) * 4)) : nullptr;
+
+  // per stage k: (phi_k, v_k) and the state gradient of the tracking term at stage k + 1
+  double sv[NF][2], sg[NF][4];
+  double x[4];
+  {
+    const double4 xi = *reinterpret_cast<const double4*>(x0 + i * 4);
+    x[0] = xi.x; x[1] = xi.y; x[2] = xi.z; x[3] = xi.w;
+  }
+  if (xo) xo[0] = make_double4(x[0], x[1], x[2], x[3]);
+  double J = 0.0;
+#pragma unroll 1
+  for (int kk = 0; kk < NF; kk += 2) {
+    const double4 u2 = up[kk >> 1];
+DPC_PRAGMA(unroll DPC_UNROLL_H)
+    for (int h = 0; h < 2; h++) {
+      const int k = kk + h;
+      const double T = h ? u2.z : u2.x, delta = h ? u2.w : u2.y;
+      const double beta = 0.5 * delta;
+      double sb, cb;
+      sincos(beta, &sb, &cb);
+      sv[k][0] = x[2];
+      sv[k][1] = x[3];
+      const Kin4Eval e1 = kin4<false>(x[2], x[3], T, beta, sb, cb);
+      const Kin4Eval e2 = kin4<false>(fma(0.5 * dt, e1.k2, x[2]), fma(0.5 * dt, e1.k3, x[3]), T, beta, sb, cb);
+      const Kin4Eval e3 = kin4<false>(fma(0.5 * dt, e2.k2, x[2]), fma(0.5 * dt, e2.k3, x[3]), T, beta, sb, cb);
+      const Kin4Eval e4 = kin4<false>(fma(dt, e3.k2, x[2]), fma(dt, e3.k3, x[3]), T, beta, sb, cb);
+      const double h6 = dt * (1.0 / 6.0);
+      x[0] = fma(h6, e1.k0 + 2.0 * e2.k0 + 2.0 * e3.k0 + e4.k0, x[0]);
+      x[1] = fma(h6, e1.k1 + 2.0 * e2.k1 + 2.0 * e3.k1 + e4.k1, x[1]);
+      x[2] = fma(h6, e1.k2 + 2.0 * e2.k2 + 2.0 * e3.k2 + e4.k2, x[2]);
+      x[3] = fma(h6, e1.k3 + 2.0 * e2.k3 + 2.0 * e3.k3 + e4.k3, x[3]);
+      J += w.r[0] * T * T + w.r[1] * delta * delta;
+      J += track_term(x, rp[k + 1], (k + 1 == NF) ? w.qf : w.q, sg[k]);
+      if (xo) xo[k + 1] = make_double4(x[0], x[1], x[2], x[3]);
+    }
+  }
+  cost[i] = J;
+
+  // backward: a = d J / d x_{k+1}
+  double4* gp = reinterpret_cast<double4*>(grad + i * (NF * 2));
+  double a[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 1
+  for (int kk = NF - 2; kk >= 0; kk -= 2) {
+    const double4 u2 = up[kk >> 1];
+    double4 g2;
+DPC_PRAGMA(unroll DPC_UNROLL_H)
+    for (int h = 1; h >= 0; h--) {
+      const int k = kk + h;
+      const double T = h ? u2.z : u2.x, delta = h ? u2.w : u2.y;
+      const double beta = 0.5 * delta;
+      double sb, cb;
+      sincos(beta, &sb, &cb);
+#pragma unroll
+      for (int c = 0; c < 4; c++) a[c] += sg[k][c];
+      const double phi = sv[k][0], v = sv[k][1];
+      const Kin4Eval e1 = kin4<true>(phi, v, T, beta, sb, cb);
+      const double p2 = fma(0.5 * dt, e1.k2, phi), v2 = fma(0.5 * dt, e1.k3, v);
+      const Kin4Eval e2 = kin4<true>(p2, v2, T, beta, sb, cb);
+      const double p3 = fma(0.5 * dt, e2.k2, phi), v3 = fma(0.5 * dt, e2.k3, v);
+      const Kin4Eval e3 = kin4<true>(p3, v3, T, beta, sb, cb);
+      const double p4 = fma(dt, e3.k2, phi), v4 = fma(dt, e3.k3, v);
+      const Kin4Eval e4 = kin4<true>(p4, v4, T, beta, sb, cb);
+      // adjoint of one stage evaluation: kb = d J / d k (4), returns the (phi, v) part of J_x' kb and adds J_u' kb
+      double gT = 0.0, gd = 0.0;
+      auto vjp = [&](const Kin4Eval& e, double vs, double kb0, double kb1, double kb2, double kb3, double& xphi,
+                     double& xv) {
+        const double wv = kb1 * e.c - kb0 * e.s;
+        const double fr = kb3 * e.dres * DPC_INV_M;
+        xphi = vs * wv;
+        xv = kb0 * e.c + kb1 * e.s + kb2 * sb * DPC_INV_LR - fr * cb;
+        gT += kb3 * (DPC_CM0 * DPC_INV_M);
+        gd += 0.5 * vs * (wv + kb2 * cb * DPC_INV_LR + fr * sb);
+      };
+      const double h6 = dt * (1.0 / 6.0), h3 = dt * (1.0 / 3.0);
+      double xp4, xv4, xp3, xv3, xp2, xv2, xp1, xv1;
+      vjp(e4, v4, h6 * a[0], h6 * a[1], h6 * a[2], h6 * a[3], xp4, xv4);
+      vjp(e3, v3, h3 * a[0], h3 * a[1], fma(dt, xp4, h3 * a[2]), fma(dt, xv4, h3 * a[3]), xp3, xv3);
+      vjp(e2, v2, h3 * a[0], h3 * a[1], fma(0.5 * dt, xp3, h3 * a[2]), fma(0.5 * dt, xv3, h3 * a[3]), xp2, xv2);
+      vjp(e1, v, h6 * a[0], h6 * a[1], fma(0.5 * dt, xp2, h6 * a[2]), fma(0.5 * dt, xv2, h6 * a[3]), xp1, xv1);
+      a[2] += xp1 + xp2 + xp3 + xp4;
+      a[3] += xv1 + xv2 + xv3 + xv4;
+      gT = fma(2.0 * w.r[0], T, gT);
+      gd = fma(2.0 * w.r[1], delta, gd);
+      if (h) { g2.z = gT; g2.w = gd; } else { g2.x = gT; g2.y = gd; }
+    }
+    gp[kk >> 1] = g2;
+  }
+}
+}  // namespace
+
+cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
+                                    const double* u, const double* ref, double* cost, double* grad, double* xtraj,
+                                    cudaStream_t stream) {
+  DpcWeights w;
+  for (int c = 0; c < 4; c++) { w.q[c] = weights[c]; w.qf[c] = weights[6 + c]; }
+  w.r[0] = weights[4];
+  w.r[1] = weights[5];
+  w.dt = dt;
+  const unsigned grid = (unsigned)((B + 127) / 128);
+  if (Nf == 40) dpc_rollout_grad_kernel<40><<<grid, 128, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
+  else if (Nf == 80) dpc_rollout_grad_kernel<80><<<grid, 128, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
+  else return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
+}  // namespace ihm2b

@@ -168,6 +168,19 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x_dev,
                           const double* lap_length_host, double* xlog_dev, double* ulog_dev,
                           int32_t* done_dev, int32_t* fail_dev, void* stream);
 
+/* ---- DPC rollout ---------------------------------------------------------
+ * the differentiable-predictive-control loss of dpc/main.py: kin4 model (:56-84), one RK4 step of dt per
+ * stage (:87-97), IHM1.5 tracking cost (:374-409; stage 0 has no tracking term, the last stage uses the _f
+ * weights), and its gradient in the controls -- what a policy trained through the rollout receives (the
+ * reference leaves the policy itself empty, dpc/main.py:617-635).  No handle: the model constants are those of
+ * dpc/main.py:23-29.  Device buffers: x0_dev [B][4] = (X, Y, phi, v), u_dev [B][Nf][2] = (T, delta),
+ * ref_dev [B][Nf+1][4] = (X_ref, Y_ref, phi_ref, v_ref) -> cost_dev [B], grad_dev [B][Nf][2],
+ * xtraj_dev [B][Nf+1][4] (optional, may be NULL).  weights_host [10] = (q_lon, q_lat, q_phi, q_v, r_T, r_delta,
+ * q_lon_f, q_lat_f, q_phi_f, q_v_f).  Nf must be 40 (dpc/main.py:31) or 80. */
+int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const double* x0_dev, const double* u_dev,
+                               const double* ref_dev, const double* weights_host, double* cost_dev,
+                               double* grad_dev, double* xtraj_dev, void* stream);
+
 /* number of kernel launches issued by this handle since creation (bench bookkeeping) */
 int64_t ihm2b_launch_count(const ihm2b_handle* h);
 

@@ -28,6 +28,8 @@
 //   fdyn6 plant ....................... python/models.py:455-606
 //   sim options / switch / lap ........ python/main.py:395-400, 475-517, 561-570
 //   nonlinear h(x,u) + slacks ......... old/generate_acaods_interface.py:190-212, 351-449
+//   DPC: kin4 ODE, RK4 step ........... dpc/main.py:56-97, constants dpc/main.py:23-37
+//   DPC: IHM1.5 tracking cost ......... dpc/main.py:374-409, doc/dpc.typ:44-56
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -951,6 +953,98 @@ void shift_iterate(int N, double* x, double* u) {  // controller.py:388-393 (lit
 // C ABI (host memory, batch-major rows).  Mirrors include/ihm2b.h so one Python harness can
 // drive both sides of a parity test.
 // =======================================================================================
+
+// ---- DPC rollout ---------------------------------------------------------------
+// kin4 model x = (X, Y, phi, v), u = (T, delta) of dpc/main.py:56-84, one RK4 step of dt = 1/20
+// (dpc/main.py:87-97), cost of dpc/main.py:374-409 (tracking terms on stages 1..Nf-1, control terms on
+// stages 0..Nf-1, terminal terms with the _f weights).  The gradient with respect to the controls is what a
+// control policy trained through the rollout receives.  Dense and generic on purpose: full 4x4 / 4x2
+// Jacobians and transposed products.
+namespace dpc {
+constexpr int DX = 4, DU = 2;
+constexpr double M = 230.0, WHEELBASE = 1.5706, CM0 = 4.950, CR0 = 297.030, CR1 = 16.665, CR2 = 0.6784;  // :23-29
+
+static void f_kin4(const double* x, const double* u, double* f, double* Jx, double* Ju) {
+  const double phi = x[2], v = x[3], T = u[0], delta = u[1];
+  const double beta = 0.5 * delta, lR = 0.5 * WHEELBASE;
+  const double vx = v * std::cos(beta);
+  const double th = std::tanh(10.0 * vx);
+  const double poly = CR0 + CR1 * vx + CR2 * vx * vx;
+  f[0] = v * std::cos(phi + beta);
+  f[1] = v * std::sin(phi + beta);
+  f[2] = v * std::sin(beta) / lR;
+  f[3] = (CM0 * T - poly * th) / M;
+  if (!Jx) return;
+  std::fill(Jx, Jx + DX * DX, 0.0);
+  std::fill(Ju, Ju + DX * DU, 0.0);
+  const double dres = (CR1 + 2.0 * CR2 * vx) * th + poly * 10.0 * (1.0 - th * th);  // d(poly tanh)/d vx
+  const double dvx_dv = std::cos(beta), dvx_dd = -0.5 * v * std::sin(beta);
+  Jx[0 * DX + 2] = -v * std::sin(phi + beta);  Jx[0 * DX + 3] = std::cos(phi + beta);
+  Jx[1 * DX + 2] = v * std::cos(phi + beta);   Jx[1 * DX + 3] = std::sin(phi + beta);
+  Jx[2 * DX + 3] = std::sin(beta) / lR;
+  Jx[3 * DX + 3] = -dres * dvx_dv / M;
+  Ju[0 * DU + 1] = -0.5 * v * std::sin(phi + beta);
+  Ju[1 * DU + 1] = 0.5 * v * std::cos(phi + beta);
+  Ju[2 * DU + 1] = 0.5 * v * std::cos(beta) / lR;
+  Ju[3 * DU + 0] = CM0 / M;
+  Ju[3 * DU + 1] = -dres * dvx_dd / M;
+}
+
+// one RK4 step; with Sx/Su also d x+/d x [4x4] and d x+/d u [4x2] by the chain rule through the stages
+static void rk4_kin4(const double* x, const double* u, double dt, double* xn, double* Sx, double* Su) {
+  const double cw[4] = {0.0, 0.5, 0.5, 1.0}, bw[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+  double k[4][DX], dkx[4][DX * DX], dku[4][DX * DU];
+  for (int s = 0; s < 4; s++) {
+    double xs[DX], Jx[DX * DX], Ju[DX * DU];
+    for (int a = 0; a < DX; a++) xs[a] = x[a] + (s ? cw[s] * dt * k[s - 1][a] : 0.0);
+    f_kin4(xs, u, k[s], Sx ? Jx : nullptr, Ju);
+    if (!Sx) continue;
+    // d xs / d x = I + c dt dk_{s-1}/dx ; d xs / d u = c dt dk_{s-1}/du
+    for (int a = 0; a < DX; a++) {
+      for (int b = 0; b < DX; b++) {
+        double acc = 0.0;
+        for (int c = 0; c < DX; c++)
+          acc += Jx[a * DX + c] * ((c == b ? 1.0 : 0.0) + (s ? cw[s] * dt * dkx[s - 1][c * DX + b] : 0.0));
+        dkx[s][a * DX + b] = acc;
+      }
+      for (int b = 0; b < DU; b++) {
+        double acc = Ju[a * DU + b];
+        for (int c = 0; c < DX; c++) acc += Jx[a * DX + c] * (s ? cw[s] * dt * dku[s - 1][c * DU + b] : 0.0);
+        dku[s][a * DU + b] = acc;
+      }
+    }
+  }
+  for (int a = 0; a < DX; a++) {
+    xn[a] = x[a];
+    for (int s = 0; s < 4; s++) xn[a] += dt * bw[s] * k[s][a];
+  }
+  if (!Sx) return;
+  for (int a = 0; a < DX; a++) {
+    for (int b = 0; b < DX; b++) {
+      Sx[a * DX + b] = (a == b) ? 1.0 : 0.0;
+      for (int s = 0; s < 4; s++) Sx[a * DX + b] += dt * bw[s] * dkx[s][a * DX + b];
+    }
+    for (int b = 0; b < DU; b++) {
+      Su[a * DU + b] = 0.0;
+      for (int s = 0; s < 4; s++) Su[a * DU + b] += dt * bw[s] * dku[s][a * DU + b];
+    }
+  }
+}
+
+// tracking term q_lon e_lon^2 + q_lat e_lat^2 + q_phi (phi - phi_ref)^2 + q_v (v - v_ref)^2 and its x-gradient
+static double track_cost(const double* x, const double* r, const double* q, double* g) {
+  const double cp = std::cos(r[2]), sp = std::sin(r[2]);
+  const double elon = cp * (x[0] - r[0]) + sp * (x[1] - r[1]);
+  const double elat = -sp * (x[0] - r[0]) + cp * (x[1] - r[1]);
+  const double ephi = x[2] - r[2], ev = x[3] - r[3];
+  g[0] = 2.0 * q[0] * elon * cp - 2.0 * q[1] * elat * sp;
+  g[1] = 2.0 * q[0] * elon * sp + 2.0 * q[1] * elat * cp;
+  g[2] = 2.0 * q[2] * ephi;
+  g[3] = 2.0 * q[3] * ev;
+  return q[0] * elon * elon + q[1] * elat * elat + q[2] * ephi * ephi + q[3] * ev * ev;
+}
+}  // namespace dpc
+
 extern "C" {
 
 int ihm2o_np(void) { return NP; }
@@ -1131,6 +1225,49 @@ int ihm2o_closed_loop(const ihm2b_config* cf, const double* s_ref, const double*
       if (ulog) { ulog[((size_t)st * B + i) * NU] = uu[0]; ulog[((size_t)st * B + i) * NU + 1] = uu[1]; }
       if (xlog) std::memcpy(xlog + ((size_t)(st + 1) * B + i) * NX, xc, NX * sizeof(double));
     }
+  }
+  return 0;
+}
+
+// x0 [B][4], u [B][Nf][2], ref [B][Nf+1][4] = (X_ref, Y_ref, phi_ref, v_ref), w[10] = (q_lon, q_lat, q_phi, q_v,
+// r_T, r_delta, q_lon_f, q_lat_f, q_phi_f, q_v_f) -> cost [B], grad [B][Nf][2] = d cost / d u, xtraj [B][Nf+1][4]
+int ihm2o_dpc_rollout_grad(int B, int Nf, double dt, const double* x0, const double* u, const double* ref,
+                           const double* w, double* cost, double* grad, double* xtraj) {
+  using namespace dpc;
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < B; i++) {
+    std::vector<double> xs((size_t)(Nf + 1) * DX), Sx((size_t)Nf * DX * DX), Su((size_t)Nf * DX * DU);
+    const double* ui = u + (size_t)i * Nf * DU;
+    const double* ri = ref + (size_t)i * (Nf + 1) * DX;
+    std::memcpy(xs.data(), x0 + (size_t)i * DX, DX * sizeof(double));
+    double J = 0.0;
+    for (int k = 0; k < Nf; k++) {
+      rk4_kin4(&xs[(size_t)k * DX], ui + k * DU, dt, &xs[(size_t)(k + 1) * DX], &Sx[(size_t)k * DX * DX],
+               &Su[(size_t)k * DX * DU]);
+      J += w[4] * ui[k * DU] * ui[k * DU] + w[5] * ui[k * DU + 1] * ui[k * DU + 1];
+    }
+    double a[DX], g[DX];
+    J += track_cost(&xs[(size_t)Nf * DX], ri + Nf * DX, w + 6, a);
+    for (int k = Nf - 1; k >= 0; k--) {
+      double* gk = grad + ((size_t)i * Nf + k) * DU;
+      for (int b = 0; b < DU; b++) {
+        double acc = 2.0 * w[4 + b] * ui[k * DU + b];
+        for (int c = 0; c < DX; c++) acc += Su[((size_t)k * DX + c) * DU + b] * a[c];
+        gk[b] = acc;
+      }
+      double an[DX];
+      for (int b = 0; b < DX; b++) {
+        an[b] = 0.0;
+        for (int c = 0; c < DX; c++) an[b] += Sx[((size_t)k * DX + c) * DX + b] * a[c];
+      }
+      if (k > 0) {
+        J += track_cost(&xs[(size_t)k * DX], ri + k * DX, w, g);
+        for (int b = 0; b < DX; b++) an[b] += g[b];
+      }
+      std::memcpy(a, an, sizeof an);
+    }
+    cost[i] = J;
+    if (xtraj) std::memcpy(xtraj + (size_t)i * (Nf + 1) * DX, xs.data(), xs.size() * sizeof(double));
   }
   return 0;
 }

@@ -140,3 +140,18 @@ def initial_iterate(cfg, batch=None):
     x[:, :, 0] = -6.0 + np.arange(N + 1) * cfg.dt
     u[:, :, 0] = cfg.T_max
     return x, u
+
+
+def dpc_rollout_grad(x0, u, ref, weights, dt=1.0 / 20):
+    """DPC rollout (dpc/main.py:56-97) + IHM1.5 cost (dpc/main.py:374-409) and its gradient in the controls.
+
+    x0 [B,4], u [B,Nf,2], ref [B,Nf+1,4], weights [10] -> cost [B], grad [B,Nf,2], xtraj [B,Nf+1,4]."""
+    lib = C.CDLL(build_oracle())
+    x0, u, ref, weights = _f(x0), _f(u), _f(ref), _f(weights)
+    B, Nf = u.shape[0], u.shape[1]
+    assert x0.shape == (B, 4) and ref.shape == (B, Nf + 1, 4) and weights.shape == (10,)
+    cost, grad, xtraj = np.zeros(B), np.zeros((B, Nf, 2)), np.zeros((B, Nf + 1, 4))
+    rc = lib.ihm2o_dpc_rollout_grad(C.c_int(B), C.c_int(Nf), C.c_double(dt), _p(x0), _p(u), _p(ref), _p(weights),
+                                    _p(cost), _p(grad), _p(xtraj))
+    assert rc == 0
+    return cost, grad, xtraj
