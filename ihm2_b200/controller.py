@@ -171,7 +171,7 @@ class IHM2Controller(Controller):
                  q_delta_f: float = 100.0, q_T_dot: float = 0.0, q_delta_dot: float = 500.0, *, batch: int = 1,
                  car_params: CarParams | None = None, params=None, track_index=None, lap_length=None,
                  integrator: str = "IRK", sim_model: int = _abi.SIM_KIN6_DYN6, nlp_solver_type: str = "SQP_RTI",
-                 nlp_solver_max_iter: int = 2) -> None:
+                 nlp_solver_max_iter: int = 2, globalization: str = "MERIT_BACKTRACKING") -> None:
         super().__init__(car_params)
         self.Nf, self.dt, self.s_target = Nf, dt, s_target
         self.config = Controller.Config(horizon_size=Nf, sampling_time=dt)
@@ -185,11 +185,13 @@ class IHM2Controller(Controller):
                                T_dot_max=T_dot_max, delta_dot_max=delta_dot_max, a_lat_max=a_lat_max, W=W, W_e=W_e,
                                integrator=_abi.IRK_GL4 if integrator.upper().startswith("IRK") else _abi.ERK4,
                                sim_model=sim_model,
-                               # controller.py:301-302 hard-codes "SQP" with 2 iterations and MERIT_BACKTRACKING; the
-                               # default here is the RTI step BASELINE.json's metric is quoted on.  "SQP" runs the full-step
-                               # loop with the KKT test (the merit line search is not implemented).
+                               # controller.py:301-302, 308 hard-codes "SQP" with 2 iterations and MERIT_BACKTRACKING; the
+                               # default here is the RTI step BASELINE.json's metric is quoted on.  "SQP" runs the loop
+                               # with the KKT test and, as in the reference, the merit-function line search.
                                nlp_solver=_abi.SQP if nlp_solver_type.upper() == "SQP" else _abi.SQP_RTI,
-                               nlp_max_iter=nlp_solver_max_iter, globalization=_abi.FIXED_STEP)
+                               nlp_max_iter=nlp_solver_max_iter,
+                               globalization=_abi.MERIT_BACKTRACKING if globalization.upper() == "MERIT_BACKTRACKING"
+                               else _abi.FIXED_STEP)
         if params is None:
             params = np.tile(self.car_params.to_vector(), (batch, 1))
         self.solver = Engine(cfg, s_ref, kappa_ref, track_index=track_index, params=params, lap_length=lap_length)

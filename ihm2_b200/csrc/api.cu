@@ -24,6 +24,10 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
                                     const double* u, const double* ref, double* cost, double* grad, double* xtraj,
                                     cudaStream_t stream);
+void launch_merit_base(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int first,
+                       cudaStream_t stream);
+void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int32_t* sqp_active,
+                        int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
@@ -61,6 +65,7 @@ struct ihm2b_handle {
   int32_t* active_dev;   // SQP mode: instances still iterating
   int32_t* order_dev;    // launch order of the QP kernel (longest first by the previous solve's iteration counts)
   bool have_order;
+  LineSearch ls;         // allocated when globalization = MERIT_BACKTRACKING
   double *x0_pin, *u0_pin;
   int32_t* status_pin;
   bool have_tracks, have_params;
@@ -196,6 +201,17 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->status_dev, B);
   ALLOC(h->active_dev, B);
   ALLOC(h->order_dev, B);
+  memset(&h->ls, 0, sizeof h->ls);
+  if (cfg->nlp_solver == IHM2B_SQP && cfg->globalization == IHM2B_MERIT_BACKTRACKING) {
+    ALLOC(h->ls.base_x, B * (N + 1) * 8);
+    ALLOC(h->ls.base_u, B * N * 2);
+    ALLOC(h->ls.step_x, B * (N + 1) * 8);
+    ALLOC(h->ls.step_u, B * N * 2);
+    ALLOC(h->ls.wgt, B * (N + 1) * 24);
+    ALLOC(h->ls.m0, B);
+    ALLOC(h->ls.alpha, B);
+    ALLOC(h->ls.mask, B);
+  }
 #undef ALLOC
   w.active = nullptr; w.sqp_it = -1; w.order = nullptr;
   h->have_order = false;
@@ -349,10 +365,13 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
     // repeat { linearise; KKT residual test with the multipliers of the last QP; QP; full step }.
     // Instances that converged (status 0) or whose QP failed (status 1 / 4) drop out through
     // the `active` mask; the others end with status 2 (ACADOS_MAXITER), which the reference
-    // tolerates (mpc_control_node.cpp:190-197).  Step length: fixed 1.0.
-    if (h->cfg.globalization != IHM2B_FIXED_STEP)
-      return fail(IHM2B_EINVAL, "globalization %d: the merit-function line search is not implemented, use IHM2B_FIXED_STEP",
-                  h->cfg.globalization);
+    // tolerates (mpc_control_node.cpp:190-197).  Step length: fixed 1.0, or (controller.py:308) backtracking on the
+    // L1 merit function: the trial iterate is linearised, its merit compared with the base iterate's, and the
+    // instances still searching shorten their step; the linearisation of the accepted trial point is the one
+    // the next SQP iteration starts from.
+    const bool line_search = h->cfg.globalization == IHM2B_MERIT_BACKTRACKING;
+    if (h->cfg.globalization != IHM2B_FIXED_STEP && !line_search)
+      return fail(IHM2B_EINVAL, "unknown globalization %d", h->cfg.globalization);
     if (h->cfg.nlp_max_iter < 1) return fail(IHM2B_EINVAL, "nlp_max_iter %d < 1", h->cfg.nlp_max_iter);
     fill_i32_kernel<<<(h->cfg.batch + 255) / 256, 256, 0, s>>>(h->cfg.batch, h->active_dev, 1);
     fill_i32_kernel<<<(h->cfg.batch + 255) / 256, 256, 0, s>>>(h->cfg.batch, h->w.status, IHM2B_MAXITER);
@@ -363,12 +382,29 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
     w.order = nullptr;
     for (int it = 0; it < h->cfg.nlp_max_iter; it++) {
       w.sqp_it = it;
-      launch_linearize(h->k, w, s);
+      if (!(line_search && it > 0)) { launch_linearize(h->k, w, s); h->launches++; }
       launch_nlp_residual(h->k, w, x0, h->cfg.nlp_tol, it > 0, status, s);
+      if (line_search) {
+        const size_t B = h->cfg.batch, N = h->cfg.N;
+        CU(cudaMemcpyAsync(h->ls.base_x, w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        CU(cudaMemcpyAsync(h->ls.base_u, w.u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+      }
       if (launch_qp_rti(h->k, w, x0, u0, status, s) != 0)
         return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
                     qp_smem_bytes(h->cfg.N), h->cfg.N);
-      h->launches += 3;
+      h->launches += 2;
+      if (line_search) {
+        launch_merit_base(h->k, w, h->ls, x0, it == 0, s);
+        h->launches++;
+        Work wt = w;
+        wt.active = h->ls.mask;
+        // alpha = 1, 0.7, ..., 0.7^8 = 0.058, then alpha_min = 0.05: ten trial points at most
+        for (int j = 0; j < 10; j++) {
+          launch_linearize(h->k, wt, s);
+          launch_merit_trial(h->k, w, h->ls, x0, h->active_dev, status, s);
+          h->launches += 2;
+        }
+      }
       if (h->cfg.schedule_by_history && it + 1 < h->cfg.nlp_max_iter) {
         // the QP of the next SQP iteration needs about as many IPM iterations as this one: longest first
         launch_build_order(h->cfg.batch, h->w.stats, 7, h->order_dev, s);

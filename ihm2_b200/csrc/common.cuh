@@ -65,4 +65,17 @@ struct Work {
   const int32_t* order;
 };
 
+// SQP merit-function line search (globalization = MERIT_BACKTRACKING): per-instance state
+struct LineSearch {
+  double* base_x;   // [B][N+1][8]  iterate the step starts from
+  double* base_u;   // [B][N][2]
+  double* step_x;   // [B][N+1][8]  full QP step
+  double* step_u;   // [B][N][2]
+  double* wgt;      // [B][N+1][24] merit weights per stage: 8 equality (k = 0: x0 embedding, k > 0: dynamics of
+                    //              interval k-1), 8 lower-side and 8 upper-side inequality rows
+  double* m0;       // [B] merit at the base iterate
+  double* alpha;    // [B] current trial step length
+  int32_t* mask;    // [B] 1 while the instance is still searching
+};
+
 }  // namespace ihm2b

@@ -845,6 +845,145 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 }
 
 // ---------------------------------------------------------------------------------------
+// SQP mode, globalization = MERIT_BACKTRACKING (new_python/controller.py:308; acados line search restated in
+// SURVEY App. C): L1 merit = cost + sum w_eq |equality defect| + sum w_lo max(0, lb - v) + w_up max(0, v - ub),
+// weights from the multipliers of the QP just solved (|mult| at the first SQP iteration, then
+// max(|mult|, (w + |mult|) / 2)); alpha <- 0.7 alpha until the merit decreases, not below 0.05.
+// One warp per problem, lane (a, q) = state / row a of the stages q, q+4, ...
+// ---------------------------------------------------------------------------------------
+constexpr double LS_ALPHA_MIN = 0.05, LS_REDUCTION = 0.7;
+
+__device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const int a, const int q, const double s0,
+                                             const double x0a, const double* __restrict__ pX,
+                                             const double* __restrict__ pU, const double* __restrict__ phi,
+                                             const double* __restrict__ pW) {
+  const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
+  const double hxN = cf.ct * cf.We[a];
+  const double hu = cf.cs * (a == 0 ? cf.W[8] + cf.W[10] : cf.W[9] + cf.W[11]);
+  const double cxu = (a == 6) ? cf.cs * cf.W[10] : (a == 7) ? cf.cs * cf.W[11] : 0.0;
+  const double gs_scale = -cf.cs * cf.W[0], gsN = -cf.ct * cf.We[0] * (s0 + cf.s_target);
+  const RowDef Rp = row_path(cf, a), Rt = row_term(cf, a);
+  double m = 0.0;
+  for (int k = q; k <= N; k += 4) {
+    const bool term = (k == N);
+    const double xa_ = pX[k * 8 + a];
+    // cost z'(H z / 2 + g) of this stage, the part that belongs to state a (and control a for a < 2)
+    if (!term) {
+      const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
+      m += xa_ * (0.5 * hx * xa_ + gx);
+      if (a >= 6) m -= cxu * pU[k * 2 + (a - 6)] * xa_;
+      if (a < 2) { const double ua_ = pU[k * 2 + a]; m += 0.5 * hu * ua_ * ua_; }
+    } else {
+      m += xa_ * (0.5 * hxN * xa_ + ((a == 0) ? gsN : 0.0));
+    }
+    // equality defects: x0 embedding at k = 0, dynamics of interval k - 1 otherwise
+    const double defect = (k == 0) ? xa_ - x0a : phi[(k - 1) * 8 + a] - xa_;
+    m += pW[k * 24 + a] * fabs(defect);
+    // inequality row a of this stage
+    const RowDef& R = term ? Rt : Rp;
+    const bool act = term ? (a < 4) : (a < 4 || k > 0);
+    if (act) {
+      const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
+      m += pW[k * 24 + 8 + a] * fmax(0.0, R.lb - v) + pW[k * 24 + 16 + a] * fmax(0.0, v - R.ub);
+    }
+  }
+  return m;
+}
+
+// after the QP: weights, merit at the base iterate (w.phi still holds the base linearisation), the full step
+__global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Work w, const LineSearch ls,
+                                                        const double* __restrict__ x0, const int first) {
+  const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
+  if (!w.active[b]) {   // converged before this QP, or the QP failed
+    if (lane == 0) ls.mask[b] = 0;
+    return;
+  }
+  const int N = cf.N, N1 = N + 1;
+  const double* pPI = w.xa + (size_t)b * N1 * 8;
+  const double* pLL = w.LT + (size_t)b * N1 * 32;
+  const double* pLU = pLL + N1 * 8;
+  double* pW = ls.wgt + (size_t)b * N1 * 24;
+  for (int k = q; k <= N; k += 4) {
+    const bool term = (k == N);
+    const bool act = term ? (a < 4) : (a < 4 || k > 0);
+    double pe = pPI[k * 8 + a];
+    if (k == 0) {
+      // multiplier of the embedding x_0 = x0 (the QP eliminates x_0 and never forms it): stationarity in x_0 at
+      // the QP solution, pi_0 = (H z + g)_x + A_0' pi_1 - C_x'(lamL - lamU); only the two rate rows touch x_0
+      const double* qX = w.x + (size_t)b * N1 * 8;
+      const double* qU = w.u + (size_t)b * N * 2;
+      const double* gBA = w.BA + (size_t)b * N * 80;
+      const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
+      pe = hx * qX[a] + ((a == 0) ? -cf.cs * cf.W[0] * x0[(size_t)b * 8] : 0.0);
+      if (a >= 6) pe -= cf.cs * cf.W[4 + a] * qU[a - 6] - (pLL[a - 4] - pLU[a - 4]);
+      for (int r = 0; r < 8; r++) pe = fma(gBA[r * 10 + 2 + a], pPI[8 + r], pe);
+    }
+    const double m[3] = {fabs(pe), act ? fabs(pLL[k * 8 + a]) : 0.0, act ? fabs(pLU[k * 8 + a]) : 0.0};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      double* wp = pW + k * 24 + j * 8 + a;
+      *wp = first ? m[j] : fmax(m[j], 0.5 * (*wp + m[j]));
+    }
+  }
+  __syncwarp();
+  const double* bx = ls.base_x + (size_t)b * N1 * 8;
+  const double* bu = ls.base_u + (size_t)b * N * 2;
+  const double m0 = wsum(merit_lane(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], bx, bu,
+                                    w.phi + (size_t)b * N * 8, pW));
+  const double* pX = w.x + (size_t)b * N1 * 8;
+  const double* pU = w.u + (size_t)b * N * 2;
+  double* sx = ls.step_x + (size_t)b * N1 * 8;
+  double* su = ls.step_u + (size_t)b * N * 2;
+  for (int i = lane; i < N1 * 8; i += 32) sx[i] = pX[i] - bx[i];
+  for (int i = lane; i < N * 2; i += 32) su[i] = pU[i] - bu[i];
+  if (lane == 0) { ls.m0[b] = m0; ls.alpha[b] = 1.0; ls.mask[b] = 1; }
+}
+
+// after the linearisation at the trial iterate: accept, or shorten the step and write the next trial iterate
+__global__ void __launch_bounds__(32) merit_trial_kernel(const KCfg cf, const Work w, const LineSearch ls,
+                                                         const double* __restrict__ x0, int32_t* __restrict__ sqp_active,
+                                                         int32_t* __restrict__ status_out) {
+  const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
+  if (!ls.mask[b]) return;
+  const int N = cf.N, N1 = N + 1;
+  double* pX = w.x + (size_t)b * N1 * 8;
+  double* pU = w.u + (size_t)b * N * 2;
+  const double m1 = wsum(merit_lane(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], pX, pU,
+                                    w.phi + (size_t)b * N * 8, ls.wgt + (size_t)b * N1 * 24));
+  const double alpha = ls.alpha[b];
+  __syncwarp();
+  if (m1 < ls.m0[b] || alpha <= LS_ALPHA_MIN) {
+    if (lane == 0) {
+      ls.mask[b] = 0;
+      w.stats[(size_t)b * 8 + 2] = alpha;   // statistics slot [2] carries the accepted step length in this mode
+      if (!(m1 == m1)) {                    // the integrator failed at the shortest step
+        w.status[b] = IHM2B_FAILURE;
+        if (status_out) status_out[b] = IHM2B_FAILURE;
+        sqp_active[b] = 0;
+      }
+    }
+    return;
+  }
+  const double an = fmax(LS_REDUCTION * alpha, LS_ALPHA_MIN);
+  const double* bx = ls.base_x + (size_t)b * N1 * 8;
+  const double* bu = ls.base_u + (size_t)b * N * 2;
+  const double* sx = ls.step_x + (size_t)b * N1 * 8;
+  const double* su = ls.step_u + (size_t)b * N * 2;
+  for (int i = lane; i < N1 * 8; i += 32) pX[i] = fma(an, sx[i], bx[i]);
+  for (int i = lane; i < N * 2; i += 32) pU[i] = fma(an, su[i], bu[i]);
+  if (lane == 0) ls.alpha[b] = an;
+}
+
+void launch_merit_base(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int first,
+                       cudaStream_t stream) {
+  merit_base_kernel<<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, first);
+}
+void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int32_t* sqp_active,
+                        int32_t* status, cudaStream_t stream) {
+  merit_trial_kernel<<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, sqp_active, status);
+}
+
+// ---------------------------------------------------------------------------------------
 // Launch order for the next solve of this handle: problems sorted by decreasing IPM iteration count of
 // the solve just finished (counting sort, counts 0..63).  A solve is a serial chain whose length is its
 // iteration count (13 .. 50 here), and a batch is only 2-3 waves of resident warps: with the long problems

@@ -132,8 +132,11 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream);
  * of the last QP, QP, full step }; instances drop out as they converge (status 0) or their QP
  * fails (1 / 4), the rest end with status 2 (ACADOS_MAXITER, tolerated by the reference,
  * mpc_control_node.cpp:190-197).  stats: [qp iterations (sum), sqp iterations, mu, res_stat,
- * res_eq, res_ineq, res_comp, IPM iterations of the last QP].  globalization must be IHM2B_FIXED_STEP in this build
- * (IHM2B_EINVAL otherwise: the merit-function line search is not implemented). */
+ * res_eq, res_ineq, res_comp, IPM iterations of the last QP].
+ * globalization = IHM2B_MERIT_BACKTRACKING (controller.py:308): each step is scaled by alpha = 1, 0.7, 0.49, ...
+ * (not below 0.05) until the L1 merit function (cost + multiplier-weighted equality defects and inequality
+ * violations) of the trial iterate is below that of the current one; multipliers take the full step; stats[2]
+ * then carries the accepted alpha of the last iteration instead of mu. */
 int ihm2b_solve_dev(ihm2b_handle* h, const double* x0_dev, double* u0_dev, int32_t* status_dev,
                     void* stream);
 /* Same call with HOST buffers: H2D of x0, shift (if do_shift), solve, D2H of u0/status,

@@ -816,6 +816,53 @@ double ocp_cost(const ihm2b_config& cf, const Qp& qp, const double* z) {
   return c;
 }
 
+// L1 merit function of the SQP line search (acados MERIT_BACKTRACKING; configured by
+// new_python/controller.py:308): cost + weighted 1-norm of the equality defects (x0 embedding, dynamics) +
+// weighted violations of the inequality rows.  Weights follow the multipliers of the last QP:
+// w = |mult| at the first SQP iteration, max(|mult|, (w + |mult|)/2) afterwards (Leineweber 1999).
+struct MeritWeights {
+  std::vector<double> eq;                    // [(N+1)*NX]: [0] = x0 embedding, [k+1] = dynamics of interval k
+  std::vector<std::vector<double>> lo, up;   // per stage, per row
+};
+
+void merit_update_weights(const Qp& qp, const QpSol& sol, bool first, MeritWeights& mw) {
+  auto upd = [first](double& w, double mult) {
+    const double m = std::fabs(mult);
+    w = first ? m : std::max(m, 0.5 * (w + m));
+  };
+  const int N = qp.N;
+  if (first) {
+    mw.eq.assign((N + 1) * NX, 0.0);
+    mw.lo.assign(N + 1, {}); mw.up.assign(N + 1, {});
+    for (int k = 0; k <= N; k++) { mw.lo[k].assign(qp.rows[k].size(), 0.0); mw.up[k].assign(qp.rows[k].size(), 0.0); }
+  }
+  for (int i = 0; i < (N + 1) * NX; i++) upd(mw.eq[i], sol.pi[i]);
+  for (int k = 0; k <= N; k++)
+    for (size_t r = 0; r < qp.rows[k].size(); r++) { upd(mw.lo[k][r], sol.lamL[k][r]); upd(mw.up[k][r], sol.lamU[k][r]); }
+}
+
+double merit_value(const ihm2b_config& cf, const Qp& qp, const MeritWeights& mw, const double* x0, const double* x,
+                   const double* u, const double* phi) {
+  const int N = cf.N;
+  std::vector<double> z((N + 1) * NZ, 0.0);
+  for (int k = 0; k <= N; k++) {
+    if (k < N) { z[k * NZ] = u[k * NU]; z[k * NZ + 1] = u[k * NU + 1]; }
+    for (int a = 0; a < NX; a++) z[k * NZ + NU + a] = x[k * NX + a];
+  }
+  double m = ocp_cost(cf, qp, z.data());
+  for (int a = 0; a < NX; a++) m += mw.eq[a] * std::fabs(x[a] - x0[a]);
+  for (int k = 0; k < N; k++)
+    for (int i = 0; i < NX; i++) m += mw.eq[(k + 1) * NX + i] * std::fabs(phi[k * NX + i] - x[(k + 1) * NX + i]);
+  for (int k = 0; k <= N; k++)
+    for (size_t r = 0; r < qp.rows[k].size(); r++) {
+      const Row& R = qp.rows[k][r];
+      double cz = 0;
+      for (int a = 0; a < NZ; a++) cz += R.c[a] * z[k * NZ + a];
+      m += mw.lo[k][r] * std::max(0.0, R.lb - cz) + mw.up[k][r] * std::max(0.0, cz - R.ub);
+    }
+  return m;
+}
+
 void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveOut& out, QpSol* keep,
                Qp* keep_qp) {
   const ihm2b_config& cf = *pb.cf;
@@ -828,9 +875,12 @@ void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveO
   std::vector<double> phi(N * NX);
   const int iters = (cf.nlp_solver == IHM2B_SQP_RTI) ? 1 : cf.nlp_max_iter;
   out = SolveOut{IHM2B_MAXITER, 0, 0, 0, 0, 0, 0, 0, 0};
-  bool have_mult = false;
+  bool have_mult = false, lin_valid = false;
+  const bool line_search = cf.nlp_solver == IHM2B_SQP && cf.globalization == IHM2B_MERIT_BACKTRACKING;
+  MeritWeights mw;
   for (int it = 0; it < iters; it++) {
-    if (!linearize(pb, x, u, qp, phi.data())) { out.status = IHM2B_FAILURE; break; }
+    // with the line search the accepted trial point has just been linearised
+    if (!lin_valid && !linearize(pb, x, u, qp, phi.data())) { out.status = IHM2B_FAILURE; break; }
     if (cf.nlp_solver == IHM2B_SQP) {
       // NLP KKT residuals at the current iterate with the last QP multipliers
       double rs = 0, re = 0, ri = 0, rc = 0;
@@ -890,6 +940,38 @@ void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveO
       if (!loose) { out.status = IHM2B_QP_FAILURE; break; }
     }
     have_mult = true;
+    if (line_search) {
+      // backtracking on the merit function: alpha <- 0.7 alpha until the merit decreases, not below alpha_min = 0.05
+      // (plain decrease: acados' sufficient-descent test is off by default); multipliers take the full step
+      const double alpha_min = 0.05, reduction = 0.7;
+      // multiplier of the embedding x_0 = x0 (ipm_solve eliminates x_0): stationarity in x_0 at the QP solution
+      for (int a = 0; a < NX; a++) {
+        double v = qp.g[NU + a];
+        for (int b = 0; b < NZ; b++) v += qp.H[(NU + a) * NZ + b] * sol.z[b];
+        for (int i = 0; i < NX; i++) v += qp.A[i * NX + a] * sol.pi[NX + i];
+        for (size_t r = 0; r < qp.rows[0].size(); r++) v -= qp.rows[0][r].c[NU + a] * (sol.lamL[0][r] - sol.lamU[0][r]);
+        sol.pi[a] = v;
+      }
+      merit_update_weights(qp, sol, it == 0, mw);
+      const double m0 = merit_value(cf, qp, mw, x0, x, u, phi.data());
+      std::vector<double> xo(x, x + (N + 1) * NX), uo(u, u + N * NU);
+      double alpha = 1.0;
+      bool ok = true;
+      for (;;) {
+        for (int k = 0; k <= N; k++) {
+          if (k < N) for (int a = 0; a < NU; a++) u[k * NU + a] = uo[k * NU + a] + alpha * (sol.z[k * NZ + a] - uo[k * NU + a]);
+          for (int a = 0; a < NX; a++) x[k * NX + a] = xo[k * NX + a] + alpha * (sol.z[k * NZ + NU + a] - xo[k * NX + a]);
+        }
+        ok = linearize(pb, x, u, qp, phi.data());
+        const double m1 = ok ? merit_value(cf, qp, mw, x0, x, u, phi.data()) : std::numeric_limits<double>::quiet_NaN();
+        if (m1 < m0 || alpha <= alpha_min) break;
+        alpha = std::max(reduction * alpha, alpha_min);
+      }
+      out.mu = alpha;  // statistics slot [2] carries the accepted step length in this mode
+      if (!ok) { out.status = IHM2B_FAILURE; break; }
+      lin_valid = true;
+      continue;
+    }
     const double alpha = 1.0;  // FIXED_STEP; (RTI always takes the full step)
     for (int k = 0; k <= N; k++) {
       if (k < N) for (int a = 0; a < NU; a++) u[k * NU + a] += alpha * (sol.z[k * NZ + a] - u[k * NU + a]);

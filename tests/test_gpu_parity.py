@@ -317,13 +317,54 @@ def test_sqp_mode_matches_oracle(torch_cuda, skidpad, fsds, Nf, B, iters):
         assert np.mean(stg[run, 1] == iters) == 1.0
 
 
-def test_sqp_rejects_unimplemented_line_search(torch_cuda, skidpad):
+@pytest.mark.parametrize("iters", [1, 2, 8])
+def test_sqp_merit_line_search_matches_oracle(torch_cuda, skidpad, fsds, iters):
+    """globalization = MERIT_BACKTRACKING (new_python/controller.py:308; 2 iterations is what :302 configures):
+    same accepted step lengths, statuses and iterates as the oracle's backtracking on the L1 merit function.
+    stats[2] holds the step length of the last iteration: the first iteration is where these inputs backtrack; by
+    the eighth most instances are converged to rounding, the merit comparison is then decided in the last bits and
+    may fall either way (with a step of ~ 0 behind it), hence the lower share there."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B = 384
+    mp, kw, (x0, x, u) = _sqp_inputs(skidpad, fsds, 40, B)
+    cfg = _abi.make_config(batch=B, n_grid=len(mp.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=iters,
+                           globalization=_abi.MERIT_BACKTRACKING, **kw)
+    eng = _engine(cfg, mp); eng.set_iterate(x, u)
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    sg = status.cpu().numpy()
+    xg, ug = [t.cpu().numpy() for t in eng.get_iterate()]
+    stg = eng.stats().cpu().numpy()
+    eng.close()
+    u0o, so, sto, xo, uo = Oracle(cfg, mp.s_ref, mp.kappa_ref).solve(x0, x, u)
+    assert np.mean(sg == so) > (0.97 if iters <= 2 else 0.95)
+    run = (sg == so) & np.isin(sg, (0, 2)) & (stg[:, 1] == sto[:, 1])
+    assert run.sum() > 0.5 * B
+    searched = run & (sg == 2)                     # the last iteration ended with a line search on both sides
+    assert np.mean(stg[searched, 2] == sto[searched, 2]) > (0.98 if iters <= 2 else 0.8)
+    if iters == 1:
+        assert (sto[searched, 2] < 1.0).sum() > 0  # and the inputs do make it backtrack
+    same = searched & (stg[:, 2] == sto[:, 2])
+    assert rel(xg[same], xo[same]) < 1e-5 and rel(ug[same], uo[same]) < 1e-5
+    # against the fixed step: the merit function of the accepted iterates is what the search is for, so just
+    # check that the two modes differ where a step was shortened
+    cfg2 = _abi.make_config(batch=B, n_grid=len(mp.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=iters,
+                            globalization=_abi.FIXED_STEP, **kw)
+    eng = _engine(cfg2, mp); eng.set_iterate(x, u)
+    eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    xf = eng.get_iterate()[0].cpu().numpy()
+    eng.close()
+    short = same & (sto[:, 2] < 1.0)
+    if short.sum():
+        assert rel(xg[short], xf[short]) > 1e-6
+
+
+def test_sqp_rejects_unknown_globalization(torch_cuda, skidpad):
     from ihm2_b200 import _abi
     from ihm2_b200.engine import Ihm2bError
-    cfg = _abi.make_config(batch=4, n_grid=len(skidpad.s_ref), nlp_solver=_abi.SQP,
-                           globalization=_abi.MERIT_BACKTRACKING)
+    cfg = _abi.make_config(batch=4, n_grid=len(skidpad.s_ref), nlp_solver=_abi.SQP, globalization=7)
     eng = _engine(cfg, skidpad)
-    with pytest.raises(Ihm2bError, match="line search"):
+    with pytest.raises(Ihm2bError, match="globalization"):
         eng.solve(torch_cuda.zeros(4, 8, dtype=torch_cuda.float64, device="cuda"))
     eng.close()
 

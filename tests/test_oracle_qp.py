@@ -140,3 +140,28 @@ def test_closed_loop_golden_and_lap_progress(built, fsds):
     assert (res["fail"] >= 30).all()
     assert (np.diff(res["xlog"][:, :, 0], axis=0) > -1e-9).all()          # s never decreases
     assert res["xlog"][30, 0, 3] > 5.0                                   # the car is up to speed
+
+
+def test_oracle_sqp_merit_backtracking_steps():
+    """SQP with MERIT_BACKTRACKING (new_python/controller.py:301-308): accepted step lengths come from
+    {0.7^j} down to the floor 0.05, the multiplier-weighted L1 merit makes some of these inputs backtrack, and a
+    converged instance (status 0) satisfies the KKT tolerances."""
+    import os
+    from ihm2_b200 import _abi
+    from ihm2_b200.track import load_packaged_track
+    from oracle.lib import Oracle
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "rti.npz"))
+    mp = load_packaged_track(str(d["track"]))
+    allowed = np.array([0.7**j for j in range(9)] + [0.05])
+    seen = []
+    for iters in (1, 2, 10):
+        cfg = _abi.make_config(batch=8, n_grid=len(mp.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=iters,
+                               globalization=_abi.MERIT_BACKTRACKING)
+        _, status, stats, x, u = Oracle(cfg, mp.s_ref, mp.kappa_ref).solve(d["x0"], d["x_in"].copy(), d["u_in"].copy())
+        assert set(np.unique(status)) <= {0, 2}
+        run = status == 2
+        assert np.all(np.abs(stats[run, 2][:, None] - allowed[None, :]).min(axis=1) < 1e-12)
+        assert np.all(stats[status == 0, 3:7] <= cfg.nlp_tol)
+        assert np.all(np.isfinite(x)) and np.all(np.isfinite(u))
+        seen += list(stats[run, 2])
+    assert min(seen) < 1.0 and max(seen) == 1.0
