@@ -39,7 +39,7 @@ class Config(C.Structure):
         ("sim_model", C.c_int32),
         ("sim_steps", C.c_int32),
         ("schedule_by_history", C.c_int32),
-        ("reserved0", C.c_int32),
+        ("qp_tolerate_maxiter", C.c_int32),
         ("dt", C.c_double),
         ("s_target", C.c_double),
         ("n_max", C.c_double),
@@ -148,6 +148,7 @@ def make_config(
     sim_steps: int = 100,
     nonlinear_constraints: bool = False,
     schedule_by_history: bool = True,
+    qp_tolerate_maxiter: bool = False,
 ) -> Config:
     """Fill ihm2b_config from `IHM2Controller.__init__` style arguments
     (new_python/controller.py:250-309; python/mpc.py:77-99 for the bounds)."""
@@ -158,6 +159,7 @@ def make_config(
     cf.globalization, cf.qp_max_iter = globalization, qp_max_iter
     cf.nonlinear_constraints = int(nonlinear_constraints)
     cf.schedule_by_history = int(schedule_by_history)
+    cf.qp_tolerate_maxiter = int(qp_tolerate_maxiter)
     cf.sim_model, cf.sim_steps = sim_model, sim_steps
     cf.dt, cf.s_target = dt, s_target
     cf.n_max, cf.v_x_max, cf.T_max, cf.delta_max = n_max, v_x_max, T_max, delta_max

@@ -127,7 +127,7 @@ __global__ void fill_i32_kernel(int n, int32_t* p, int32_t v) {
 void fill_kcfg(const ihm2b_config& c, KCfg& k) {
   memset(&k, 0, sizeof k);
   k.B = c.batch; k.N = c.N; k.n_grid = c.n_grid;
-  k.integrator = c.integrator; k.qp_max_iter = c.qp_max_iter;
+  k.integrator = c.integrator; k.qp_max_iter = c.qp_max_iter; k.qp_tolerate_maxiter = c.qp_tolerate_maxiter;
   k.dt = c.dt; k.s_target = c.s_target;
   k.n_max = c.n_max; k.v_x_max = c.v_x_max; k.T_max = c.T_max; k.delta_max = c.delta_max;
   k.g_T_max = c.g_T_max; k.g_delta_max = c.g_delta_max;

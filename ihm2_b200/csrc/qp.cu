@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
       const bool loose = res_g <= 1e-6 * (1.0 + mag_g) && res_b <= 1e-6 * (1.0 + mag_b) &&
                          res_d <= 1e-6 * (1.0 + mag_d) && res_m <= 1e-6;
-      st = loose ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
+      st = (loose || (cf.qp_tolerate_maxiter && qp_status == 1)) ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
     }
     double* sp = w.stats + (size_t)b * 8;
     if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics

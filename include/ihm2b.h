@@ -69,7 +69,10 @@ typedef struct ihm2b_config {
   int32_t schedule_by_history; /* 1 (default of the Python layer): the QP kernel launches the problems of a solve
                              longest first, by the IPM iteration counts of the handle's previous solve (in a
                              closed loop: the previous control step).  Scheduling only; results are unchanged. */
-  int32_t reserved0;
+  int32_t qp_tolerate_maxiter; /* 1: a QP whose interior point stops at qp_max_iter without reaching the tolerances is
+                             used as it is and the solve goes on / reports success, as acados' SQP / SQP_RTI do with
+                             ACADOS_MAXITER from the QP solver (a vanishing step or NaN stay QP failures);
+                             0 (default): such a QP ends the solve with status 4 unless it is converged to 1e-6 */
   double dt;              /* sampling time (controller.py:255) */
   double s_target;        /* controller.py:256 */
   double n_max, v_x_max, T_max, delta_max; /* python/mpc.py:77-89 */

@@ -937,7 +937,7 @@ void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveO
       // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
       const bool loose = sol.res_g <= 1e-6 * (1 + sol.mag_g) && sol.res_b <= 1e-6 * (1 + sol.mag_b) &&
                          sol.res_d <= 1e-6 * (1 + sol.mag_d) && sol.res_m <= 1e-6;
-      if (!loose) { out.status = IHM2B_QP_FAILURE; break; }
+      if (!loose && !(cf.qp_tolerate_maxiter && sol.status == 1)) { out.status = IHM2B_QP_FAILURE; break; }
     }
     have_mult = true;
     if (line_search) {

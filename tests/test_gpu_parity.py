@@ -123,6 +123,31 @@ def test_config2_rti_matches_oracle(config2):
     assert same_iters > 0.98
 
 
+def test_qp_tolerate_maxiter_like_acados(torch_cuda, skidpad, config2):
+    """qp_tolerate_maxiter: a QP that stops at the iteration cap is used as it is and the solve reports success, as
+    acados does with ACADOS_MAXITER from its QP solver.  Same statuses as the oracle with the same option; the
+    problems that converge anyway are untouched; the capped ones (infeasible QPs: the iterate at the cap is not a
+    solution and depends on the last bits) are only required to be finite."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B = 512
+    cfg = _abi.make_config(batch=B, n_grid=len(skidpad.s_ref), qp_tolerate_maxiter=True)
+    x0, x, u = config2["x0"][:B], config2["x_in"][:B], config2["u_in"][:B]
+    eng = _engine(cfg, skidpad); eng.set_iterate(x, u)
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    sg = status.cpu().numpy(); u0 = u0.cpu().numpy(); stg = eng.stats().cpu().numpy()
+    eng.close()
+    u0o, so, sto, xo, uo = Oracle(cfg, skidpad.s_ref, skidpad.kappa_ref).solve(x0, x, u)
+    strict = config2["status"][:B]
+    assert np.mean(sg == so) > 0.99
+    assert (sg[strict == 0] == 0).all()
+    conv = strict == 0
+    np.testing.assert_array_equal(u0[conv], config2["u0"][:B][conv])
+    capped = (strict == 4) & (sg == 0)
+    assert capped.sum() > 0.5 * (strict == 4).sum() and (stg[capped, 0] == cfg.qp_max_iter).all()
+    assert np.isfinite(u0[capped]).all()
+
+
 def test_config2_solution_properties(config2):
     """Size-independent checks at the full batch: the accepted solutions satisfy the linearised
     dynamics of their own QP, the measured state is embedded, and all bounds hold."""
