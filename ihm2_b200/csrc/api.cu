@@ -24,6 +24,9 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
                                     const double* u, const double* ref, double* cost, double* grad, double* xtraj,
                                     cudaStream_t stream);
+cudaError_t launch_project(long long B, int n_grid, const double* s_ref, const double* X_ref, const double* Y_ref,
+                           const double* phi_ref, const int32_t* track, const double* pose, const double* s_guess,
+                           double s_tol, double* frenet, double* ref, int32_t* flag, cudaStream_t stream);
 void launch_merit_base(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int first,
                        cudaStream_t stream);
 void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int32_t* sqp_active,
@@ -636,6 +639,19 @@ int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const doubl
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
   if (batch == 0) return IHM2B_OK;
   CU(launch_dpc_rollout_grad(batch, Nf, dt, weights, x0, u, ref, cost, grad, xtraj, static_cast<cudaStream_t>(stream)));
+  return IHM2B_OK;
+}
+
+int ihm2b_project_dev(int64_t batch, int32_t n_grid, const double* s_ref, const double* X_ref, const double* Y_ref,
+                      const double* phi_ref, const int32_t* track, const double* pose, const double* s_guess,
+                      double s_tol, double* frenet, double* ref, int32_t* flag, void* stream) {
+  if (!s_ref || !X_ref || !Y_ref || !phi_ref || !pose || !s_guess || !frenet) return fail(IHM2B_EINVAL, "null argument");
+  if (batch < 0 || n_grid < 3 || !(s_tol > 0.0)) return fail(IHM2B_EINVAL, "bad batch %lld, n_grid %d or s_tol %g", (long long)batch, n_grid, s_tol);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
+  if (batch == 0) return IHM2B_OK;
+  CU(launch_project(batch, n_grid, s_ref, X_ref, Y_ref, phi_ref, track, pose, s_guess, s_tol, frenet, ref, flag,
+                    static_cast<cudaStream_t>(stream)));
   return IHM2B_OK;
 }
 

@@ -187,6 +187,19 @@ int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const doubl
                                const double* ref_dev, const double* weights_host, double* cost_dev,
                                double* grad_dev, double* xtraj_dev, void* stream);
 
+/* ---- Cartesian pose -> Frenet state ------------------------------------------
+ * Track::project (src/ihm2/src/common/tracks.cpp:200-288) followed by the control node's lateral offset and
+ * heading error (src/ihm2/src/mpc_control_node.cpp:142-157), for a batch of cars.  No handle.  Device buffers:
+ * tables s_ref / X_ref / Y_ref / phi_ref [n_tracks][n_grid] (the columns of the track CSV, tracks.cpp:132-149),
+ * track_index_dev [B] (NULL: track 0), pose_dev [B][3] = (X, Y, phi), s_guess_dev [B]; s_tol is the half-width of
+ * the search window in metres (2.0 in the node).  Outputs: frenet_dev [B][3] = (s, n, psi); optional (NULL to skip)
+ * ref_dev [B][3] = (X_ref, Y_ref, phi_ref) at the projection and flag_dev [B] = 1 where the node would throw
+ * "tangent x normal is too small". */
+int ihm2b_project_dev(int64_t batch, int32_t n_grid, const double* s_ref_dev, const double* X_ref_dev,
+                      const double* Y_ref_dev, const double* phi_ref_dev, const int32_t* track_index_dev,
+                      const double* pose_dev, const double* s_guess_dev, double s_tol, double* frenet_dev,
+                      double* ref_dev, int32_t* flag_dev, void* stream);
+
 /* number of kernel launches issued by this handle since creation (bench bookkeeping) */
 int64_t ihm2b_launch_count(const ihm2b_handle* h);
 

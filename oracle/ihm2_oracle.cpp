@@ -30,6 +30,8 @@
 //   nonlinear h(x,u) + slacks ......... old/generate_acaods_interface.py:190-212, 351-449
 //   DPC: kin4 ODE, RK4 step ........... dpc/main.py:56-97, constants dpc/main.py:23-37
 //   DPC: IHM1.5 tracking cost ......... dpc/main.py:374-409, doc/dpc.typ:44-56
+//   Cartesian pose -> Frenet (s, n, psi)  src/ihm2/src/common/tracks.cpp:183-288 (Track::project),
+//                                        src/ihm2/src/common/math.cpp:19-25, src/ihm2/src/mpc_control_node.cpp:142-157
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -1350,6 +1352,74 @@ int ihm2o_dpc_rollout_grad(int B, int Nf, double dt, const double* x0, const dou
     }
     cost[i] = J;
     if (xtraj) std::memcpy(xtraj + (size_t)i * (Nf + 1) * DX, xs.data(), xs.size() * sizeof(double));
+  }
+  return 0;
+}
+
+// ---- Cartesian pose -> Frenet state -------------------------------------------
+// Track::project (tracks.cpp:200-288): window of table points with s within s_guess +- s_tol (one more point on
+// each side), closest point, second end of the segment chosen by the larger angle seen from the car, orthogonal
+// projection on that segment; phi_ref from the linear interpolant anchored at the closest point (tracks.cpp:191-198,
+// 169-170).  Then the control node's n and psi (mpc_control_node.cpp:148-157).
+namespace proj {
+double wrap_to_pi(double x) {  // math.cpp:19-25
+  double t = std::fmod(x + M_PI, 2 * M_PI);
+  if (t < 0) t += 2 * M_PI;
+  return t - M_PI;
+}
+long long locate_index(const double* v, int n, double x) { return std::upper_bound(v, v + n, x) - v - 1; }  // tracks.cpp:183-185
+double angle3pt(const double* a, const double* b, const double* c) {  // tracks.cpp:187-189
+  return wrap_to_pi(std::atan2(c[1] - b[1], c[0] - b[0]) - std::atan2(a[1] - b[1], a[0] - b[0]));
+}
+}  // namespace proj
+
+// tables [n_tracks][n_grid]; pose [B][3] = (X, Y, phi); out frenet [B][3] = (s, n, psi), ref [B][3] = (X_ref, Y_ref,
+// phi_ref) at the projection, flag [B] = 1 where |tangent x normal| < 1e-6 (the node throws there)
+int ihm2o_project(int B, int n_grid, const double* s_ref, const double* X_ref, const double* Y_ref,
+                  const double* phi_ref, const int32_t* track, const double* pose, const double* s_guess,
+                  double s_tol, double* frenet, double* ref, int32_t* flag) {
+  using namespace proj;
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < B; i++) {
+    const size_t off = (size_t)(track ? track[i] : 0) * n_grid;
+    const double *sr = s_ref + off, *Xr = X_ref + off, *Yr = Y_ref + off, *pr = phi_ref + off;
+    const double car[2] = {pose[i * 3], pose[i * 3 + 1]};
+    const double s_low = std::max(s_guess[i] - s_tol, sr[0]), s_up = std::min(s_guess[i] + s_tol, sr[n_grid - 1]);
+    long long id_low = locate_index(sr, n_grid, s_low), id_up = locate_index(sr, n_grid, s_up);
+    if (id_low > 0) --id_low;
+    if (id_up < n_grid - 1) ++id_up;
+    const long long rows = id_up - id_low + 1;
+    long long id_min = 0;
+    double best = std::numeric_limits<double>::infinity();
+    for (long long j = 0; j < rows; j++) {
+      const double dx = Xr[id_low + j] - car[0], dy = Yr[id_low + j] - car[1];
+      const double d = dx * dx + dy * dy;
+      if (d < best) { best = d; id_min = j; }
+    }
+    const long long id_prev = (id_min == 0) ? rows - 1 : id_min - 1;
+    const long long id_next = (id_min == rows - 1) ? 0 : id_min + 1;
+    auto pt = [&](long long j, double* o) { o[0] = Xr[id_low + j]; o[1] = Yr[id_low + j]; };
+    double pm[2], pp[2], pn[2];
+    pt(id_min, pm); pt(id_prev, pp); pt(id_next, pn);
+    const double angle_prev = std::fabs(angle3pt(pm, car, pp)), angle_next = std::fabs(angle3pt(pm, car, pn));
+    const double *a, *b;
+    double sa, sb;
+    if (angle_prev > angle_next) { a = pp; b = pm; sa = sr[id_prev + id_low]; sb = sr[id_min + id_low]; }
+    else { a = pm; b = pn; sa = sr[id_min + id_low]; sb = sr[id_next + id_low]; }
+    const double dx = b[0] - a[0], dy = b[1] - a[1];
+    const double lambda = ((car[0] - a[0]) * dx + (car[1] - a[1]) * dy) / (dx * dx + dy * dy);
+    const double s = sa + lambda * (sb - sa);
+    const double Xp = a[0] + lambda * (b[0] - a[0]), Yp = a[1] + lambda * (b[1] - a[1]);
+    // the reference indexes its (n_grid - 1)-row coefficient table with id_min + id_low unclamped
+    const long long ind = std::min<long long>(id_min + id_low, n_grid - 2);
+    const double phir = pr[ind] + (pr[ind + 1] - pr[ind]) / (sr[ind + 1] - sr[ind]) * (s - sr[ind]);
+    const double rho = wrap_to_pi(phir);
+    const double psi = wrap_to_pi(pose[i * 3 + 2] - rho);
+    const double e = std::hypot(Xp - car[0], Yp - car[1]);
+    const double tpr = (car[1] - Yp) * std::cos(rho) - (car[0] - Xp) * std::sin(rho);
+    frenet[i * 3] = s; frenet[i * 3 + 1] = e * (tpr > 0.0 ? 1.0 : -1.0); frenet[i * 3 + 2] = psi;
+    if (ref) { ref[i * 3] = Xp; ref[i * 3 + 1] = Yp; ref[i * 3 + 2] = phir; }
+    if (flag) flag[i] = std::fabs(tpr) < 1e-6;
   }
   return 0;
 }

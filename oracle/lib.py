@@ -155,3 +155,20 @@ def dpc_rollout_grad(x0, u, ref, weights, dt=1.0 / 20):
                                     _p(cost), _p(grad), _p(xtraj))
     assert rc == 0
     return cost, grad, xtraj
+
+
+def project(s_ref, X_ref, Y_ref, phi_ref, pose, s_guess, s_tol=2.0, track=None):
+    """Track::project + the control node's Frenet conversion (tracks.cpp:200-288, mpc_control_node.cpp:142-157).
+
+    tables [n_tracks, n_grid] (or [n_grid]); pose [B,3] = (X, Y, phi); s_guess [B] -> frenet [B,3] = (s, n, psi),
+    ref [B,3] = (X_ref, Y_ref, phi_ref) at the projection, flag [B]."""
+    lib = C.CDLL(build_oracle())
+    s_ref, X_ref, Y_ref, phi_ref = [_f(np.atleast_2d(a)) for a in (s_ref, X_ref, Y_ref, phi_ref)]
+    pose, s_guess = _f(pose), _f(s_guess)
+    B = pose.shape[0]
+    tr = None if track is None else np.ascontiguousarray(track, dtype=np.int32)
+    frenet, ref, flag = np.zeros((B, 3)), np.zeros((B, 3)), np.zeros(B, np.int32)
+    rc = lib.ihm2o_project(C.c_int(B), C.c_int(s_ref.shape[1]), _p(s_ref), _p(X_ref), _p(Y_ref), _p(phi_ref), _p(tr),
+                           _p(pose), _p(s_guess), C.c_double(s_tol), _p(frenet), _p(ref), _p(flag))
+    assert rc == 0
+    return frenet, ref, flag
