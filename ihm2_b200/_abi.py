@@ -16,6 +16,7 @@ ERK4, IRK_GL4 = 0, 1
 SQP_RTI, SQP = 0, 1
 FIXED_STEP, MERIT_BACKTRACKING = 0, 1
 SIM_FKIN6, SIM_FDYN6, SIM_KIN6_DYN6 = 0, 1, 2
+SIM_KIN6C, SIM_DYN6C, SIM_KIN6C_DYN6C = 3, 4, 5  # Cartesian plants of the ROS sim node
 STATUS_SUCCESS, STATUS_FAILURE, STATUS_MAXITER, STATUS_MINSTEP, STATUS_QP_FAILURE = 0, 1, 2, 3, 4
 
 (P_M, P_IZ, P_LR, P_LF, P_CM0, P_CR0, P_CR1, P_CR2, P_TT, P_TD, P_ZCG, P_TRACKW, P_CDOWN,

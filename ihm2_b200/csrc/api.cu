@@ -503,7 +503,7 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double
   int rc = check_ready(h);
   if (rc) return rc;
   if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
-  if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6_DYN6) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
+  if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6C_DYN6C) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
   launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, static_cast<cudaStream_t>(stream));
   h->launches++;
   CU(cudaGetLastError());

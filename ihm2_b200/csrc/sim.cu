@@ -28,8 +28,10 @@ __device__ __forceinline__ double lat_pacejka(const double* p, double al) {  // 
 }
 
 // rows 0..5 of the fdyn6 right-hand side (rows 6, 7 are the actuator lags, handled in closed form)
+// cart: the Cartesian dyn6 of python/models.py:310-452 instead (pose kinematics, slip angles atan2(v_y_i, v_x_i)
+// [- delta] assigned wheel by wheel, drag switched by tanh(1000 v_x), r_kin = v_x sin(beta) / l_R)
 __device__ void fdyn6_rhs(const double* __restrict__ x, const double* __restrict__ p, const TrackView& tr,
-                          double* __restrict__ f) {
+                          double* __restrict__ f, const bool cart) {
   const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
   const double m = p[IHM2B_P_M], g = p[IHM2B_P_G], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF], wb = lR + lF;
   const double tw = p[IHM2B_P_TRACKW];
@@ -41,18 +43,18 @@ __device__ void fdyn6_rhs(const double* __restrict__ x, const double* __restrict
   sincos(dl, &sd, &cd);
   const double vxL = vx - 0.5 * tw * r, vxR = vx + 0.5 * tw * r;
   const double vyF = vy + lF * r, vlatR = vy - lR * r;
-  const double aFL = atan2(-sd * vxL + cd * vyF, smooth_abs_nonzero(cd * vxL + sd * vyF));
-  const double aFR = atan2(-sd * vxR + cd * vyF, smooth_abs_nonzero(cd * vxR + sd * vyF));
-  const double aRL = atan2(vlatR, smooth_abs_nonzero(vxL));
-  const double aRR = atan2(vlatR, smooth_abs_nonzero(vxR));
-  const bool cross = p[IHM2B_P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
+  const double aFL = cart ? atan2(vyF, vxL) - dl : atan2(-sd * vxL + cd * vyF, smooth_abs_nonzero(cd * vxL + sd * vyF));
+  const double aFR = cart ? atan2(vyF, vxR) - dl : atan2(-sd * vxR + cd * vyF, smooth_abs_nonzero(cd * vxR + sd * vyF));
+  const double aRL = atan2(vlatR, cart ? vxL : smooth_abs_nonzero(vxL));
+  const double aRR = atan2(vlatR, cart ? vxR : smooth_abs_nonzero(vxR));
+  const bool cross = !cart && p[IHM2B_P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
   const double muFL = lat_pacejka(p, cross ? aRR : aFL), muFR = lat_pacejka(p, cross ? aRL : aFR);
   const double muRL = lat_pacejka(p, cross ? aFR : aRL), muRR = lat_pacejka(p, cross ? aFL : aRR);
-  const double Fdrag = -(p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx) * tanh(10.0 * vx);
+  const double Fdrag = -(p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx) * tanh((cart ? 1000.0 : 10.0) * vx);
   const double C = lR / wb;
   const double td = sd / cd, Ctd = C * td;
   const double sbeta = Ctd * rsqrt(1.0 + Ctd * Ctd);
-  const double dtau = p[IHM2B_P_KTV] * (hypot(vx, vy) * sbeta / lR - r);
+  const double dtau = p[IHM2B_P_KTV] * ((cart ? vx : hypot(vx, vy)) * sbeta / lR - r);
   const double idn = 1.0 / (-m * g - 0.25 * Fdown);
   const double lonL = p[IHM2B_P_CM0] * (T - dtau) * idn, lonR = p[IHM2B_P_CM0] * (T + dtau) * idn;
   // body-frame force per unit vertical load of each wheel, and its yaw arm
@@ -72,16 +74,46 @@ __device__ void fdyn6_rhs(const double* __restrict__ x, const double* __restrict
   const double idet = 1.0 / (a11 * a22 - a12 * a21);
   const double ax = (Fx0 * a22 - a12 * Fy0) * idet, ay = (a11 * Fy0 - a21 * Fx0) * idet;
   const double Mz = Mz0 + gzx * ax + gzy * ay;
-  double kap, dkap, sp, cp;
-  kappa_lookup(tr, x[0], kap, dkap);
+  double sp, cp;
   sincos(psi, &sp, &cp);
-  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
-  f[0] = sdot;
-  f[1] = vx * sp + vy * cp;
-  f[2] = r - kap * sdot;
+  if (cart) {
+    f[0] = vx * cp - vy * sp;
+    f[1] = vx * sp + vy * cp;
+    f[2] = r;
+  } else {
+    double kap, dkap;
+    kappa_lookup(tr, x[0], kap, dkap);
+    const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+    f[0] = sdot;
+    f[1] = vx * sp + vy * cp;
+    f[2] = r - kap * sdot;
+  }
   f[3] = ax + vy * r;
   f[4] = ay - vx * r;
   f[5] = Mz / p[IHM2B_P_IZ];
+}
+
+// rows 0..5 of the plant right-hand side for the model chosen for this step
+__device__ __forceinline__ void plant_rhs(const int model, const double* x, const double u0, const double u1,
+                                          const double* p, const TrackView& tr, double* f) {
+  if (model == IHM2B_SIM_FKIN6) {
+    fkin6<false>(x, u0, u1, p, tr, f, nullptr);
+  } else if (model == IHM2B_SIM_KIN6C) {
+    // Cartesian kin6 (python/models.py:168-229): the v_x, v_y rows of fkin6, pose kinematics, and r_dot = v_y_dot / l_R
+    // (fkin6 has l_R * v_y_dot - beta_dot there, :307)
+    double xx[NX];
+    for (int r = 0; r < NX; r++) xx[r] = x[r];
+    xx[0] = 0.0; xx[1] = 0.0;
+    fkin6<false>(xx, u0, u1, p, tr, f, nullptr);
+    double sp, cp;
+    sincos(x[2], &sp, &cp);
+    f[0] = x[3] * cp - x[4] * sp;
+    f[1] = x[3] * sp + x[4] * cp;
+    f[2] = x[5];
+    f[5] = f[4] / p[IHM2B_P_LR];
+  } else {
+    fdyn6_rhs(x, p, tr, f, model == IHM2B_SIM_DYN6C);
+  }
 }
 
 constexpr int MAX_FP = 80;
@@ -121,7 +153,10 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
     const double C = p[IHM2B_P_LR] / (p[IHM2B_P_LR] + p[IHM2B_P_LF]);
     const double beta = atan(C * tan(x[7]));
     model = ((x[3] * x[3] + x[4] * x[4]) * sin(beta) / p[IHM2B_P_LR] <= sc.sw) ? IHM2B_SIM_FKIN6 : IHM2B_SIM_FDYN6;
+  } else if (model == IHM2B_SIM_KIN6C_DYN6C) {  // sim_node.cpp:199
+    model = (hypot(x[3], x[4]) < sc.sw) ? IHM2B_SIM_KIN6C : IHM2B_SIM_DYN6C;
   }
+  const bool cartesian = sc.model >= IHM2B_SIM_KIN6C;
   const double h = sc.h, itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
   double Ai[4], bw[4];
   for (int j = 0; j < 4; j++) { Ai[j] = h * sc.A[i * 4 + j]; bw[j] = h * sc.b[j]; }
@@ -138,7 +173,7 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
     if (first) {  // first sub-step: start from f(x); afterwards from the previous sub-step's stages
       double xx[NX], f[NX];
       for (int r = 0; r < NX; r++) xx[r] = x[r];
-      if (model == IHM2B_SIM_FKIN6) fkin6<false>(xx, u0, u1, p, tr, f, nullptr); else fdyn6_rhs(xx, p, tr, f);
+      plant_rhs(model, xx, u0, u1, p, tr, f);
       for (int r = 0; r < 6; r++) { K[r] = f[r]; Kp[r] = f[r]; }
       first = false;
     } else {
@@ -162,7 +197,7 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
         xs[r] = v;
       }
       double f[NX];
-      if (model == IHM2B_SIM_FKIN6) fkin6<false>(xs, u0, u1, p, tr, f, nullptr); else fdyn6_rhs(xs, p, tr, f);
+      plant_rhs(model, xs, u0, u1, p, tr, f);
       double dmax = 0.0, kmax = 0.0;
       for (int r = 0; r < 6; r++) { dmax = fmax(dmax, fabs(f[r] - K[r])); kmax = fmax(kmax, fabs(f[r])); K[r] = f[r]; }
       if (!(dmax == dmax)) dmax = 1e300;
@@ -182,6 +217,8 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
     x[6] += dT; x[7] += dD;
     if (!ok) break;
   }
+  // the sim node keeps the car from going backwards (sim_node.cpp:256-260)
+  if (cartesian && (x[3] < 0.0 || (x[6] <= 0.1 && x[3] < 0.01))) { x[3] = 0.0; x[4] = 0.0; x[5] = 0.0; }
   if (i == 0) {
     for (int r = 0; r < NX; r++) xout[(size_t)b * NX + r] = ok ? x[r] : nan("");
     if (model_out) model_out[b] = model;

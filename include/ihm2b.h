@@ -38,7 +38,11 @@ enum ihm2b_error { IHM2B_OK = 0, IHM2B_EINVAL = 1, IHM2B_ECUDA = 2, IHM2B_ENOMEM
 enum ihm2b_integrator { IHM2B_ERK4 = 0, IHM2B_IRK_GL4 = 1 };
 enum ihm2b_nlp_solver { IHM2B_SQP_RTI = 0, IHM2B_SQP = 1 };
 enum ihm2b_globalization { IHM2B_FIXED_STEP = 0, IHM2B_MERIT_BACKTRACKING = 1 };
-enum ihm2b_sim_model { IHM2B_SIM_FKIN6 = 0, IHM2B_SIM_FDYN6 = 1, IHM2B_SIM_KIN6_DYN6 = 2 };
+enum ihm2b_sim_model { IHM2B_SIM_FKIN6 = 0, IHM2B_SIM_FDYN6 = 1, IHM2B_SIM_KIN6_DYN6 = 2,
+  /* Cartesian plants of the ROS sim node (python/models.py:168-229 kin6, :310-452 dyn6): state (X, Y, phi, v_x, v_y, r,
+   * T, delta); KIN6C_DYN6C switches on hypot(v_x, v_y) < sim_switch (v_dyn, sim_node.cpp:199) and all three apply the
+   * node's no-reverse clamp after the step (sim_node.cpp:256-260) */
+  IHM2B_SIM_KIN6C = 3, IHM2B_SIM_DYN6C = 4, IHM2B_SIM_KIN6C_DYN6C = 5 };
 enum ihm2b_status {
   IHM2B_SUCCESS = 0, IHM2B_FAILURE = 1, IHM2B_MAXITER = 2, IHM2B_MINSTEP = 3, IHM2B_QP_FAILURE = 4
 };

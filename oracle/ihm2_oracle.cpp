@@ -180,7 +180,9 @@ inline double lat_pacejka(const double* p, double a) {  // python/models.py:69-7
 }
 
 // total body-frame forces / yaw moment for given accelerations (a_x, a_y)
-void fdyn6_forces(const double* x, const double* p, double ax, double ay, double* FxFyMz) {
+// cart: the Cartesian dyn6 of python/models.py:310-452 (slip angles :376-379 wheel by wheel without the smooth
+// absolute value, drag :399 with tanh(1000 v_x), r_kin :409 from v_x alone)
+void fdyn6_forces(const double* x, const double* p, double ax, double ay, double* FxFyMz, bool cart = false) {
   const double vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
   const double m = p[P_M], g = p[P_G], lR = p[P_LR], lF = p[P_LF], wb = lR + lF;
   const double tw = p[P_TRACKW];
@@ -199,20 +201,20 @@ void fdyn6_forces(const double* x, const double* p, double ax, double ay, double
   const double vlatFL = -sd * vxFL + cd * vyF, vlatFR = -sd * vxFR + cd * vyF;
   const double vlonRL = vx - 0.5 * tw * r, vlonRR = vx + 0.5 * tw * r;
   const double vlatR = vy - lR * r;
-  const double aFL = std::atan2(vlatFL, smooth_abs_nonzero(vlonFL));
-  const double aFR = std::atan2(vlatFR, smooth_abs_nonzero(vlonFR));
-  const double aRL = std::atan2(vlatR, smooth_abs_nonzero(vlonRL));
-  const double aRR = std::atan2(vlatR, smooth_abs_nonzero(vlonRR));
-  const bool cross = p[P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
+  const double aFL = cart ? std::atan2(vyF, vxFL) - dl : std::atan2(vlatFL, smooth_abs_nonzero(vlonFL));
+  const double aFR = cart ? std::atan2(vyF, vxFR) - dl : std::atan2(vlatFR, smooth_abs_nonzero(vlonFR));
+  const double aRL = cart ? std::atan2(vlatR, vlonRL) : std::atan2(vlatR, smooth_abs_nonzero(vlonRL));
+  const double aRR = cart ? std::atan2(vlatR, vlonRR) : std::atan2(vlatR, smooth_abs_nonzero(vlonRR));
+  const bool cross = !cart && p[P_CROSS] != 0.0;  // literal quirk python/models.py:543-546
   const double FlatFL = FzFL * lat_pacejka(p, cross ? aRR : aFL);
   const double FlatFR = FzFR * lat_pacejka(p, cross ? aRL : aFR);
   const double FlatRL = FzRL * lat_pacejka(p, cross ? aFR : aRL);
   const double FlatRR = FzRR * lat_pacejka(p, cross ? aFL : aRR);
-  const double th = std::tanh(10.0 * vx);
+  const double th = std::tanh((cart ? 1000.0 : 10.0) * vx);
   const double Fdrag = -(p[P_CR0] + p[P_CR1] * vx + p[P_CR2] * vx * vx) * th;
   const double C = lR / wb;
   const double beta = std::atan(C * std::tan(dl));
-  const double rkin = std::hypot(vx, vy) * std::sin(beta) / lR;
+  const double rkin = (cart ? vx : std::hypot(vx, vy)) * std::sin(beta) / lR;
   const double dtau = p[P_KTV] * (rkin - r);
   const double dn = -m * g - 0.25 * Fdown;
   const double FlonFL = p[P_CM0] * (T - dtau) * FzFL / dn;
@@ -226,13 +228,13 @@ void fdyn6_forces(const double* x, const double* p, double ax, double ay, double
               FlonRR * tw / 2 - FlatRR * lR - FlonRL * tw / 2 - FlatRL * lR;
 }
 
-void fdyn6(const double* x, const double* u, const double* p, const Track& tr, double* f) {
+void fdyn6_any(const double* x, const double* u, const double* p, const Track& tr, double* f, bool cart) {
   const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5];
   const double m = p[P_M];
   double F0[3], F1[3], F2[3];
-  fdyn6_forces(x, p, 0.0, 0.0, F0);
-  fdyn6_forces(x, p, 1.0, 0.0, F1);
-  fdyn6_forces(x, p, 0.0, 1.0, F2);
+  fdyn6_forces(x, p, 0.0, 0.0, F0, cart);
+  fdyn6_forces(x, p, 1.0, 0.0, F1, cart);
+  fdyn6_forces(x, p, 0.0, 1.0, F2, cart);
   // m a = F0 + Gx a_x + Gy a_y  (first two rows)  ->  2x2 solve
   const double a11 = m - (F1[0] - F0[0]), a12 = -(F2[0] - F0[0]);
   const double a21 = -(F1[1] - F0[1]), a22 = m - (F2[1] - F0[1]);
@@ -240,23 +242,44 @@ void fdyn6(const double* x, const double* u, const double* p, const Track& tr, d
   const double ax = (F0[0] * a22 - a12 * F0[1]) / det;
   const double ay = (a11 * F0[1] - a21 * F0[0]) / det;
   const double Mz = F0[2] + (F1[2] - F0[2]) * ax + (F2[2] - F0[2]) * ay;
-  double kap, dkap;
-  kappa_lookup(tr, x[0], kap, dkap);
   const double cp = std::cos(psi), sp = std::sin(psi);
-  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
-  f[0] = sdot;
-  f[1] = vx * sp + vy * cp;
-  f[2] = r - kap * sdot;
+  if (cart) {  // python/models.py:420-422
+    f[0] = vx * cp - vy * sp;
+    f[1] = vx * sp + vy * cp;
+    f[2] = r;
+  } else {
+    double kap, dkap;
+    kappa_lookup(tr, x[0], kap, dkap);
+    const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+    f[0] = sdot;
+    f[1] = vx * sp + vy * cp;
+    f[2] = r - kap * sdot;
+  }
   f[3] = ax + vy * r;  // a_x = vxdot - vy r
   f[4] = ay - vx * r;  // a_y = vydot + vx r
   f[5] = Mz / p[P_IZ];
   f[6] = (u[0] - x[6]) / p[P_TT];
   f[7] = (u[1] - x[7]) / p[P_TD];
 }
+void fdyn6(const double* x, const double* u, const double* p, const Track& tr, double* f) { fdyn6_any(x, u, p, tr, f, false); }
+void dyn6c(const double* x, const double* u, const double* p, const Track& tr, double* f) { fdyn6_any(x, u, p, tr, f, true); }
 
 typedef void (*rhs_fn)(const double*, const double*, const double*, const Track&, double*);
 void fkin6_rhs(const double* x, const double* u, const double* p, const Track& tr, double* f) {
   fkin6(x, u, p, tr, f, nullptr);
+}
+// Cartesian kin6 (python/models.py:168-229): shares the v_x, v_y, T, delta rows with fkin6; pose kinematics; and
+// r_dot = v_y_dot / l_R (:226) where fkin6 has l_R * v_y_dot - beta_dot
+void kin6c(const double* x, const double* u, const double* p, const Track& tr, double* f) {
+  double xx[NX];
+  std::memcpy(xx, x, sizeof xx);
+  xx[0] = xx[1] = 0.0;
+  fkin6(xx, u, p, tr, f, nullptr);
+  const double cp = std::cos(x[2]), sp = std::sin(x[2]);
+  f[0] = x[3] * cp - x[4] * sp;
+  f[1] = x[3] * sp + x[4] * cp;
+  f[2] = x[5];
+  f[5] = f[4] / p[P_LR];
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1003,21 +1026,27 @@ int sim_step(const Problem& pb, const double* x, const double* u, double* xn) {
     const double beta = std::atan(C * std::tan(x[7]));
     const double v2 = x[3] * x[3] + x[4] * x[4];
     model = (v2 * std::sin(beta) / pb.p[P_LR] <= cf.sim_switch) ? IHM2B_SIM_FKIN6 : IHM2B_SIM_FDYN6;
+  } else if (model == IHM2B_SIM_KIN6C_DYN6C) {  // sim_node.cpp:199
+    model = (std::hypot(x[3], x[4]) < cf.sim_switch) ? IHM2B_SIM_KIN6C : IHM2B_SIM_DYN6C;
   }
+  const bool cartesian = cf.sim_model >= IHM2B_SIM_KIN6C;
   Tableau tb{4, cf.sim_A, cf.sim_b};
   const double h = cf.dt / cf.sim_steps;
   double xc[NX], xt[NX];
   std::memcpy(xc, x, sizeof xc);
   for (int st = 0; st < cf.sim_steps; st++) {
-    int rc = (model == IHM2B_SIM_FKIN6)
-                 ? irk_step(fkin6_rhs, true, tb, xc, u, pb.p, pb.tr, h, xt, nullptr)
-                 : irk_step(fdyn6, false, tb, xc, u, pb.p, pb.tr, h, xt, nullptr);
+    int rc = (model == IHM2B_SIM_FKIN6)   ? irk_step(fkin6_rhs, true, tb, xc, u, pb.p, pb.tr, h, xt, nullptr)
+             : (model == IHM2B_SIM_FDYN6) ? irk_step(fdyn6, false, tb, xc, u, pb.p, pb.tr, h, xt, nullptr)
+             : (model == IHM2B_SIM_KIN6C) ? irk_step(kin6c, false, tb, xc, u, pb.p, pb.tr, h, xt, nullptr)
+                                          : irk_step(dyn6c, false, tb, xc, u, pb.p, pb.tr, h, xt, nullptr);
     if (rc < 0) {
       for (int a = 0; a < NX; a++) xn[a] = std::numeric_limits<double>::quiet_NaN();
       return model;
     }
     std::memcpy(xc, xt, sizeof xc);
   }
+  // the sim node keeps the car from going backwards (sim_node.cpp:256-260)
+  if (cartesian && (xc[3] < 0.0 || (xc[6] <= 0.1 && xc[3] < 0.01))) xc[3] = xc[4] = xc[5] = 0.0;
   std::memcpy(xn, xc, sizeof xc);
   return model;
 }

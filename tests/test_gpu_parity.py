@@ -247,6 +247,36 @@ def test_sim_step_matches_oracle_random(torch_cuda, fsds):
     eng.close()
 
 
+def test_cartesian_plants_match_oracle(torch_cuda, fsds):
+    """Cartesian kin6 / dyn6 of the ROS sim node (python/models.py:168-229, 310-452): one 50 ms step,
+    model chosen by speed (sim_node.cpp:199), no-reverse clamp (:256-260)."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B = 256
+    rng = np.random.default_rng(6)
+    x = np.stack([rng.uniform(-50, 50, B), rng.uniform(-50, 50, B), rng.uniform(-3.2, 3.2, B), rng.uniform(0.0, 20, B),
+                  rng.uniform(-0.5, 0.5, B), rng.uniform(-0.5, 0.5, B), rng.uniform(-300, 300, B), rng.uniform(-0.3, 0.3, B)], 1)
+    x[:16, 3] = rng.uniform(0.0, 0.02, 16); x[:16, 6] = rng.uniform(-100, 0.1, 16)     # braking to a stop: the clamp
+    u = np.stack([x[:, 6] + rng.uniform(-50, 50, B), x[:, 7] + rng.uniform(-0.02, 0.02, B)], 1)
+    for model in (_abi.SIM_KIN6C_DYN6C, _abi.SIM_KIN6C, _abi.SIM_DYN6C):
+        cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), sim_model=model)
+        eng = _engine(cfg, fsds)
+        xn, md = eng.sim_step(torch_cuda.as_tensor(x, device="cuda"), torch_cuda.as_tensor(u, device="cuda"))
+        xo, mo = Oracle(cfg, fsds.s_ref, fsds.kappa_ref).sim_step(x, u)
+        eng.close()
+        np.testing.assert_array_equal(md.cpu().numpy(), mo)
+        if model == _abi.SIM_KIN6C_DYN6C:
+            assert (mo == _abi.SIM_KIN6C).sum() > 10 and (mo == _abi.SIM_DYN6C).sum() > 10
+        good = ~np.isnan(xo).any(axis=1)
+        xg = xn.cpu().numpy()
+        err = np.abs(xg[good] - xo[good]) / np.maximum(1.0, np.abs(xo[good]))
+        assert good.sum() > 0.9 * B and err.max() < 1e-8, (model, err.max(axis=0))
+        stopped = (xo[:, 3] == 0.0) & good
+        assert (xg[stopped, 3:6] == 0.0).all()
+        if model != _abi.SIM_DYN6C:                       # dyn6 alone is not meant for a car at rest
+            assert stopped.sum() > 0
+
+
 def test_closed_loop_matches_golden(torch_cuda, fsds):
     """python/main.py:448-517 with the NMPC enabled: shift -> solve -> plant step, 40 steps on the device."""
     from ihm2_b200 import _abi

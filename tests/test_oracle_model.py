@@ -159,3 +159,71 @@ def test_golden_model_vectors(orc):
         xi, Si = orc.integrate(1, g["x"][i], g["u"][i], 0.05)
         np.testing.assert_allclose(xi, g["irk_x"][i], rtol=1e-12, atol=1e-11)
         np.testing.assert_allclose(Si, g["irk_S"][i], rtol=1e-10, atol=1e-11)
+
+
+def test_cartesian_dyn6_satisfies_the_reference_implicit_form():
+    """Independent pin of the oracle's Cartesian dyn6: a numpy transcription of the implicit residual of
+    python/models.py:310-452, evaluated at the oracle's state derivative, must vanish; kin6 (:168-229) explicitly."""
+    import ctypes as C
+    from ihm2_b200 import _abi
+    from ihm2_b200.track import load_packaged_track
+    from oracle.lib import Oracle, _p, _f
+    mp = load_packaged_track("fsds_default")
+    B = 64
+    rng = np.random.default_rng(8)
+    x = np.stack([rng.uniform(-50, 50, B), rng.uniform(-50, 50, B), rng.uniform(-3, 3, B), rng.uniform(0.5, 25, B),
+                  rng.uniform(-1, 1, B), rng.uniform(-1, 1, B), rng.uniform(-400, 400, B), rng.uniform(-0.4, 0.4, B)], 1)
+    u = np.stack([rng.uniform(-500, 500, B), rng.uniform(-0.5, 0.5, B)], 1)
+    P = _abi.default_params()
+    m, g, lR, lF, tw, zcg = [P[i] for i in (_abi.P_M, _abi.P_G, _abi.P_LR, _abi.P_LF, _abi.P_TRACKW, _abi.P_ZCG)]
+    wb, C_ = lR + lF, lR / (lR + lF)
+    h = 1e-7
+    for kind, model in ((3, _abi.SIM_KIN6C), (4, _abi.SIM_DYN6C)):
+        cfg = _abi.make_config(batch=1, n_grid=len(mp.s_ref), sim_model=model, sim_steps=1)
+        orc = Oracle(cfg, mp.s_ref, mp.kappa_ref)
+        for i in range(B):
+            # state derivative from one tiny explicit-Euler-sized plant step: (x+ - x) / h with h -> 0 is not exact,
+            # so ask the integrator for a very short step and compare to first order
+            cfg.dt = h
+            xn, _ = Oracle(cfg, mp.s_ref, mp.kappa_ref).sim_step(x[i:i + 1], u[i:i + 1])
+            xd = (xn[0] - x[i]) / h
+            X, Y, phi, vx, vy, r, T, dl = x[i]
+            if model == _abi.SIM_KIN6C:
+                td = np.tan(dl)
+                beta = np.arctan(C_ * td)
+                ddl = (u[i, 1] - dl) / P[_abi.P_TD]
+                bd = C_ * (1 + td * td) / (1 + C_ * C_ * td * td) * ddl
+                Fm = P[_abi.P_CM0] * T
+                Fd = -(P[_abi.P_CR0] + P[_abi.P_CR1] * vx + P[_abi.P_CR2] * vx * vx) * np.tanh(10 * vx)
+                vd = ((0.5 * Fm + Fd) * np.cos(beta) + 0.5 * Fm * np.cos(dl - beta)) / m
+                ref = np.array([vx * np.cos(phi) - vy * np.sin(phi), vx * np.sin(phi) + vy * np.cos(phi), r,
+                                vd * np.cos(beta) - bd * vy, vd * np.sin(beta) + bd * vx, (vd * np.sin(beta) + bd * vx) / lR])
+                assert np.abs(xd[:6] - ref).max() < 2e-4 * max(1.0, np.abs(ref).max()), (i, xd[:6], ref)
+                continue
+            ax, ay = xd[3] - vy * r, xd[4] + vx * r
+            Fdown = 0.5 * P[_abi.P_CDOWN] * vx * vx
+            stat = 0.5 * m * g * lF / wb
+            lon, lat = 0.5 * m * ax * zcg / wb, 0.5 * m * ay * zcg / tw
+            Fz = dict(FL=-(stat - lon + lat + 0.25 * Fdown), FR=-(stat - lon - lat + 0.25 * Fdown),
+                      RL=-(stat + lon + lat + 0.25 * Fdown), RR=-(stat + lon - lat + 0.25 * Fdown))
+            vxw = dict(FL=vx - 0.5 * tw * r, FR=vx + 0.5 * tw * r, RL=vx - 0.5 * tw * r, RR=vx + 0.5 * tw * r)
+            vyw = dict(FL=vy + lF * r, FR=vy + lF * r, RL=vy - lR * r, RR=vy - lR * r)
+            al = {k: np.arctan2(vyw[k], vxw[k]) - (dl if k[0] == "F" else 0.0) for k in Fz}
+            Ba, Ca, Da, Ea = [P[j] for j in (_abi.P_BA, _abi.P_CA, _abi.P_DA, _abi.P_EA)]
+            Fy = {k: Fz[k] * Da * np.sin(Ca * np.arctan(Ba * al[k] - Ea * (Ba * al[k] - np.arctan(Ba * al[k])))) for k in Fz}
+            Fdrag = -(P[_abi.P_CR0] + P[_abi.P_CR1] * vx + P[_abi.P_CR2] * vx * vx) * np.tanh(1000 * vx)
+            td = np.tan(dl)
+            sb = C_ * td / np.sqrt(1 + C_ * C_ * td * td)
+            dtau = P[_abi.P_KTV] * (vx * sb / lR - r)
+            dn = -m * g - 0.25 * Fdown
+            Fx = {k: P[_abi.P_CM0] * (T + (dtau if k[1] == "R" else -dtau)) * Fz[k] / dn for k in Fz}
+            cd, sd = np.cos(dl), np.sin(dl)
+            res = np.array([
+                xd[0] - (vx * np.cos(phi) - vy * np.sin(phi)), xd[1] - (vx * np.sin(phi) + vy * np.cos(phi)), xd[2] - r,
+                m * ax - ((Fx["FR"] + Fx["FL"]) * cd - (Fy["FR"] + Fy["FL"]) * sd + Fx["RR"] + Fx["RL"] + Fdrag),
+                m * ay - ((Fx["FR"] + Fx["FL"]) * sd + (Fy["FR"] + Fy["FL"]) * cd + Fy["RR"] + Fy["RL"]),
+                P[_abi.P_IZ] * xd[5] - ((Fx["FR"] * cd - Fy["FR"] * sd) * tw / 2 + (Fx["FR"] * sd + Fy["FR"] * cd) * lF
+                                        - (Fx["FL"] * cd - Fy["FL"] * sd) * tw / 2 + (Fx["FL"] * sd + Fy["FL"] * cd) * lF
+                                        + Fx["RR"] * tw / 2 - Fy["RR"] * lR - Fx["RL"] * tw / 2 - Fy["RL"] * lR)])
+            scale = np.array([1, 1, 1, m * 10, m * 10, P[_abi.P_IZ] * 10])
+            assert np.abs(res / scale).max() < 5e-4, (i, res)
