@@ -24,6 +24,9 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
                                     const double* u, const double* ref, double* cost, double* grad, double* xtraj,
                                     cudaStream_t stream);
+cudaError_t launch_dpc_rollout_grad_f32(long long B, int Nf, double dt, const double* weights, const float* x0,
+                                        const float* u, const float* ref, float* cost, float* grad, float* xtraj,
+                                        cudaStream_t stream);
 cudaError_t launch_project(long long B, int n_grid, const double* s_ref, const double* X_ref, const double* Y_ref,
                            const double* phi_ref, const int32_t* track, const double* pose, const double* s_guess,
                            double s_tol, double* frenet, double* ref, int32_t* flag, cudaStream_t stream);
@@ -639,6 +642,18 @@ int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const doubl
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
   if (batch == 0) return IHM2B_OK;
   CU(launch_dpc_rollout_grad(batch, Nf, dt, weights, x0, u, ref, cost, grad, xtraj, static_cast<cudaStream_t>(stream)));
+  return IHM2B_OK;
+}
+
+int ihm2b_dpc_rollout_grad_f32_dev(int64_t batch, int32_t Nf, double dt, const float* x0, const float* u, const float* ref,
+                                   const double* weights, float* cost, float* grad, float* xtraj, void* stream) {
+  if (!x0 || !u || !ref || !weights || !cost || !grad) return fail(IHM2B_EINVAL, "null argument");
+  if (batch < 0 || !(dt > 0.0)) return fail(IHM2B_EINVAL, "bad batch %lld or dt %g", (long long)batch, dt);
+  if (Nf != 40 && Nf != 80) return fail(IHM2B_EINVAL, "Nf = %d: the rollout kernel is built for Nf = 40 and 80", Nf);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
+  if (batch == 0) return IHM2B_OK;
+  CU(launch_dpc_rollout_grad_f32(batch, Nf, dt, weights, x0, u, ref, cost, grad, xtraj, static_cast<cudaStream_t>(stream)));
   return IHM2B_OK;
 }
 

@@ -94,21 +94,26 @@ class MotionPlanner:
 
 def rollout_grad(x0: torch.Tensor, u: torch.Tensor, ref: torch.Tensor, weights: DPCWeights | np.ndarray | None = None,
                  step: float = dt, want_trajectory: bool = False):
-    """x0 [B,4], u [B,Nf,2], ref [B,Nf+1,4] (contiguous fp64 CUDA tensors) -> cost [B], grad [B,Nf,2] (, x [B,Nf+1,4])."""
+    """x0 [B,4], u [B,Nf,2], ref [B,Nf+1,4] (contiguous CUDA tensors, all fp64 like the reference or all fp32) ->
+    cost [B], grad [B,Nf,2] (, x [B,Nf+1,4]) in the same dtype."""
     if not torch.cuda.is_available():
         raise engine.Ihm2bError("ihm2_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     lib = engine.load_library()
     B, n = u.shape[0], u.shape[1]
+    dtype = u.dtype
+    if dtype not in (torch.float64, torch.float32):
+        raise ValueError(f"fp64 or fp32 tensors expected, got {dtype}")
     for t, shape in ((x0, (B, nx)), (u, (B, n, nu)), (ref, (B, n + 1, nx))):
-        if tuple(t.shape) != shape or t.dtype != torch.float64:
-            raise ValueError(f"expected fp64 tensor of shape {shape}, got {t.dtype} {tuple(t.shape)}")
+        if tuple(t.shape) != shape or t.dtype != dtype:
+            raise ValueError(f"expected {dtype} tensor of shape {shape}, got {t.dtype} {tuple(t.shape)}")
     w = weights.as_array() if isinstance(weights, DPCWeights) else np.ascontiguousarray(
         DPCWeights().as_array() if weights is None else weights, dtype=np.float64)
     assert w.shape == (10,)
-    cost = torch.empty(B, dtype=torch.float64, device=u.device)
+    cost = torch.empty(B, dtype=dtype, device=u.device)
     grad = torch.empty_like(u)
-    xtraj = torch.empty((B, n + 1, nx), dtype=torch.float64, device=u.device) if want_trajectory else None
-    rc = lib.ihm2b_dpc_rollout_grad_dev(
+    xtraj = torch.empty((B, n + 1, nx), dtype=dtype, device=u.device) if want_trajectory else None
+    entry = lib.ihm2b_dpc_rollout_grad_dev if dtype == torch.float64 else lib.ihm2b_dpc_rollout_grad_f32_dev
+    rc = entry(
         C.c_int64(B), C.c_int32(n), C.c_double(step), engine._dptr(x0), engine._dptr(u), engine._dptr(ref),
         w.ctypes.data_as(C.c_void_p), engine._dptr(cost), engine._dptr(grad), engine._dptr(xtraj), engine._stream())
     if rc != 0:

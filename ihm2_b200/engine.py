@@ -24,7 +24,7 @@ EXPORTS = (
     "ihm2b_set_track_index", "ihm2b_set_params", "ihm2b_set_iterate_dev", "ihm2b_get_iterate_dev",
     "ihm2b_reset_iterate", "ihm2b_shift_iterate", "ihm2b_solve_dev", "ihm2b_compute_control_host",
     "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_closed_loop_dev",
-    "ihm2b_dpc_rollout_grad_dev", "ihm2b_project_dev", "ihm2b_launch_count",
+    "ihm2b_dpc_rollout_grad_dev", "ihm2b_dpc_rollout_grad_f32_dev", "ihm2b_project_dev", "ihm2b_launch_count",
 )
 
 

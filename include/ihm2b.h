@@ -191,6 +191,12 @@ int ihm2b_dpc_rollout_grad_dev(int64_t batch, int32_t Nf, double dt, const doubl
                                const double* ref_dev, const double* weights_host, double* cost_dev,
                                double* grad_dev, double* xtraj_dev, void* stream);
 
+/* fp32 variant of the call above (the optional reduced-precision path; north_star tolerance 1e-4 relative): same
+ * layout with float buffers, weights still double on the host */
+int ihm2b_dpc_rollout_grad_f32_dev(int64_t batch, int32_t Nf, double dt, const float* x0_dev, const float* u_dev,
+                                   const float* ref_dev, const double* weights_host, float* cost_dev,
+                                   float* grad_dev, float* xtraj_dev, void* stream);
+
 /* ---- Cartesian pose -> Frenet state ------------------------------------------
  * Track::project (src/ihm2/src/common/tracks.cpp:200-288) followed by the control node's lateral offset and
  * heading error (src/ihm2/src/mpc_control_node.cpp:142-157), for a batch of cars.  No handle.  Device buffers:

@@ -33,6 +33,23 @@ def test_dpc_rollout_matches_oracle(B):
     assert _rel(grad.cpu().numpy(), og) < RTOL
 
 
+def test_dpc_rollout_fp32_within_stated_tolerance():
+    """The optional fp32 path: north_star's bar for fp32 is 1e-4 relative (per field, against the fp64 oracle)."""
+    from ihm2_b200 import dpc
+
+    B = 4096
+    x0, u, ref, w = dpc_inputs(B, seed=21)
+    f32 = [torch.tensor(a, dtype=torch.float32, device="cuda") for a in (x0, u, ref)]
+    cost, grad, xtraj = dpc.rollout_grad(*f32, w, want_trajectory=True)
+    assert cost.dtype == grad.dtype == torch.float32
+    # the oracle sees the same (rounded) inputs
+    oc, og, ox = olib.dpc_rollout_grad(*[t.double().cpu().numpy() for t in f32], w)
+    assert _rel(xtraj.double().cpu().numpy(), ox) < 1e-4
+    assert _rel(cost.double().cpu().numpy(), oc) < 1e-4
+    g = grad.double().cpu().numpy()
+    assert _rel(g[..., 0], og[..., 0]) < 1e-4 and _rel(g[..., 1], og[..., 1]) < 1e-4
+
+
 def test_dpc_rollout_n80_and_bad_horizon():
     from ihm2_b200 import dpc, engine
 
