@@ -20,8 +20,11 @@ from .projection import Track
 
 def closed_loop_cartesian(eng: Engine, track: Track, state: torch.Tensor, n_steps: int, T_max: float = 500.0,
                           delta_max: float = 0.5, s_tol: float = 2.0, track_index: torch.Tensor | None = None,
-                          log: bool = False):
+                          log: bool = False, controller=None):
     """state [B,8] = (X, Y, phi, v_x, v_y, r, T, delta) on the device, updated in place.
+
+    `controller(frenet [B,3], state [B,8]) -> u [B,2]`, when given, replaces the NMPC (e.g. a batched
+    `StanleyController`, the reference's fallback of new_python/controller.py:162-234); `eng` then only steps the plant.
 
     Returns dict(state, laps [B] int, lap_step [B] step index of the first completed lap or -1, fail [B] step of the
     first controller failure / plant NaN / lost projection or -1, s [B] last projected arc length, and with log=True
@@ -45,7 +48,10 @@ def closed_loop_cartesian(eng: Engine, track: Track, state: torch.Tensor, n_step
         frenet, flag = track.project(state[:, :3].contiguous(), s_guess, s_tol, track_index)
         s = frenet[:, 0]
         wrapped = alive & (s < s_last - 0.5 * L)                              # crossed the start of the table
-        if bool(wrapped.any()):
+        if controller is not None:
+            laps += wrapped.int()
+            lap_step = torch.where(wrapped & (lap_step < 0), torch.full_like(lap_step, step), lap_step)
+        elif bool(wrapped.any()):
             # the warm start lives one lap ahead of the new measurement: bring it back
             x_it, u_it = eng.get_iterate()
             x_it[wrapped, :, 0] -= L[wrapped, None]
@@ -54,10 +60,14 @@ def closed_loop_cartesian(eng: Engine, track: Track, state: torch.Tensor, n_step
             lap_step = torch.where(wrapped & (lap_step < 0), torch.full_like(lap_step, step), lap_step)
         s_last = torch.where(alive, s, s_last)
         s_guess = torch.where(alive, torch.fmod(s + state[:, 3] * dt, L), s_guess)   # mpc_control_node.cpp:145
-        x0 = torch.cat([frenet, state[:, 3:]], 1).contiguous()
-        eng.shift_iterate()
-        u0, status = eng.solve(x0)
-        ok = (status == 0) | (status == 2)                                    # mpc_control_node.cpp:190-197
+        if controller is not None:
+            u0 = controller(frenet, state)
+            ok = torch.isfinite(u0).all(1)
+        else:
+            x0 = torch.cat([frenet, state[:, 3:]], 1).contiguous()
+            eng.shift_iterate()
+            u0, status = eng.solve(x0)
+            ok = (status == 0) | (status == 2)                                # mpc_control_node.cpp:190-197
         u = u_prev.clone()
         u[:, 0] = torch.clamp(u0[:, 0], -T_max, T_max)                        # sim_node.cpp:148-149
         u[:, 1] = torch.clamp(torch.maximum(torch.minimum(u0[:, 1], u_prev[:, 1] + ddelta_max), u_prev[:, 1] - ddelta_max),
