@@ -40,7 +40,9 @@ def closed_loop_cartesian(eng: Engine, track: Track, state: torch.Tensor, n_step
     lap_step = torch.full((B,), -1, dtype=torch.int32, device=dev)
     fail = torch.full((B,), -1, dtype=torch.int32, device=dev)
     s_last = torch.zeros(B, dtype=torch.float64, device=dev)
-    ddelta_max = 0.01 * 2 * delta_max / 1.0                                   # sim_node.cpp:147
+    # sim_node.cpp:147 allows 0.01 * 2 delta_max / 1.0 per message, i.e. a full steering sweep per second at the node's
+    # 100 Hz; one message per control period dt here
+    ddelta_max = dt * 2 * delta_max / 1.0
     poses = [state.clone()] if log else None
     controls = [] if log else None
     for step in range(n_steps):
@@ -74,7 +76,8 @@ def closed_loop_cartesian(eng: Engine, track: Track, state: torch.Tensor, n_step
                               -delta_max, delta_max)
         u = torch.where((alive & ok)[:, None], u, u_prev)
         xn, _ = eng.sim_step(state, u)
-        bad = alive & (~ok | (flag != 0) | torch.isnan(xn).any(1))
+        lost = (flag != 0) if controller is None else torch.zeros_like(ok)   # the exception is the MPC node's (:154-156)
+        bad = alive & (~ok | lost | torch.isnan(xn).any(1))
         fail = torch.where(bad, torch.full_like(fail, step), fail)
         move = (alive & ~bad)[:, None]
         state.copy_(torch.where(move, xn, state))

@@ -64,3 +64,39 @@ def test_project_full_size_roundtrip():
     f = frenet.cpu().numpy()
     assert np.abs(f[:, 0] - s).max() < 0.2 and np.abs(f[:, 1] - n).max() < 0.03 and np.abs(f[:, 2] - psi).max() < 0.03
     assert int(flag.sum()) == 0
+
+
+def test_stanley_baseline_follows_the_centre_line_on_the_cartesian_plant():
+    """The two-node loop (projection -> controller -> Cartesian kin6/dyn6 plant) with the reference's Stanley fallback
+    (new_python/controller.py:162-234) as the controller: the cars settle at v_ref on the centre line."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.cartesian_loop import closed_loop_cartesian
+    from ihm2_b200.controller import StanleyController
+    from ihm2_b200.engine import Engine
+    from ihm2_b200.projection import Track
+
+    mp = load_packaged_track("fsds_competition_1")
+    B, v_ref, n_steps = 8, 5.0, 400
+    cfg = _abi.make_config(batch=B, n_grid=len(mp.s_ref), sim_model=_abi.SIM_KIN6C_DYN6C)
+    eng = Engine(cfg, mp.s_ref, mp.kappa_ref, lap_length=np.array([mp.lap_length]))
+    trk = Track(mp)
+    i0 = len(mp.s_ref) // 3
+    state = torch.zeros(B, 8, dtype=torch.float64, device="cuda")
+    state[:, 0], state[:, 1], state[:, 2] = float(mp.X_ref[i0]), float(mp.Y_ref[i0]), float(mp.phi_ref[i0])
+    state[:, 1] += torch.linspace(-0.3, 0.3, B, dtype=torch.float64, device="cuda")
+    stanley = StanleyController()
+    s_tab, k_tab = torch.tensor(mp.s_ref, device="cuda"), torch.tensor(mp.kappa_ref, device="cuda")
+
+    def controller(frenet, st):
+        idx = torch.searchsorted(s_tab, frenet[:, 0].contiguous()).clamp(1, len(s_tab) - 1)
+        w = (frenet[:, 0] - s_tab[idx - 1]) / (s_tab[idx] - s_tab[idx - 1])
+        kappa = k_tab[idx - 1] + w * (k_tab[idx] - k_tab[idx - 1])
+        return stanley.compute_control(frenet[:, 1], frenet[:, 2], st[:, 3], torch.full_like(kappa, v_ref), kappa)
+
+    out = closed_loop_cartesian(eng, trk, state, n_steps, controller=controller, log=True)
+    eng.close()
+    assert (out["fail"] < 0).all()
+    s_end = out["s"].cpu().numpy()
+    assert np.all(np.abs(s_end - (v_ref * n_steps * cfg.dt - 6.0)) < 6.0)      # ~ 5 m/s minus the start-up
+    frenet, _ = trk.project(out["state"][:, :3].contiguous(), out["s"])
+    assert frenet[:, 1].abs().max().item() < 0.1 and (out["state"][:, 3] - v_ref).abs().max().item() < 0.2
