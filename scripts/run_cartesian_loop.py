@@ -1,5 +1,5 @@
 """Closed loop with the Cartesian kin6 / dyn6 plants (ROS sim node semantics) + projection + NMPC, one car per
-track (or B copies).  python scripts/run_cartesian_loop.py [track=fsds_competition_1] [n_steps=1200] [B=1] [mode=rti]"""
+track (or B copies).  python scripts/run_cartesian_loop.py [track=fsds_competition_1] [n_steps=1200] [B=1] [mode=rti] [s_target=40]"""
 import json, os, sys, time
 import numpy as np, torch
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
@@ -13,8 +13,9 @@ name = sys.argv[1] if len(sys.argv) > 1 else "fsds_competition_1"
 n_steps = int(sys.argv[2]) if len(sys.argv) > 2 else 1200
 B = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 mode = sys.argv[4] if len(sys.argv) > 4 else "rti"
+s_target = float(sys.argv[5]) if len(sys.argv) > 5 else 40.0
 mp = load_packaged_track(name)
-kw = dict(sim_model=_abi.SIM_KIN6C_DYN6C)
+kw = dict(sim_model=_abi.SIM_KIN6C_DYN6C, s_target=s_target)
 if mode.startswith("sqp"):
     kw.update(nlp_solver=_abi.SQP, nlp_max_iter=2, globalization=_abi.MERIT_BACKTRACKING)
 if mode.endswith("tolerant"):
@@ -38,7 +39,7 @@ torch.cuda.synchronize(); t0 = time.perf_counter()
 out = closed_loop_cartesian(eng, trk, state, n_steps, log=(B == 1))
 torch.cuda.synchronize(); wall = time.perf_counter() - t0
 laps, lap_step, fail = [out[k].cpu().numpy() for k in ("laps", "lap_step", "fail")]
-res = {"track": name, "mode": mode, "instances": B, "n_steps": n_steps, "lap_length": mp.lap_length, "wall_s": wall,
+res = {"track": name, "mode": mode, "s_target": s_target, "instances": B, "n_steps": n_steps, "lap_length": mp.lap_length, "wall_s": wall,
        "laps_completed": int((laps > 0).sum()), "failed": int((fail >= 0).sum()),
        "first_lap_time_s": float(np.median((lap_step[lap_step >= 0] + 1) * cfg.dt)) if (lap_step >= 0).any() else None,
        "median_fail_step": float(np.median(fail[fail >= 0])) if (fail >= 0).any() else None,
@@ -48,5 +49,5 @@ if B == 1:
     res["v_x_max"] = float(np.nanmax(P[:, 3])); res["v_x_mean"] = float(np.nanmean(P[:, 3]))
 print(json.dumps(res))
 os.makedirs("gpurun_out", exist_ok=True)
-json.dump(res, open(f"gpurun_out/cartesian_loop_{name}_{mode}_{B}.json", "w"), indent=1)
+json.dump(res, open(f"gpurun_out/cartesian_loop_{name}_{mode}_{B}_st{int(s_target)}.json", "w"), indent=1)
 eng.close()
