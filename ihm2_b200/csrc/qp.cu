@@ -140,7 +140,11 @@ __device__ __forceinline__ RowDef row_path(const KCfg& cf, int r) {
 __device__ __forceinline__ RowDef row_term(const KCfg& cf, int r) {
   RowDef R;
   R.iu = 0; R.cu = 0.0; R.cx = 1.0;
+#ifdef IHM2B_EXPERIMENT_TERMINAL_6_7   // experiment only: the terminal box on (n, v_x, T, delta) instead of the literal set
+  R.ix = (r == 0) ? 1 : (r == 1) ? 3 : (r == 2) ? 6 : 7;
+#else
   R.ix = (r == 0) ? 1 : (r == 1) ? 3 : (r == 2) ? 4 : 5;
+#endif
   const double bd = (r == 0) ? cf.n_max : (r == 1) ? cf.v_x_max : (r == 2) ? cf.T_max : cf.delta_max;
   R.lb = -bd; R.ub = bd;
   return R;
@@ -163,7 +167,11 @@ __device__ __forceinline__ CtDef ct_path(int a) {
 }
 __device__ __forceinline__ CtDef ct_term(int a) {
   CtDef d;
+#ifdef IHM2B_EXPERIMENT_TERMINAL_6_7
+  d.i1 = (a == 1) ? 0 : (a == 3) ? 1 : (a == 6) ? 2 : 3; d.c1 = (a == 1 || a == 3 || a == 6 || a == 7) ? 1.0 : 0.0;
+#else
   d.i1 = (a == 1) ? 0 : (a == 3) ? 1 : (a == 4) ? 2 : 3; d.c1 = (a == 1 || a == 3 || a == 4 || a == 5) ? 1.0 : 0.0;
+#endif
   d.i2 = 0; d.c2 = 0.0;
   return d;
 }
