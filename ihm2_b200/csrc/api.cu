@@ -35,7 +35,7 @@ void launch_merit_base(const KCfg& cf, const Work& w, const LineSearch& ls, cons
 void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int32_t* sqp_active,
                         int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
-                     const double* u, double* xn, int32_t* model, cudaStream_t stream);
+                     const double* u, double* xn, int32_t* model, int32_t* order_scratch, cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
                              const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
                              int32_t* fail, int32_t* active_mask, cudaStream_t stream);
@@ -69,6 +69,7 @@ struct ihm2b_handle {
   double *x0_dev, *u0_dev, *xn_dev;
   int32_t* status_dev;
   int32_t* active_dev;   // SQP mode: instances still iterating
+  int32_t* sim_order_dev;  // [B + 2] plant step: instances grouped by the model they take, two counters
   int32_t* order_dev;    // launch order of the QP kernel (longest first by the previous solve's iteration counts)
   bool have_order;
   LineSearch ls;         // allocated when globalization = MERIT_BACKTRACKING
@@ -207,6 +208,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->status_dev, B);
   ALLOC(h->active_dev, B);
   ALLOC(h->order_dev, B);
+  ALLOC(h->sim_order_dev, B + 2);
   memset(&h->ls, 0, sizeof h->ls);
   if (cfg->nlp_solver == IHM2B_SQP && cfg->globalization == IHM2B_MERIT_BACKTRACKING) {
     ALLOC(h->ls.base_x, B * (N + 1) * 8);
@@ -507,7 +509,7 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double
   if (rc) return rc;
   if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
   if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6C_DYN6C) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
-  launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, static_cast<cudaStream_t>(stream));
+  launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, h->sim_order_dev, static_cast<cudaStream_t>(stream));
   h->launches++;
   CU(cudaGetLastError());
   return IHM2B_OK;
@@ -536,7 +538,7 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
     rc = ihm2b_shift_iterate(h, stream);
     if (!rc) rc = ihm2b_solve_dev(h, x, h->u0_dev, h->status_dev, stream);
     if (rc) { h->w.active = nullptr; return rc; }
-    launch_sim_step(h->cfg, h->k, h->w, x, h->u0_dev, h->xn_dev, nullptr, s);
+    launch_sim_step(h->cfg, h->k, h->w, x, h->u0_dev, h->xn_dev, nullptr, h->sim_order_dev, s);
     launch_closed_loop_post((int)B, step, h->track, h->lap_len, h->status_dev, h->u0_dev, h->xn_dev, x, xlog, ulog, done,
                             failp, masked ? h->active_dev : nullptr, s);
     h->launches += 2;

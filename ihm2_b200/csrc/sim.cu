@@ -134,10 +134,11 @@ struct SimCfg {
 // blockDim 128 = 32 problems; lane group of 4 = one problem
 __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Work w, const double* __restrict__ xin,
                                                         const double* __restrict__ uin, double* __restrict__ xout,
-                                                        int32_t* __restrict__ model_out) {
+                                                        int32_t* __restrict__ model_out, const int32_t* __restrict__ order) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int b = gid >> 2, i = gid & 3;
-  if (b >= sc.B) return;  // whole 4-lane groups leave together
+  const int slot = gid >> 2, i = gid & 3;
+  if (slot >= sc.B) return;  // whole 4-lane groups leave together
+  const int b = order ? order[slot] : slot;
   if (w.active && !w.active[b]) return;   // closed loop: instance finished its lap or stopped
   const unsigned gm = 0xFu << (threadIdx.x & 28);
   const int t = w.track[b];
@@ -225,15 +226,44 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
   }
 }
 
+// With a model switch the eight instances of a warp would mix the kinematic and the (several times longer) dynamic
+// right-hand side and every warp would run both; this puts the instances that take the kinematic model first and the
+// others last (order within a class is whatever the atomics give: results do not depend on it).
+__global__ void sim_partition_kernel(int B, int mode, double sw, const double* __restrict__ params, const double* __restrict__ x,
+                                     const int32_t* __restrict__ active, int32_t* __restrict__ counters, int32_t* __restrict__ order) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  bool kin;
+  if (mode == IHM2B_SIM_KIN6_DYN6) {
+    const double lR = params[(size_t)b * NP + IHM2B_P_LR], C = lR / (lR + params[(size_t)b * NP + IHM2B_P_LF]);
+    const double beta = atan(C * tan(x[(size_t)b * NX + 7]));
+    const double vx = x[(size_t)b * NX + 3], vy = x[(size_t)b * NX + 4];
+    kin = (vx * vx + vy * vy) * sin(beta) / lR <= sw;
+  } else {
+    kin = hypot(x[(size_t)b * NX + 3], x[(size_t)b * NX + 4]) < sw;
+  }
+  if (active && !active[b]) kin = true;   // idle instances cost nothing wherever they sit
+  if (kin) order[atomicAdd(&counters[0], 1)] = b;
+  else order[B - 1 - atomicAdd(&counters[1], 1)] = b;
+}
+
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u,
-                     double* xn, int32_t* model, cudaStream_t stream) {
+                     double* xn, int32_t* model, int32_t* order_scratch, cudaStream_t stream) {
   SimCfg sc;
   sc.B = cf.B; sc.n_grid = cf.n_grid; sc.model = cfg.sim_model; sc.n_sub = cfg.sim_steps > 0 ? cfg.sim_steps : 1;
   sc.h = cfg.dt / sc.n_sub; sc.sw = cfg.sim_switch;
   for (int i = 0; i < 16; i++) sc.A[i] = cfg.sim_A[i];
   for (int i = 0; i < 4; i++) sc.b[i] = cfg.sim_b[i];
   const int threads = 128, total = cf.B * 4;
-  sim_step_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn, model);
+  const int32_t* order = nullptr;
+  const bool switching = cfg.sim_model == IHM2B_SIM_KIN6_DYN6 || cfg.sim_model == IHM2B_SIM_KIN6C_DYN6C;
+  if (switching && order_scratch && cf.B > 8) {   // order_scratch: [B] order + 2 counters
+    cudaMemsetAsync(order_scratch + cf.B, 0, 2 * sizeof(int32_t), stream);
+    sim_partition_kernel<<<(cf.B + 255) / 256, 256, 0, stream>>>(cf.B, cfg.sim_model, cfg.sim_switch, w.params, x, w.active,
+                                                                 order_scratch + cf.B, order_scratch);
+    order = order_scratch;
+  }
+  sim_step_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn, model, order);
 }
 
 // closed-loop bookkeeping after solve + plant step (python/main.py:503-517): an instance stops at
