@@ -52,6 +52,9 @@ template <> struct Vec4<float> { using type = float4; };
 #ifndef DPC_MIN_BLOCKS
 #define DPC_MIN_BLOCKS 8
 #endif
+#ifndef DPC_BLOCK
+#define DPC_BLOCK 128
+#endif
 #if DPC_NOINLINE
 #define DPC_INLINE __noinline__
 #else
@@ -94,7 +97,7 @@ __device__ __forceinline__ T track_term(const T x[4], const V4 r, const T* q, T 
 }
 
 template <int NF, typename T>
-__global__ void __launch_bounds__(128, DPC_MIN_BLOCKS)
+__global__ void __launch_bounds__(DPC_BLOCK, DPC_MIN_BLOCKS)
 dpc_rollout_grad_kernel(long long B, DpcWeights<T> w, const T* __restrict__ x0, const T* __restrict__ u,
                         const T* __restrict__ ref, T* __restrict__ cost, T* __restrict__ grad, T* __restrict__ xtraj) {
   static_assert(NF % 2 == 0, "stages move in pairs");
@@ -203,9 +206,9 @@ cudaError_t launch_dpc_t(long long B, int Nf, double dt, const double* weights, 
   w.r[0] = T(weights[4]);
   w.r[1] = T(weights[5]);
   w.dt = T(dt);
-  const unsigned grid = (unsigned)((B + 127) / 128);
-  if (Nf == 40) dpc_rollout_grad_kernel<40, T><<<grid, 128, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
-  else if (Nf == 80) dpc_rollout_grad_kernel<80, T><<<grid, 128, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
+  const unsigned grid = (unsigned)((B + DPC_BLOCK - 1) / DPC_BLOCK);
+  if (Nf == 40) dpc_rollout_grad_kernel<40, T><<<grid, DPC_BLOCK, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
+  else if (Nf == 80) dpc_rollout_grad_kernel<80, T><<<grid, DPC_BLOCK, 0, stream>>>(B, w, x0, u, ref, cost, grad, xtraj);
   else return cudaErrorInvalidValue;
   return cudaGetLastError();
 }
