@@ -67,6 +67,11 @@ class Config(C.Structure):
         ("track_half_W", C.c_double),
         ("slack_z", C.c_double),
         ("slack_Z", C.c_double),
+        ("T_dot_max", C.c_double),
+        ("delta_dot_max", C.c_double),
+        ("qp_split_step", C.c_int32),
+        ("qp_infeas_exit", C.c_int32),
+        ("qp_thr0", C.c_double),
     ]
 
 
@@ -119,6 +124,21 @@ def _collocation_tableau(c: np.ndarray):
     return A, b, c
 
 
+# Interior-point presets.  The HPIPM rows restate `d_ocp_qp_ipm_arg_set_default` (mu0, residual tolerances, split
+# step) with acados' own iteration cap of 50 (`qp_solver_iter_max`) in place of HPIPM's 15 / 30 / 100, as remembered:
+# HPIPM / acados are not in this image, so the numbers are unpinned.  The QP is strictly convex, so every
+# preset converges to the same point; they differ in iteration count and in what happens to infeasible QPs.
+# "B200" (default): start barrier parameter matched to the size of the cost gradient of this OCP (the terminal
+# weight times the progress reference, ~ 3e4), and an early exit for primal-infeasible QPs.
+HPIPM_MODES = {
+    "B200":      dict(mu0=3e3, tol=1e-9, tol_comp=1e-8, max_iter=50, split_step=False, infeas_exit=True),
+    "SPEED_ABS": dict(mu0=1e1, tol=1e-9, tol_comp=1e-8, max_iter=50, split_step=True, infeas_exit=False),
+    "SPEED":     dict(mu0=1e1, tol=1e-6, tol_comp=1e-6, max_iter=50, split_step=True, infeas_exit=False),
+    "BALANCE":   dict(mu0=1e1, tol=1e-8, tol_comp=1e-8, max_iter=50, split_step=False, infeas_exit=False),
+    "ROBUST":    dict(mu0=1e2, tol=1e-8, tol_comp=1e-8, max_iter=100, split_step=False, infeas_exit=False),
+}
+
+
 def make_config(
     batch: int,
     n_grid: int,
@@ -139,10 +159,11 @@ def make_config(
     nlp_solver: int = SQP_RTI,
     nlp_max_iter: int = 2,
     globalization: int = FIXED_STEP,
-    qp_max_iter: int = 50,
-    qp_mu0: float = 10.0,
-    qp_tol: float = 1e-9,
-    qp_tol_comp: float = 1e-8,
+    qp_max_iter: int | None = None,
+    qp_mu0: float | None = None,
+    qp_tol: float | None = None,
+    qp_tol_comp: float | None = None,
+    hpipm_mode: str | None = None,
     nlp_tol: float = 1e-6,
     cost_scaling: bool = True,
     sim_model: int = SIM_KIN6_DYN6,
@@ -150,9 +171,23 @@ def make_config(
     nonlinear_constraints: bool = False,
     schedule_by_history: bool = True,
     qp_tolerate_maxiter: bool = False,
+    qp_split_step: bool | None = None,
+    qp_infeas_exit: bool | None = None,
+    qp_thr0: float = 0.1,
 ) -> Config:
     """Fill ihm2b_config from `IHM2Controller.__init__` style arguments
-    (new_python/controller.py:250-309; python/mpc.py:77-99 for the bounds)."""
+    (new_python/controller.py:250-309; python/mpc.py:77-99 for the bounds).
+
+    `hpipm_mode` (new_python/controller.py:304 selects "SPEED_ABS"; python/generate_all.py:107-116 "ROBUST") picks
+    one of the interior-point presets of HPIPM_MODES; None is this library's own default.  Explicit qp_* arguments
+    override the preset."""
+    mode = dict(HPIPM_MODES["B200" if hpipm_mode is None else hpipm_mode])
+    qp_max_iter = mode["max_iter"] if qp_max_iter is None else qp_max_iter
+    qp_mu0 = mode["mu0"] if qp_mu0 is None else qp_mu0
+    qp_tol = mode["tol"] if qp_tol is None else qp_tol
+    qp_tol_comp = mode["tol_comp"] if qp_tol_comp is None else qp_tol_comp
+    qp_split_step = mode["split_step"] if qp_split_step is None else qp_split_step
+    qp_infeas_exit = mode["infeas_exit"] if qp_infeas_exit is None else qp_infeas_exit
     p = default_params()
     cf = Config()
     cf.batch, cf.N, cf.n_tracks, cf.n_grid = batch, Nf, n_tracks, n_grid
@@ -182,5 +217,7 @@ def make_config(
     cf.sim_b[:] = b.tolist()
     cf.sim_switch = 3.0
     cf.track_half_L, cf.track_half_W = 0.5 * 3.19, 0.5 * 1.55  # python/constants.py:56-57
-    cf.slack_z = cf.slack_Z = 100.0
+    cf.slack_z = cf.slack_Z = 100.0  # zl = zu = Zl = Zu = 100 (old/generate_acaods_interface.py:383-390)
+    cf.T_dot_max, cf.delta_dot_max = T_dot_max, delta_dot_max
+    cf.qp_split_step, cf.qp_infeas_exit, cf.qp_thr0 = int(qp_split_step), int(qp_infeas_exit), qp_thr0
     return cf

@@ -96,6 +96,14 @@ typedef struct ihm2b_config {
   double sim_switch;      /* fkin6 -> fdyn6 when v^2 sin(beta)/l_R > sim_switch (main.py:482-489) */
   double track_half_L, track_half_W; /* car half length / width for the track constraint */
   double slack_z, slack_Z; /* L1 / L2 slack penalties (old/...interface.py:383-390) */
+  double T_dot_max, delta_dot_max; /* bounds of the T_dot / delta_dot rows of h (old/...interface.py:418-436) */
+  /* ---- interior-point strategy (HPIPM mode presets are filled in by the host layer, see
+   * ihm2_b200/_abi.py:hpipm_mode; new_python/controller.py:304 selects SPEED_ABS) ---- */
+  int32_t qp_split_step;  /* 1: separate primal and dual step lengths (HPIPM split_step, on in the SPEED modes) */
+  int32_t qp_infeas_exit; /* 1: stop a QP whose primal infeasibility stagnates while the barrier parameter has
+                             collapsed (status 4 after a few iterations instead of qp_max_iter); HPIPM has no such
+                             test, 0 reproduces it */
+  double qp_thr0;         /* floor of the initial slacks t (HPIPM thr0 = 0.1) */
 } ihm2b_config;
 
 typedef struct ihm2b_handle ihm2b_handle;

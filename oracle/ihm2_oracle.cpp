@@ -35,6 +35,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <vector>
@@ -58,12 +60,14 @@ struct Track {
   int n;              // table length (3 laps x 500 in the reference)
   const double* s;    // s_ref[n], strictly increasing
   const double* k;    // kappa_ref[n]
+  const double* wr = nullptr;   // right_width[n], left_width[n] (may be null: no track constraint)
+  const double* wl = nullptr;
 };
 
 // CasADi interpolant("linear", lookup_mode "exact"): binary search for the interval that
 // contains s, clamped to [0, n-2] so that values outside the grid extrapolate linearly
 // (python/models.py:290-295).  Returns kappa and the slope of the active segment.
-inline void kappa_lookup(const Track& tr, double s, double& kap, double& dkap) {
+inline void table_lookup(const Track& tr, const double* tab, double s, double& val, double& slope) {
   int lo = 0, hi = tr.n;  // upper_bound
   while (lo < hi) {
     int mid = (lo + hi) >> 1;
@@ -72,8 +76,55 @@ inline void kappa_lookup(const Track& tr, double s, double& kap, double& dkap) {
   int i = lo - 1;
   if (i < 0) i = 0;
   if (i > tr.n - 2) i = tr.n - 2;
-  dkap = (tr.k[i + 1] - tr.k[i]) / (tr.s[i + 1] - tr.s[i]);
-  kap = tr.k[i] + dkap * (s - tr.s[i]);
+  slope = (tab[i + 1] - tab[i]) / (tr.s[i + 1] - tr.s[i]);
+  val = tab[i] + slope * (s - tr.s[i]);
+}
+inline void kappa_lookup(const Track& tr, double s, double& kap, double& dkap) { table_lookup(tr, tr.k, s, kap, dkap); }
+
+// Nonlinear path constraints h(x, u) of the gen-1 OCP (old/generate_acaods_interface.py:312-325 for the
+// 8-state Frenet model; bounds and slacks :351-449), on the quantities of the current controller model
+// (python/models.py:232-307: F_Rx, F_Fx, beta as in fkin6):
+//   h0 =  n - L/2 sin|psi| + W/2 cos psi - right_width(s)      (literal signs)
+//   h1 = -n + L/2 sin|psi| + W/2 cos psi - left_width(s)
+//   h2 = T_dot = (u_T - T) / t_T,   h3 = delta_dot = (u_delta - delta) / t_delta
+//   h4 = a_lat = (-F_Rx sin(beta) + F_Fx sin(delta - beta)) / m + (v_x^2 + v_y^2) sin(beta) / l_R
+// width interpolants are "linear" CasADi interpolants on s_ref (old/generate.py:44-46).  Jh [5][10] in (x, u) order.
+constexpr int NH = 5, NH_E = 2;
+void con_h(const double* x, const double* u, const double* p, const Track& tr, double half_L, double half_W,
+           double* h, double (*Jh)[10]) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], T = x[6], dl = x[7];
+  const double m = p[P_M], lR = p[P_LR], lF = p[P_LF], C = lR / (lR + lF);
+  double wr = 0, dwr = 0, wl = 0, dwl = 0;
+  if (tr.wr) table_lookup(tr, tr.wr, x[0], wr, dwr);
+  if (tr.wl) table_lookup(tr, tr.wl, x[0], wl, dwl);
+  const double sp = std::sin(std::fabs(psi)), cp = std::cos(psi);
+  const double sg = (psi > 0) - (psi < 0);   // d|psi|/dpsi (CasADi: sign)
+  h[0] = n - half_L * sp + half_W * cp - wr;
+  h[1] = -n + half_L * sp + half_W * cp - wl;
+  h[2] = (u[0] - T) / p[P_TT];
+  h[3] = (u[1] - dl) / p[P_TD];
+  const double Fm = p[P_CM0] * T;
+  const double th = std::tanh(10.0 * vx);
+  const double poly = p[P_CR0] + p[P_CR1] * vx + p[P_CR2] * vx * vx;
+  const double FRx = 0.5 * Fm - poly * th, FFx = 0.5 * Fm;
+  const double td = std::tan(dl), beta = std::atan(C * td);
+  const double sb = std::sin(beta), cb = std::cos(beta), sdb = std::sin(dl - beta), cdb = std::cos(dl - beta);
+  const double G = C * (1.0 + td * td) / (1.0 + C * C * td * td);
+  const double v2 = vx * vx + vy * vy;
+  h[4] = (-FRx * sb + FFx * sdb) / m + v2 * sb / lR;
+  if (!Jh) return;
+  for (int i = 0; i < NH; i++)
+    for (int j = 0; j < 10; j++) Jh[i][j] = 0.0;
+  const double dabs = std::cos(std::fabs(psi)) * sg;   // d sin|psi| / d psi
+  Jh[0][0] = -dwr; Jh[0][1] = 1.0;  Jh[0][2] = -half_L * dabs - half_W * std::sin(psi);
+  Jh[1][0] = -dwl; Jh[1][1] = -1.0; Jh[1][2] = half_L * dabs - half_W * std::sin(psi);
+  Jh[2][6] = -1.0 / p[P_TT]; Jh[2][8] = 1.0 / p[P_TT];
+  Jh[3][7] = -1.0 / p[P_TD]; Jh[3][9] = 1.0 / p[P_TD];
+  const double dFd = -(p[P_CR1] + 2.0 * p[P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th);
+  Jh[4][3] = -dFd * sb / m + 2.0 * vx * sb / lR;
+  Jh[4][4] = 2.0 * vy * sb / lR;
+  Jh[4][6] = 0.5 * p[P_CM0] * (sdb - sb) / m;
+  Jh[4][7] = (-FRx * cb * G + FFx * cdb * (1.0 - G)) / m + v2 * cb * G / lR;
 }
 
 // fkin6 continuous dynamics and (optionally) its Jacobian J[8][10] w.r.t. (x,u),
@@ -466,13 +517,18 @@ namespace {
 // z_k = (u_k, x_k).  The LINEAR_LS cost is exactly quadratic and all path constraints are
 // linear, so only the dynamics are linearised.
 // ---------------------------------------------------------------------------------------
-struct Row { double c[NZ]; double lb, ub; };
+// One two-sided inequality row  lb <= c'z + e <= ub  of a stage (z = (u, x)).  soft: the row carries a lower and an
+// upper slack, lb - sL <= c'z + e <= ub + sU, sL, sU >= 0, penalised by z_s (sL + sU) + Z_s/2 (sL^2 + sU^2)
+// (acados idxsbx / idxsh with zl = zu, Zl = Zu: old/generate_acaods_interface.py:383-398, 413, 417, 438, 449).
+struct Row { double c[NZ]; double e, lb, ub; int soft; };
 
 struct Qp {
   int N;
   std::vector<double> A, B, c;        // [N][8][8], [N][8][2], [N][8]: x+ = A x + B u + c
   std::vector<double> H, g;           // [N+1][10][10], [N+1][10]
   std::vector<std::vector<Row>> rows; // [N+1]
+  std::vector<int> nstatic;           // [N+1] rows that do not depend on the linearisation point
+  std::vector<double> zs, Zs;         // [N+1] slack penalties of the stage (cost scaling applied)
   double x0[NX];
 };
 
@@ -509,31 +565,66 @@ void build_cost(const ihm2b_config& cf, double s0, Qp& qp) {
 
 void build_rows(const ihm2b_config& cf, Qp& qp) {
   const int N = cf.N;
+  const bool nl = cf.nonlinear_constraints != 0;
   qp.rows.assign(N + 1, {});
-  auto unit = [](int idx, double lb, double ub) {
-    Row r; std::memset(&r, 0, sizeof r); r.c[idx] = 1.0; r.lb = lb; r.ub = ub; return r;
+  qp.nstatic.assign(N + 1, 0);
+  qp.zs.assign(N + 1, 0.0); qp.Zs.assign(N + 1, 0.0);
+  auto unit = [](int idx, double lb, double ub, int soft) {
+    Row r; std::memset(&r, 0, sizeof r); r.c[idx] = 1.0; r.lb = lb; r.ub = ub; r.soft = soft; return r;
   };
   for (int k = 0; k <= N; k++) {
     auto& R = qp.rows[k];
+    // acados scales the slack penalties of a stage like the rest of its cost (ocp_nlp_cost_ls scaling)
+    qp.zs[k] = (k < N ? cf.cost_scale_stage : cf.cost_scale_terminal) * cf.slack_z;
+    qp.Zs[k] = (k < N ? cf.cost_scale_stage : cf.cost_scale_terminal) * cf.slack_Z;
     if (k < N) {
-      R.push_back(unit(0, -cf.T_max, cf.T_max));          // idxbu (mpc.py:86-89)
-      R.push_back(unit(1, -cf.delta_max, cf.delta_max));
+      R.push_back(unit(0, -cf.T_max, cf.T_max, 0));          // idxbu (mpc.py:86-89)
+      R.push_back(unit(1, -cf.delta_max, cf.delta_max, 0));
       Row g0; std::memset(&g0, 0, sizeof g0);             // C, D (mpc.py:91-99)
       g0.c[0] = 1.0; g0.c[NU + 6] = -1.0; g0.lb = -cf.g_T_max; g0.ub = cf.g_T_max;
       Row g1; std::memset(&g1, 0, sizeof g1);
       g1.c[1] = 1.0; g1.c[NU + 7] = -1.0; g1.lb = -cf.g_delta_max; g1.ub = cf.g_delta_max;
       R.push_back(g0); R.push_back(g1);
-      if (k > 0) {  // idxbx = [1,3,6,7] (mpc.py:78-80); stage 0 carries x0 instead
-        R.push_back(unit(NU + 1, -cf.n_max, cf.n_max));
-        R.push_back(unit(NU + 3, 0.0, cf.v_x_max));
-        R.push_back(unit(NU + 6, -cf.T_max, cf.T_max));
-        R.push_back(unit(NU + 7, -cf.delta_max, cf.delta_max));
+      if (k > 0) {  // idxbx = [1,3,6,7] (mpc.py:78-80); stage 0 carries x0 instead.
+        // With the gen-1 slack sets the bounds at positions idxsbx = [2, 3] of idxbx are soft
+        // (old/generate_acaods_interface.py:413): here T and delta.
+        R.push_back(unit(NU + 1, -cf.n_max, cf.n_max, 0));
+        R.push_back(unit(NU + 3, 0.0, cf.v_x_max, 0));
+        R.push_back(unit(NU + 6, -cf.T_max, cf.T_max, nl));
+        R.push_back(unit(NU + 7, -cf.delta_max, cf.delta_max, nl));
       }
-    } else {  // idxbx_e = [1,3,4,5] with the n / v_x / T / delta bounds (literal, mpc.py:81-83)
-      R.push_back(unit(NU + 1, -cf.n_max, cf.n_max));
-      R.push_back(unit(NU + 3, -cf.v_x_max, cf.v_x_max));
-      R.push_back(unit(NU + 4, -cf.T_max, cf.T_max));
-      R.push_back(unit(NU + 5, -cf.delta_max, cf.delta_max));
+    } else {  // idxbx_e = [1,3,4,5] with the n / v_x / T / delta bounds (literal, mpc.py:81-83); idxsbx_e = [2, 3]
+      R.push_back(unit(NU + 1, -cf.n_max, cf.n_max, 0));
+      R.push_back(unit(NU + 3, -cf.v_x_max, cf.v_x_max, 0));
+      R.push_back(unit(NU + 4, -cf.T_max, cf.T_max, nl));
+      R.push_back(unit(NU + 5, -cf.delta_max, cf.delta_max, nl));
+    }
+    qp.nstatic[k] = (int)R.size();
+  }
+}
+
+// rows of the linearised h(x, u) (all soft, idxsh = all: old/generate_acaods_interface.py:438, 449), appended
+// after the static rows:  lh <= h(zbar) + Jh (z - zbar) <= uh
+void build_h_rows(const ihm2b_config& cf, const double* p, const Track& tr, const double* x, const double* u, Qp& qp) {
+  if (!cf.nonlinear_constraints) return;
+  const int N = cf.N;
+  const double lh[NH] = {-1e3, -1e3, -cf.T_dot_max, -cf.delta_dot_max, -cf.a_lat_max};
+  const double uh[NH] = {0.0, 0.0, cf.T_dot_max, cf.delta_dot_max, cf.a_lat_max};
+  for (int k = 0; k <= N; k++) {
+    auto& R = qp.rows[k];
+    R.resize(qp.nstatic[k]);
+    double h[NH], Jh[NH][10];
+    const double uz[NU] = {0.0, 0.0};
+    const double* uk = (k < N) ? &u[k * NU] : uz;
+    con_h(&x[k * NX], uk, p, tr, cf.track_half_L, cf.track_half_W, h, Jh);
+    const int nh = (k < N) ? NH : NH_E;
+    for (int i = 0; i < nh; i++) {
+      Row r; std::memset(&r, 0, sizeof r);
+      double e = h[i];
+      for (int a = 0; a < NX; a++) { r.c[NU + a] = Jh[i][a]; e -= Jh[i][a] * x[k * NX + a]; }
+      if (k < N) for (int a = 0; a < NU; a++) { r.c[a] = Jh[i][NX + a]; e -= Jh[i][NX + a] * uk[a]; }
+      r.e = e; r.lb = lh[i]; r.ub = uh[i]; r.soft = 1;
+      R.push_back(r);
     }
   }
 }
@@ -542,51 +633,68 @@ struct QpSol {
   std::vector<double> z;     // [N+1][10]
   std::vector<double> pi;    // [N+1][8]  (pi[0] unused)
   std::vector<std::vector<double>> lamL, lamU, tL, tU;
-  int iters, status;         // status: 0 ok, 1 max iter, 2 min step, 3 nan
+  std::vector<std::vector<double>> sL, sU, lamSL, lamSU;   // slacks of the soft rows and the multipliers of s >= 0
+  int iters, status;         // status: 0 ok, 1 max iter, 2 min step, 3 nan, 4 infeasible (stagnation exit)
   double mu, res_g, res_b, res_d, res_m, mag_g, mag_b, mag_d;
 };
+
+inline double row_val(const Row& R, const double* z) {
+  double v = R.e;
+  for (int a = 0; a < NZ; a++) v += R.c[a] * z[a];
+  return v;
+}
 
 // Mehrotra predictor-corrector primal-dual IPM; KKT step by a Riccati recursion
 // (what HPIPM's d_ocp_qp_ipm_solve does: SURVEY App. C).  Works on the residual (delta)
 // form of the Newton system, x_0 is held fixed (stage 0 embeds the measured state).
+// Soft rows: the slack pair (sL, sU) and the multipliers of sL, sU >= 0 are eliminated row by row from the Newton
+// system (HPIPM does the same with its `Zs_inv` vectors), which only changes the barrier weight and the
+// first-order term the row contributes to the Riccati recursion:
+//   D = Z + lam/t + lamS/s,   gamma_eff = (lam/t)(Z + lamS/s)/D,   q_eff = q - (lam/t)(r_s + q + q_S)/D.
 void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
   const int N = qp.N;
-  const double tau = 0.995, thr0 = 0.1;
+  const double tau = 0.995, thr0 = cf.qp_thr0 > 0 ? cf.qp_thr0 : 0.1;
+  static const bool trace = std::getenv("IHM2O_TRACE") != nullptr;
   // ---- initialisation: primal from the caller (warm), slacks / multipliers cold ----
   for (int a = 0; a < NX; a++) s.z[NU + a] = qp.x0[a];
   s.pi.assign((N + 1) * NX, 0.0);
-  s.lamL.assign(N + 1, {}); s.lamU.assign(N + 1, {}); s.tL.assign(N + 1, {}); s.tU.assign(N + 1, {});
+  auto fit = [&](std::vector<std::vector<double>>& v) { v.assign(N + 1, {}); for (int k = 0; k <= N; k++) v[k].assign(qp.rows[k].size(), 0.0); };
+  fit(s.lamL); fit(s.lamU); fit(s.tL); fit(s.tU); fit(s.sL); fit(s.sU); fit(s.lamSL); fit(s.lamSU);
   int nineq = 0;
   for (int k = 0; k <= N; k++) {
     const auto& R = qp.rows[k];
-    const int nr = (int)R.size();
-    s.lamL[k].resize(nr); s.lamU[k].resize(nr); s.tL[k].resize(nr); s.tU[k].resize(nr);
-    for (int r = 0; r < nr; r++) {
-      double cz = 0;
-      for (int a = 0; a < NZ; a++) cz += R[r].c[a] * s.z[k * NZ + a];
-      s.tL[k][r] = std::max(cz - R[r].lb, thr0);
-      s.tU[k][r] = std::max(R[r].ub - cz, thr0);
+    for (size_t r = 0; r < R.size(); r++) {
+      const double cz = row_val(R[r], &s.z[k * NZ]);
+      if (R[r].soft) {
+        s.sL[k][r] = s.sU[k][r] = thr0;
+        s.lamSL[k][r] = s.lamSU[k][r] = cf.qp_mu0 / thr0;
+        nineq += 2;
+      }
+      s.tL[k][r] = std::max(cz + s.sL[k][r] - R[r].lb, thr0);
+      s.tU[k][r] = std::max(R[r].ub + s.sU[k][r] - cz, thr0);
       s.lamL[k][r] = cf.qp_mu0 / s.tL[k][r];
       s.lamU[k][r] = cf.qp_mu0 / s.tU[k][r];
       nineq += 2;
     }
   }
   std::vector<double> rg((N + 1) * NZ), rb(N * NX);
-  std::vector<std::vector<double>> rdL(N + 1), rdU(N + 1), rmL(N + 1), rmU(N + 1);
-  std::vector<std::vector<double>> dlamL(N + 1), dlamU(N + 1), dtL(N + 1), dtU(N + 1);
-  for (int k = 0; k <= N; k++) {
-    const size_t nr = qp.rows[k].size();
-    rdL[k].resize(nr); rdU[k].resize(nr); rmL[k].resize(nr); rmU[k].resize(nr);
-    dlamL[k].resize(nr); dlamU[k].resize(nr); dtL[k].resize(nr); dtU[k].resize(nr);
-  }
+  std::vector<std::vector<double>> rdL, rdU, rmL, rmU, rmSL, rmSU, rsL, rsU;
+  std::vector<std::vector<double>> dlamL, dlamU, dtL, dtU, dsL, dsU, dlamSL, dlamSU;
+  fit(rdL); fit(rdU); fit(rmL); fit(rmU); fit(rmSL); fit(rmSU); fit(rsL); fit(rsU);
+  fit(dlamL); fit(dlamU); fit(dtL); fit(dtU); fit(dsL); fit(dsU); fit(dlamSL); fit(dlamSU);
   std::vector<double> Ht((N + 1) * NZ * NZ), rgt((N + 1) * NZ);
   std::vector<double> P((N + 1) * NX * NX), pv((N + 1) * NX), Kfb(N * NU * NX), kff(N * NU);
   std::vector<double> Linv(N * 4), dz((N + 1) * NZ), dpi((N + 1) * NX);
   s.status = 1;
   int it = 0;
+  const double mu_floor = 0.1 * cf.qp_tol_comp;
+  int at_floor = 0;
+  double prev_res_g = std::numeric_limits<double>::infinity();
+  double mu_hist[8] = {0};
+  int short_steps = 0;
   for (;; it++) {
     // ---- residuals ----
-    double mg = 0, mb = 0, md = 0, res_g = 0, res_b = 0, res_d = 0, res_m = 0, mu = 0;
+    double mg = 0, mb = 0, res_g = 0, res_b = 0, res_d = 0, res_m = 0, mu = 0;
     for (int k = 0; k <= N; k++) {
       const double* z = &s.z[k * NZ];
       for (int a = 0; a < NZ; a++) {
@@ -614,17 +722,27 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
       for (int a = 0; a < NX; a++) rg[k * NZ + NU + a] -= s.pi[k * NX + a];
       const auto& R = qp.rows[k];
       for (size_t r = 0; r < R.size(); r++) {
-        double cz = 0;
-        for (int a = 0; a < NZ; a++) cz += R[r].c[a] * z[a];
+        const double cz = row_val(R[r], z);
         for (int a = 0; a < NZ; a++) rg[k * NZ + a] -= R[r].c[a] * (s.lamL[k][r] - s.lamU[k][r]);
-        rdL[k][r] = cz - R[r].lb - s.tL[k][r];
-        rdU[k][r] = R[r].ub - cz - s.tU[k][r];
-        md = std::max(md, std::max(std::fabs(R[r].lb), std::fabs(R[r].ub)));
-        res_d = std::max(res_d, std::max(std::fabs(rdL[k][r]), std::fabs(rdU[k][r])));
+        rdL[k][r] = cz + s.sL[k][r] - R[r].lb - s.tL[k][r];
+        rdU[k][r] = R[r].ub + s.sU[k][r] - cz - s.tU[k][r];
+        // slack residuals relative to the size of the row's bounds (the rows span 0.02 ... 1e6)
+        const double sc = 1.0 + std::min(std::fabs(R[r].lb), std::fabs(R[r].ub));
+        res_d = std::max(res_d, std::max(std::fabs(rdL[k][r]), std::fabs(rdU[k][r])) / sc);
         rmL[k][r] = s.lamL[k][r] * s.tL[k][r];
         rmU[k][r] = s.lamU[k][r] * s.tU[k][r];
         res_m = std::max(res_m, std::max(rmL[k][r], rmU[k][r]));
+
         mu += rmL[k][r] + rmU[k][r];
+        if (R[r].soft) {
+          rmSL[k][r] = s.lamSL[k][r] * s.sL[k][r];
+          rmSU[k][r] = s.lamSU[k][r] * s.sU[k][r];
+          res_m = std::max(res_m, std::max(rmSL[k][r], rmSU[k][r]));
+          mu += rmSL[k][r] + rmSU[k][r];
+          rsL[k][r] = qp.Zs[k] * s.sL[k][r] + qp.zs[k] - s.lamL[k][r] - s.lamSL[k][r];
+          rsU[k][r] = qp.Zs[k] * s.sU[k][r] + qp.zs[k] - s.lamU[k][r] - s.lamSU[k][r];
+          res_g = std::max(res_g, std::max(std::fabs(rsL[k][r]), std::fabs(rsU[k][r])));
+        }
       }
       const int a0 = (k == 0) ? NU : NZ;  // x_0 is not a variable
       for (int a = 0; a < (k == 0 ? NU : NZ); a++) res_g = std::max(res_g, std::fabs(rg[k * NZ + a]));
@@ -632,13 +750,33 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
     }
     mu /= nineq;
     s.mu = mu; s.res_g = res_g; s.res_b = res_b; s.res_d = res_d; s.res_m = res_m; s.iters = it;
-    s.mag_g = mg; s.mag_b = mb; s.mag_d = md;
+    s.mag_g = mg; s.mag_b = mb; s.mag_d = 0.0;
+    if (trace) std::fprintf(stderr, "it %2d res_g %.2e res_b %.2e res_d %.2e res_m %.2e mu %.2e\n", it, res_g, res_b, res_d, res_m, mu);
     if (!(res_g == res_g) || !(res_b == res_b) || !(mu == mu)) { s.status = 3; return; }
     const double tol = cf.qp_tol;
-    if (res_g <= tol * (1 + mg) && res_b <= tol * (1 + mb) && res_d <= tol * (1 + md) && res_m <= cf.qp_tol_comp) {
+    const double tol_comp = cf.qp_tol_comp;
+    if (res_g <= tol * (1 + mg) && res_b <= tol * (1 + mb) && res_d <= tol && res_m <= tol_comp) {
       s.status = 0; return;
     }
+    // converged as far as the arithmetic allows: feasibility and complementarity at the tight tolerances, the
+    // barrier parameter at its floor, stationarity within 1e-6 relative and no longer improving (thin interiors
+    // leave gamma = lam / t ~ 1e9+ and the Riccati step loses the last digits of the stationarity residual)
+    const bool loose = res_g <= 1e-6 * (1 + mg) && res_b <= tol * (1 + mb) && res_d <= tol && res_m <= tol_comp;
+    if (loose && mu <= 2.0 * mu_floor && res_g >= 0.1 * prev_res_g) { s.status = 0; return; }
+    prev_res_g = res_g;
+    // numerical breakdown: four iterations with the barrier parameter at its floor and still no acceptable point (the
+    // classical Riccati recursion cannot resolve the step once lam / t ~ 1e15 sits next to an O(1) Hessian: thin
+    // interiors, < 1 % of the config-2 batch).  Reported as an iteration-limit stop.
+    if (mu <= 2.0 * mu_floor && ++at_floor >= 4) { s.status = 1; return; }
     if (it >= cf.qp_max_iter) { s.status = 1; return; }
+    if (cf.qp_infeas_exit) {
+      // primal infeasible QP: the step lengths collapse against rows that cannot be met and the multipliers of
+      // those rows grow, so the barrier parameter stops decreasing.  Eight iterations in a row with a step below
+      // 0.5 and no decrease of the barrier parameter over them end the solve (a feasible problem loses a factor 2+
+      // per iteration once it is centred).
+      if (it >= 8 && short_steps >= 8 && mu >= mu_hist[it & 7]) { s.status = 4; return; }
+      mu_hist[it & 7] = mu;
+    }
 
     auto kkt_solve = [&]() {
       // modified Hessian / gradient
@@ -647,9 +785,18 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
         for (int a = 0; a < NZ; a++) rgt[k * NZ + a] = rg[k * NZ + a];
         const auto& R = qp.rows[k];
         for (size_t r = 0; r < R.size(); r++) {
-          const double gam = s.lamL[k][r] / s.tL[k][r] + s.lamU[k][r] / s.tU[k][r];
-          const double q = (rmL[k][r] + s.lamL[k][r] * rdL[k][r]) / s.tL[k][r] -
-                           (rmU[k][r] + s.lamU[k][r] * rdU[k][r]) / s.tU[k][r];
+          double gL = s.lamL[k][r] / s.tL[k][r], gU = s.lamU[k][r] / s.tU[k][r];
+          double qL = (rmL[k][r] + s.lamL[k][r] * rdL[k][r]) / s.tL[k][r];
+          double qU = (rmU[k][r] + s.lamU[k][r] * rdU[k][r]) / s.tU[k][r];
+          if (R[r].soft) {
+            const double gSL = s.lamSL[k][r] / s.sL[k][r], gSU = s.lamSU[k][r] / s.sU[k][r];
+            const double DL = qp.Zs[k] + gL + gSL, DU = qp.Zs[k] + gU + gSU;
+            qL -= gL * (rsL[k][r] + qL + rmSL[k][r] / s.sL[k][r]) / DL;
+            qU -= gU * (rsU[k][r] + qU + rmSU[k][r] / s.sU[k][r]) / DU;
+            gL *= (qp.Zs[k] + gSL) / DL;
+            gU *= (qp.Zs[k] + gSU) / DU;
+          }
+          const double gam = gL + gU, q = qL - qU;
           for (int a = 0; a < NZ; a++) {
             rgt[k * NZ + a] += R[r].c[a] * q;
             for (int b = 0; b < NZ; b++) Ht[(k * NZ + a) * NZ + b] += gam * R[r].c[a] * R[r].c[b];
@@ -739,53 +886,90 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
         for (size_t r = 0; r < R.size(); r++) {
           double cdz = 0;
           for (int a = 0; a < NZ; a++) cdz += R[r].c[a] * dz[k * NZ + a];
-          dtL[k][r] = cdz + rdL[k][r];
-          dtU[k][r] = -cdz + rdU[k][r];
+          if (R[r].soft) {
+            const double gL = s.lamL[k][r] / s.tL[k][r], gU = s.lamU[k][r] / s.tU[k][r];
+            const double qL = (rmL[k][r] + s.lamL[k][r] * rdL[k][r]) / s.tL[k][r];
+            const double qU = (rmU[k][r] + s.lamU[k][r] * rdU[k][r]) / s.tU[k][r];
+            const double DL = qp.Zs[k] + gL + s.lamSL[k][r] / s.sL[k][r], DU = qp.Zs[k] + gU + s.lamSU[k][r] / s.sU[k][r];
+            dsL[k][r] = -(rsL[k][r] + qL + rmSL[k][r] / s.sL[k][r] + gL * cdz) / DL;
+            dsU[k][r] = -(rsU[k][r] + qU + rmSU[k][r] / s.sU[k][r] - gU * cdz) / DU;
+            dlamSL[k][r] = -(rmSL[k][r] + s.lamSL[k][r] * dsL[k][r]) / s.sL[k][r];
+            dlamSU[k][r] = -(rmSU[k][r] + s.lamSU[k][r] * dsU[k][r]) / s.sU[k][r];
+          }
+          dtL[k][r] = cdz + dsL[k][r] + rdL[k][r];
+          dtU[k][r] = -cdz + dsU[k][r] + rdU[k][r];
           dlamL[k][r] = -(rmL[k][r] + s.lamL[k][r] * dtL[k][r]) / s.tL[k][r];
           dlamU[k][r] = -(rmU[k][r] + s.lamU[k][r] * dtU[k][r]) / s.tU[k][r];
         }
       }
     };
-    auto max_step = [&]() {
-      double al = 1.0;
+    // largest step in [0, 1] that keeps the slacks (primal) / the multipliers (dual) non-negative
+    auto max_step = [&](double& al_p, double& al_d) {
+      al_p = al_d = 1.0;
       for (int k = 0; k <= N; k++)
         for (size_t r = 0; r < qp.rows[k].size(); r++) {
-          if (dlamL[k][r] < 0) al = std::min(al, -s.lamL[k][r] / dlamL[k][r]);
-          if (dlamU[k][r] < 0) al = std::min(al, -s.lamU[k][r] / dlamU[k][r]);
-          if (dtL[k][r] < 0) al = std::min(al, -s.tL[k][r] / dtL[k][r]);
-          if (dtU[k][r] < 0) al = std::min(al, -s.tU[k][r] / dtU[k][r]);
+          if (dlamL[k][r] < 0) al_d = std::min(al_d, -s.lamL[k][r] / dlamL[k][r]);
+          if (dlamU[k][r] < 0) al_d = std::min(al_d, -s.lamU[k][r] / dlamU[k][r]);
+          if (dtL[k][r] < 0) al_p = std::min(al_p, -s.tL[k][r] / dtL[k][r]);
+          if (dtU[k][r] < 0) al_p = std::min(al_p, -s.tU[k][r] / dtU[k][r]);
+          if (qp.rows[k][r].soft) {
+            if (dlamSL[k][r] < 0) al_d = std::min(al_d, -s.lamSL[k][r] / dlamSL[k][r]);
+            if (dlamSU[k][r] < 0) al_d = std::min(al_d, -s.lamSU[k][r] / dlamSU[k][r]);
+            if (dsL[k][r] < 0) al_p = std::min(al_p, -s.sL[k][r] / dsL[k][r]);
+            if (dsU[k][r] < 0) al_p = std::min(al_p, -s.sU[k][r] / dsU[k][r]);
+          }
         }
-      return al;
+      if (!cf.qp_split_step) al_p = al_d = std::min(al_p, al_d);
     };
     // ---- predictor ----
     kkt_solve();
-    const double al_aff = max_step();
+    double ap_aff, ad_aff;
+    max_step(ap_aff, ad_aff);
     double mu_aff = 0;
     for (int k = 0; k <= N; k++)
       for (size_t r = 0; r < qp.rows[k].size(); r++) {
-        mu_aff += (s.lamL[k][r] + al_aff * dlamL[k][r]) * (s.tL[k][r] + al_aff * dtL[k][r]);
-        mu_aff += (s.lamU[k][r] + al_aff * dlamU[k][r]) * (s.tU[k][r] + al_aff * dtU[k][r]);
+        mu_aff += (s.lamL[k][r] + ad_aff * dlamL[k][r]) * (s.tL[k][r] + ap_aff * dtL[k][r]);
+        mu_aff += (s.lamU[k][r] + ad_aff * dlamU[k][r]) * (s.tU[k][r] + ap_aff * dtU[k][r]);
+        if (qp.rows[k][r].soft) {
+          mu_aff += (s.lamSL[k][r] + ad_aff * dlamSL[k][r]) * (s.sL[k][r] + ap_aff * dsL[k][r]);
+          mu_aff += (s.lamSU[k][r] + ad_aff * dlamSU[k][r]) * (s.sU[k][r] + ap_aff * dsU[k][r]);
+        }
       }
     mu_aff /= nineq;
     const double sig = std::pow(mu_aff / mu, 3.0);
     // centring target; floored so the iterates stay on the central path at mu ~ 0.1 tol_comp
     // instead of diving to round-off, which wrecks the conditioning of the Riccati recursion
-    const double mu_t = std::max(sig * mu, 0.1 * cf.qp_tol_comp);
+    const double mu_t = std::max(sig * mu, mu_floor);
     // ---- corrector ----
     for (int k = 0; k <= N; k++)
       for (size_t r = 0; r < qp.rows[k].size(); r++) {
         rmL[k][r] += dlamL[k][r] * dtL[k][r] - mu_t;
         rmU[k][r] += dlamU[k][r] * dtU[k][r] - mu_t;
+        if (qp.rows[k][r].soft) {
+          rmSL[k][r] += dlamSL[k][r] * dsL[k][r] - mu_t;
+          rmSU[k][r] += dlamSU[k][r] * dsU[k][r] - mu_t;
+        }
       }
     kkt_solve();
-    const double al = std::min(1.0, tau * max_step());
-    if (al < 1e-12) { s.status = 2; return; }
+    double ap, ad;
+    max_step(ap, ad);
+    // fraction to the boundary: 0.995 far from the solution, -> 1 with the barrier parameter (Mehrotra), which
+    // restores the fast local convergence of the last iterations
+    const double tau_k = std::max(tau, 1.0 - mu_t);
+    ap = std::min(1.0, tau_k * ap); ad = std::min(1.0, tau_k * ad);
+    if (trace) std::fprintf(stderr, "      al_aff %.3f/%.3f sig %.2e mu_t %.2e  al %.3f/%.3f\n", ap_aff, ad_aff, sig, mu_t, ap, ad);
+    if (std::min(ap, ad) < 1e-12) { s.status = 2; return; }
+    short_steps = (std::min(ap, ad) < 0.5) ? short_steps + 1 : 0;
     for (int k = 0; k <= N; k++) {
-      for (int a = 0; a < NZ; a++) s.z[k * NZ + a] += al * dz[k * NZ + a];
-      if (k > 0) for (int a = 0; a < NX; a++) s.pi[k * NX + a] += al * dpi[k * NX + a];
+      for (int a = 0; a < NZ; a++) s.z[k * NZ + a] += ap * dz[k * NZ + a];
+      if (k > 0) for (int a = 0; a < NX; a++) s.pi[k * NX + a] += ad * dpi[k * NX + a];
       for (size_t r = 0; r < qp.rows[k].size(); r++) {
-        s.lamL[k][r] += al * dlamL[k][r]; s.lamU[k][r] += al * dlamU[k][r];
-        s.tL[k][r] += al * dtL[k][r]; s.tU[k][r] += al * dtU[k][r];
+        s.lamL[k][r] += ad * dlamL[k][r]; s.lamU[k][r] += ad * dlamU[k][r];
+        s.tL[k][r] += ap * dtL[k][r]; s.tU[k][r] += ap * dtU[k][r];
+        if (qp.rows[k][r].soft) {
+          s.sL[k][r] += ap * dsL[k][r]; s.sU[k][r] += ap * dsU[k][r];
+          s.lamSL[k][r] += ad * dlamSL[k][r]; s.lamSU[k][r] += ad * dlamSU[k][r];
+        }
       }
     }
   }
@@ -825,10 +1009,16 @@ bool linearize(const Problem& pb, const double* x, const double* u, Qp& qp, doub
       if (!(xn[i] == xn[i])) ok = false;
     }
   }
+  if (!qp.rows.empty()) build_h_rows(*pb.cf, pb.p, pb.tr, x, u, qp);
   return ok;
 }
 
 struct SolveOut { int status, qp_iters, sqp_iters; double mu, res_stat, res_eq, res_ineq, res_comp, cost; };
+
+// Value of a soft row's slack penalty with the slack eliminated: the cheapest feasible slack of a row at value v is
+// its violation (the penalty is increasing in s >= 0), so the NLP in (x, u, s) equals the NLP in (x, u) with
+// cost + sum z_s viol + Z_s/2 viol^2.  The SQP-level quantities (cost, merit, KKT residuals) use this form.
+inline double soft_penalty(double zs, double Zs, double viol) { return viol * (zs + 0.5 * Zs * viol); }
 
 double ocp_cost(const ihm2b_config& cf, const Qp& qp, const double* z) {
   double c = 0;
@@ -838,6 +1028,13 @@ double ocp_cost(const ihm2b_config& cf, const Qp& qp, const double* z) {
       for (int b = 0; b < NZ; b++) hz += qp.H[(k * NZ + a) * NZ + b] * z[k * NZ + b];
       c += z[k * NZ + a] * (0.5 * hz + qp.g[k * NZ + a]);
     }
+  // soft rows (the h rows are evaluated through their linearisation: exact at the linearisation point)
+  for (int k = 0; k <= cf.N; k++)
+    for (const Row& R : qp.rows[k])
+      if (R.soft) {
+        const double v = row_val(R, &z[k * NZ]);
+        c += soft_penalty(qp.zs[k], qp.Zs[k], std::max(0.0, R.lb - v) + std::max(0.0, v - R.ub));
+      }
   return c;
 }
 
@@ -881,8 +1078,8 @@ double merit_value(const ihm2b_config& cf, const Qp& qp, const MeritWeights& mw,
   for (int k = 0; k <= N; k++)
     for (size_t r = 0; r < qp.rows[k].size(); r++) {
       const Row& R = qp.rows[k][r];
-      double cz = 0;
-      for (int a = 0; a < NZ; a++) cz += R.c[a] * z[k * NZ + a];
+      if (R.soft) continue;   // the exact penalty of a soft row is part of the cost
+      const double cz = row_val(R, &z[k * NZ]);
       m += mw.lo[k][r] * std::max(0.0, R.lb - cz) + mw.up[k][r] * std::max(0.0, cz - R.ub);
     }
   return m;
@@ -932,12 +1129,18 @@ void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveO
         }
         for (size_t r = 0; r < qp.rows[k].size(); r++) {
           const Row& R = qp.rows[k][r];
-          double cz = 0;
-          for (int a = 0; a < NZ; a++) cz += R.c[a] * z[a];
-          ri = std::max(ri, std::max(R.lb - cz, cz - R.ub));
+          const double cz = row_val(R, z);
+          // soft row: slack eliminated, s* = violation of the side (see soft_penalty)
+          const double sL = R.soft ? std::max(0.0, R.lb - cz) : 0.0, sU = R.soft ? std::max(0.0, cz - R.ub) : 0.0;
+          ri = std::max(ri, std::max(R.lb - sL - cz, cz - R.ub - sU));
           if (have_mult) {
             for (int a = 0; a < NZ; a++) rg[a] -= R.c[a] * (sol.lamL[k][r] - sol.lamU[k][r]);
-            rc = std::max(rc, std::max(std::fabs(sol.lamL[k][r] * (cz - R.lb)), std::fabs(sol.lamU[k][r] * (R.ub - cz))));
+            rc = std::max(rc, std::max(std::fabs(sol.lamL[k][r] * (cz + sL - R.lb)), std::fabs(sol.lamU[k][r] * (R.ub + sU - cz))));
+            if (R.soft) {
+              rc = std::max(rc, std::max(std::fabs(sol.lamSL[k][r] * sL), std::fabs(sol.lamSU[k][r] * sU)));
+              rs = std::max(rs, std::fabs(qp.Zs[k] * sL + qp.zs[k] - sol.lamL[k][r] - sol.lamSL[k][r]));
+              rs = std::max(rs, std::fabs(qp.Zs[k] * sU + qp.zs[k] - sol.lamU[k][r] - sol.lamSU[k][r]));
+            }
           }
         }
         for (int a = (k == 0 ? 0 : 0); a < (k == 0 ? NU : NZ); a++) rs = std::max(rs, std::fabs(rg[a]));
@@ -962,7 +1165,9 @@ void solve_one(const Problem& pb, const double* x0, double* x, double* u, SolveO
       // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
       const bool loose = sol.res_g <= 1e-6 * (1 + sol.mag_g) && sol.res_b <= 1e-6 * (1 + sol.mag_b) &&
                          sol.res_d <= 1e-6 * (1 + sol.mag_d) && sol.res_m <= 1e-6;
-      if (!loose && !(cf.qp_tolerate_maxiter && sol.status == 1)) { out.status = IHM2B_QP_FAILURE; break; }
+      // acados' SQP / SQP_RTI carry on with the iterate of a QP solver that stopped at its iteration limit; the
+      // early exit for infeasible QPs (status 4, not in HPIPM) stands in for that limit
+      if (!loose && !(cf.qp_tolerate_maxiter && (sol.status == 1 || sol.status == 4))) { out.status = IHM2B_QP_FAILURE; break; }
     }
     have_mult = true;
     if (line_search) {
@@ -1197,25 +1402,28 @@ int ihm2o_integrate(int kind, const double* tabA, const double* tabb, double h, 
   return irk_step(fdyn6, false, tb, x, u, p, tr, h, xn, nullptr);
 }
 
-static Problem make_problem(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                            const int32_t* track_index, const double* params, int i) {
-  const int t = track_index ? track_index[i] : 0;
+// track tables of the batched entry points: s_ref, kappa_ref and (optional) right / left widths, [n_tracks][n_grid]
+struct ihm2o_tracks { const double *s_ref, *kappa_ref, *right_width, *left_width; };
+
+static Problem make_problem(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index,
+                            const double* params, int i) {
+  const size_t off = (size_t)(track_index ? track_index[i] : 0) * cf->n_grid;
   Problem pb;
   pb.cf = cf;
-  pb.tr = Track{cf->n_grid, s_ref + (size_t)t * cf->n_grid, kappa_ref + (size_t)t * cf->n_grid};
+  pb.tr = Track{cf->n_grid, tk->s_ref + off, tk->kappa_ref + off, tk->right_width ? tk->right_width + off : nullptr,
+                tk->left_width ? tk->left_width + off : nullptr};
   pb.p = params + (size_t)i * NP;
   return pb;
 }
 
 // A [B][N][8][8], Bm [B][N][8][2], phi [B][N][8]
-int ihm2o_linearize(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                    const int32_t* track_index, const double* params, const double* x,
+int ihm2o_linearize(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index, const double* params, const double* x,
                     const double* u, double* A, double* Bm, double* phi) {
   const int N = cf->N;
   int bad = 0;
 #pragma omp parallel for schedule(dynamic) reduction(+ : bad)
   for (int i = 0; i < cf->batch; i++) {
-    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    Problem pb = make_problem(cf, tk, track_index, params, i);
     Qp qp; qp.N = N;
     std::vector<double> ph(N * NX);
     if (!linearize(pb, x + (size_t)i * (N + 1) * NX, u + (size_t)i * N * NU, qp, ph.data())) bad++;
@@ -1228,13 +1436,12 @@ int ihm2o_linearize(const ihm2b_config* cf, const double* s_ref, const double* k
 
 // One controller call per instance: (optional literal shift) + SQP(-RTI) solve.
 // x [B][N+1][8], u [B][N][2] in/out; u0 [B][2]; status [B]; stats [B][8].
-int ihm2o_solve(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                const int32_t* track_index, const double* params, const double* x0, double* x,
+int ihm2o_solve(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index, const double* params, const double* x0, double* x,
                 double* u, double* u0, int32_t* status, double* stats, int do_shift) {
   const int N = cf->N;
 #pragma omp parallel for schedule(dynamic)
   for (int i = 0; i < cf->batch; i++) {
-    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    Problem pb = make_problem(cf, tk, track_index, params, i);
     double* xi = x + (size_t)i * (N + 1) * NX;
     double* ui = u + (size_t)i * N * NU;
     if (do_shift) shift_iterate(N, xi, ui);
@@ -1251,18 +1458,18 @@ int ihm2o_solve(const ihm2b_config* cf, const double* s_ref, const double* kappa
   return 0;
 }
 
-// Debug view of ONE problem's first QP and its IPM solution, for the KKT-certificate test.
-// Row storage padded to 8 rows per stage: Crow [N+1][8][10], lb/ub/lamL/lamU/tL/tU [N+1][8],
-// nrows [N+1].  z [N+1][10], pi [N+1][8].
-int ihm2o_qp_debug(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                   const double* params, const double* x0, const double* x, const double* u,
-                   double* A, double* Bm, double* c, double* H, double* g, double* Crow, double* lb,
-                   double* ub, int32_t* nrows, double* z, double* pi, double* lamL, double* lamU,
-                   double* tL, double* tU, double* info /* iters,status,mu,res_g,res_b,res_d,res_m */) {
-  const int N = cf->N;
+// Debug view of ONE problem's first QP and its IPM solution, for the KKT-certificate tests.
+// Row storage padded to 16 rows per stage: Crow [N+1][16][10], e/lb/ub/lamL/lamU/tL/tU/sL/sU/lamSL/lamSU [N+1][16],
+// soft [N+1][16], nrows [N+1], zZ [N+1][2] slack penalties (z_s, Z_s) of the stage.  z [N+1][10], pi [N+1][8].
+int ihm2o_qp_debug(const ihm2b_config* cf, const ihm2o_tracks* tk, const double* params, const double* x0,
+                   const double* x, const double* u, double* A, double* Bm, double* c, double* H, double* g,
+                   double* Crow, double* e, double* lb, double* ub, int32_t* soft, int32_t* nrows, double* zZ,
+                   double* z, double* pi, double* lamL, double* lamU, double* tL, double* tU, double* sL, double* sU,
+                   double* lamSL, double* lamSU, double* info /* iters,status,mu,res_g,res_b,res_d,res_m */) {
+  const int N = cf->N, PR = 16;
   ihm2b_config c1 = *cf;
   c1.batch = 1; c1.nlp_solver = IHM2B_SQP_RTI;
-  Problem pb = make_problem(&c1, s_ref, kappa_ref, nullptr, params, 0);
+  Problem pb = make_problem(&c1, tk, nullptr, params, 0);
   std::vector<double> xi(x, x + (N + 1) * NX), ui(u, u + N * NU);
   SolveOut so; QpSol sol; Qp qp;
   solve_one(pb, x0, xi.data(), ui.data(), so, &sol, &qp);
@@ -1273,11 +1480,13 @@ int ihm2o_qp_debug(const ihm2b_config* cf, const double* s_ref, const double* ka
   std::memcpy(g, qp.g.data(), sizeof(double) * (N + 1) * NZ);
   for (int k = 0; k <= N; k++) {
     nrows[k] = (int)qp.rows[k].size();
+    zZ[k * 2] = qp.zs[k]; zZ[k * 2 + 1] = qp.Zs[k];
     for (int r = 0; r < nrows[k]; r++) {
-      std::memcpy(Crow + ((size_t)k * 8 + r) * NZ, qp.rows[k][r].c, sizeof(double) * NZ);
-      lb[k * 8 + r] = qp.rows[k][r].lb; ub[k * 8 + r] = qp.rows[k][r].ub;
-      lamL[k * 8 + r] = sol.lamL[k][r]; lamU[k * 8 + r] = sol.lamU[k][r];
-      tL[k * 8 + r] = sol.tL[k][r]; tU[k * 8 + r] = sol.tU[k][r];
+      const int q = k * PR + r;
+      std::memcpy(Crow + (size_t)q * NZ, qp.rows[k][r].c, sizeof(double) * NZ);
+      e[q] = qp.rows[k][r].e; lb[q] = qp.rows[k][r].lb; ub[q] = qp.rows[k][r].ub; soft[q] = qp.rows[k][r].soft;
+      lamL[q] = sol.lamL[k][r]; lamU[q] = sol.lamU[k][r]; tL[q] = sol.tL[k][r]; tU[q] = sol.tU[k][r];
+      sL[q] = sol.sL[k][r]; sU[q] = sol.sU[k][r]; lamSL[q] = sol.lamSL[k][r]; lamSU[q] = sol.lamSU[k][r];
     }
   }
   std::memcpy(z, sol.z.data(), sizeof(double) * (N + 1) * NZ);
@@ -1287,13 +1496,19 @@ int ihm2o_qp_debug(const ihm2b_config* cf, const double* s_ref, const double* ka
   return so.status;
 }
 
+// h(x, u) and its Jacobian [5][10] at one point (track 0, first parameter vector)
+void ihm2o_con_h(const ihm2b_config* cf, const ihm2o_tracks* tk, const double* params, const double* x,
+                 const double* u, double* h, double* Jh) {
+  Problem pb = make_problem(cf, tk, nullptr, params, 0);
+  con_h(x, u, pb.p, pb.tr, cf->track_half_L, cf->track_half_W, h, reinterpret_cast<double(*)[10]>(Jh));
+}
+
 // x [B][8], u [B][2] -> xn [B][8], model [B]
-int ihm2o_sim_step(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                   const int32_t* track_index, const double* params, const double* x,
+int ihm2o_sim_step(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index, const double* params, const double* x,
                    const double* u, double* xn, int32_t* model) {
 #pragma omp parallel for schedule(dynamic)
   for (int i = 0; i < cf->batch; i++) {
-    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    Problem pb = make_problem(cf, tk, track_index, params, i);
     const int m = sim_step(pb, x + (size_t)i * NX, u + (size_t)i * NU, xn + (size_t)i * NX);
     if (model) model[i] = m;
   }
@@ -1301,20 +1516,25 @@ int ihm2o_sim_step(const ihm2b_config* cf, const double* s_ref, const double* ka
 }
 
 // python/main.py:448-517 with the NMPC enabled.  xs [B][8] in/out; iterate x/u in/out;
-// xlog [n_steps+1][B][8], ulog [n_steps][B][2] (optional); done/fail [B] step index or -1.
-int ihm2o_closed_loop(const ihm2b_config* cf, const double* s_ref, const double* kappa_ref,
-                      const int32_t* track_index, const double* params, const double* lap_length,
-                      int n_steps, double* xs, double* x, double* u, double* xlog, double* ulog,
-                      int32_t* done, int32_t* fail) {
+// xlog [n_steps+1][B][8], ulog [n_steps][B][2] (optional); done/fail [B] step index or -1;
+// lap_time [B] (optional): python/main.py:561-570 -- dt x (second - first index at which mod(s, lap_length) jumps by
+// more than 1 between consecutive states), NaN while fewer than two jumps have been seen; cost_sum [B] (optional):
+// sum of the OCP cost at the solution over the control steps taken.
+int ihm2o_closed_loop(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index, const double* params,
+                      const double* lap_length, int n_steps, double* xs, double* x, double* u, double* xlog,
+                      double* ulog, int32_t* done, int32_t* fail, double* lap_time, double* cost_sum) {
   const int N = cf->N, B = cf->batch;
 #pragma omp parallel for schedule(dynamic)
   for (int i = 0; i < B; i++) {
-    Problem pb = make_problem(cf, s_ref, kappa_ref, track_index, params, i);
+    Problem pb = make_problem(cf, tk, track_index, params, i);
     const int t = track_index ? track_index[i] : 0;
     double* xi = x + (size_t)i * (N + 1) * NX;
     double* ui = u + (size_t)i * N * NU;
     double* xc = xs + (size_t)i * NX;
     done[i] = fail[i] = -1;
+    int jumps = 0, first_jump = -1;
+    if (lap_time) lap_time[i] = std::numeric_limits<double>::quiet_NaN();
+    if (cost_sum) cost_sum[i] = 0.0;
     if (xlog) std::memcpy(xlog + (size_t)i * NX, xc, NX * sizeof(double));
     for (int st = 0; st < n_steps; st++) {
       bool active = done[i] < 0 && fail[i] < 0;
@@ -1324,7 +1544,7 @@ int ihm2o_closed_loop(const ihm2b_config* cf, const double* s_ref, const double*
         SolveOut so;
         solve_one(pb, xc, xi, ui, so, nullptr, nullptr);
         if (so.status != IHM2B_SUCCESS && so.status != IHM2B_MAXITER) { fail[i] = st; active = false; }
-        else { uu[0] = ui[0]; uu[1] = ui[1]; }
+        else { uu[0] = ui[0]; uu[1] = ui[1]; if (cost_sum) cost_sum[i] += so.cost; }
       }
       if (active) {
         double xn[NX];
@@ -1332,7 +1552,16 @@ int ihm2o_closed_loop(const ihm2b_config* cf, const double* s_ref, const double*
         bool nan = false;
         for (int a = 0; a < NX; a++) nan |= !(xn[a] == xn[a]);
         if (nan) fail[i] = st;  // main.py:503-512: keep the last state
-        else std::memcpy(xc, xn, sizeof xn);
+        else {
+          const double L = lap_length[t];
+          const double m0 = xc[0] - L * std::floor(xc[0] / L), m1 = xn[0] - L * std::floor(xn[0] / L);   // np.mod
+          if (std::fabs(m1 - m0) > 1.0) {   // main.py:561-566
+            if (jumps == 0) first_jump = st;
+            else if (jumps == 1 && lap_time) lap_time[i] = cf->dt * (st - first_jump);
+            jumps++;
+          }
+          std::memcpy(xc, xn, sizeof xn);
+        }
         if (!nan && xc[0] > lap_length[t] + 1.0) done[i] = st;  // main.py:515
       }
       if (ulog) { ulog[((size_t)st * B + i) * NU] = uu[0]; ulog[((size_t)st * B + i) * NU + 1] = uu[1]; }

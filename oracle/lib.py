@@ -32,10 +32,15 @@ def _f(a):
     return np.ascontiguousarray(a, dtype=np.float64)
 
 
+class _Tracks(C.Structure):   # struct ihm2o_tracks
+    _fields_ = [("s_ref", C.c_void_p), ("kappa_ref", C.c_void_p), ("right_width", C.c_void_p), ("left_width", C.c_void_p)]
+
+
 class Oracle:
     """Holds one problem set (config + tracks + per-instance params) like an ihm2b handle."""
 
-    def __init__(self, cfg, s_ref, kappa_ref, track_index=None, params=None):
+    def __init__(self, cfg, s_ref, kappa_ref, track_index=None, params=None, widths=None):
+        """widths = (right_width, left_width) tables shaped like s_ref (needed with nonlinear_constraints)."""
         from ihm2_b200._abi import default_params
 
         self.lib = C.CDLL(build_oracle())
@@ -49,6 +54,13 @@ class Oracle:
             np.zeros(B, np.int32) if track_index is None else track_index, dtype=np.int32)
         self.params = _f(np.tile(default_params(), (B, 1)) if params is None else params)
         assert self.params.shape == (B, NP)
+        self.right_width = self.left_width = None
+        if widths is not None:
+            self.right_width, self.left_width = (_f(np.atleast_2d(w)) for w in widths)
+            assert self.right_width.shape == self.s_ref.shape and self.left_width.shape == self.s_ref.shape
+        elif cfg.nonlinear_constraints:
+            raise ValueError("nonlinear_constraints needs the track widths")
+        self._tk = _Tracks(_p(self.s_ref), _p(self.kappa_ref), _p(self.right_width), _p(self.left_width))
 
     # ---- single-point model / integrator evaluations (track 0, instance 0 params) ----
     def fkin6(self, x, u, jac=True):
@@ -78,8 +90,7 @@ class Oracle:
 
     # ---- batched path ----
     def _common(self):
-        return (C.byref(self.cfg), _p(self.s_ref), _p(self.kappa_ref), _p(self.track_index),
-                _p(self.params))
+        return (C.byref(self.cfg), C.byref(self._tk), _p(self.track_index), _p(self.params))
 
     def linearize(self, x, u):
         B, N = self.cfg.batch, self.cfg.N
@@ -98,21 +109,28 @@ class Oracle:
         return u0, status, stats, x, u
 
     def qp_debug(self, x0, x, u):
-        N = self.cfg.N
+        """First QP of one problem and its IPM solution; rows padded to 16 per stage."""
+        N, PR = self.cfg.N, 16
         out = dict(
             A=np.zeros((N, NX, NX)), B=np.zeros((N, NX, NU)), c=np.zeros((N, NX)),
-            H=np.zeros((N + 1, NZ, NZ)), g=np.zeros((N + 1, NZ)), C=np.zeros((N + 1, 8, NZ)),
-            lb=np.zeros((N + 1, 8)), ub=np.zeros((N + 1, 8)), nrows=np.zeros(N + 1, np.int32),
-            z=np.zeros((N + 1, NZ)), pi=np.zeros((N + 1, NX)), lamL=np.zeros((N + 1, 8)),
-            lamU=np.zeros((N + 1, 8)), tL=np.zeros((N + 1, 8)), tU=np.zeros((N + 1, 8)),
-            info=np.zeros(7))
-        order = ["A", "B", "c", "H", "g", "C", "lb", "ub", "nrows", "z", "pi", "lamL", "lamU", "tL",
-                 "tU", "info"]
-        st = self.lib.ihm2o_qp_debug(C.byref(self.cfg), _p(self.s_ref), _p(self.kappa_ref),
-                                     _p(self.params), _p(_f(x0)), _p(_f(x)), _p(_f(u)),
-                                     *[_p(out[k]) for k in order])
+            H=np.zeros((N + 1, NZ, NZ)), g=np.zeros((N + 1, NZ)), C=np.zeros((N + 1, PR, NZ)),
+            e=np.zeros((N + 1, PR)), lb=np.zeros((N + 1, PR)), ub=np.zeros((N + 1, PR)),
+            soft=np.zeros((N + 1, PR), np.int32), nrows=np.zeros(N + 1, np.int32), zZ=np.zeros((N + 1, 2)),
+            z=np.zeros((N + 1, NZ)), pi=np.zeros((N + 1, NX)), lamL=np.zeros((N + 1, PR)),
+            lamU=np.zeros((N + 1, PR)), tL=np.zeros((N + 1, PR)), tU=np.zeros((N + 1, PR)),
+            sL=np.zeros((N + 1, PR)), sU=np.zeros((N + 1, PR)), lamSL=np.zeros((N + 1, PR)),
+            lamSU=np.zeros((N + 1, PR)), info=np.zeros(7))
+        order = ["A", "B", "c", "H", "g", "C", "e", "lb", "ub", "soft", "nrows", "zZ", "z", "pi", "lamL", "lamU", "tL",
+                 "tU", "sL", "sU", "lamSL", "lamSU", "info"]
+        st = self.lib.ihm2o_qp_debug(C.byref(self.cfg), C.byref(self._tk), _p(self.params), _p(_f(x0)), _p(_f(x)),
+                                     _p(_f(u)), *[_p(out[k]) for k in order])
         out["status"] = st
         return out
+
+    def con_h(self, x, u):
+        h = np.zeros(5); J = np.zeros((5, NZ))
+        self.lib.ihm2o_con_h(C.byref(self.cfg), C.byref(self._tk), _p(self.params), _p(_f(x)), _p(_f(u)), _p(h), _p(J))
+        return h, J
 
     def sim_step(self, x, u):
         B = self.cfg.batch
@@ -127,9 +145,11 @@ class Oracle:
         xlog = np.zeros((n_steps + 1, B, NX)) if log else None
         ulog = np.zeros((n_steps, B, NU)) if log else None
         done = np.zeros(B, np.int32); fail = np.zeros(B, np.int32)
+        lap_time = np.zeros(B); cost_sum = np.zeros(B)
         self.lib.ihm2o_closed_loop(*self._common(), _p(lap), C.c_int(n_steps), _p(xs), _p(x), _p(u),
-                                   _p(xlog), _p(ulog), _p(done), _p(fail))
-        return dict(x=xs, x_pred=x, u_pred=u, xlog=xlog, ulog=ulog, done=done, fail=fail)
+                                   _p(xlog), _p(ulog), _p(done), _p(fail), _p(lap_time), _p(cost_sum))
+        return dict(x=xs, x_pred=x, u_pred=u, xlog=xlog, ulog=ulog, done=done, fail=fail, lap_time=lap_time,
+                    cost_sum=cost_sum)
 
 
 def initial_iterate(cfg, batch=None):

@@ -41,8 +41,8 @@ def test_constraint_rows_match_reference_definition(qp):
     assert list(q["nrows"]) == [4] + [8] * (N - 1) + [4]
     C = q["C"][7]
     assert C[2, 0] == 1 and C[2, 2 + 6] == -1 and C[3, 1] == 1 and C[3, 2 + 7] == -1   # mpc.py:91-97
-    np.testing.assert_allclose(q["ub"][7], [500, 0.5, 1000, 0.02, 2, 31, 500, 0.5])
-    np.testing.assert_allclose(q["lb"][7], [-500, -0.5, -1000, -0.02, -2, 0, -500, -0.5])
+    np.testing.assert_allclose(q["ub"][7, :8], [500, 0.5, 1000, 0.02, 2, 31, 500, 0.5])
+    np.testing.assert_allclose(q["lb"][7, :8], [-500, -0.5, -1000, -0.02, -2, 0, -500, -0.5])
     # terminal idxbx_e = [1,3,4,5] with the n / v_x / T / delta limits (literal quirk, mpc.py:81-83)
     idx = [int(np.argmax(q["C"][N, r])) - 2 for r in range(4)]
     assert idx == [1, 3, 4, 5]
