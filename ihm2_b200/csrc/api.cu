@@ -141,6 +141,8 @@ void fill_kcfg(const ihm2b_config& c, KCfg& k) {
   memcpy(k.W, c.W, sizeof k.W); memcpy(k.We, c.W_e, sizeof k.We);
   k.cs = c.cost_scale_stage; k.ct = c.cost_scale_terminal;
   k.mu0 = c.qp_mu0; k.tol = c.qp_tol; k.tol_comp = c.qp_tol_comp;
+  k.thr0 = c.qp_thr0 > 0.0 ? c.qp_thr0 : 0.1;
+  k.split_step = c.qp_split_step; k.infeas_exit = c.qp_infeas_exit;
   memcpy(k.irk_A, c.irk_A, sizeof k.irk_A); memcpy(k.irk_b, c.irk_b, sizeof k.irk_b);
 }
 

@@ -21,7 +21,8 @@ struct KCfg {
   double n_max, v_x_max, T_max, delta_max, g_T_max, g_delta_max;
   double W[IHM2B_NY], We[IHM2B_NYN];
   double cs, ct;               // cost scaling: stage, terminal
-  double mu0, tol, tol_comp;
+  double mu0, tol, tol_comp, thr0;
+  int split_step, infeas_exit;
   double irk_A[16], irk_b[4];
 };
 

@@ -36,7 +36,7 @@ namespace ihm2b {
 
 namespace {
 
-constexpr double TAU = 0.995, THR0 = 0.1;
+constexpr double TAU = 0.995;
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
 #ifndef PF_
@@ -243,8 +243,9 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   const double gsN = -cf.ct * cf.We[0] * (s0 + cf.s_target);
   const double ds_ref = cf.s_target / N;
   const double mag_g = fmax(fmax(fabs(gs_scale * s0), fabs(gs_scale * (s0 + ds_ref * (N - 1)))), fabs(gsN));
-  const double mag_d = fmax(fmax(fmax(cf.T_max, cf.delta_max), fmax(cf.g_T_max, cf.g_delta_max)), fmax(cf.n_max, cf.v_x_max));
   const RowDef Rp = row_path(cf, a), Rt = row_term(cf, a);
+  // slack residuals are measured relative to the size of the row's bounds (the rows span 0.02 ... 1e6)
+  const double iscP = 1.0 / (1.0 + fmin(fabs(Rp.lb), fabs(Rp.ub))), iscT = 1.0 / (1.0 + fmin(fabs(Rt.lb), fabs(Rt.ub)));
   const CtDef ctP = ct_path(a), ctT = ct_term(a);
   const int rounds = (N + 4) >> 2;           // stage-parallel loops: stage k = q + 4 i
   __syncwarp();
@@ -264,7 +265,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       gam = lamL * itL + lamU * itU;
       psi = lamL * rdL * itL - lamU * rdU * itU;
       dl = lamL - lamU;
-      rd_m = nmax(rd_m, nmax(fabs(rdL), fabs(rdU)));
+      rd_m = nmax(rd_m, nmax(fabs(rdL), fabs(rdU)) * (term ? iscT : iscP));
       rm_m = nmax(rm_m, nmax(lamL * tL, lamU * tU));
       S0 += lamL * tL + lamU * tU;
     }
@@ -288,7 +289,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
     double lamL = 0.0, lamU = 0.0, tL = 1.0, tU = 1.0;
     if (act) {
-      tL = fmax(v - R.lb, THR0); tU = fmax(R.ub - v, THR0);
+      tL = fmax(v - R.lb, cf.thr0); tU = fmax(R.ub - v, cf.thr0);
       lamL = cf.mu0 / tL; lamU = cf.mu0 / tU;
     }
     if (on) {
@@ -300,7 +301,10 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   __syncwarp();
   const double inv_n = 1.0 / (16.0 * N);  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4)
   double mu = 0.0, res_g = 0.0, res_b = 0.0, res_d = 0.0, res_m = 0.0;
-  int it = 0, qp_status = 1;
+  int it = 0, qp_status = 1, at_floor = 0, short_steps = 0;
+  const double mu_floor = 0.1 * cf.tol_comp;
+  double prev_res_g = __longlong_as_double(0x7ff0000000000000LL);
+  double mu_hist = 0.0;   // lane i < 8 keeps the barrier parameter of the last iteration with it % 8 == i
 
 #ifdef IHM2B_PHASE_TIMERS
   long long tph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -398,9 +402,24 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       d[0] = res_g; d[1] = res_b; d[2] = res_d; d[3] = res_m; d[4] = mu;
     }
     if (!(res_g == res_g) || !(res_b == res_b) || !(mu == mu)) { qp_status = 3; break; }
-    if (res_g <= cf.tol * (1.0 + mag_g) && res_b <= cf.tol * (1.0 + mag_b) && res_d <= cf.tol * (1.0 + mag_d) &&
-        res_m <= cf.tol_comp) { qp_status = 0; break; }
-    if (it >= cf.qp_max_iter) break;
+    {
+      const bool feas = res_b <= cf.tol * (1.0 + mag_b) && res_d <= cf.tol && res_m <= cf.tol_comp;
+      if (feas && res_g <= cf.tol * (1.0 + mag_g)) { qp_status = 0; break; }
+      // converged as far as the arithmetic allows: feasibility and complementarity at the tight tolerances, the
+      // barrier parameter at its floor, stationarity within 1e-6 relative and no longer improving
+      if (feas && res_g <= 1e-6 * (1.0 + mag_g) && mu <= 2.0 * mu_floor && res_g >= 0.1 * prev_res_g) { qp_status = 0; break; }
+      prev_res_g = res_g;
+      // numerical breakdown: four iterations with the barrier parameter at its floor and still no acceptable point
+      if (mu <= 2.0 * mu_floor && ++at_floor >= 4) { qp_status = 1; break; }
+      if (it >= cf.qp_max_iter) { qp_status = 1; break; }
+      if (cf.infeas_exit) {
+        // primal infeasible QP: eight iterations in a row with a step below 0.5 and no decrease of the barrier
+        // parameter over them end the solve (status 4 after a few iterations instead of qp_max_iter)
+        const double mu_old = __shfl_sync(FULL, mu_hist, it & 7);
+        if (it >= 8 && short_steps >= 8 && mu >= mu_old) { qp_status = 4; break; }
+        if (lane == (it & 7)) mu_hist = mu;
+      }
+    }
     __syncwarp();
     TICK(1)
 
@@ -477,7 +496,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
 
     TICK(2)
     // ================= D..H: predictor (pred = 1), corrector (pred = 0)
-    double alpha = 1.0, mu_t = 0.0;
+    double alpha = 1.0, alpha_d = 1.0, mu_t = 0.0;
     bool bad = false;
     for (int pred = 1; pred >= 0; pred--) {
       // ---- forward substitution: du = K dx + kf, dx+ = A dx + B du + rb
@@ -517,7 +536,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       __syncwarp();
       TICK(3)
       // ---- inequality rows at the step (stage-parallel): slack / multiplier steps, step length
-      double ratio = 0.0, S1 = 0.0, S2 = 0.0;
+      double ratio = 0.0, ratio_d = 0.0, S1 = 0.0, S1d = 0.0, S2 = 0.0;   // ratio: primal (slacks), ratio_d: dual (multipliers)
       // the global-memory inputs of a round (L2) are fetched one round ahead of their use
       auto load_rows = [&](int i) {
         const int kk = q + 4 * i;
@@ -551,16 +570,18 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
           const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
           if (pred) {
             const double dlL = -lamL - lamL * dtL * itL, dlU = -lamU - lamU * dtU * itU;
-            S1 += lamL * dtL + tL * dlL + lamU * dtU + tU * dlU;
+            S1 += lamL * dtL + lamU * dtU; S1d += tL * dlL + tU * dlU;
             S2 += dlL * dtL + dlU * dtU;
             pD1[k * 8 + a] = dlL * dtL; pD2[k * 8 + a] = dlU * dtU;
-            ratio = nmax(ratio, nmax(nmax(1.0 + dtL * itL, 1.0 + dtU * itU), nmax(-dtL * itL, -dtU * itU)));
+            ratio_d = nmax(ratio_d, nmax(1.0 + dtL * itL, 1.0 + dtU * itU));
+            ratio = nmax(ratio, nmax(-dtL * itL, -dtU * itU));
           } else {
             const double dlL = -lamL - (cur.d1 - mu_t + lamL * dtL) * itL;
             const double dlU = -lamU - (cur.d2 - mu_t + lamU * dtU) * itU;
             pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
             ddl = dlL - dlU;
-            ratio = nmax(ratio, nmax(nmax(-dlL / lamL, -dlU / lamU), nmax(-dtL * itL, -dtU * itU)));
+            ratio_d = nmax(ratio_d, nmax(-dlL / lamL, -dlU / lamU));
+            ratio = nmax(ratio, nmax(-dtL * itL, -dtU * itU));
           }
         }
         if (!pred) {
@@ -574,18 +595,22 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
           }
         }
       }
-      ratio = wmax(ratio);
-      if (!(ratio == ratio)) { bad = true; break; }
+      ratio = wmax(ratio); ratio_d = wmax(ratio_d);
+      if (!(ratio == ratio) || !(ratio_d == ratio_d)) { bad = true; break; }
+      if (!cf.split_step) ratio = ratio_d = nmax(ratio, ratio_d);
       if (!pred) {
-        alpha = TAU * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
+        // fraction to the boundary: 0.995 far from the solution, -> 1 with the barrier parameter (Mehrotra)
+        const double tau_k = fmax(TAU, 1.0 - mu_t);
+        alpha = tau_k * ((ratio > 1.0) ? 1.0 / ratio : 1.0);
+        alpha_d = tau_k * ((ratio_d > 1.0) ? 1.0 / ratio_d : 1.0);
         break;
       }
-      const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0;
-      S1 = wsum(S1); S2 = wsum(S2);
-      const double mu_aff = (S0 + al_aff * (S1 + al_aff * S2)) * inv_n;
+      const double al_aff = (ratio > 1.0) ? 1.0 / ratio : 1.0, ad_aff = (ratio_d > 1.0) ? 1.0 / ratio_d : 1.0;
+      S1 = wsum(S1); S1d = wsum(S1d); S2 = wsum(S2);
+      const double mu_aff = (S0 + al_aff * S1 + ad_aff * S1d + al_aff * ad_aff * S2) * inv_n;
       const double sr = mu_aff / mu;
       // centring target, floored so the iterates stay on the central path at ~0.1 tol_comp
-      mu_t = fmax(sr * sr * sr * mu, 0.1 * cf.tol_comp);
+      mu_t = fmax(sr * sr * sr * mu, mu_floor);
       // ---- corrector term chi of every row (stage-parallel); what the backward sweep adds per state
       // (C' chi) goes to the gamma slot, the two control entries to the kfc slot
       auto load_chi = [&](int i) {
@@ -652,7 +677,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     TICK(4)
     if (w.dbg && b == 0 && lane == 0 && it < 64) { w.dbg[it * 8 + 5] = alpha; w.dbg[it * 8 + 6] = mu_t; }
     if (bad) { qp_status = 3; break; }
-    if (alpha < 1e-12) { qp_status = 2; break; }
+    if (fmin(alpha, alpha_d) < 1e-12) { qp_status = 2; break; }
+    short_steps = (fmin(alpha, alpha_d) < 0.5) ? short_steps + 1 : 0;
     __syncwarp();
 
     // ================= I: costate recursion of the Newton step -> d pi (kept in the rg slot)
@@ -709,8 +735,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         v = row_value(R, term, cur.uv, cur.xv);
         tL = cur.tL; tU = cur.tU;
         const double dtL = cdz + (v - R.lb - tL), dtU = -cdz + (R.ub - v - tU);
-        lamL = fma(alpha, cur.d1, cur.lamL);
-        lamU = fma(alpha, cur.d2, cur.lamU);
+        lamL = fma(alpha_d, cur.d1, cur.lamL);
+        lamU = fma(alpha_d, cur.d2, cur.lamU);
         tL = fma(alpha, dtL, tL); tU = fma(alpha, dtU, tU);
         // the row at the updated point, from the values the primal update below will store
         v = row_value(R, term, fma(alpha, pDU[(term ? 0 : k) * 2 + R.iu], cur.uv), fma(alpha, pDX[k * 8 + R.ix], cur.xv));
@@ -721,7 +747,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       // rows_A separate these stores from the row loads of the stage above.
       if (on) {
         pX[k * 8 + a] = fma(alpha, pDX[k * 8 + a], cur.xa);
-        pPI[k * 8 + a] = fma(alpha, pRG[k * 8 + a], cur.pia);
+        pPI[k * 8 + a] = fma(alpha_d, pRG[k * 8 + a], cur.pia);
         if (a < 2 && !term) pU[k * 2 + a] = fma(alpha, pDU[k * 2 + a], pU[k * 2 + a]);
       }
     }
@@ -742,8 +768,10 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     else {
       // accept an IPM that stalled above the tight tolerance but is converged to 1e-6
       const bool loose = res_g <= 1e-6 * (1.0 + mag_g) && res_b <= 1e-6 * (1.0 + mag_b) &&
-                         res_d <= 1e-6 * (1.0 + mag_d) && res_m <= 1e-6;
-      st = (loose || (cf.qp_tolerate_maxiter && qp_status == 1)) ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
+                         res_d <= 1e-6 && res_m <= 1e-6;
+      // acados carries on with the iterate of a QP solver that stopped at its iteration limit; the early exit for
+      // infeasible QPs (4, not in HPIPM) stands in for that limit
+      st = (loose || (cf.qp_tolerate_maxiter && (qp_status == 1 || qp_status == 4))) ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
     }
     double* sp = w.stats + (size_t)b * 8;
     if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics

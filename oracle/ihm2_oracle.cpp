@@ -727,8 +727,8 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
         rdL[k][r] = cz + s.sL[k][r] - R[r].lb - s.tL[k][r];
         rdU[k][r] = R[r].ub + s.sU[k][r] - cz - s.tU[k][r];
         // slack residuals relative to the size of the row's bounds (the rows span 0.02 ... 1e6)
-        const double sc = 1.0 + std::min(std::fabs(R[r].lb), std::fabs(R[r].ub));
-        res_d = std::max(res_d, std::max(std::fabs(rdL[k][r]), std::fabs(rdU[k][r])) / sc);
+        const double isc = 1.0 / (1.0 + std::min(std::fabs(R[r].lb), std::fabs(R[r].ub)));
+        res_d = std::max(res_d, std::max(std::fabs(rdL[k][r]), std::fabs(rdU[k][r])) * isc);
         rmL[k][r] = s.lamL[k][r] * s.tL[k][r];
         rmU[k][r] = s.lamU[k][r] * s.tU[k][r];
         res_m = std::max(res_m, std::max(rmL[k][r], rmU[k][r]));

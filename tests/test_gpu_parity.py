@@ -127,7 +127,8 @@ def test_qp_tolerate_maxiter_like_acados(torch_cuda, skidpad, config2):
     """qp_tolerate_maxiter: a QP that stops at the iteration cap is used as it is and the solve reports success, as
     acados does with ACADOS_MAXITER from its QP solver.  Same statuses as the oracle with the same option; the
     problems that converge anyway are untouched; the capped ones (infeasible QPs: the iterate at the cap is not a
-    solution and depends on the last bits) are only required to be finite."""
+    solution and depends on the last bits) are only required to be finite.  With the default preset the early exit
+    for infeasible QPs stands in for the cap."""
     from ihm2_b200 import _abi
     from oracle.lib import Oracle
     B = 512
@@ -144,7 +145,8 @@ def test_qp_tolerate_maxiter_like_acados(torch_cuda, skidpad, config2):
     conv = strict == 0
     np.testing.assert_array_equal(u0[conv], config2["u0"][:B][conv])
     capped = (strict == 4) & (sg == 0)
-    assert capped.sum() > 0.5 * (strict == 4).sum() and (stg[capped, 0] == cfg.qp_max_iter).all()
+    # the stopped QPs end where the oracle's do: at the early exit for infeasible QPs (the default preset) or the cap
+    assert capped.sum() > 0.5 * (strict == 4).sum() and np.mean(stg[capped, 0] == sto[capped, 0]) > 0.98
     assert np.isfinite(u0[capped]).all()
 
 
