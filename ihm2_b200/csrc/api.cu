@@ -14,11 +14,11 @@
 #include "common.cuh"
 
 namespace ihm2b {
-void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
+int launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream);
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream);
-int qp_smem_bytes(int N);
-void launch_build_order(int B, const double* stats, int col, int32_t* order, cudaStream_t stream);
+int qp_smem_bytes(int N, int nl);
+void launch_build_order(int B, const int32_t* last_it, int32_t* order, cudaStream_t stream);
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream);
 cudaError_t launch_dpc_rollout_grad(long long B, int Nf, double dt, const double* weights, const double* x0,
@@ -36,9 +36,12 @@ void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, con
                         int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, int32_t* order_scratch, cudaStream_t stream);
-void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
-                             const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
-                             int32_t* fail, int32_t* active_mask, cudaStream_t stream);
+void launch_closed_loop_post(int B, int step, double dt, const int32_t* track, const double* lap, const int32_t* status,
+                             const double* u0, const double* xn, const double* stats, double* xs, double* xlog,
+                             double* ulog, int32_t* done, int32_t* fail, int32_t* active_mask, int32_t* lap_state,
+                             double* lap_time, double* cost_sum, cudaStream_t stream);
+void launch_solve_finish(const KCfg& cf, const Work& w, const double* x0, const double* snap_x, const double* snap_u,
+                         double* u0, int closed_loop_mask, cudaStream_t stream);
 }  // namespace ihm2b
 
 using namespace ihm2b;
@@ -63,19 +66,21 @@ struct ihm2b_handle {
   Work w;
   int device;
   std::vector<void*> allocs;
-  double *s_ref, *kappa_ref, *params, *lap_len, *actw, *actw_sim;
+  double *s_ref, *kappa_ref, *wr, *wl, *params, *lap_len, *actw, *actw_sim;
   int32_t* track;
   // scratch for the host entry point and the closed loop
   double *x0_dev, *u0_dev, *xn_dev;
   int32_t* status_dev;
   int32_t* active_dev;   // SQP mode: instances still iterating
+  int32_t* lap_state_dev;  // [B][2] closed loop: jumps of mod(s, lap_length) seen, step of the first one
   int32_t* sim_order_dev;  // [B + 2] plant step: instances grouped by the model they take, two counters
   int32_t* order_dev;    // launch order of the QP kernel (longest first by the previous solve's iteration counts)
   bool have_order;
+  double *snap_x, *snap_u;  // iterate at the start of a solve (restored for the instances whose solve fails)
   LineSearch ls;         // allocated when globalization = MERIT_BACKTRACKING
   double *x0_pin, *u0_pin;
   int32_t* status_pin;
-  bool have_tracks, have_params;
+  bool have_tracks, have_widths, have_params;
   bool profile;
   cudaEvent_t ev[3];
   double prof_ms[2];   // accumulated linearise / QP kernel time
@@ -143,6 +148,10 @@ void fill_kcfg(const ihm2b_config& c, KCfg& k) {
   k.mu0 = c.qp_mu0; k.tol = c.qp_tol; k.tol_comp = c.qp_tol_comp;
   k.thr0 = c.qp_thr0 > 0.0 ? c.qp_thr0 : 0.1;
   k.split_step = c.qp_split_step; k.infeas_exit = c.qp_infeas_exit;
+  k.nl = c.nonlinear_constraints ? 1 : 0;
+  k.half_L = c.track_half_L; k.half_W = c.track_half_W; k.a_lat_max = c.a_lat_max;
+  k.T_dot_max = c.T_dot_max; k.delta_dot_max = c.delta_dot_max;
+  k.slack_z = c.slack_z; k.slack_Z = c.slack_Z;
   memcpy(k.irk_A, c.irk_A, sizeof k.irk_A); memcpy(k.irk_b, c.irk_b, sizeof k.irk_b);
 }
 
@@ -162,8 +171,9 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
     return fail(IHM2B_EINVAL, "unknown integrator %d", cfg->integrator);
   if (cfg->nlp_solver != IHM2B_SQP_RTI && cfg->nlp_solver != IHM2B_SQP)
     return fail(IHM2B_EINVAL, "unknown nlp_solver %d", cfg->nlp_solver);
-  if (cfg->nonlinear_constraints)
-    return fail(IHM2B_EINVAL, "nonlinear_constraints: not implemented in this build");
+  if (cfg->nonlinear_constraints && !(cfg->slack_Z > 0.0 && cfg->slack_z >= 0.0 && cfg->a_lat_max > 0.0 &&
+                                      cfg->T_dot_max > 0.0 && cfg->delta_dot_max > 0.0))
+    return fail(IHM2B_EINVAL, "nonlinear_constraints: slack_Z, a_lat_max, T_dot_max and delta_dot_max must be positive");
   int ndev = 0;
   CU(cudaGetDeviceCount(&ndev));
   if (ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
@@ -172,7 +182,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   h->cfg = *cfg;
   fill_kcfg(*cfg, h->k);
   h->launches = 0;
-  h->have_tracks = h->have_params = false;
+  h->have_tracks = h->have_widths = h->have_params = false;
   h->profile = false; h->prof_ms[0] = h->prof_ms[1] = 0.0; h->prof_n = 0;
   for (int i = 0; i < 3; i++) h->ev[i] = nullptr;
   CU(cudaGetDevice(&h->device));
@@ -193,15 +203,19 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(w.BA, B * N * 80);
   ALLOC(w.c, B * N * 8);
   ALLOC(w.phi, B * N * 8);
-  ALLOC(w.LT, B * (N + 1) * 32);
-  ALLOC(w.K, B * N * 16);
-  ALLOC(w.kff, B * N * 2);
-  ALLOC(w.Minv, B * N * 4);
-  ALLOC(w.kfc, B * N * 2);
-  ALLOC(w.D, B * (N + 1) * 16);
+  const size_t RS = cfg->nonlinear_constraints ? 16 : 8;   // inequality row slots per stage
+  ALLOC(w.LT, B * (N + 1) * 4 * RS);
+  ALLOC(w.D, B * (N + 1) * 2 * RS);
   ALLOC(w.xa, B * (N + 1) * 8);
-  ALLOC(w.ua, B * N * 2);
+  if (cfg->nonlinear_constraints) {
+    ALLOC(h->wr, (size_t)cfg->n_tracks * cfg->n_grid);
+    ALLOC(h->wl, (size_t)cfg->n_tracks * cfg->n_grid);
+    ALLOC(w.HC, B * (N + 1) * 16);
+    ALLOC(w.SS, B * (N + 1) * 8 * 16);
+    ALLOC(w.CAB, B * (N + 1) * 2 * 16);
+  }
   ALLOC(w.stats, B * 8);
+  ALLOC(w.last_it, B);
   ALLOC(w.status, B);
   ALLOC(w.dbg, 64 * 8);
   ALLOC(h->x0_dev, B * 8);
@@ -211,6 +225,9 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(h->active_dev, B);
   ALLOC(h->order_dev, B);
   ALLOC(h->sim_order_dev, B + 2);
+  ALLOC(h->lap_state_dev, B * 2);
+  ALLOC(h->snap_x, B * (N + 1) * 8);
+  ALLOC(h->snap_u, B * N * 2);
   memset(&h->ls, 0, sizeof h->ls);
   if (cfg->nlp_solver == IHM2B_SQP && cfg->globalization == IHM2B_MERIT_BACKTRACKING) {
     ALLOC(h->ls.base_x, B * (N + 1) * 8);
@@ -232,7 +249,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
     if (e != cudaSuccess) rc = fail(IHM2B_ENOMEM, "cudaMallocHost: %s", cudaGetErrorString(e));
   }
   if (rc != IHM2B_OK) { ihm2b_destroy(h); return rc; }
-  w.s_ref = h->s_ref; w.kappa_ref = h->kappa_ref; w.params = h->params; w.track = h->track;
+  w.s_ref = h->s_ref; w.kappa_ref = h->kappa_ref; w.wr = h->wr; w.wl = h->wl; w.params = h->params; w.track = h->track;
   w.actw = h->actw; w.actw_sim = h->actw_sim;
   *out = h;
   return ihm2b_reset_iterate(h, nullptr);
@@ -252,7 +269,8 @@ int ihm2b_destroy(ihm2b_handle* h) {
 int ihm2b_set_tracks(ihm2b_handle* h, const double* s_ref, const double* kappa_ref, const double* rw,
                      const double* lw) {
   if (!h || !s_ref || !kappa_ref) return fail(IHM2B_EINVAL, "null argument");
-  (void)rw; (void)lw;  // widths only enter the nonlinear track constraint (not in this build)
+  if (h->cfg.nonlinear_constraints && (!rw || !lw))
+    return fail(IHM2B_EINVAL, "nonlinear_constraints: the track constraint needs right_width and left_width");
   const size_t n = (size_t)h->cfg.n_tracks * h->cfg.n_grid;
   for (int t = 0; t < h->cfg.n_tracks; t++)
     for (int i = 1; i < h->cfg.n_grid; i++)
@@ -260,6 +278,11 @@ int ihm2b_set_tracks(ihm2b_handle* h, const double* s_ref, const double* kappa_r
         return fail(IHM2B_EINVAL, "s_ref of track %d is not strictly increasing at %d", t, i);
   CU(cudaMemcpy(h->s_ref, s_ref, n * sizeof(double), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(h->kappa_ref, kappa_ref, n * sizeof(double), cudaMemcpyHostToDevice));
+  if (h->cfg.nonlinear_constraints) {
+    CU(cudaMemcpy(h->wr, rw, n * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->wl, lw, n * sizeof(double), cudaMemcpyHostToDevice));
+    h->have_widths = true;
+  }
   h->have_tracks = true;
   return IHM2B_OK;
 }
@@ -359,6 +382,7 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream) {
 static int check_ready(ihm2b_handle* h) {
   if (!h) return fail(IHM2B_EINVAL, "null handle");
   if (!h->have_tracks) return fail(IHM2B_EINVAL, "ihm2b_set_tracks has not been called");
+  if (h->cfg.nonlinear_constraints && !h->have_widths) return fail(IHM2B_EINVAL, "nonlinear_constraints: no track widths set");
   if (!h->have_params) return fail(IHM2B_EINVAL, "ihm2b_set_params has not been called");
   return IHM2B_OK;
 }
@@ -370,6 +394,11 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
   if (rc) return rc;
   if (!x0) return fail(IHM2B_EINVAL, "null x0");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  {
+    const size_t B = h->cfg.batch, N = h->cfg.N;
+    CU(cudaMemcpyAsync(h->snap_x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    CU(cudaMemcpyAsync(h->snap_u, h->w.u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  }
   if (h->cfg.nlp_solver == IHM2B_SQP) {
     // acados ocp_nlp_sqp restated (configured by new_python/controller.py:301-302):
     // repeat { linearise; KKT residual test with the multipliers of the last QP; QP; full step }.
@@ -392,7 +421,7 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
     w.order = nullptr;
     for (int it = 0; it < h->cfg.nlp_max_iter; it++) {
       w.sqp_it = it;
-      if (!(line_search && it > 0)) { launch_linearize(h->k, w, s); h->launches++; }
+      if (!(line_search && it > 0)) h->launches += launch_linearize(h->k, w, s);
       launch_nlp_residual(h->k, w, x0, h->cfg.nlp_tol, it > 0, status, s);
       if (line_search) {
         const size_t B = h->cfg.batch, N = h->cfg.N;
@@ -401,7 +430,7 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
       }
       if (launch_qp_rti(h->k, w, x0, u0, status, s) != 0)
         return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
-                    qp_smem_bytes(h->cfg.N), h->cfg.N);
+                    qp_smem_bytes(h->cfg.N, h->k.nl), h->cfg.N);
       h->launches += 2;
       if (line_search) {
         launch_merit_base(h->k, w, h->ls, x0, it == 0, s);
@@ -410,34 +439,39 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
         wt.active = h->ls.mask;
         // alpha = 1, 0.7, ..., 0.7^8 = 0.058, then alpha_min = 0.05: ten trial points at most
         for (int j = 0; j < 10; j++) {
-          launch_linearize(h->k, wt, s);
+          h->launches += launch_linearize(h->k, wt, s);
           launch_merit_trial(h->k, w, h->ls, x0, h->active_dev, status, s);
-          h->launches += 2;
+          h->launches++;
         }
       }
       if (h->cfg.schedule_by_history && it + 1 < h->cfg.nlp_max_iter) {
         // the QP of the next SQP iteration needs about as many IPM iterations as this one: longest first
-        launch_build_order(h->cfg.batch, h->w.stats, 7, h->order_dev, s);
+        launch_build_order(h->cfg.batch, h->w.last_it, h->order_dev, s);
         w.order = h->order_dev;
         h->launches++;
       }
     }
+    // all instances, at the iterate and the h linearisation the solve ends with
+    launch_solve_finish(h->k, w, x0, h->snap_x, h->snap_u, u0, 0, s);
+    h->launches++;
     CU(cudaGetLastError());
     return IHM2B_OK;
   }
   // RTI preparation phase: linearise at the (shifted) iterate; the measured state only
   // enters the feedback phase, as the fixed x_0 of the QP.
   if (h->profile) cudaEventRecord(h->ev[0], s);
-  launch_linearize(h->k, h->w, s);
+  h->launches += launch_linearize(h->k, h->w, s);
   if (h->profile) cudaEventRecord(h->ev[1], s);
   h->w.order = (h->have_order && h->cfg.schedule_by_history) ? h->order_dev : nullptr;
   if (launch_qp_rti(h->k, h->w, x0, u0, status, s) != 0)
     return fail(IHM2B_ECUDA, "QP kernel needs %d bytes of shared memory per problem (N = %d too large)",
-                qp_smem_bytes(h->cfg.N), h->cfg.N);
+                qp_smem_bytes(h->cfg.N, h->k.nl), h->cfg.N);
   if (h->profile) cudaEventRecord(h->ev[2], s);
+  launch_solve_finish(h->k, h->w, x0, h->snap_x, h->snap_u, nullptr, 1, s);
+  h->launches++;
   if (h->cfg.schedule_by_history) {
     // next solve of this handle (closed loop: the next control step) launches its long problems first
-    launch_build_order(h->cfg.batch, h->w.stats, 0, h->order_dev, s);
+    launch_build_order(h->cfg.batch, h->w.last_it, h->order_dev, s);
     h->have_order = true;
     h->launches++;
   }
@@ -448,7 +482,7 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0, double* u0, int32_t* stat
     cudaEventElapsedTime(&b, h->ev[1], h->ev[2]);
     h->prof_ms[0] += a; h->prof_ms[1] += b; h->prof_n++;
   }
-  h->launches += 2;
+  h->launches += 1;
   CU(cudaGetLastError());
   return IHM2B_OK;
 }
@@ -487,8 +521,7 @@ int ihm2b_linearize_dev(ihm2b_handle* h, double* A, double* Bm, double* phi, voi
   int rc = check_ready(h);
   if (rc) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  launch_linearize(h->k, h->w, s);
-  h->launches++;
+  h->launches += launch_linearize(h->k, h->w, s);
   const size_t rows = (size_t)h->cfg.batch * h->cfg.N * 8;
   if (A || Bm) {
     split_ba_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(rows, h->w.BA, A, Bm);
@@ -518,7 +551,7 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double
 }
 
 int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const double* lap_length, double* xlog,
-                          double* ulog, int32_t* done, int32_t* failp, void* stream) {
+                          double* ulog, int32_t* done, int32_t* failp, double* lap_time, double* cost_sum, void* stream) {
   int rc = check_ready(h);
   if (rc) return rc;
   if (!x || !lap_length || !done || !failp || n_steps < 0) return fail(IHM2B_EINVAL, "bad argument");
@@ -527,6 +560,9 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
   CU(cudaMemcpyAsync(h->lap_len, lap_length, (size_t)h->cfg.n_tracks * sizeof(double), cudaMemcpyHostToDevice, s));
   CU(cudaMemsetAsync(done, 0xFF, B * sizeof(int32_t), s));   // -1
   CU(cudaMemsetAsync(failp, 0xFF, B * sizeof(int32_t), s));
+  CU(cudaMemsetAsync(h->lap_state_dev, 0, 2 * B * sizeof(int32_t), s));
+  if (lap_time) CU(cudaMemsetAsync(lap_time, 0xFF, B * sizeof(double), s));   // NaN until two jumps have been seen
+  if (cost_sum) CU(cudaMemsetAsync(cost_sum, 0, B * sizeof(double), s));
   if (xlog) CU(cudaMemcpyAsync(xlog, x, B * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
   // instances that finished their lap or stopped on a solver failure cost nothing in later steps: every
   // kernel of the step honours the mask (RTI mode only; the SQP loop owns the mask during a solve)
@@ -541,8 +577,8 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
     if (!rc) rc = ihm2b_solve_dev(h, x, h->u0_dev, h->status_dev, stream);
     if (rc) { h->w.active = nullptr; return rc; }
     launch_sim_step(h->cfg, h->k, h->w, x, h->u0_dev, h->xn_dev, nullptr, h->sim_order_dev, s);
-    launch_closed_loop_post((int)B, step, h->track, h->lap_len, h->status_dev, h->u0_dev, h->xn_dev, x, xlog, ulog, done,
-                            failp, masked ? h->active_dev : nullptr, s);
+    launch_closed_loop_post((int)B, step, h->cfg.dt, h->track, h->lap_len, h->status_dev, h->u0_dev, h->xn_dev, h->w.stats, x,
+                            xlog, ulog, done, failp, masked ? h->active_dev : nullptr, h->lap_state_dev, lap_time, cost_sum, s);
     h->launches += 2;
   }
   h->w.active = nullptr;

@@ -24,6 +24,10 @@ struct KCfg {
   double mu0, tol, tol_comp, thr0;
   int split_step, infeas_exit;
   double irk_A[16], irk_b[4];
+  // soft nonlinear constraints h(x, u) (old/generate_acaods_interface.py:312-325, 351-449), nl = 1
+  int nl;
+  double half_L, half_W, a_lat_max, T_dot_max, delta_dot_max;
+  double slack_z, slack_Z;     // L1 / L2 slack penalties before the cost scaling
 };
 
 // Device workspace of one handle.  Batch-major, one contiguous block per problem and per
@@ -32,6 +36,8 @@ struct Work {
   // problem data
   const double* s_ref;      // [n_tracks][n_grid]
   const double* kappa_ref;  // [n_tracks][n_grid]
+  const double* wr;         // [n_tracks][n_grid] right / left track widths (nl only)
+  const double* wl;
   const int32_t* track;     // [B]
   const double* params;     // [B][NP]
   const double* actw;       // [B][8]  (I + h/t_T A)^-1 1, (I + h/t_delta A)^-1 1 (controller tableau)
@@ -43,19 +49,21 @@ struct Work {
   double* BA;               // [B][N][8][10]
   double* c;                // [B][N][8]
   double* phi;              // [B][N][8]
-  // interior point state: lamL, lamU, tL, tU per row
-  double* LT;               // [B][N+1][4][8]
-  // Riccati factor of the current IPM iteration
-  double* K;                // [B][N][8][2]   (unused by the current QP kernel: the gains live in shared memory)
-  double* kff;              // [B][N][2]      predictor feed-forward
-  double* Minv;             // [B][N][4]      inverse of M_uu (i00,i01,i11,pad)
-  double* kfc;              // [B][N][2]      corrected feed-forward (kff + corrector part)
-  double* D;                // [B][N+1][2][8] second-order terms dlam_aff * dt_aff (L, U)
-  // candidate solution (affine, then corrected)
-  double* xa;               // [B][N+1][8]
-  double* ua;               // [B][N][2]
+  // interior point state: lamL, lamU, tL, tU per row (RS = 8 row slots per stage, 16 with nl)
+  double* LT;               // [B][N+1][4][RS]
+  double* D;                // [B][N+1][2][RS] second-order terms dlam_aff * dt_aff (L, U) / first-order hand-over
+  double* xa;               // [B][N+1][8]     costate pi
+  // soft nonlinear constraints (nl = 1; the interior-point arrays above then carry 16 row slots per stage:
+  // slots 0..7 the rows of python/mpc.py, slots 8..12 the rows of h)
+  double* HC;               // [B][N+1][16] linearised h rows: [0..2] d h0 / d (s, n, psi), [3] e0; [4..6], [7] the same
+                            //              for h1; [8..11] d h4 / d (v_x, v_y, T, delta), [12] e4; [13] e2, [14] e3
+                            //              (row value = coefficients . z + e; h2, h3 have the constant coefficients -+1/t)
+  double* SS;               // [B][N+1][8][16] slacks of the soft rows: sL, sU, their multipliers, second-order
+                            //              terms / steps of both, slack steps
+  double* CAB;              // [B][N+1][2][16] corrector terms per state / control: chi = CA - mu_t CB
   // outputs
   double* stats;            // [B][8]
+  int32_t* last_it;         // [B] IPM iterations of the last QP (launch order of the next one)
   int32_t* status;          // [B]
   double* dbg;              // [64][8] per-iteration trace of problem 0 (development aid), may be NULL
   // SQP mode (nlp_solver = SQP): instances still iterating, index of the current SQP iteration

@@ -110,12 +110,52 @@ __global__ void __launch_bounds__(128) linearize_erk4_kernel(const KCfg cf, cons
   }
 }
 
+// linearised rows of h(x, u) at the current iterate, all N + 1 stages: one thread per (problem, stage)
+__global__ void __launch_bounds__(128) con_h_kernel(const KCfg cf, const Work w) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int N1 = cf.N + 1;
+  if (gid >= cf.B * N1) return;
+  const int b = gid / N1, k = gid - b * N1;
+  if (w.active && !w.active[b]) return;
+  const int t = w.track[b];
+  const size_t to = (size_t)t * cf.n_grid;
+  TrackView tr{cf.n_grid, w.s_ref + to, w.kappa_ref + to};
+  double p[NP];
+  {
+    const double2* pp = reinterpret_cast<const double2*>(w.params + (size_t)b * NP);
+#pragma unroll
+    for (int i = 0; i < NP / 2; i++) { double2 v = __ldg(pp + i); p[2 * i] = v.x; p[2 * i + 1] = v.y; }
+  }
+  double x[NX];
+  {
+    const double2* xp = reinterpret_cast<const double2*>(w.x + (size_t)gid * NX);
+#pragma unroll
+    for (int i = 0; i < NX / 2; i++) { double2 v = xp[i]; x[2 * i] = v.x; x[2 * i + 1] = v.y; }
+  }
+  const bool term = (k == cf.N);
+  double2 uu = make_double2(0.0, 0.0);
+  if (!term) uu = *reinterpret_cast<const double2*>(w.u + ((size_t)b * cf.N + k) * NU);
+  double out[16];
+  con_h_rows(x, uu.x, uu.y, p, tr, w.wr + to, w.wl + to, cf.half_L, cf.half_W, term, out);
+  double2* hp = reinterpret_cast<double2*>(w.HC + (size_t)gid * 16);
+#pragma unroll
+  for (int i = 0; i < 8; i++) hp[i] = make_double2(out[2 * i], out[2 * i + 1]);
+}
+
 void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream);
 
-void launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream) {
-  if (cf.integrator == IHM2B_IRK_GL4) { launch_linearize_irk(cf, w, stream); return; }
+// returns the number of kernels launched
+int launch_linearize(const KCfg& cf, const Work& w, cudaStream_t stream) {
+  int n = 1;
+  if (cf.nl) {
+    const int total = cf.B * (cf.N + 1);
+    con_h_kernel<<<(total + 127) / 128, 128, 0, stream>>>(cf, w);
+    n = 2;
+  }
+  if (cf.integrator == IHM2B_IRK_GL4) { launch_linearize_irk(cf, w, stream); return n; }
   const int total = cf.B * cf.N;
   linearize_erk4_kernel<<<(total + 127) / 128, 128, 0, stream>>>(cf, w);
+  return n;
 }
 
 }  // namespace ihm2b

@@ -33,6 +33,17 @@ __device__ __forceinline__ void kappa_lookup(const TrackView& tr, double sq, dou
   kap = ka + dkap * (sq - sa);
 }
 
+// Index of the table segment that contains sq (the same clamped "exact" lookup), for tables other than kappa.
+__device__ __forceinline__ int table_segment(const TrackView& tr, double sq) {
+  const int n = tr.n;
+  const double s0 = __ldg(tr.s), s1 = __ldg(tr.s + n - 1);
+  double g = (sq - s0) / (s1 - s0) * (double)(n - 1);
+  int i = (g > 0.0) ? ((g < (double)(n - 2)) ? (int)g : n - 2) : 0;
+  while (i > 0 && __ldg(tr.s + i) > sq) i--;
+  while (i < n - 2 && __ldg(tr.s + i + 1) <= sq) i++;
+  return i;
+}
+
 // Sparsity patterns (bit j = column j of (x0..x7, u0, u1)).
 //   JMASK[i]: structural non-zeros of row i of d f / d (x,u)
 //   SMASK[i]: structural non-zeros of row i of any stage sensitivity d k / d (x0,u) and of
@@ -127,6 +138,70 @@ __device__ __forceinline__ void fkin6(const double* __restrict__ x, const double
   J[5][9] = lR * J[4][9] - dbdot_du;
   J[6][6] = -itT; J[6][8] = itT;
   J[7][7] = -itD; J[7][9] = itD;
+}
+
+// Nonlinear path constraints h(x, u) of the gen-1 OCP (old/generate_acaods_interface.py:312-325 for the 8-state
+// Frenet model; bounds and slack sets :351-449) on the quantities of the controller model above:
+//   h0 =  n - L/2 sin|psi| + W/2 cos psi - right_width(s),   h1 = -n + L/2 sin|psi| + W/2 cos psi - left_width(s)
+//   h2 = (u_T - T) / t_T,   h3 = (u_delta - delta) / t_delta
+//   h4 = a_lat = (-F_Rx sin beta + F_Fx sin(delta - beta)) / m + (v_x^2 + v_y^2) sin(beta) / l_R
+// (width tables: linear interpolants on s_ref, old/generate.py:44-46).  Writes the 16 doubles of Work::HC for one
+// stage: the structurally non-zero Jacobian entries and e_i = h_i - J_i z (row value = J_i z + e_i).
+// term: only h0, h1 exist at the terminal stage (con_h_expr_e), the other entries are zero.
+__device__ __forceinline__ void con_h_rows(const double* __restrict__ x, const double u0, const double u1,
+                                           const double* __restrict__ p, const TrackView& tr,
+                                           const double* __restrict__ wr, const double* __restrict__ wl,
+                                           const double half_L, const double half_W, const bool term,
+                                           double* __restrict__ out) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], T = x[6], dl = x[7];
+  const int i = table_segment(tr, x[0]);
+  const double sa = __ldg(tr.s + i), ids = 1.0 / (__ldg(tr.s + i + 1) - sa);
+  const double ra = __ldg(wr + i), la = __ldg(wl + i);
+  const double dwr = (__ldg(wr + i + 1) - ra) * ids, dwl = (__ldg(wl + i + 1) - la) * ids;
+  const double wrv = ra + dwr * (x[0] - sa), wlv = la + dwl * (x[0] - sa);
+  double sp, cp, sa_, ca_;
+  sincos(psi, &sp, &cp);
+  sincos(fabs(psi), &sa_, &ca_);
+  const double sg = (psi > 0.0) ? 1.0 : (psi < 0.0) ? -1.0 : 0.0;   // d |psi| / d psi (CasADi: sign)
+  const double dabs = ca_ * sg;
+  const double h0 = n - half_L * sa_ + half_W * cp - wrv;
+  const double h1 = -n + half_L * sa_ + half_W * cp - wlv;
+  const double j02 = -half_L * dabs - half_W * sp, j12 = half_L * dabs - half_W * sp;
+  out[0] = -dwr; out[1] = 1.0; out[2] = j02;
+  out[3] = h0 - (-dwr) * x[0] - n - j02 * psi;
+  out[4] = -dwl; out[5] = -1.0; out[6] = j12;
+  out[7] = h1 - (-dwl) * x[0] + n - j12 * psi;
+  if (term) {
+#pragma unroll
+    for (int j = 8; j < 16; j++) out[j] = 0.0;
+    return;
+  }
+  const double m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
+  const double C = lR / (lR + lF), im = 1.0 / m;
+  const double itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
+  const double h2 = (u0 - T) / p[IHM2B_P_TT], h3 = (u1 - dl) / p[IHM2B_P_TD];
+  const double Fm = p[IHM2B_P_CM0] * T;
+  const double th = tanh(10.0 * vx);
+  const double poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
+  const double FRx = 0.5 * Fm - poly * th, FFx = 0.5 * Fm;
+  double sd, cd;
+  sincos(dl, &sd, &cd);
+  const double td = sd / cd, Ctd = C * td, den = 1.0 + Ctd * Ctd;
+  const double cb = rsqrt(den), sb = Ctd * cb;
+  const double G = C * (1.0 + td * td) / den;
+  const double cdb = cd * cb + sd * sb, sdb = sd * cb - cd * sb;
+  const double v2 = vx * vx + vy * vy;
+  const double h4 = (-FRx * sb + FFx * sdb) * im + v2 * sb / lR;
+  const double dFd = -(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th);
+  const double j43 = -dFd * sb * im + 2.0 * vx * sb / lR;
+  const double j44 = 2.0 * vy * sb / lR;
+  const double j46 = 0.5 * p[IHM2B_P_CM0] * (sdb - sb) * im;
+  const double j47 = (-FRx * cb * G + FFx * cdb * (1.0 - G)) * im + v2 * cb * G / lR;
+  out[8] = j43; out[9] = j44; out[10] = j46; out[11] = j47;
+  out[12] = h4 - j43 * vx - j44 * vy - j46 * T - j47 * dl;
+  out[13] = h2 - (-itT) * T - itT * u0;
+  out[14] = h3 - (-itD) * dl - itD * u1;
+  out[15] = 0.0;
 }
 
 }  // namespace ihm2b

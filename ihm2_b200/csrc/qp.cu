@@ -39,11 +39,15 @@ namespace {
 constexpr double TAU = 0.995;
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int PER_STAGE = 58;   // doubles of shared memory per stage
+constexpr int PER_STAGE_NL = PER_STAGE + 20;   // + barrier weights of the dense h rows [4], linearised h rows [16]
 #ifndef PF_
 #define PF_ 2
 #endif
 #ifndef QP_MIN_BLOCKS
 #define QP_MIN_BLOCKS 11   // problems (warps) per SM the register allocation is held to
+#endif
+#ifndef QP_MIN_BLOCKS_NL
+#define QP_MIN_BLOCKS_NL 8
 #endif
 #ifndef PAR_UNROLL
 #define PAR_UNROLL 1
@@ -178,14 +182,132 @@ __device__ __forceinline__ CtDef ct_term(int a) {
 __device__ __forceinline__ double ct_apply(const CtDef& d, const double* q) { return d.c1 * q[d.i1] + d.c2 * q[d.i2]; }
 __device__ __forceinline__ double ctc_apply(const CtDef& d, const double* q) { return d.c1 * q[d.i1] + fabs(d.c2) * q[d.i2]; }
 
+
+// ---------------------------------------------------------------------------------------
+// Soft rows (NL): a soft two-sided row  lb - sL <= v <= ub + sU,  sL, sU >= 0  with the penalty
+// z (sL + sU) + Z/2 (sL^2 + sU^2) (acados idxsbx / idxsh with zl = zu, Zl = Zu:
+// old/generate_acaods_interface.py:383-398, 413, 417, 438, 449).  The slack pair and the multipliers of
+// s >= 0 are eliminated row by row from the Newton system (HPIPM does the same with its Zs_inv vectors), which only
+// changes the barrier weight and the first-order term the row hands to the Riccati recursion:
+//   D = Z + lam/t + lamS/s,   gamma_eff = (lam/t)(Z + lamS/s)/D,   q_eff = q - (lam/t)(r_s + q + q_S)/D.
+// ---------------------------------------------------------------------------------------
+struct RowSt { double lamL, lamU, tL, tU, sL, sU, lsL, lsU; };   // state of one row (s, ls: soft rows only)
+struct RowA { double gam, psi, dl; };
+struct Norms { double rd, rm, rs, S0; };
+
+// residual-side quantities of one row at value v: barrier weight gam, first-order term psi (= q_eff - lam, lower minus
+// upper), multiplier difference dl; accumulates the residual norms and the complementarity sum
+__device__ __forceinline__ RowA soft_row_A(const bool act, const bool soft, const double v, const double lb, const double ub,
+                                           const double isc, const double Z, const double zz, const RowSt& r, Norms& nm) {
+  RowA o{0.0, 0.0, 0.0};
+  if (act) {
+    const double itL = 1.0 / r.tL, itU = 1.0 / r.tU;
+    const double rdL = soft ? v + r.sL - lb - r.tL : v - lb - r.tL;
+    const double rdU = soft ? ub + r.sU - v - r.tU : ub - v - r.tU;
+    double gL = r.lamL * itL, gU = r.lamU * itU;
+    double pL = r.lamL * rdL * itL, pU = r.lamU * rdU * itU;
+    nm.rd = nmax(nm.rd, nmax(fabs(rdL), fabs(rdU)) * isc);
+    nm.rm = nmax(nm.rm, nmax(r.lamL * r.tL, r.lamU * r.tU));
+    nm.S0 += r.lamL * r.tL + r.lamU * r.tU;
+    if (soft) {
+      const double gSL = r.lsL / r.sL, gSU = r.lsU / r.sU;
+      const double rsL = Z * r.sL + zz - r.lamL - r.lsL, rsU = Z * r.sU + zz - r.lamU - r.lsU;
+      nm.rs = nmax(nm.rs, nmax(fabs(rsL), fabs(rsU)));
+      nm.rm = nmax(nm.rm, nmax(r.lsL * r.sL, r.lsU * r.sU));
+      nm.S0 += r.lsL * r.sL + r.lsU * r.sU;
+      const double iDL = 1.0 / (Z + gL + gSL), iDU = 1.0 / (Z + gU + gSU);
+      pL -= gL * (rsL + (r.lamL + pL) + r.lsL) * iDL;
+      pU -= gU * (rsU + (r.lamU + pU) + r.lsU) * iDU;
+      gL *= (Z + gSL) * iDL; gU *= (Z + gSU) * iDU;
+    }
+    o.gam = gL + gU; o.psi = pL - pU; o.dl = r.lamL - r.lamU;
+  }
+  return o;
+}
+
+// Newton step of one row for a given primal step cdz = C dz of the row.  cL, cU / cSL, cSU: second-order corrections of
+// the complementarity products (0 in the predictor, dlam_aff dt_aff - mu_t in the corrector).
+struct RowStep { double dlL, dlU, dtL, dtU, dsL, dsU, dlsL, dlsU; };
+__device__ __forceinline__ RowStep soft_row_step(const bool soft, const double v, const double lb, const double ub, const double cdz,
+                                                 const double Z, const double zz, const RowSt& r, const double cL, const double cU,
+                                                 const double cSL, const double cSU) {
+  RowStep o;
+  const double itL = 1.0 / r.tL, itU = 1.0 / r.tU;
+  const double rdL = soft ? v + r.sL - lb - r.tL : v - lb - r.tL;
+  const double rdU = soft ? ub + r.sU - v - r.tU : ub - v - r.tU;
+  o.dsL = 0.0; o.dsU = 0.0; o.dlsL = 0.0; o.dlsU = 0.0;
+  if (soft) {
+    const double isL = 1.0 / r.sL, isU = 1.0 / r.sU;
+    const double gL = r.lamL * itL, gU = r.lamU * itU;
+    const double qL = r.lamL + (cL + r.lamL * rdL) * itL, qU = r.lamU + (cU + r.lamU * rdU) * itU;
+    const double wL = Z * r.sL + zz - r.lamL - r.lsL + qL + r.lsL + cSL * isL;
+    const double wU = Z * r.sU + zz - r.lamU - r.lsU + qU + r.lsU + cSU * isU;
+    const double iDL = 1.0 / (Z + gL + r.lsL * isL), iDU = 1.0 / (Z + gU + r.lsU * isU);
+    o.dsL = -(wL + gL * cdz) * iDL;
+    o.dsU = -(wU - gU * cdz) * iDU;
+    o.dlsL = -r.lsL - (cSL + r.lsL * o.dsL) * isL;
+    o.dlsU = -r.lsU - (cSU + r.lsU * o.dsU) * isU;
+  }
+  o.dtL = cdz + o.dsL + rdL; o.dtU = -cdz + o.dsU + rdU;
+  o.dlL = -r.lamL - (cL + r.lamL * o.dtL) * itL;
+  o.dlU = -r.lamU - (cU + r.lamU * o.dtU) * itU;
+  return o;
+}
+
+// Row a of h (a < 5) as seen by the kernels that work on global memory (SQP residuals, merit, cost): bounds, the
+// position of the row's coefficients in a stage's 16 doubles of Work::HC, and what state a receives from the h rows.
+struct HLane {
+  int i0, i1, i2, co, eo, r1, r2, so1;
+  bool dense, rate;
+  double ratec, lb, ub, hc2r;
+  __device__ HLane(const KCfg& cf, int a, double itT, double itD) {
+    ub = (a < 2) ? 0.0 : (a == 2) ? cf.T_dot_max : (a == 3) ? cf.delta_dot_max : cf.a_lat_max;
+    lb = (a < 2) ? -1e3 : -ub;
+    i0 = (a < 2) ? 0 : (a == 2) ? 6 : (a == 3) ? 7 : 3; i1 = (a < 2) ? 1 : 4; i2 = (a < 2) ? 2 : 6;
+    dense = (a < 2) || (a == 4); rate = (a == 2 || a == 3);
+    co = (a == 0) ? 0 : (a == 1) ? 4 : 8;
+    eo = (a == 0) ? 3 : (a == 1) ? 7 : (a == 2) ? 13 : (a == 3) ? 14 : (a == 4) ? 12 : 15;
+    ratec = (a == 2) ? itT : (a == 3) ? itD : 0.0;
+    r1 = (a < 3) ? 0 : 4; r2 = (a < 3) ? 1 : (a == 6) ? 2 : 3;
+    so1 = (a < 3) ? a : (a == 3) ? 8 : (a == 4) ? 9 : (a == 6) ? 10 : (a == 7) ? 11 : 15;
+    hc2r = (a == 6) ? -itT : (a == 7) ? -itD : 0.0;
+  }
+  // value of the row at (x, u) of its stage (the same expression as the QP kernel's hrow_val)
+  __device__ double value(const double* __restrict__ h, const double* __restrict__ x, double u0, double u1, int a) const {
+    const double c0 = dense ? h[co] : -ratec, c1 = dense ? h[co + 1] : ratec;
+    const double c2 = dense ? h[co + 2] : 0.0, c3 = (a == 4) ? h[co + 3] : 0.0;
+    const double X1 = (a == 2) ? u0 : (a == 3) ? u1 : x[i1];
+    return fma(c0, x[i0], fma(c1, X1, fma(c2, x[i2], fma(c3, x[7], h[eo]))));
+  }
+};
+// value of a soft row's slack penalty with the slack eliminated: the cheapest feasible slack of a row at value v is
+// its violation, so the NLP in (x, u, s) equals the NLP in (x, u) with cost + sum z viol + Z/2 viol^2
+__device__ __forceinline__ double soft_penalty(double zs, double Zs, double viol) { return viol * (zs + 0.5 * Zs * viol); }
+
+// corrector right-hand side of one row as chi = A - mu_t B (A from the second-order products d, B from the centring)
+__device__ __forceinline__ void soft_row_chi(const bool soft, const double Z, const RowSt& r, const double dL, const double dU,
+                                             const double dSL, const double dSU, double& A, double& B) {
+  const double itL = 1.0 / r.tL, itU = 1.0 / r.tU;
+  double aL = dL * itL, bL = itL, aU = dU * itU, bU = itU;
+  if (soft) {
+    const double isL = 1.0 / r.sL, isU = 1.0 / r.sU;
+    const double gL = r.lamL * itL, gU = r.lamU * itU;
+    const double fL = gL / (Z + gL + r.lsL * isL), fU = gU / (Z + gU + r.lsU * isU);
+    aL = aL * (1.0 - fL) - fL * dSL * isL; bL = bL * (1.0 - fL) - fL * isL;
+    aU = aU * (1.0 - fU) - fU * dSU * isU; bU = bU * (1.0 - fU) - fU * isU;
+  }
+  A = aL - aU; B = bL - bU;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
 // grid = B, block = 32, dynamic shared memory = ((N+1) * PER_STAGE + S_TOT) doubles.
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
-template <int NT>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
-__global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf, const Work w,
+// NL: soft nonlinear constraints h(x, u) and soft bounds (16 row slots per stage instead of 8, see Work::HC)
+template <int NT, bool NL>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
+__global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf, const Work w,
                                                      const double* __restrict__ x0,
                                                      double* __restrict__ u0_out,
                                                      int32_t* __restrict__ status_out) {
@@ -204,7 +326,10 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   double* const pK = pRB + N1 * 8;       // [N1][8][2]
   double* const pKF = pK + N1 * 16;      // [N1][4]   kff[2], kfc[2]
   double* const pMI = pKF + N1 * 4;      // [N1][4]   i00 i01 i11 pad
-  double* const sc = pMI + N1 * 4;
+  double* const pGH = pMI + N1 * 4;      // NL: [N1][4]  barrier weights of the rows h0, h1, h4 (and 0)
+  double* const pHC = pGH + (NL ? N1 * 4 : 0);   // NL: [N1][16] linearised h rows (Work::HC)
+  double* const sc = pHC + (NL ? N1 * 16 : 0);
+  constexpr int RS = NL ? 16 : 8;        // row slots per stage
   // Global memory (L2-resident while the problem is in flight): what only the stage-parallel
   // phases touch, accessed as 256 contiguous bytes per warp instruction; and [B A], whose operand
   // fragments the serial sweeps load into registers PF stages ahead of their use.
@@ -213,12 +338,12 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   double* __restrict__ const pX = w.x + (size_t)b * N1 * 8;           // [N1][8]   iterate, updated in place
   double* __restrict__ const pU = w.u + (size_t)b * N * 2;            // [N][2]
   double* __restrict__ const pPI = w.xa + (size_t)b * N1 * 8;         // [N1][8]   costate
-  double* __restrict__ const pLL = w.LT + (size_t)b * N1 * 32;        // [N1][8]   lamL, lamU, tL, tU
-  double* __restrict__ const pLU = pLL + N1 * 8;
-  double* __restrict__ const pTL = pLU + N1 * 8;
-  double* __restrict__ const pTU = pTL + N1 * 8;
-  double* __restrict__ const pD1 = w.D + (size_t)b * N1 * 16;         // [N1][8]   psi -> dlam_aff*dt_aff (L) -> dlamL
-  double* __restrict__ const pD2 = pD1 + N1 * 8;                      // [N1][8]   dl  -> dlam_aff*dt_aff (U) -> dlamU
+  double* __restrict__ const pLL = w.LT + (size_t)b * N1 * 4 * RS;    // [N1][RS]  lamL, lamU, tL, tU
+  double* __restrict__ const pLU = pLL + N1 * RS;
+  double* __restrict__ const pTL = pLU + N1 * RS;
+  double* __restrict__ const pTU = pTL + N1 * RS;
+  double* __restrict__ const pD1 = w.D + (size_t)b * N1 * 2 * RS;     // [N1][RS]  psi -> dlam_aff*dt_aff (L) -> dlamL
+  double* __restrict__ const pD2 = pD1 + N1 * RS;                     // [N1][RS]  dl  -> dlam_aff*dt_aff (U) -> dlamU
   double* const sv = sc + S_V;
   double* const pDX = pGX; double* const pDU = pGU;
 
@@ -248,6 +373,60 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
   const double iscP = 1.0 / (1.0 + fmin(fabs(Rp.lb), fabs(Rp.ub))), iscT = 1.0 / (1.0 + fmin(fabs(Rt.lb), fabs(Rt.ub)));
   const CtDef ctP = ct_path(a), ctT = ct_term(a);
   const int rounds = (N + 4) >> 2;           // stage-parallel loops: stage k = q + 4 i
+  // ---- NL: row slot 8 + a of a stage is row a of h (a < 5; terminal: a < 2), all soft; of the static rows T and
+  // delta (terminal: the rows on v_y and r) are soft (idxsbx = [2, 3] of idxbx / idxbx_e)
+  double itT = 0.0, itD = 0.0;
+  if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
+  const double Zp = cf.cs * cf.slack_Z, zp = cf.cs * cf.slack_z, Zt = cf.ct * cf.slack_Z, zt = cf.ct * cf.slack_z;
+  const double hub = (a < 2) ? 0.0 : (a == 2) ? cf.T_dot_max : (a == 3) ? cf.delta_dot_max : cf.a_lat_max;
+  const double hlb = (a < 2) ? -1e3 : -hub;
+  const double isc1 = 1.0 / (1.0 + fmin(fabs(hlb), fabs(hub)));
+  const int hi0 = (a < 2) ? 0 : (a == 2) ? 6 : (a == 3) ? 7 : 3, hi1 = (a < 2) ? 1 : 4, hi2 = (a < 2) ? 2 : 6;
+  const bool hdense = (a < 2) || (a == 4), hrate = (a == 2 || a == 3);
+  const int hco = (a == 0) ? 0 : (a == 1) ? 4 : 8;                 // the row's coefficients in pHC (dense rows)
+  const int heo = (a == 0) ? 3 : (a == 1) ? 7 : (a == 2) ? 13 : (a == 3) ? 14 : (a == 4) ? 12 : 15;
+  const double ratec = (a == 2) ? itT : (a == 3) ? itD : 0.0;      // h2, h3: -ratec on T / delta, +ratec on the control
+  // what state a receives from the h rows: coefficient pHC[so1] of row hr1, and pHC[4 + a] of h1 (a < 3) or the
+  // constant -1/t of the rate row hr2 (a = 6, 7)
+  const int hr1 = (a < 3) ? 0 : 4, hr2 = (a < 3) ? 1 : (a == 6) ? 2 : 3;
+  const int so1 = (a < 3) ? a : (a == 3) ? 8 : (a == 4) ? 9 : (a == 6) ? 10 : 11;
+  const double hc2r = (a == 6) ? -itT : (a == 7) ? -itD : 0.0;
+  struct HRow { double c0, c1, c2, c3, e; };
+  auto hrow_coef = [&](int k) {
+    const double* h = pHC + k * 16;
+    HRow r;
+    r.c0 = hdense ? h[hco] : -ratec; r.c1 = hdense ? h[hco + 1] : ratec;
+    r.c2 = hdense ? h[hco + 2] : 0.0; r.c3 = (a == 4) ? h[hco + 3] : 0.0;
+    r.e = h[heo];
+    return r;
+  };
+  // value of h row a at the stage whose state component a this lane holds in xa (u0v, u1v: the stage's controls)
+  auto hrow_val = [&](const HRow& r, double xa_, double u0v, double u1v) {
+    const double X0 = __shfl_sync(FULL, xa_, hi0, GROUP), X1s = __shfl_sync(FULL, xa_, hi1, GROUP);
+    const double X2 = __shfl_sync(FULL, xa_, hi2, GROUP), X3 = __shfl_sync(FULL, xa_, 7, GROUP);
+    const double X1 = (a == 2) ? u0v : (a == 3) ? u1v : X1s;
+    return fma(r.c0, X0, fma(r.c1, X1, fma(r.c2, X2, fma(r.c3, X3, r.e))));
+  };
+  auto hrow_cdz = [&](const HRow& r, int k) {
+    const double X1 = hrate ? pGU[k * 2 + (a - 2)] : pGX[k * 8 + hi1];
+    return fma(r.c0, pGX[k * 8 + hi0], fma(r.c1, X1, fma(r.c2, pGX[k * 8 + hi2], r.c3 * pGX[k * 8 + 7])));
+  };
+  // SS arrays (NL)
+  double* __restrict__ const pSL = NL ? w.SS + (size_t)b * N1 * 8 * 16 : nullptr;   // [N1][16] each
+  double* __restrict__ const pSU = pSL + N1 * 16;
+  double* __restrict__ const pLSL = pSU + N1 * 16;
+  double* __restrict__ const pLSU = pLSL + N1 * 16;
+  double* __restrict__ const pDS1 = pLSU + N1 * 16;   // dlamS_aff * ds_aff (L) -> dlamSL
+  double* __restrict__ const pDS2 = pDS1 + N1 * 16;
+  double* __restrict__ const pE1 = pDS2 + N1 * 16;    // dsL, dsU of the corrected step
+  double* __restrict__ const pE2 = pE1 + N1 * 16;
+  double* __restrict__ const pCA = NL ? w.CAB + (size_t)b * N1 * 2 * 16 : nullptr;  // [N1][16]: [a] state a, [8 + a] control a
+  double* __restrict__ const pCB = pCA + N1 * 16;
+  if (NL) {
+    const double* __restrict__ gHC = w.HC + (size_t)b * N1 * 16;
+    for (int e = lane; e < N1 * 16; e += 32) pHC[e] = gHC[e];
+    for (int e = lane; e < N1 * 4; e += 32) pGH[e] = 0.0;
+  }
   __syncwarp();
 
   // ------------------------------------------------------------------ initialisation
@@ -278,7 +457,82 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       if (a < 4 && !term) pMI[k * 4 + a] = (a < 2) ? ((a == 0 ? hu0 : hu1) + gam + gp2) : (-(a == 2 ? c10 : c11) - gam);
     }
   };
+  // NL form of the row pass: both row slots of the lane, soft rows with their slacks eliminated; the rows' first-order
+  // terms are handed over per state / control (pD1 / pD2 [k][a] state a, [k][8 + a] control a), the barrier weights
+  // of the dense rows h0, h1, h4 go to pGH for the Riccati sweep (their C' gam C is not diagonal)
+  double rs_m = 0.0;
+  auto rows_A_nl = [&](int k, bool on, bool term, bool act0, double v0, const RowSt& r0, bool act1, double v1, const RowSt& r1) {
+    const RowDef& R = term ? Rt : Rp;
+    const double Z = term ? Zt : Zp, zz = term ? zt : zp;
+    const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
+    Norms nm{rd_m, rm_m, rs_m, S0};
+    const RowA A0 = soft_row_A(act0, soft0, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
+    const RowA A1 = soft_row_A(act1, true, v1, hlb, hub, isc1, Z, zz, r1, nm);
+    rd_m = nm.rd; rm_m = nm.rm; rs_m = nm.rs; S0 = nm.S0;
+    const CtDef& ct = term ? ctT : ctP;
+    const double* h = pHC + k * 16;
+    const double hc1 = (a != 5) ? h[so1] : 0.0, hc2 = (a < 3) ? h[4 + a] : hc2r;
+    const int ap2 = (a + 2) & 7;
+    const double g1 = __shfl_sync(FULL, A0.gam, ct.i1, GROUP), g2 = __shfl_sync(FULL, A0.gam, ct.i2, GROUP), gp2 = __shfl_sync(FULL, A0.gam, ap2, GROUP);
+    const double p1 = __shfl_sync(FULL, A0.psi, ct.i1, GROUP), p2 = __shfl_sync(FULL, A0.psi, ct.i2, GROUP), pp2 = __shfl_sync(FULL, A0.psi, ap2, GROUP);
+    const double l1 = __shfl_sync(FULL, A0.dl, ct.i1, GROUP), l2 = __shfl_sync(FULL, A0.dl, ct.i2, GROUP), lp2 = __shfl_sync(FULL, A0.dl, ap2, GROUP);
+    const double hg2 = __shfl_sync(FULL, A1.gam, hr2, GROUP), ug = __shfl_sync(FULL, A1.gam, ap2, GROUP);
+    const double hp1 = __shfl_sync(FULL, A1.psi, hr1, GROUP), hp2 = __shfl_sync(FULL, A1.psi, hr2, GROUP), up = __shfl_sync(FULL, A1.psi, ap2, GROUP);
+    const double hl1 = __shfl_sync(FULL, A1.dl, hr1, GROUP), hl2 = __shfl_sync(FULL, A1.dl, hr2, GROUP), ul = __shfl_sync(FULL, A1.dl, ap2, GROUP);
+    if (on) {
+      pGAM[k * 8 + a] = (term ? hxN : hx) + ct.c1 * g1 + fabs(ct.c2) * g2 + ((a >= 6) ? hc2 * hc2 * hg2 : 0.0);
+      pD1[k * 16 + a] = ct.c1 * p1 + ct.c2 * p2 + hc1 * hp1 + hc2 * hp2;
+      pD2[k * 16 + a] = ct.c1 * l1 + ct.c2 * l2 + hc1 * hl1 + hc2 * hl2;
+      if (!term) {
+        if (a < 2) {
+          const double rc = (a == 0) ? itT : itD;
+          pD1[k * 16 + 8 + a] = A0.psi + pp2 + rc * up;
+          pD2[k * 16 + 8 + a] = A0.dl + lp2 + rc * ul;
+          pMI[k * 4 + a] = (a == 0 ? hu0 : hu1) + A0.gam + gp2 + rc * rc * ug;
+        } else if (a < 4) {
+          pMI[k * 4 + a] = -(a == 2 ? c10 : c11) - A0.gam - ratec * ratec * A1.gam;
+        }
+      }
+      if (a < 2) pGH[k * 4 + a] = A1.gam;
+      if (a == 4) pGH[k * 4 + 2] = A1.gam;
+    }
+  };
   // slacks / multipliers cold (t = max(distance, thr0), lam = mu0 / t), pi = 0
+  if constexpr (NL) {
+    PAR_LOOP for (int i = 0; i < rounds; i++) {
+      const int kk = q + 4 * i;
+      const bool on = (kk <= N);
+      const int k = on ? kk : N;
+      const bool term = (k == N);
+      const RowDef& R = term ? Rt : Rp;
+      const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+      const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
+      const double xa_ = pX[k * 8 + a], u0v = pU[(term ? 0 : k) * 2], u1v = pU[(term ? 0 : k) * 2 + 1];
+      const double v0 = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
+      const HRow hr = hrow_coef(k);
+      const double v1 = hrow_val(hr, xa_, u0v, u1v);
+      RowSt r0{0.0, 0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0}, r1 = r0;
+      if (act0) {
+        if (soft0) { r0.sL = r0.sU = cf.thr0; r0.lsL = r0.lsU = cf.mu0 / cf.thr0; }
+        r0.tL = fmax(soft0 ? v0 + r0.sL - R.lb : v0 - R.lb, cf.thr0); r0.tU = fmax(soft0 ? R.ub + r0.sU - v0 : R.ub - v0, cf.thr0);
+        r0.lamL = cf.mu0 / r0.tL; r0.lamU = cf.mu0 / r0.tU;
+      }
+      if (act1) {
+        r1.sL = r1.sU = cf.thr0; r1.lsL = r1.lsU = cf.mu0 / cf.thr0;
+        r1.tL = fmax(v1 + r1.sL - hlb, cf.thr0); r1.tU = fmax(hub + r1.sU - v1, cf.thr0);
+        r1.lamL = cf.mu0 / r1.tL; r1.lamU = cf.mu0 / r1.tU;
+      }
+      if (on) {
+        const int e0 = k * 16 + a, e1 = e0 + 8;
+        pLL[e0] = r0.lamL; pLU[e0] = r0.lamU; pTL[e0] = r0.tL; pTU[e0] = r0.tU;
+        pSL[e0] = r0.sL; pSU[e0] = r0.sU; pLSL[e0] = r0.lsL; pLSU[e0] = r0.lsU;
+        pLL[e1] = r1.lamL; pLU[e1] = r1.lamU; pTL[e1] = r1.tL; pTU[e1] = r1.tU;
+        pSL[e1] = r1.sL; pSU[e1] = r1.sU; pLSL[e1] = r1.lsL; pLSU[e1] = r1.lsU;
+        pPI[k * 8 + a] = 0.0;
+      }
+      rows_A_nl(k, on, term, act0, v0, r0, act1, v1, r1);
+    }
+  } else
   PAR_LOOP for (int i = 0; i < rounds; i++) {
     const int kk = q + 4 * i;
     const bool on = (kk <= N);
@@ -299,7 +553,8 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
     rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
   }
   __syncwarp();
-  const double inv_n = 1.0 / (16.0 * N);  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4)
+  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4); NL: 28 at stage 0, 40 on the path, 20 at the end (soft rows count twice)
+  const double inv_n = NL ? 1.0 / (40.0 * N + 8.0) : 1.0 / (16.0 * N);
   double mu = 0.0, res_g = 0.0, res_b = 0.0, res_d = 0.0, res_m = 0.0;
   int it = 0, qp_status = 1, at_floor = 0, short_steps = 0;
   const double mu_floor = 0.1 * cf.tol_comp;
@@ -355,10 +610,12 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       const int ku = term ? 0 : k, kn = term ? k : k + 1, j = a & 1;
       ResIn in;
       in.xa = pX[k * 8 + a]; in.pia = pPI[k * 8 + a];
-      in.p1 = pD1[k * 8 + ct.i1]; in.p2 = pD1[k * 8 + ct.i2]; in.l1 = pD2[k * 8 + ct.i1]; in.l2 = pD2[k * 8 + ct.i2];
+      if (NL) { in.p1 = pD1[k * 16 + a]; in.l1 = pD2[k * 16 + a]; in.p2 = 0.0; in.l2 = 0.0; }   // handed over per state
+      else { in.p1 = pD1[k * 8 + ct.i1]; in.p2 = pD1[k * 8 + ct.i2]; in.l1 = pD2[k * 8 + ct.i1]; in.l2 = pD2[k * 8 + ct.i2]; }
       in.u0 = pU[ku * 2]; in.u1 = pU[ku * 2 + 1];
       in.c = pC[(term ? 0 : k) * 8 + a]; in.xn = pX[kn * 8 + a]; in.xj = pX[k * 8 + 6 + j];
-      in.q0 = pD2[k * 8 + j]; in.q1 = pD2[k * 8 + 2 + j]; in.s0 = pD1[k * 8 + j]; in.s1 = pD1[k * 8 + 2 + j];
+      if (NL) { in.q0 = pD2[k * 16 + 8 + j]; in.s0 = pD1[k * 16 + 8 + j]; in.q1 = 0.0; in.s1 = 0.0; }
+      else { in.q0 = pD2[k * 8 + j]; in.q1 = pD2[k * 8 + 2 + j]; in.s0 = pD1[k * 8 + j]; in.s1 = pD1[k * 8 + 2 + j]; }
       return in;
     };
     ResIn rnx = load_res(0);
@@ -370,7 +627,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         const bool term = (k == N);
         const CtDef& ct = term ? ctT : ctP;
         const double xa_ = in.xa, pia = in.pia;
-        const double psi_s = ct.c1 * in.p1 + ct.c2 * in.p2, dl_s = ct.c1 * in.l1 + ct.c2 * in.l2;
+        const double psi_s = NL ? in.p1 : ct.c1 * in.p1 + ct.c2 * in.p2, dl_s = NL ? in.l1 : ct.c1 * in.l1 + ct.c2 * in.l2;
         double base_x;
         if (!term) {
           const double u0 = in.u0, u1 = in.u1;
@@ -394,7 +651,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         pGX[k * 8 + a] = base_x + psi_s;
       }
     }
-    res_g = wmax(rg_m); res_b = wmax(rb_m); res_d = wmax(rd_m); res_m = wmax(rm_m);
+    res_g = wmax(NL ? nmax(rg_m, rs_m) : rg_m); res_b = wmax(rb_m); res_d = wmax(rd_m); res_m = wmax(rm_m);
     S0 = wsum(S0);
     mu = S0 * inv_n;
     if (w.dbg && b == 0 && lane == 0 && it < 64) {
@@ -446,6 +703,14 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       const int o11 = (t == 1) ? (int)(pGU - smem) + (g & 1) : (int)(pMI - smem) + (g & 1);
       const int s11 = (t == 1) ? 2 : 4;
       const bool k11a = (t == 1 && g < 2) || (lane == 0), k11b = (lane == 4);
+      // NL: C' gam C of the dense rows h0, h1, h4 as one more product into the xx tile: slot t = row (h0, h1, h4, -),
+      // this lane holds the coefficient of state g in that row
+      const bool hval = (t < 2) ? (g < 3) : (t == 2 && g >= 3 && g != 5);
+      const int hoff = (t < 2) ? 4 * t + g : (g == 3) ? 8 : (g == 4) ? 9 : (g == 6) ? 10 : 11;
+      if constexpr (NL) {   // terminal stage: h0, h1
+        const double cH = hval ? pHC[N * 16 + hoff] : 0.0;
+        dmma(P0, P1, pGH[N * 4 + t] * cH, cH);
+      }
       auto load_E = [&](int k) {
         const double* p = gBA + k * 80 + ra;
         return Frag4{p[2 + g], p[12 + g], p[g & 1], p[10 + (g & 1)]};   // A[2t][g], A[2t+1][g], B[2t][g&1], B[2t+1][g&1]
@@ -460,6 +725,10 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         double T00a = dgA ? dgv : 0.0, T00b = dgB ? dgv : 0.0;
         double T01a = k01a ? v01 : 0.0, T01b = k01b ? v01 : 0.0;
         double T11a = k11a ? v11 : 0.0, T11b = k11b ? v11 : 0.0;
+        if constexpr (NL) {
+          const double cH = hval ? pHC[k * 16 + hoff] : 0.0;
+          dmma(T00a, T00b, pGH[k * 4 + t] * cH, cH);
+        }
         // ---- step 1: W' tiles (rows = columns of E, columns = rows of P)
         double W0a = 0.0, W0b = 0.0;
         double W1a = (g == 2) ? pp0 : 0.0, W1b = (g == 2) ? pp1 : 0.0;     // column 10: v = P rb + p
@@ -482,6 +751,16 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         const double Kb0 = -(i00 * xb0 + i01 * xb1), Kb1 = -(i01 * xb0 + i11 * xb1);   // K[:, 2t+1]
         P0 = fma(xg0, Ka0, fma(xg1, Ka1, T00a));
         P1 = fma(xg0, Kb0, fma(xg1, Kb1, T00b));
+#ifndef QP_NO_SYMMETRISE   // rounding asymmetry of P drifts over the 40 stages once lam / t ~ 1e12 sits next to an O(1) Hessian: without this the
+                          // interior point needs up to 50 % more iterations on thin interiors and fails where the oracle (which symmetrises) does not
+        {   // P <- (P + P') / 2: the transposed entries P[2t][g], P[2t+1][g] sit in lanes (2t, g >> 1), (2t + 1, g >> 1)
+          const int sa = ((2 * t) << 2) | (g >> 1), sb = ((2 * t + 1) << 2) | (g >> 1);
+          const double a0 = __shfl_sync(FULL, P0, sa), a1 = __shfl_sync(FULL, P1, sa);
+          const double b0 = __shfl_sync(FULL, P0, sb), b1 = __shfl_sync(FULL, P1, sb);
+          P0 = 0.5 * (P0 + ((g & 1) ? a1 : a0));
+          P1 = 0.5 * (P1 + ((g & 1) ? b1 : b0));
+        }
+#endif
         pp0 = fma(Ka0, mvu0, fma(Ka1, mvu1, mva));
         pp1 = fma(Kb0, mvu0, fma(Kb1, mvu1, mvb));
         sts2_if(g == 0, pK + k * 16 + 4 * t, Ka0, Ka1);
@@ -551,6 +830,93 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         in.xa = 0.0; in.pia = 0.0;
         return in;
       };
+      if constexpr (NL) {
+        PAR_LOOP for (int i = 0; i < rounds; i++) {
+          const int kk = q + 4 * i;
+          const bool on = (kk <= N);
+          const int k = on ? kk : N;
+          const bool term = (k == N);
+          const RowDef& R = term ? Rt : Rp;
+          const double Z = term ? Zt : Zp, zz = term ? zt : zp;
+          const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+          const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
+          const int e0 = k * 16 + a, e1 = e0 + 8;
+          const double xa_ = pX[k * 8 + a], u0v = pU[(term ? 0 : k) * 2], u1v = pU[(term ? 0 : k) * 2 + 1];
+          const double v0 = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
+          const HRow hr = hrow_coef(k);
+          const double v1 = hrow_val(hr, xa_, u0v, u1v);
+          const double cdz0 = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
+          const double cdz1 = hrow_cdz(hr, k);
+          double ddl0 = 0.0, ddl1 = 0.0, A0 = 0.0, B0 = 0.0, A1 = 0.0, B1 = 0.0;
+#pragma unroll
+          for (int hh = 0; hh < 2; hh++) {
+            const bool act = hh ? act1 : act0, soft = hh ? true : soft0;
+            const int e = hh ? e1 : e0;
+            if (act) {
+              const double v = hh ? v1 : v0, lb = hh ? hlb : R.lb, ub = hh ? hub : R.ub, cdz = hh ? cdz1 : cdz0;
+              RowSt r{pLL[e], pLU[e], pTL[e], pTU[e], 1.0, 1.0, 0.0, 0.0};
+              if (soft) { r.sL = pSL[e]; r.sU = pSU[e]; r.lsL = pLSL[e]; r.lsU = pLSU[e]; }
+              if (pred) {
+                const RowStep st = soft_row_step(soft, v, lb, ub, cdz, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
+                S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
+                const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
+                double dSL = 0.0, dSU = 0.0;
+                S2 += dL + dU;
+                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                if (soft) {
+                  dSL = st.dlsL * st.dsL; dSU = st.dlsU * st.dsU;
+                  S1 += r.lsL * st.dsL + r.lsU * st.dsU; S1d += r.sL * st.dlsL + r.sU * st.dlsU; S2 += dSL + dSU;
+                  ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
+                  ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
+                  pDS1[e] = dSL; pDS2[e] = dSU;
+                }
+                pD1[e] = dL; pD2[e] = dU;
+                soft_row_chi(soft, Z, r, dL, dU, dSL, dSU, hh ? A1 : A0, hh ? B1 : B0);
+              } else {
+                const double cSL = soft ? pDS1[e] - mu_t : 0.0, cSU = soft ? pDS2[e] - mu_t : 0.0;
+                const RowStep st = soft_row_step(soft, v, lb, ub, cdz, Z, zz, r, pD1[e] - mu_t, pD2[e] - mu_t, cSL, cSU);
+                pD1[e] = st.dlL; pD2[e] = st.dlU;
+                (hh ? ddl1 : ddl0) = st.dlL - st.dlU;
+                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                if (soft) {
+                  pDS1[e] = st.dlsL; pDS2[e] = st.dlsU; pE1[e] = st.dsL; pE2[e] = st.dsU;
+                  ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
+                  ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
+                }
+              }
+            }
+          }
+          const CtDef& ct = term ? ctT : ctP;
+          const double* h = pHC + k * 16;
+          const double hc1 = (a != 5) ? h[so1] : 0.0, hc2 = (a < 3) ? h[4 + a] : hc2r;
+          const int ap2 = (a + 2) & 7;
+          if (pred) {
+            // corrector right-hand side chi = A - mu_t B of every row, handed over per state / control
+            const double a1 = __shfl_sync(FULL, A0, ct.i1, GROUP), a2 = __shfl_sync(FULL, A0, ct.i2, GROUP), a3 = __shfl_sync(FULL, A0, ap2, GROUP);
+            const double b1 = __shfl_sync(FULL, B0, ct.i1, GROUP), b2 = __shfl_sync(FULL, B0, ct.i2, GROUP), b3 = __shfl_sync(FULL, B0, ap2, GROUP);
+            const double ha1 = __shfl_sync(FULL, A1, hr1, GROUP), ha2 = __shfl_sync(FULL, A1, hr2, GROUP), ha3 = __shfl_sync(FULL, A1, ap2, GROUP);
+            const double hb1 = __shfl_sync(FULL, B1, hr1, GROUP), hb2 = __shfl_sync(FULL, B1, hr2, GROUP), hb3 = __shfl_sync(FULL, B1, ap2, GROUP);
+            if (on) {
+              pCA[k * 16 + a] = ct.c1 * a1 + ct.c2 * a2 + hc1 * ha1 + hc2 * ha2;
+              pCB[k * 16 + a] = ct.c1 * b1 + ct.c2 * b2 + hc1 * hb1 + hc2 * hb2;
+              if (a < 2 && !term) {
+                const double rc = (a == 0) ? itT : itD;
+                pCA[k * 16 + 8 + a] = A0 + a3 + rc * ha3;
+                pCB[k * 16 + 8 + a] = B0 + b3 + rc * hb3;
+              }
+            }
+          } else {
+            const double d1 = __shfl_sync(FULL, ddl0, ct.i1, GROUP), d2 = __shfl_sync(FULL, ddl0, ct.i2, GROUP);
+            const double hd1 = __shfl_sync(FULL, ddl1, hr1, GROUP), hd2 = __shfl_sync(FULL, ddl1, hr2, GROUP);
+            if (on) {
+              const double hdz = term ? hxN * pDX[k * 8 + a] : hx * pDX[k * 8 + a] + hxu0 * pDU[k * 2] + hxu1 * pDU[k * 2 + 1];
+              pGAM[k * 8 + a] = pRG[k * 8 + a] - (ct.c1 * d1 + ct.c2 * d2 + hc1 * hd1 + hc2 * hd2) + hdz;
+            }
+          }
+        }
+      } else {
       RowIn nxt = load_rows(0);
       PAR_LOOP for (int i = 0; i < rounds; i++) {
         const RowIn cur = nxt;
@@ -595,6 +961,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
           }
         }
       }
+      }
       ratio = wmax(ratio); ratio_d = wmax(ratio_d);
       if (!(ratio == ratio) || !(ratio_d == ratio_d)) { bad = true; break; }
       if (!cf.split_step) ratio = ratio_d = nmax(ratio, ratio_d);
@@ -618,6 +985,15 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         const int e = ((kk <= N) ? kk : N) * 8 + a;
         return Frag4{pD1[e], pD2[e], pTL[e], pTU[e]};
       };
+      if constexpr (NL) {
+        PAR_LOOP for (int i = 0; i < rounds; i++) {
+          const int k = q + 4 * i;
+          if (k <= N) {
+            pGAM[k * 8 + a] = pCA[k * 16 + a] - mu_t * pCB[k * 16 + a];
+            if (a < 2 && k < N) pKF[k * 4 + 2 + a] = pCA[k * 16 + 8 + a] - mu_t * pCB[k * 16 + 8 + a];
+          }
+        }
+      } else {
       Frag4 cnx = load_chi(0);
       PAR_LOOP for (int i = 0; i < rounds; i++) {
         const Frag4 cc = cnx;
@@ -636,6 +1012,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
           pGAM[k * 8 + a] = ct.c1 * c1v + ct.c2 * c2v;
           if (a < 2 && !term) pKF[k * 4 + 2 + a] = chi + cp2;
         }
+      }
       }
       __syncwarp();
       TICK(4)
@@ -719,6 +1096,59 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       in.xa = pX[e]; in.pia = pPI[e];
       return in;
     };
+    if constexpr (NL) {
+      rs_m = 0.0;
+      PAR_LOOP for (int i = 0; i < rounds; i++) {
+        const int kk = q + 4 * i;
+        const bool on = (kk <= N);
+        const int k = on ? kk : N;
+        const bool term = (k == N);
+        const RowDef& R = term ? Rt : Rp;
+        const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+        const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
+        const int e0 = k * 16 + a, e1 = e0 + 8, ku = term ? 0 : k;
+        const double xa_ = pX[k * 8 + a], pia = pPI[k * 8 + a], u0v = pU[ku * 2], u1v = pU[ku * 2 + 1];
+        const HRow hr = hrow_coef(k);
+        const double v0o = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
+        const double v1o = hrow_val(hr, xa_, u0v, u1v);
+        const double cdz0 = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
+        const double cdz1 = hrow_cdz(hr, k);
+        // the primal point after the step, and the rows there
+        const double xn_ = fma(alpha, pDX[k * 8 + a], xa_);
+        const double u0n = term ? u0v : fma(alpha, pDU[k * 2], u0v), u1n = term ? u1v : fma(alpha, pDU[k * 2 + 1], u1v);
+        const double v0 = row_value(R, term, R.iu ? u1n : u0n, __shfl_sync(FULL, xn_, R.ix, GROUP));
+        const double v1 = hrow_val(hr, xn_, u0n, u1n);
+        RowSt r0{0.0, 0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0}, r1 = r0;
+#pragma unroll
+        for (int hh = 0; hh < 2; hh++) {
+          const bool act = hh ? act1 : act0, soft = hh ? true : soft0;
+          const int e = hh ? e1 : e0;
+          if (act) {
+            const double vo = hh ? v1o : v0o, lb = hh ? hlb : R.lb, ub = hh ? hub : R.ub, cdz = hh ? cdz1 : cdz0;
+            RowSt r{pLL[e], pLU[e], pTL[e], pTU[e], 1.0, 1.0, 0.0, 0.0};
+            double dsL = 0.0, dsU = 0.0;
+            if (soft) { r.sL = pSL[e]; r.sU = pSU[e]; r.lsL = pLSL[e]; r.lsU = pLSU[e]; dsL = pE1[e]; dsU = pE2[e]; }
+            const double rdL = soft ? vo + r.sL - lb - r.tL : vo - lb - r.tL;
+            const double rdU = soft ? ub + r.sU - vo - r.tU : ub - vo - r.tU;
+            r.tL = fma(alpha, cdz + dsL + rdL, r.tL); r.tU = fma(alpha, -cdz + dsU + rdU, r.tU);
+            r.lamL = fma(alpha_d, pD1[e], r.lamL); r.lamU = fma(alpha_d, pD2[e], r.lamU);
+            pLL[e] = r.lamL; pLU[e] = r.lamU; pTL[e] = r.tL; pTU[e] = r.tU;
+            if (soft) {
+              r.sL = fma(alpha, dsL, r.sL); r.sU = fma(alpha, dsU, r.sU);
+              r.lsL = fma(alpha_d, pDS1[e], r.lsL); r.lsU = fma(alpha_d, pDS2[e], r.lsU);
+              pSL[e] = r.sL; pSU[e] = r.sU; pLSL[e] = r.lsL; pLSU[e] = r.lsU;
+            }
+            if (hh) r1 = r; else r0 = r;
+          }
+        }
+        rows_A_nl(k, on, term, act0, v0, r0, act1, v1, r1);
+        if (on) {
+          pX[k * 8 + a] = xn_;
+          pPI[k * 8 + a] = fma(alpha_d, pRG[k * 8 + a], pia);
+          if (a < 2 && !term) pU[k * 2 + a] = a ? u1n : u0n;
+        }
+      }
+    } else {
     RowIn unx = load_upd(0);
     PAR_LOOP for (int i = 0; i < rounds; i++) {
       const RowIn cur = unx;
@@ -751,6 +1181,7 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
         if (a < 2 && !term) pU[k * 2 + a] = fma(alpha, pDU[k * 2 + a], pU[k * 2 + a]);
       }
     }
+    }
     __syncwarp();
     TICK(7)
     it++;
@@ -774,10 +1205,11 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
       st = (loose || (cf.qp_tolerate_maxiter && (qp_status == 1 || qp_status == 4))) ? IHM2B_SUCCESS : IHM2B_QP_FAILURE;
     }
     double* sp = w.stats + (size_t)b * 8;
-    if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics
-      sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m; sp[7] = 0.0;
+    w.last_it[b] = it;           // launch order of the handle's next QP
+    if (w.sqp_it < 0) {          // RTI: one QP per call, its residuals are the statistics ([7], the cost: ocp_cost_kernel)
+      sp[0] = it; sp[1] = 1.0; sp[2] = mu; sp[3] = res_g; sp[4] = res_b; sp[5] = res_d; sp[6] = res_m;
     } else {                     // SQP: the NLP residuals (sp[3..6]) are written by nlp_residual_kernel
-      sp[0] = (w.sqp_it > 0 ? sp[0] : 0.0) + it; sp[1] = w.sqp_it + 1; sp[2] = mu; sp[7] = it;   // [7]: IPM iterations of this QP
+      sp[0] = (w.sqp_it > 0 ? sp[0] : 0.0) + it; sp[1] = w.sqp_it + 1; sp[2] = mu;
       if (st != IHM2B_SUCCESS) w.active[b] = 0;   // the iteration stops at a failed QP (status 1 / 4)
       else st = IHM2B_MAXITER;                    // until the residual test of a later iteration says converged
     }
@@ -794,19 +1226,27 @@ __global__ void __launch_bounds__(32, QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf
 // linearisation (phi, [B A]).  One warp per problem, lane (a, q) = state / row a of the
 // stages q, q+4, ...  grid = B, block = 32.
 // ---------------------------------------------------------------------------------------
+template <bool NL>
 __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const Work w, const double* __restrict__ x0,
                                                           const double nlp_tol, const int have_mult,
                                                           int32_t* __restrict__ status_out) {
   const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
   if (w.active && !w.active[b]) return;
   const int N = cf.N, N1 = N + 1;
+  constexpr int RS = NL ? 16 : 8;
   const double* gBA = w.BA + (size_t)b * N * 80;
   const double* phi = w.phi + (size_t)b * N * 8;
   const double* pX = w.x + (size_t)b * N1 * 8;
   const double* pU = w.u + (size_t)b * N * 2;
   const double* pPI = w.xa + (size_t)b * N1 * 8;
-  const double* pLL = w.LT + (size_t)b * N1 * 32;
-  const double* pLU = pLL + N1 * 8;
+  const double* pLL = w.LT + (size_t)b * N1 * 4 * RS;
+  const double* pLU = pLL + N1 * RS;
+  const double* pLSL = NL ? w.SS + ((size_t)b * 8 + 2) * N1 * 16 : nullptr;   // multipliers of sL, sU >= 0
+  const double* pLSU = pLSL + N1 * 16;
+  const double* gHC = NL ? w.HC + (size_t)b * N1 * 16 : nullptr;
+  double itT = 0.0, itD = 0.0;
+  if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
+  const HLane hl(cf, a, itT, itD);
   const double s0 = x0[(size_t)b * 8];
   const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
   const double hxN = cf.ct * cf.We[a];
@@ -818,27 +1258,48 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
   const CtDef ctP = ct_path(a), ctT = ct_term(a);
   double rs = 0.0, re = fabs(pX[a] - x0[(size_t)b * 8 + a]), ri = 0.0, rc = 0.0;
   const unsigned seg = 0xffu << (8 * q);   // the segments run different trip counts
+  // one two-sided row at value v: residuals; returns lamL - lamU.  Soft rows: slack eliminated, s* = violation
+  auto row_res = [&](bool soft, double v, double lb, double ub, int e, double Z, double zz) {
+    const double sL = soft ? fmax(0.0, lb - v) : 0.0, sU = soft ? fmax(0.0, v - ub) : 0.0;
+    ri = nmax(ri, nmax(lb - sL - v, v - ub - sU));
+    if (!have_mult) return 0.0;
+    const double lamL = pLL[e], lamU = pLU[e];
+    rc = nmax(rc, nmax(fabs(lamL * (v + sL - lb)), fabs(lamU * (ub + sU - v))));
+    if (NL && soft) {
+      const double lsL = pLSL[e], lsU = pLSU[e];
+      rc = nmax(rc, nmax(fabs(lsL * sL), fabs(lsU * sU)));
+      rs = nmax(rs, nmax(fabs(Z * sL + zz - lamL - lsL), fabs(Z * sU + zz - lamU - lsU)));
+    }
+    return lamL - lamU;
+  };
   for (int k = q; k <= N; k += 4) {
     const bool term = (k == N);
     const double xa_ = pX[k * 8 + a];
+    const double Z = (term ? cf.ct : cf.cs) * cf.slack_Z, zz = (term ? cf.ct : cf.cs) * cf.slack_z;
     // inequality row a of this stage
     const RowDef& R = term ? Rt : Rp;
     const bool act = term ? (a < 4) : (a < 4 || k > 0);
-    double dl = 0.0;
+    double dl = 0.0, dl1 = 0.0;
     if (act) {
       const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
-      ri = nmax(ri, nmax(R.lb - v, v - R.ub));
-      if (have_mult) {
-        const double lamL = pLL[k * 8 + a], lamU = pLU[k * 8 + a];
-        dl = lamL - lamU;
-        rc = nmax(rc, nmax(fabs(lamL * (v - R.lb)), fabs(lamU * (R.ub - v))));
-      }
+      dl = row_res(NL && (term ? (a == 2 || a == 3) : (a >= 6)), v, R.lb, R.ub, k * RS + a, Z, zz);
+    }
+    if (NL && (term ? (a < 2) : (a < 5))) {
+      const double v1 = hl.value(gHC + k * 16, pX + k * 8, term ? 0.0 : pU[k * 2], term ? 0.0 : pU[k * 2 + 1], a);
+      dl1 = row_res(true, v1, hl.lb, hl.ub, k * RS + 8 + a, Z, zz);
     }
     // C'(lamL - lamU): the rows of this stage live in the 8 lanes of this segment
     const CtDef& ct = term ? ctT : ctP;
     const double d1 = __shfl_sync(seg, dl, ct.i1, GROUP), d2 = __shfl_sync(seg, dl, ct.i2, GROUP);
     const double dj = __shfl_sync(seg, dl, a & 1, GROUP), dj2 = __shfl_sync(seg, dl, 2 + (a & 1), GROUP);
-    const double cdl = ct.c1 * d1 + ct.c2 * d2;
+    double cdl = ct.c1 * d1 + ct.c2 * d2, cdu = dj + dj2;
+    if (NL) {
+      const double h1 = __shfl_sync(seg, dl1, hl.r1, GROUP), h2 = __shfl_sync(seg, dl1, hl.r2, GROUP);
+      const double hj = __shfl_sync(seg, dl1, 2 + (a & 1), GROUP);
+      const double* h = gHC + k * 16;
+      cdl += h[hl.so1] * h1 + ((a < 3) ? h[4 + a] : hl.hc2r) * h2;   // h[15] = 0 for the state no row touches
+      cdu += ((a & 1) ? itD : itT) * hj;
+    }
     double rgx;
     if (!term) {
       const double u0 = pU[k * 2], u1 = pU[k * 2 + 1];
@@ -855,7 +1316,7 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
       }
       const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
       rgx = hx * xa_ + hxu0 * u0 + hxu1 * u1 + gx + atp - (have_mult ? pPI[k * 8 + a] : 0.0) - cdl;
-      const double rgu = (j == 0 ? hu0 * u0 - c10 * pX[k * 8 + 6] : hu1 * u1 - c11 * pX[k * 8 + 7]) + btp - (dj + dj2);
+      const double rgu = (j == 0 ? hu0 * u0 - c10 * pX[k * 8 + 6] : hu1 * u1 - c11 * pX[k * 8 + 7]) + btp - cdu;
       if (a < 2) rs = nmax(rs, fabs(rgu));
     } else {
       rgx = hxN * xa_ + ((a == 0) ? gsN : 0.0) - (have_mult ? pPI[k * 8 + a] : 0.0) - cdl;
@@ -877,7 +1338,8 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
 
 void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double nlp_tol, int have_mult,
                          int32_t* status, cudaStream_t stream) {
-  nlp_residual_kernel<<<cf.B, 32, 0, stream>>>(cf, w, x0, nlp_tol, have_mult, status);
+  if (cf.nl) nlp_residual_kernel<true><<<cf.B, 32, 0, stream>>>(cf, w, x0, nlp_tol, have_mult, status);
+  else nlp_residual_kernel<false><<<cf.B, 32, 0, stream>>>(cf, w, x0, nlp_tol, have_mult, status);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -889,10 +1351,12 @@ void launch_nlp_residual(const KCfg& cf, const Work& w, const double* x0, double
 // ---------------------------------------------------------------------------------------
 constexpr double LS_ALPHA_MIN = 0.05, LS_REDUCTION = 0.7;
 
-__device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const int a, const int q, const double s0,
-                                             const double x0a, const double* __restrict__ pX,
-                                             const double* __restrict__ pU, const double* __restrict__ phi,
-                                             const double* __restrict__ pW) {
+// this lane's share of the OCP cost at (x, u): z'(H z / 2 + g) per stage, plus (NL) the penalties of the soft rows
+// with their slacks eliminated (the h rows through their current linearisation Work::HC: exact at its point)
+template <bool NL>
+__device__ __forceinline__ double cost_lane(const KCfg& cf, const int N, const int a, const int q, const double s0,
+                                            const double* __restrict__ pX, const double* __restrict__ pU,
+                                            const double* __restrict__ gHC, const HLane& hl) {
   const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
   const double hxN = cf.ct * cf.We[a];
   const double hu = cf.cs * (a == 0 ? cf.W[8] + cf.W[10] : cf.W[9] + cf.W[11]);
@@ -903,7 +1367,6 @@ __device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const 
   for (int k = q; k <= N; k += 4) {
     const bool term = (k == N);
     const double xa_ = pX[k * 8 + a];
-    // cost z'(H z / 2 + g) of this stage, the part that belongs to state a (and control a for a < 2)
     if (!term) {
       const double gx = (a == 0) ? gs_scale * (s0 + cf.s_target * k / N) : 0.0;
       m += xa_ * (0.5 * hx * xa_ + gx);
@@ -912,13 +1375,42 @@ __device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const 
     } else {
       m += xa_ * (0.5 * hxN * xa_ + ((a == 0) ? gsN : 0.0));
     }
+    if (NL) {
+      const double Z = (term ? cf.ct : cf.cs) * cf.slack_Z, zz = (term ? cf.ct : cf.cs) * cf.slack_z;
+      if (term ? (a == 2 || a == 3) : (a >= 6 && k > 0)) {
+        const RowDef& R = term ? Rt : Rp;
+        const double v = row_value(R, term, 0.0, pX[k * 8 + R.ix]);
+        m += soft_penalty(zz, Z, fmax(0.0, R.lb - v) + fmax(0.0, v - R.ub));
+      }
+      if (term ? (a < 2) : (a < 5)) {
+        const double v1 = hl.value(gHC + k * 16, pX + k * 8, term ? 0.0 : pU[k * 2], term ? 0.0 : pU[k * 2 + 1], a);
+        m += soft_penalty(zz, Z, fmax(0.0, hl.lb - v1) + fmax(0.0, v1 - hl.ub));
+      }
+    }
+  }
+  return m;
+}
+
+// L1 merit: cost + weighted equality defects + weighted violations of the hard inequality rows (the exact penalty of
+// a soft row is part of the cost)
+template <bool NL>
+__device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const int a, const int q, const double s0,
+                                             const double x0a, const double* __restrict__ pX,
+                                             const double* __restrict__ pU, const double* __restrict__ phi,
+                                             const double* __restrict__ pW, const double* __restrict__ gHC, const HLane& hl) {
+  const RowDef Rp = row_path(cf, a), Rt = row_term(cf, a);
+  double m = cost_lane<NL>(cf, N, a, q, s0, pX, pU, gHC, hl);
+  for (int k = q; k <= N; k += 4) {
+    const bool term = (k == N);
+    const double xa_ = pX[k * 8 + a];
     // equality defects: x0 embedding at k = 0, dynamics of interval k - 1 otherwise
     const double defect = (k == 0) ? xa_ - x0a : phi[(k - 1) * 8 + a] - xa_;
     m += pW[k * 24 + a] * fabs(defect);
     // inequality row a of this stage
     const RowDef& R = term ? Rt : Rp;
     const bool act = term ? (a < 4) : (a < 4 || k > 0);
-    if (act) {
+    const bool soft = NL && (term ? (a == 2 || a == 3) : (a >= 6));
+    if (act && !soft) {
       const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
       m += pW[k * 24 + 8 + a] * fmax(0.0, R.lb - v) + pW[k * 24 + 16 + a] * fmax(0.0, v - R.ub);
     }
@@ -926,7 +1418,42 @@ __device__ __forceinline__ double merit_lane(const KCfg& cf, const int N, const 
   return m;
 }
 
+// End of a solve: cost of the OCP at the returned iterate -> stats[7]; u0 = u_0 of the iterate (SQP mode: with a
+// shortened last step it is not the QP's control); an instance whose solve failed (status 1 / 3 / 4) gets the iterate
+// it had before the call back, as the reference leaves x_pred / u_pred untouched when solver.solve() fails
+// (new_python/controller.py:397-403).
+template <bool NL>
+__global__ void __launch_bounds__(32) solve_finish_kernel(const KCfg cf, const Work w, const double* __restrict__ x0,
+                                                          const double* __restrict__ snap_x, const double* __restrict__ snap_u,
+                                                          double* __restrict__ u0_out, const int closed_loop_mask) {
+  const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
+  if (closed_loop_mask && w.active && !w.active[b]) return;   // closed loop: retired instance
+  const int N = cf.N, N1 = N + 1;
+  double* pX = w.x + (size_t)b * N1 * 8;
+  double* pU = w.u + (size_t)b * N * 2;
+  double itT = 0.0, itD = 0.0;
+  if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
+  const HLane hl(cf, a, itT, itD);
+  const double c = wsum(cost_lane<NL>(cf, N, a, q, x0[(size_t)b * 8], pX, pU, NL ? w.HC + (size_t)b * N1 * 16 : nullptr, hl));
+  if (lane == 0) w.stats[(size_t)b * 8 + 7] = c;
+  if (u0_out && lane < 2) u0_out[(size_t)b * 2 + lane] = pU[lane];
+  const int st = w.status[b];
+  if (snap_x && st != IHM2B_SUCCESS && st != IHM2B_MAXITER) {
+    const double* sx = snap_x + (size_t)b * N1 * 8;
+    const double* su = snap_u + (size_t)b * N * 2;
+    for (int i = lane; i < N1 * 8; i += 32) pX[i] = sx[i];
+    for (int i = lane; i < N * 2; i += 32) pU[i] = su[i];
+  }
+}
+
+void launch_solve_finish(const KCfg& cf, const Work& w, const double* x0, const double* snap_x, const double* snap_u,
+                         double* u0, int closed_loop_mask, cudaStream_t stream) {
+  if (cf.nl) solve_finish_kernel<true><<<cf.B, 32, 0, stream>>>(cf, w, x0, snap_x, snap_u, u0, closed_loop_mask);
+  else solve_finish_kernel<false><<<cf.B, 32, 0, stream>>>(cf, w, x0, snap_x, snap_u, u0, closed_loop_mask);
+}
+
 // after the QP: weights, merit at the base iterate (w.phi still holds the base linearisation), the full step
+template <bool NL>
 __global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Work w, const LineSearch ls,
                                                         const double* __restrict__ x0, const int first) {
   const int lane = threadIdx.x, a = lane & 7, q = lane >> 3, b = blockIdx.x;
@@ -935,10 +1462,15 @@ __global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Wor
     return;
   }
   const int N = cf.N, N1 = N + 1;
+  constexpr int RS = NL ? 16 : 8;
   const double* pPI = w.xa + (size_t)b * N1 * 8;
-  const double* pLL = w.LT + (size_t)b * N1 * 32;
-  const double* pLU = pLL + N1 * 8;
+  const double* pLL = w.LT + (size_t)b * N1 * 4 * RS;
+  const double* pLU = pLL + N1 * RS;
   double* pW = ls.wgt + (size_t)b * N1 * 24;
+  const double* gHC = NL ? w.HC + (size_t)b * N1 * 16 : nullptr;
+  double itT = 0.0, itD = 0.0;
+  if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
+  const HLane hl(cf, a, itT, itD);
   for (int k = q; k <= N; k += 4) {
     const bool term = (k == N);
     const bool act = term ? (a < 4) : (a < 4 || k > 0);
@@ -952,9 +1484,11 @@ __global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Wor
       const double hx = cf.cs * (cf.W[a] + (a == 6 ? cf.W[10] : a == 7 ? cf.W[11] : 0.0));
       pe = hx * qX[a] + ((a == 0) ? -cf.cs * cf.W[0] * x0[(size_t)b * 8] : 0.0);
       if (a >= 6) pe -= cf.cs * cf.W[4 + a] * qU[a - 6] - (pLL[a - 4] - pLU[a - 4]);
+      if (NL)   // the h rows of stage 0 depend on x_0 too
+        pe -= gHC[hl.so1] * (pLL[8 + hl.r1] - pLU[8 + hl.r1]) + ((a < 3) ? gHC[4 + a] : hl.hc2r) * (pLL[8 + hl.r2] - pLU[8 + hl.r2]);
       for (int r = 0; r < 8; r++) pe = fma(gBA[r * 10 + 2 + a], pPI[8 + r], pe);
     }
-    const double m[3] = {fabs(pe), act ? fabs(pLL[k * 8 + a]) : 0.0, act ? fabs(pLU[k * 8 + a]) : 0.0};
+    const double m[3] = {fabs(pe), act ? fabs(pLL[k * RS + a]) : 0.0, act ? fabs(pLU[k * RS + a]) : 0.0};
 #pragma unroll
     for (int j = 0; j < 3; j++) {
       double* wp = pW + k * 24 + j * 8 + a;
@@ -964,8 +1498,8 @@ __global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Wor
   __syncwarp();
   const double* bx = ls.base_x + (size_t)b * N1 * 8;
   const double* bu = ls.base_u + (size_t)b * N * 2;
-  const double m0 = wsum(merit_lane(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], bx, bu,
-                                    w.phi + (size_t)b * N * 8, pW));
+  const double m0 = wsum(merit_lane<NL>(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], bx, bu,
+                                        w.phi + (size_t)b * N * 8, pW, gHC, hl));
   const double* pX = w.x + (size_t)b * N1 * 8;
   const double* pU = w.u + (size_t)b * N * 2;
   double* sx = ls.step_x + (size_t)b * N1 * 8;
@@ -976,6 +1510,7 @@ __global__ void __launch_bounds__(32) merit_base_kernel(const KCfg cf, const Wor
 }
 
 // after the linearisation at the trial iterate: accept, or shorten the step and write the next trial iterate
+template <bool NL>
 __global__ void __launch_bounds__(32) merit_trial_kernel(const KCfg cf, const Work w, const LineSearch ls,
                                                          const double* __restrict__ x0, int32_t* __restrict__ sqp_active,
                                                          int32_t* __restrict__ status_out) {
@@ -984,8 +1519,12 @@ __global__ void __launch_bounds__(32) merit_trial_kernel(const KCfg cf, const Wo
   const int N = cf.N, N1 = N + 1;
   double* pX = w.x + (size_t)b * N1 * 8;
   double* pU = w.u + (size_t)b * N * 2;
-  const double m1 = wsum(merit_lane(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], pX, pU,
-                                    w.phi + (size_t)b * N * 8, ls.wgt + (size_t)b * N1 * 24));
+  double itT = 0.0, itD = 0.0;
+  if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
+  const HLane hl(cf, a, itT, itD);
+  const double m1 = wsum(merit_lane<NL>(cf, N, a, q, x0[(size_t)b * 8], x0[(size_t)b * 8 + a], pX, pU,
+                                        w.phi + (size_t)b * N * 8, ls.wgt + (size_t)b * N1 * 24,
+                                        NL ? w.HC + (size_t)b * N1 * 16 : nullptr, hl));
   const double alpha = ls.alpha[b];
   __syncwarp();
   if (m1 < ls.m0[b] || alpha <= LS_ALPHA_MIN) {
@@ -1012,11 +1551,13 @@ __global__ void __launch_bounds__(32) merit_trial_kernel(const KCfg cf, const Wo
 
 void launch_merit_base(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int first,
                        cudaStream_t stream) {
-  merit_base_kernel<<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, first);
+  if (cf.nl) merit_base_kernel<true><<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, first);
+  else merit_base_kernel<false><<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, first);
 }
 void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, const double* x0, int32_t* sqp_active,
                         int32_t* status, cudaStream_t stream) {
-  merit_trial_kernel<<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, sqp_active, status);
+  if (cf.nl) merit_trial_kernel<true><<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, sqp_active, status);
+  else merit_trial_kernel<false><<<cf.B, 32, 0, stream>>>(cf, w, ls, x0, sqp_active, status);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1025,14 +1566,13 @@ void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, con
 // iteration count (13 .. 50 here), and a batch is only 2-3 waves of resident warps: with the long problems
 // first the last wave is not left waiting for a 50-iteration straggler.  One block.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* __restrict__ stats, int col, int32_t* __restrict__ order) {
+__global__ void __launch_bounds__(1024) build_order_kernel(int B, const int32_t* __restrict__ last_it, int32_t* __restrict__ order) {
   __shared__ int cnt[64], start[64];
   const int tid = threadIdx.x;
   if (tid < 64) cnt[tid] = 0;
   __syncthreads();
   for (int b = tid; b < B; b += blockDim.x) {
-    const double it = stats[(size_t)b * 8 + col];
-    const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
+    const int key = min(63, max(0, last_it[b]));
     atomicAdd(&cnt[key], 1);
   }
   __syncthreads();
@@ -1042,36 +1582,43 @@ __global__ void __launch_bounds__(1024) build_order_kernel(int B, const double* 
   }
   __syncthreads();
   for (int b = tid; b < B; b += blockDim.x) {
-    const double it = stats[(size_t)b * 8 + col];
-    const int key = (it == it) ? min(63, max(0, (int)it)) : 63;
+    const int key = min(63, max(0, last_it[b]));
     order[atomicAdd(&start[key], 1)] = b;
   }
 }
 
-void launch_build_order(int B, const double* stats, int col, int32_t* order, cudaStream_t stream) {
-  build_order_kernel<<<1, 1024, 0, stream>>>(B, stats, col, order);
+void launch_build_order(int B, const int32_t* last_it, int32_t* order, cudaStream_t stream) {
+  build_order_kernel<<<1, 1024, 0, stream>>>(B, last_it, order);
 }
 
-int qp_smem_bytes(int N) { return ((N + 1) * PER_STAGE + S_TOT) * (int)sizeof(double); }
+int qp_smem_bytes(int N, int nl) { return ((N + 1) * (nl ? PER_STAGE_NL : PER_STAGE) + S_TOT) * (int)sizeof(double); }
+
+namespace {
+// the dynamic shared-memory limit is a per-device attribute of each kernel instance: remembered per (instance, device)
+template <class K>
+int launch_qp_instance(K kernel, int slot, const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
+                       cudaStream_t stream) {
+  static int configured[4][64] = {};
+  const int bytes = qp_smem_bytes(cf.N, cf.nl);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+  if (dev < 0 || dev >= 64 || configured[slot][dev] < bytes) {
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
+    if (dev >= 0 && dev < 64) configured[slot][dev] = bytes;
+  }
+  kernel<<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
+  return 0;
+}
+}  // namespace
 
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream) {
-  const int bytes = qp_smem_bytes(cf.N);
-  static int configured40 = 0, configured = 0;
-  if (cf.N == 40) {
-    if (!configured40) {
-      if (cudaFuncSetAttribute(qp_rti_kernel<40>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
-      configured40 = 1;
-    }
-    qp_rti_kernel<40><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
-    return 0;
+  if (cf.nl) {
+    if (cf.N == 40) return launch_qp_instance(qp_rti_kernel<40, true>, 2, cf, w, x0, u0, status, stream);
+    return launch_qp_instance(qp_rti_kernel<0, true>, 3, cf, w, x0, u0, status, stream);
   }
-  if (configured < bytes) {
-    if (cudaFuncSetAttribute(qp_rti_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
-    configured = bytes;
-  }
-  qp_rti_kernel<0><<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
-  return 0;
+  if (cf.N == 40) return launch_qp_instance(qp_rti_kernel<40, false>, 0, cf, w, x0, u0, status, stream);
+  return launch_qp_instance(qp_rti_kernel<0, false>, 1, cf, w, x0, u0, status, stream);
 }
 
 }  // namespace ihm2b

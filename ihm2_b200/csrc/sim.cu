@@ -269,11 +269,16 @@ void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, con
 // closed-loop bookkeeping after solve + plant step (python/main.py:503-517): an instance stops at
 // its first solver failure (status not in {0, 2}) or NaN in the plant (state kept), and is done
 // when s > lap_length + 1.
-__global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restrict__ track, const double* __restrict__ lap,
+// Lap time as python/main.py:561-570 computes it from the state log: dt x (second - first index at which
+// mod(s, lap_length) jumps by more than 1 between consecutive states); NaN until two jumps have been seen.
+// cost_sum: OCP cost at the solution (stats[7]) summed over the control steps taken.
+__global__ void closed_loop_post_kernel(int B, int step, double dt, const int32_t* __restrict__ track, const double* __restrict__ lap,
                                         const int32_t* __restrict__ status, const double* __restrict__ u0,
-                                        const double* __restrict__ xn, double* __restrict__ xs, double* __restrict__ xlog,
+                                        const double* __restrict__ xn, const double* __restrict__ stats,
+                                        double* __restrict__ xs, double* __restrict__ xlog,
                                         double* __restrict__ ulog, int32_t* __restrict__ done, int32_t* __restrict__ fail,
-                                        int32_t* __restrict__ active_mask) {
+                                        int32_t* __restrict__ active_mask, int32_t* __restrict__ lap_state,
+                                        double* __restrict__ lap_time, double* __restrict__ cost_sum) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   bool active = done[b] < 0 && fail[b] < 0;
@@ -281,13 +286,21 @@ __global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restri
   if (active) {
     const int st = status[b];
     if (st != IHM2B_SUCCESS && st != IHM2B_MAXITER) { fail[b] = step; active = false; }
-    else { uu0 = u0[b * 2]; uu1 = u0[b * 2 + 1]; }
+    else { uu0 = u0[b * 2]; uu1 = u0[b * 2 + 1]; if (cost_sum) cost_sum[b] += stats[(size_t)b * 8 + 7]; }
   }
   if (active) {
     bool isnan_ = false;
     for (int r = 0; r < 8; r++) isnan_ |= !(xn[b * 8 + r] == xn[b * 8 + r]);
     if (isnan_) fail[b] = step;
     else {
+      const double L = lap[track[b]], sa = xs[b * 8], sb = xn[b * 8];
+      const double m0 = sa - L * floor(sa / L), m1 = sb - L * floor(sb / L);   // np.mod
+      if (fabs(m1 - m0) > 1.0) {
+        const int jumps = lap_state[b * 2];
+        if (jumps == 0) lap_state[b * 2 + 1] = step;
+        else if (jumps == 1 && lap_time) lap_time[b] = dt * (step - lap_state[b * 2 + 1]);
+        lap_state[b * 2] = jumps + 1;
+      }
       for (int r = 0; r < 8; r++) xs[b * 8 + r] = xn[b * 8 + r];
       if (xn[b * 8] > lap[track[b]] + 1.0) done[b] = step;
     }
@@ -297,10 +310,12 @@ __global__ void closed_loop_post_kernel(int B, int step, const int32_t* __restri
   if (xlog) for (int r = 0; r < 8; r++) xlog[((size_t)(step + 1) * B + b) * 8 + r] = xs[b * 8 + r];
 }
 
-void launch_closed_loop_post(int B, int step, const int32_t* track, const double* lap, const int32_t* status,
-                             const double* u0, const double* xn, double* xs, double* xlog, double* ulog, int32_t* done,
-                             int32_t* fail, int32_t* active_mask, cudaStream_t stream) {
-  closed_loop_post_kernel<<<(B + 127) / 128, 128, 0, stream>>>(B, step, track, lap, status, u0, xn, xs, xlog, ulog, done, fail, active_mask);
+void launch_closed_loop_post(int B, int step, double dt, const int32_t* track, const double* lap, const int32_t* status,
+                             const double* u0, const double* xn, const double* stats, double* xs, double* xlog,
+                             double* ulog, int32_t* done, int32_t* fail, int32_t* active_mask, int32_t* lap_state,
+                             double* lap_time, double* cost_sum, cudaStream_t stream) {
+  closed_loop_post_kernel<<<(B + 127) / 128, 128, 0, stream>>>(B, step, dt, track, lap, status, u0, xn, stats, xs, xlog, ulog,
+                                                               done, fail, active_mask, lap_state, lap_time, cost_sum);
 }
 
 }  // namespace ihm2b

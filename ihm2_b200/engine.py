@@ -79,7 +79,9 @@ class Engine:
     """One ihm2b handle: B independent NMPC problems on the current CUDA device."""
 
     def __init__(self, cfg: Config, s_ref, kappa_ref, track_index=None, params=None,
-                 lap_length=None, device=None):
+                 lap_length=None, device=None, widths=None):
+        """widths = (right_width, left_width) tables shaped like s_ref: needed with cfg.nonlinear_constraints (the
+        track rows of h, old/generate_acaods_interface.py:312-318)."""
         if not torch.cuda.is_available():
             raise Ihm2bError("ihm2_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = load_library()
@@ -95,7 +97,12 @@ class Engine:
         kappa_ref = np.ascontiguousarray(np.atleast_2d(kappa_ref), dtype=np.float64)
         if s_ref.shape != (cfg.n_tracks, cfg.n_grid) or kappa_ref.shape != s_ref.shape:
             raise ValueError(f"track tables must be [{cfg.n_tracks}, {cfg.n_grid}]")
-        self._check(self.lib.ihm2b_set_tracks(self._h, _hptr(s_ref), _hptr(kappa_ref), None, None))
+        rw = lw = None
+        if widths is not None:
+            rw, lw = (np.ascontiguousarray(np.atleast_2d(t), dtype=np.float64) for t in widths)
+            if rw.shape != s_ref.shape or lw.shape != s_ref.shape:
+                raise ValueError(f"width tables must be [{cfg.n_tracks}, {cfg.n_grid}]")
+        self._check(self.lib.ihm2b_set_tracks(self._h, _hptr(s_ref), _hptr(kappa_ref), _hptr(rw), _hptr(lw)))
         ti = np.zeros(self.B, np.int32) if track_index is None else np.ascontiguousarray(track_index, dtype=np.int32)
         self._check(self.lib.ihm2b_set_track_index(self._h, _hptr(ti)))
         p = np.tile(_abi.default_params(), (self.B, 1)) if params is None else np.ascontiguousarray(params, dtype=np.float64)
@@ -191,9 +198,11 @@ class Engine:
         ulog = self._new(n_steps, self.B, NU) if log else None
         done = self._new(self.B, dtype=torch.int32)
         fail = self._new(self.B, dtype=torch.int32)
+        lap_time, cost_sum = self._new(self.B), self._new(self.B)
         self._check(self.lib.ihm2b_closed_loop_dev(self._h, C.c_int32(n_steps), _dptr(x), _hptr(self.lap_length),
-                                                   _dptr(xlog), _dptr(ulog), _dptr(done), _dptr(fail), _stream()))
-        return dict(x=x, xlog=xlog, ulog=ulog, done=done, fail=fail)
+                                                   _dptr(xlog), _dptr(ulog), _dptr(done), _dptr(fail), _dptr(lap_time),
+                                                   _dptr(cost_sum), _stream()))
+        return dict(x=x, xlog=xlog, ulog=ulog, done=done, fail=fail, lap_time=lap_time, cost_sum=cost_sum)
 
     # ---- measurement aids ----
     def profile(self, on: bool = True):

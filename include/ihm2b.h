@@ -147,7 +147,11 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream);
  * of the last QP, QP, full step }; instances drop out as they converge (status 0) or their QP
  * fails (1 / 4), the rest end with status 2 (ACADOS_MAXITER, tolerated by the reference,
  * mpc_control_node.cpp:190-197).  stats: [qp iterations (sum), sqp iterations, mu, res_stat,
- * res_eq, res_ineq, res_comp, IPM iterations of the last QP].
+ * res_eq, res_ineq, res_comp, cost of the OCP at the returned iterate].
+ * nonlinear_constraints = 1 adds the soft rows h(x, u) of the gen-1 OCP (right / left track boundary with the car
+ * footprint, T_dot, delta_dot, a_lat: old/generate_acaods_interface.py:312-325, bounds / slack sets :351-449), makes the
+ * state bounds on T and delta soft (idxsbx = [2, 3]) and eliminates the slacks inside the interior point; it needs the
+ * width tables of ihm2b_set_tracks.
  * globalization = IHM2B_MERIT_BACKTRACKING (controller.py:308): each step is scaled by alpha = 1, 0.7, 0.49, ...
  * (not below 0.05) until the L1 merit function (cost + multiplier-weighted equality defects and inequality
  * violations) of the trial iterate is below that of the current one; multipliers take the full step; stats[2]
@@ -181,10 +185,15 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev
  * x_dev [B][8] in/out (current state); lap_length_host [n_tracks].
  * Optional logs (may be NULL): xlog_dev [n_steps+1][B][8], ulog_dev [n_steps][B][2].
  * done_dev [B]: step index at which s > lap_length + 1 (or -1), fail_dev [B]: step index of
- * the first failure (solver status not in {0,2} or NaN in the plant), or -1. */
+ * the first failure (solver status not in {0,2} or NaN in the plant), or -1.
+ * Optional per-instance results (may be NULL): lap_time_dev [B], the lap time as python/main.py:561-570 computes it
+ * from the state log -- dt x (second - first index at which mod(s, lap_length) jumps by more than 1 between
+ * consecutive states), NaN while fewer than two jumps have been seen; cost_sum_dev [B], the OCP cost at the solution
+ * summed over the control steps taken ("mean cost"). */
 int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x_dev,
                           const double* lap_length_host, double* xlog_dev, double* ulog_dev,
-                          int32_t* done_dev, int32_t* fail_dev, void* stream);
+                          int32_t* done_dev, int32_t* fail_dev, double* lap_time_dev, double* cost_sum_dev,
+                          void* stream);
 
 /* ---- DPC rollout ---------------------------------------------------------
  * the differentiable-predictive-control loss of dpc/main.py: kin4 model (:56-84), one RK4 step of dt per

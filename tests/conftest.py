@@ -33,3 +33,10 @@ def fsds():
     from ihm2_b200.track import load_packaged_track
 
     return load_packaged_track("fsds_default")
+
+
+@pytest.fixture(scope="session")
+def torch_cuda(built):
+    import torch
+    assert torch.cuda.is_available(), "these tests need the B200"
+    return torch
