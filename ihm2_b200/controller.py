@@ -157,6 +157,13 @@ class IHM2Controller(Controller):
     a numpy input this convention is kept).  `x_pred [B, Nf+1, 8]` / `u_pred [B, Nf, 2]` stay
     readable attributes.  `integrator`, `params`, `track_index` are additions (defaults reproduce
     the reference: IRK 4 stages, python/constants.py, one track).
+
+    `nonlinear_constraints=True` adds the soft rows h(x, u) of the gen-1 OCP (track boundaries with the car footprint
+    from `right_width` / `left_width` tables shaped like `s_ref`, T_dot, delta_dot, a_lat <= `a_lat_max`:
+    old/generate_acaods_interface.py:312-325, 351-449) and makes the state bounds on T and delta soft.
+    `hpipm_mode` picks an interior-point preset (controller.py:304 selects "SPEED_ABS"; None: this library's own);
+    `qp_tolerate_maxiter=True` is acados' rule of carrying on with a QP that stopped at its iteration limit
+    (mpc_control_node.cpp:190-197).
     """
     id = "ihm2"
     nx = 8
@@ -171,7 +178,9 @@ class IHM2Controller(Controller):
                  q_delta_f: float = 100.0, q_T_dot: float = 0.0, q_delta_dot: float = 500.0, *, batch: int = 1,
                  car_params: CarParams | None = None, params=None, track_index=None, lap_length=None,
                  integrator: str = "IRK", sim_model: int = _abi.SIM_KIN6_DYN6, nlp_solver_type: str = "SQP_RTI",
-                 nlp_solver_max_iter: int = 2, globalization: str = "MERIT_BACKTRACKING") -> None:
+                 nlp_solver_max_iter: int = 2, globalization: str = "MERIT_BACKTRACKING",
+                 nonlinear_constraints: bool = False, right_width=None, left_width=None, hpipm_mode: str | None = None,
+                 qp_tolerate_maxiter: bool = False) -> None:
         super().__init__(car_params)
         self.Nf, self.dt, self.s_target = Nf, dt, s_target
         self.config = Controller.Config(horizon_size=Nf, sampling_time=dt)
@@ -191,10 +200,18 @@ class IHM2Controller(Controller):
                                nlp_solver=_abi.SQP if nlp_solver_type.upper() == "SQP" else _abi.SQP_RTI,
                                nlp_max_iter=nlp_solver_max_iter,
                                globalization=_abi.MERIT_BACKTRACKING if globalization.upper() == "MERIT_BACKTRACKING"
-                               else _abi.FIXED_STEP)
+                               else _abi.FIXED_STEP,
+                               nonlinear_constraints=nonlinear_constraints, hpipm_mode=hpipm_mode,
+                               qp_tolerate_maxiter=qp_tolerate_maxiter)
+        widths = None
+        if nonlinear_constraints:
+            if right_width is None or left_width is None:
+                raise ValueError("nonlinear_constraints needs the right_width / left_width tables of the track")
+            widths = (np.atleast_2d(np.asarray(right_width, dtype=np.float64)), np.atleast_2d(np.asarray(left_width, dtype=np.float64)))
         if params is None:
             params = np.tile(self.car_params.to_vector(), (batch, 1))
-        self.solver = Engine(cfg, s_ref, kappa_ref, track_index=track_index, params=params, lap_length=lap_length)
+        self.solver = Engine(cfg, s_ref, kappa_ref, track_index=track_index, params=params, lap_length=lap_length,
+                             widths=widths)
         self.batch = batch
 
     @property

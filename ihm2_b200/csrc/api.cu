@@ -174,9 +174,11 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   if (cfg->nonlinear_constraints && !(cfg->slack_Z > 0.0 && cfg->slack_z >= 0.0 && cfg->a_lat_max > 0.0 &&
                                       cfg->T_dot_max > 0.0 && cfg->delta_dot_max > 0.0))
     return fail(IHM2B_EINVAL, "nonlinear_constraints: slack_Z, a_lat_max, T_dot_max and delta_dot_max must be positive");
-  int ndev = 0;
+  int ndev = 0, dev = 0;
   CU(cudaGetDeviceCount(&ndev));
   if (ndev == 0) return fail(IHM2B_ECUDA, "no CUDA device");
+  CU(cudaGetDevice(&dev));
+  *out = nullptr;
   ihm2b_handle* h = new (std::nothrow) ihm2b_handle();
   if (!h) return fail(IHM2B_ENOMEM, "host allocation failed");
   h->cfg = *cfg;
@@ -185,7 +187,8 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   h->have_tracks = h->have_widths = h->have_params = false;
   h->profile = false; h->prof_ms[0] = h->prof_ms[1] = 0.0; h->prof_n = 0;
   for (int i = 0; i < 3; i++) h->ev[i] = nullptr;
-  CU(cudaGetDevice(&h->device));
+  h->device = dev;
+  h->x0_pin = h->u0_pin = nullptr; h->status_pin = nullptr;
   const size_t B = cfg->batch, N = cfg->N;
   Work& w = h->w;
   memset(&w, 0, sizeof w);
@@ -251,8 +254,10 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   if (rc != IHM2B_OK) { ihm2b_destroy(h); return rc; }
   w.s_ref = h->s_ref; w.kappa_ref = h->kappa_ref; w.wr = h->wr; w.wl = h->wl; w.params = h->params; w.track = h->track;
   w.actw = h->actw; w.actw_sim = h->actw_sim;
+  rc = ihm2b_reset_iterate(h, nullptr);
+  if (rc != IHM2B_OK) { ihm2b_destroy(h); return rc; }
   *out = h;
-  return ihm2b_reset_iterate(h, nullptr);
+  return IHM2B_OK;
 }
 
 int ihm2b_destroy(ihm2b_handle* h) {
@@ -356,6 +361,16 @@ int ihm2b_get_iterate_dev(ihm2b_handle* h, double* x, double* u, void* stream) {
   const size_t B = h->cfg.batch, N = h->cfg.N;
   if (x) CU(cudaMemcpyAsync(x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
   if (u) CU(cudaMemcpyAsync(u, h->w.u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  return IHM2B_OK;
+}
+
+int ihm2b_get_iterate_host(ihm2b_handle* h, double* x, double* u) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  const size_t B = h->cfg.batch, N = h->cfg.N;
+  cudaStream_t s = nullptr;
+  if (x) CU(cudaMemcpyAsync(x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (u) CU(cudaMemcpyAsync(u, h->w.u, B * N * 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
   return IHM2B_OK;
 }
 
@@ -539,6 +554,37 @@ int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats, void* stream) {
   return IHM2B_OK;
 }
 
+int ihm2b_get_multipliers_dev(ihm2b_handle* h, double* pi, double* lamL, double* lamU, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t B = h->cfg.batch, N1 = h->cfg.N + 1, RS = h->k.nl ? 16 : 8;
+  if (pi) CU(cudaMemcpyAsync(pi, h->w.xa, B * N1 * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  const size_t row = N1 * RS * sizeof(double);   // one problem's block of one quantity; LT holds 4 of them per problem
+  if (lamL) CU(cudaMemcpy2DAsync(lamL, row, h->w.LT, 4 * row, row, B, cudaMemcpyDeviceToDevice, s));
+  if (lamU) CU(cudaMemcpy2DAsync(lamU, row, h->w.LT + N1 * RS, 4 * row, row, B, cudaMemcpyDeviceToDevice, s));
+  return IHM2B_OK;
+}
+
+int ihm2b_get_slacks_dev(ihm2b_handle* h, double* sL, double* sU, double* lamSL, double* lamSU, void* stream) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  if (!h->k.nl) return fail(IHM2B_EINVAL, "no soft rows without nonlinear_constraints");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t B = h->cfg.batch, N1 = h->cfg.N + 1;
+  const size_t row = N1 * 16 * sizeof(double);
+  double* out[4] = {sL, sU, lamSL, lamSU};
+  for (int i = 0; i < 4; i++)
+    if (out[i]) CU(cudaMemcpy2DAsync(out[i], row, h->w.SS + i * N1 * 16, 8 * row, row, B, cudaMemcpyDeviceToDevice, s));
+  return IHM2B_OK;
+}
+
+int ihm2b_get_h_rows_dev(ihm2b_handle* h, double* hc, void* stream) {
+  if (!h || !hc) return fail(IHM2B_EINVAL, "null argument");
+  if (!h->k.nl) return fail(IHM2B_EINVAL, "no h rows without nonlinear_constraints");
+  CU(cudaMemcpyAsync(hc, h->w.HC, (size_t)h->cfg.batch * (h->cfg.N + 1) * 16 * sizeof(double), cudaMemcpyDeviceToDevice,
+                     static_cast<cudaStream_t>(stream)));
+  return IHM2B_OK;
+}
+
 int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double* xn, int32_t* model, void* stream) {
   int rc = check_ready(h);
   if (rc) return rc;
@@ -586,13 +632,13 @@ int ihm2b_closed_loop_dev(ihm2b_handle* h, int32_t n_steps, double* x, const dou
   return IHM2B_OK;
 }
 
-/* development aid (not part of the public header): per-iteration IPM trace of problem 0 */
+/* per-iteration IPM trace of problem 0 */
 int ihm2b_debug_trace(ihm2b_handle* h, double* host64x8) {
   if (!h || !host64x8) return IHM2B_EINVAL;
   return cudaMemcpy(host64x8, h->w.dbg, 64 * 8 * sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess ? IHM2B_OK : IHM2B_ECUDA;
 }
 
-/* development / measurement aids (not part of the public header) ----------------------
+/* measurement aids ----------------------------------------------------------------------
  * per-kernel device times of ihm2b_solve_dev: when enabled every solve synchronises on its
  * own events; ihm2b_profile_read returns the mean linearise / QP kernel time in ms. */
 int ihm2b_profile_enable(ihm2b_handle* h, int on) {

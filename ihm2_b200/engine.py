@@ -21,10 +21,12 @@ _lib = None
 # every symbol include/ihm2b.h declares
 EXPORTS = (
     "ihm2b_create", "ihm2b_destroy", "ihm2b_last_error", "ihm2b_version", "ihm2b_set_tracks",
-    "ihm2b_set_track_index", "ihm2b_set_params", "ihm2b_set_iterate_dev", "ihm2b_get_iterate_dev",
+    "ihm2b_set_track_index", "ihm2b_set_params", "ihm2b_set_iterate_dev", "ihm2b_get_iterate_dev", "ihm2b_get_iterate_host",
     "ihm2b_reset_iterate", "ihm2b_shift_iterate", "ihm2b_solve_dev", "ihm2b_compute_control_host",
     "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_closed_loop_dev",
+    "ihm2b_get_multipliers_dev", "ihm2b_get_slacks_dev", "ihm2b_get_h_rows_dev",
     "ihm2b_dpc_rollout_grad_dev", "ihm2b_dpc_rollout_grad_f32_dev", "ihm2b_project_dev", "ihm2b_launch_count",
+    "ihm2b_profile_enable", "ihm2b_profile_read", "ihm2b_debug_trace", "ihm2b_measure_fp64_tflops",
 )
 
 
@@ -145,6 +147,14 @@ class Engine:
         self._check(self.lib.ihm2b_get_iterate_dev(self._h, _dptr(x), _dptr(u), _stream()))
         return x, u
 
+    def get_iterate_host(self, x: np.ndarray | None = None, u: np.ndarray | None = None):
+        """x_pred / u_pred into host arrays (pass views of pinned tensors for the full PCIe rate); synchronous."""
+        x = np.empty((self.B, self.N + 1, NX)) if x is None else x
+        u = np.empty((self.B, self.N, NU)) if u is None else u
+        assert x.flags.c_contiguous and u.flags.c_contiguous and x.dtype == np.float64 and u.dtype == np.float64
+        self._check(self.lib.ihm2b_get_iterate_host(self._h, _hptr(x), _hptr(u)))
+        return x, u
+
     def reset_iterate(self):
         self._check(self.lib.ihm2b_reset_iterate(self._h, _stream()))
 
@@ -181,6 +191,25 @@ class Engine:
         st = self._new(self.B, 8)
         self._check(self.lib.ihm2b_get_stats_dev(self._h, _dptr(st), _stream()))
         return st
+
+    def multipliers(self):
+        """(pi [B,N+1,8], lamL [B,N+1,RS], lamU [B,N+1,RS]) of the last QP; RS = 8 row slots per stage, 16 with h rows."""
+        RS = 16 if self.cfg.nonlinear_constraints else 8
+        pi, lamL, lamU = self._new(self.B, self.N + 1, NX), self._new(self.B, self.N + 1, RS), self._new(self.B, self.N + 1, RS)
+        self._check(self.lib.ihm2b_get_multipliers_dev(self._h, _dptr(pi), _dptr(lamL), _dptr(lamU), _stream()))
+        return pi, lamL, lamU
+
+    def slacks(self):
+        """(sL, sU, lamSL, lamSU) [B,N+1,16] of the soft rows (nonlinear_constraints only)."""
+        out = [self._new(self.B, self.N + 1, 16) for _ in range(4)]
+        self._check(self.lib.ihm2b_get_slacks_dev(self._h, *[_dptr(t) for t in out], _stream()))
+        return out
+
+    def h_rows(self):
+        """Linearised rows of h at the last linearisation point, [B,N+1,16] (layout of Work::HC)."""
+        hc = self._new(self.B, self.N + 1, 16)
+        self._check(self.lib.ihm2b_get_h_rows_dev(self._h, _dptr(hc), _stream()))
+        return hc
 
     # ---- plant / closed loop ----
     def sim_step(self, x: torch.Tensor, u: torch.Tensor):

@@ -21,7 +21,8 @@ def nominal_iterate(track: str = "skidpad", n_steps: int = 20, **cfg_kwargs):
     moving.  Returns (x_nom [8], x_pred [N+1,8], u_pred [N,2]) as numpy arrays."""
     mp = load_packaged_track(track)
     cfg = _abi.make_config(batch=1, n_grid=len(mp.s_ref), **cfg_kwargs)
-    eng = Engine(cfg, mp.s_ref, mp.kappa_ref)
+    widths = (mp.right_widths, mp.left_widths) if cfg.nonlinear_constraints else None
+    eng = Engine(cfg, mp.s_ref, mp.kappa_ref, widths=widths)
     x = torch.zeros(1, NX, dtype=torch.float64, device=eng.device)
     x[0, 0] = -6.0
     for _ in range(n_steps):

@@ -163,6 +163,11 @@ int ihm2b_solve_dev(ihm2b_handle* h, const double* x0_dev, double* u0_dev, int32
 int ihm2b_compute_control_host(ihm2b_handle* h, const double* x0_host, double* u0_host,
                                int32_t* status_host, int do_shift);
 
+/* x_pred / u_pred to HOST buffers (the reference reads every stage back after each solve,
+ * new_python/controller.py:402-403: solver.get(i, "x" | "u")): x_host [B][N+1][8], u_host [B][N][2], either may be
+ * NULL; synchronous.  Page-locked destination buffers copy at the full PCIe rate. */
+int ihm2b_get_iterate_host(ihm2b_handle* h, double* x_host, double* u_host);
+
 /* ---- pieces of the path, exposed for parity tests ------------------------------------
  * integrator + forward sensitivities at the current iterate (acados sim_erk / sim_irk inside
  * the SQP preparation phase).  Outputs batch-major: A [B][N][8][8], Bm [B][N][8][2],
@@ -172,6 +177,21 @@ int ihm2b_linearize_dev(ihm2b_handle* h, double* A_dev, double* B_dev, double* p
 /* per-instance statistics [B][8]: qp iterations, sqp iterations, final mu, res_stat, res_eq,
  * res_ineq, res_comp, cost */
 int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats_dev, void* stream);
+
+/* ---- multipliers of the last QP (KKT certificates) -------------------------------------
+ * replaces solver.get(i, "pi" | "lam") of AcadosOcpSolver.  RS = 8 inequality row slots per stage (16 with
+ * nonlinear_constraints: slots 8..12 are the rows of h); slot order of a path stage: (u_T, u_delta, u_T - T, u_delta - delta,
+ * n, v_x, T, delta), terminal stage: idxbx_e = (n, v_x, v_y, r); absent rows (slots 4..7 at stage 0, >= 4 at stage N,
+ * the padding) carry zeros.  pi_dev [B][N+1][8]: pi_k multiplies x_k = A x_{k-1} + B u_{k-1} + c (k >= 1; pi_0 is not
+ * formed, x_0 is eliminated).  lamL_dev / lamU_dev [B][N+1][RS]: multipliers of the lower / upper side of each row.
+ * Sign convention: stationarity reads H z + g + [B' pi_{k+1}; A' pi_{k+1} - pi_k] - C'(lamL - lamU) = 0. */
+int ihm2b_get_multipliers_dev(ihm2b_handle* h, double* pi_dev, double* lamL_dev, double* lamU_dev, void* stream);
+/* slacks of the soft rows and the multipliers of s >= 0, [B][N+1][16] each (nonlinear_constraints only; any pointer
+ * may be NULL) */
+int ihm2b_get_slacks_dev(ihm2b_handle* h, double* sL_dev, double* sU_dev, double* lamSL_dev, double* lamSU_dev,
+                         void* stream);
+/* the linearised rows of h at the last linearisation point, [B][N+1][16] (layout: csrc/common.cuh, Work::HC) */
+int ihm2b_get_h_rows_dev(ihm2b_handle* h, double* hc_dev, void* stream);
 
 /* ---- plant ---------------------------------------------------------------------------
  * replaces AcadosSimSolver.simulate(x, u) with the model switch of python/main.py:475-502.
@@ -227,8 +247,19 @@ int ihm2b_project_dev(int64_t batch, int32_t n_grid, const double* s_ref_dev, co
                       const double* pose_dev, const double* s_guess_dev, double s_tol, double* frenet_dev,
                       double* ref_dev, int32_t* flag_dev, void* stream);
 
-/* number of kernel launches issued by this handle since creation (bench bookkeeping) */
+/* ---- diagnostics / measurement aids ------------------------------------------------------
+ * number of kernel launches issued by this handle since creation (bench bookkeeping) */
 int64_t ihm2b_launch_count(const ihm2b_handle* h);
+/* per-kernel device times of ihm2b_solve_dev (RTI mode): when enabled every solve synchronises on its own events;
+ * ihm2b_profile_read returns the mean linearisation / QP kernel time in ms since the last enable (ms2[2]) */
+int ihm2b_profile_enable(ihm2b_handle* h, int on);
+int ihm2b_profile_read(ihm2b_handle* h, double* ms2_host);
+/* per-iteration interior-point trace of problem 0 of the last QP: host [64][8] =
+ * (res_g, res_b, res_d, res_m, mu, alpha, mu_target, -) per iteration */
+int ihm2b_debug_trace(ihm2b_handle* h, double* host64x8);
+/* FP64 throughput of the current device in TFLOP/s (the roofline denominator MEASURED_PEAKS.json does not carry):
+ * the larger of a DFMA chain (CUDA cores) and a DMMA chain (mma.m8n8k4.f64) */
+int ihm2b_measure_fp64_tflops(double* tflops_host);
 
 #ifdef __cplusplus
 }

@@ -214,3 +214,51 @@ def test_oracle_completes_a_lap_and_times_it(built, fsds):
     assert abs(res["lap_time"][0] - cfg.dt * (idx[1] - idx[0])) < 1e-12
     assert 30.0 < res["lap_time"][0] < 60.0
     assert np.abs(res["xlog"][: res["done"][0], 0, 1]).max() <= cfg.n_max + 0.05     # on the track all the way
+
+
+def _slots_from_qp_debug(q, nl):
+    """Oracle rows (static rows first, then h rows) -> the 8 / 16 row slots per stage of the C ABI, batch of one."""
+    RS = 16 if nl else 8
+    out = {k: np.zeros((1, N + 1, RS)) for k in ("lamL", "lamU", "sL", "sU", "lamSL", "lamSU")}
+    hc = np.zeros((1, N + 1, 16))
+    for k in range(N + 1):
+        nst = 4 if k in (0, N) else 8
+        for r in range(q["nrows"][k]):
+            slot = r if r < nst else 8 + (r - nst)
+            for f in out:
+                out[f][0, k, slot] = q[f][k, r]
+            if r >= nst:
+                i, Cr = r - nst, q["C"][k, r]
+                if i == 0: hc[0, k, 0:3] = Cr[2:5]; hc[0, k, 3] = q["e"][k, r]
+                if i == 1: hc[0, k, 4:7] = Cr[2:5]; hc[0, k, 7] = q["e"][k, r]
+                if i == 2: hc[0, k, 13] = q["e"][k, r]
+                if i == 3: hc[0, k, 14] = q["e"][k, r]
+                if i == 4: hc[0, k, 8:12] = Cr[[2 + 3, 2 + 4, 2 + 6, 2 + 7]]; hc[0, k, 12] = q["e"][k, r]
+    return out, hc
+
+
+@pytest.mark.parametrize("nl", [False, True])
+def test_vectorised_kkt_check_agrees_on_the_oracle_solution(built, fsds, nl):
+    """tests/kkt_check.py (the certificate the GPU tests apply to whole batches) on the oracle's own solution."""
+    from kkt_check import kkt_residuals
+    cfg = _abi.make_config(batch=1, n_grid=len(fsds.s_ref), nonlinear_constraints=nl)
+    o = Oracle(cfg, fsds.s_ref, fsds.kappa_ref, widths=_widths(fsds))
+    x0, xs, us = _nl_problem(fsds, 30, 0.3)
+    q = o.qp_debug(x0, xs, us)
+    assert q["status"] == 0
+    sl, hc = _slots_from_qp_debug(q, nl)
+    z = q["z"]
+    r = kkt_residuals(cfg, x0[None], q["A"][None], q["B"][None], q["c"][None], z[None, :, 2:], z[None, :N, :2], q["pi"][None],
+                      sl["lamL"], sl["lamU"], params=_abi.default_params()[None], hc=hc if nl else None,
+                      slacks=(sl["sL"], sl["sU"], sl["lamSL"], sl["lamSU"]) if nl else None)
+    print({k: float(v[0]) for k, v in r.items()})
+    assert r["stat"][0] < 1e-6 and r["dyn"][0] < 1e-9 and r["x0"][0] == 0 and r["prim"][0] < 1e-8
+    assert r["comp"][0] < 1e-6 and r["dual"][0] <= 0
+    if nl:
+        assert r["slack_stat"][0] < 1e-6 and r["slack_comp"][0] < 1e-6 and r["slack_sign"][0] <= 0
+    # and it is not vacuous: a perturbed solution fails it
+    zb = z.copy(); zb[5, 3] += 1e-3
+    rb = kkt_residuals(cfg, x0[None], q["A"][None], q["B"][None], q["c"][None], zb[None, :, 2:], zb[None, :N, :2], q["pi"][None],
+                       sl["lamL"], sl["lamU"], params=_abi.default_params()[None], hc=hc if nl else None,
+                       slacks=(sl["sL"], sl["sU"], sl["lamSL"], sl["lamSU"]) if nl else None)
+    assert rb["dyn"][0] > 1e-6
