@@ -14,7 +14,8 @@
 //
 // Mapping: a block owns NI = 32 shooting intervals and keeps their LU factors, stage slopes and
 // Jacobians in SHARED memory (372 doubles per interval, interval-interleaved so every access is
-// conflict-free).  Phase 1: one thread per interval runs the two Newton solves.  Phase 2: one
+// conflict-free).  Phase 1: four lanes per interval (one collocation stage each) run the two Newton solves in
+// registers, exchanging slopes and pivot rows by shuffles.  Phase 2: one
 // thread per (interval, 2-3 columns of d/d(x,u)) -- 128 threads, the column is warp-uniform -- runs
 // the block forward substitution of its column through the shared factors and writes its
 // column of [B A].  Phase 3: one thread per interval forms c and phi.  (A thread-per-interval
@@ -95,183 +96,211 @@ struct VPoint {
 }  // namespace
 
 
-// ---- phase 1: Newton solves of one interval; factors, slopes, Jacobians -> shared memory (sm already offset by the
-// interval's lane: entry e at sm[e * NI]).  Returns false on NaN.
-__device__ bool irk_newton(const double* __restrict__ x, double u0, double u1, const double* __restrict__ p,
-                           const TrackView& tr, double h, const double* __restrict__ A4, const double* __restrict__ b4,
-                           const double* __restrict__ wT, const double* __restrict__ wD, double* __restrict__ sm) {
-#define KS(i, a) sm[(OFF_K + (i) * 8 + (a)) * NI]
-  double* const Mv = sm + OFF_MV * NI;
-  double* const Mp = sm + OFF_MP * NI;
+// ---- phase 1, four lanes per interval (lane t of the group owns collocation stage t): the stage evaluations
+// (tanh / sincos / curvature lookup), the rows of the Newton matrices and the LU factorisations are spread over the
+// four lanes and exchanged by 4-lane shuffles; nothing touches shared memory until the converged factors, slopes and
+// Jacobians are written for phase 2.  All 32 lanes of the warp (8 intervals) run the same number of Newton iterations;
+// an interval that has converged stops updating and re-evaluates at the point its factors belong to, so its result
+// does not depend on its neighbours in the warp.
+constexpr unsigned FULLW = 0xffffffffu;
+__device__ __forceinline__ double g4(double v, int src) { return __shfl_sync(FULLW, v, src, 4); }
+__device__ __forceinline__ double g4max(double v) {
+  v = fmax(v, __shfl_xor_sync(FULLW, v, 1)); v = fmax(v, __shfl_xor_sync(FULLW, v, 2));
+  return v;
+}
+__device__ __forceinline__ double g4sum(double v) {
+  v += __shfl_xor_sync(FULLW, v, 1); v += __shfl_xor_sync(FULLW, v, 2);
+  return v;
+}
+
+// LU (no pivoting, unit L, reciprocal pivots on the diagonal: the layout lu_solve reads) of the n x n matrix whose rows
+// t * RPL .. t * RPL + RPL - 1 lane t holds, and the solution of M x = b; x returned in b (own rows).
+template <int RPL>
+__device__ __forceinline__ void lu4_factor_solve(double (&M)[RPL][4 * RPL], double (&b)[RPL], const int t) {
+  constexpr int n = 4 * RPL;
+#pragma unroll
+  for (int p = 0; p < n; p++) {
+    const int owner = p / RPL, pr = p % RPL;
+    const double rp = g4(1.0 / M[pr][p], owner);
+    double prow[n];
+#pragma unroll
+    for (int c = p + 1; c < n; c++) prow[c] = g4(M[pr][c], owner);
+    const double pb = g4(b[pr], owner);
+#pragma unroll
+    for (int r = 0; r < RPL; r++) {
+      const bool below = (t * RPL + r > p);
+      const double l = M[r][p] * rp;
+      if (below) {
+        M[r][p] = l;
+#pragma unroll
+        for (int c = p + 1; c < n; c++) M[r][c] = fma(-l, prow[c], M[r][c]);
+        b[r] = fma(-l, pb, b[r]);
+      }
+    }
+    if (t == owner) M[pr][p] = rp;
+  }
+  double xs[n];
+#pragma unroll
+  for (int p = n - 1; p >= 0; p--) {
+    const int owner = p / RPL, pr = p % RPL;
+    double v = b[pr];
+#pragma unroll
+    for (int c = p + 1; c < n; c++) v = fma(-M[pr][c], xs[c], v);
+    xs[p] = g4(v * M[pr][p], owner);
+  }
+#pragma unroll
+  for (int r = 0; r < RPL; r++) {
+    double v = 0.0;
+#pragma unroll
+    for (int o = 0; o < 4; o++) v = (t == o) ? xs[o * RPL + r] : v;
+    b[r] = v;
+  }
+}
+
+__device__ bool irk_newton4(const int t, const double* __restrict__ x, double u0, double u1, const double* __restrict__ p,
+                            const TrackView& tr, double h, const double* __restrict__ A4, const double* __restrict__ b4,
+                            const double* __restrict__ wT, const double* __restrict__ wD, double* __restrict__ sm) {
   const double m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
   const double C = lR / (lR + lF), im = 1.0 / m;
   const double itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
-  // ---- actuators: K = w (u - x) / t
-  double Ti[NS], Di[NS];
+  double ha[NS];
 #pragma unroll
-  for (int i = 0; i < NS; i++) { KS(i, 6) = wT[i] * (u0 - x[6]) * itT; KS(i, 7) = wD[i] * (u1 - x[7]) * itD; }
+  for (int j = 0; j < NS; j++) ha[j] = h * A4[t * NS + j];
+  // stage value of a component from the slopes of the four lanes
+  auto stage_val = [&](double x0, double Kown) {
+    double v = x0;
 #pragma unroll
-  for (int i = 0; i < NS; i++) {
-    double a = x[6], d = x[7];
+    for (int j = 0; j < NS; j++) v = fma(ha[j], g4(Kown, j), v);
+    return v;
+  };
+  // ---- actuators: K = w (u - x) / t  (closed form, every lane knows all four)
+  const double c6 = (u0 - x[6]) * itT, c7 = (u1 - x[7]) * itD;
+  double K[NX];
+  K[6] = wT[t] * c6; K[7] = wD[t] * c7;
+  double Ti = x[6], Di = x[7];
 #pragma unroll
-    for (int j = 0; j < NS; j++) { a = fma(h * A4[i * NS + j], KS(j, 6), a); d = fma(h * A4[i * NS + j], KS(j, 7), d); }
-    Ti[i] = a; Di[i] = d;
-  }
-  // ---- (v_x, v_y): Newton on 8 unknowns
-  VPoint vp[NS];
-#pragma unroll
-  for (int i = 0; i < NS; i++) {
+  for (int j = 0; j < NS; j++) { Ti = fma(ha[j], wT[j] * c6, Ti); Di = fma(ha[j], wD[j] * c7, Di); }
+  // ---- (v_x, v_y): Newton on 8 unknowns, rows 2t, 2t + 1 on this lane
+  VPoint vp;
+  {
     double sd, cd;
-    sincos(Di[i], &sd, &cd);
+    sincos(Di, &sd, &cd);
     const double td = sd / cd, Ctd = C * td, den = 1.0 + Ctd * Ctd;
-    vp[i].cb = rsqrt(den); vp[i].sb = Ctd * vp[i].cb;
-    vp[i].bdot = C * (1.0 + td * td) / den * KS(i, 7);
-    vp[i].cdb = cd * vp[i].cb + sd * vp[i].sb;
-    vp[i].Fm = p[IHM2B_P_CM0] * Ti[i];
+    vp.cb = rsqrt(den); vp.sb = Ctd * vp.cb;
+    vp.bdot = C * (1.0 + td * td) / den * K[7];
+    vp.cdb = cd * vp.cb + sd * vp.sb;
+    vp.Fm = p[IHM2B_P_CM0] * Ti;
   }
-  double Rv[8];
-  auto veval = [&](const VPoint& v, double vx, double vy, double& f3, double& f4, double& dvd) {
+  auto veval = [&](double vx, double vy, double& f3, double& f4, double& dvd) {
     const double th = tanh(10.0 * vx);
     const double poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
-    const double FRx = 0.5 * v.Fm - poly * th;
-    const double vdot = (FRx * v.cb + 0.5 * v.Fm * v.cdb) * im;
-    f3 = vdot * v.cb - v.bdot * vy;
-    f4 = vdot * v.sb + v.bdot * vx;
-    dvd = (-(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th)) * v.cb * im;
+    const double FRx = 0.5 * vp.Fm - poly * th;
+    const double vdot = (FRx * vp.cb + 0.5 * vp.Fm * vp.cdb) * im;
+    f3 = vdot * vp.cb - vp.bdot * vy;
+    f4 = vdot * vp.sb + vp.bdot * vx;
+    dvd = (-(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th)) * vp.cb * im;
   };
-#pragma unroll
-  for (int i = 0; i < NS; i++) { double d, f3, f4; veval(vp[i], x[3], x[4], f3, f4, d); KS(i, 3) = f3; KS(i, 4) = f4; }
-  bool ok = true;
+  { double d; veval(x[3], x[4], K[3], K[4], d); }
+  bool ok = true, conv = false;
+  double Mv[2][8];
+  double P3 = K[3], P4 = K[4];      // the point the factors belong to (frozen at convergence)
 #pragma unroll 1
   for (int it = 0;; it++) {
-#pragma unroll
-    for (int i = 0; i < NS; i++) {
-      double vx = x[3], vy = x[4];
-#pragma unroll
-      for (int j = 0; j < NS; j++) { vx = fma(h * A4[i * NS + j], KS(j, 3), vx); vy = fma(h * A4[i * NS + j], KS(j, 4), vy); }
-      double f3, f4, dvd;
-      veval(vp[i], vx, vy, f3, f4, dvd);
-      Rv[2 * i] = KS(i, 3) - f3; Rv[2 * i + 1] = KS(i, 4) - f4;
-      const double J33 = dvd * vp[i].cb, J34 = -vp[i].bdot, J43 = dvd * vp[i].sb + vp[i].bdot;
-#pragma unroll
-      for (int j = 0; j < NS; j++) {
-        const double ha = h * A4[i * NS + j], e = (i == j) ? 1.0 : 0.0;
-        Mv[((2 * i) * 8 + 2 * j) * NI] = e - ha * J33;      Mv[((2 * i) * 8 + 2 * j + 1) * NI] = -ha * J34;
-        Mv[((2 * i + 1) * 8 + 2 * j) * NI] = -ha * J43;     Mv[((2 * i + 1) * 8 + 2 * j + 1) * NI] = e;
-      }
-    }
-    lu_factor<8>(Mv);
-    lu_solve<8>(Mv, Rv);
-    double dmax = 0.0, kmax = 0.0;
-#pragma unroll
-    for (int i = 0; i < NS; i++) {
-      const double k3 = KS(i, 3) - Rv[2 * i], k4 = KS(i, 4) - Rv[2 * i + 1];
-      KS(i, 3) = k3; KS(i, 4) = k4;
-      dmax = fmax(dmax, fmax(fabs(Rv[2 * i]), fabs(Rv[2 * i + 1])));
-      kmax = fmax(kmax, fmax(fabs(k3), fabs(k4)));
-    }
-    if (!(dmax == dmax)) { ok = false; break; }
-    if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) break;
-  }
-  // ---- r: explicit, r' = l_R v_y' - beta'   (python/models.py:304)
-  double vxi[NS], vyi[NS], ri[NS];
-#pragma unroll
-  for (int i = 0; i < NS; i++) KS(i, 5) = lR * KS(i, 4) - vp[i].bdot;
-#pragma unroll
-  for (int i = 0; i < NS; i++) {
-    double a = x[3], b = x[4], c = x[5];
+    if (!conv) { P3 = K[3]; P4 = K[4]; }
+    const double vx = stage_val(x[3], P3), vy = stage_val(x[4], P4);
+    double f3, f4, dvd;
+    veval(vx, vy, f3, f4, dvd);
+    double R[2] = {P3 - f3, P4 - f4};
+    const double J33 = dvd * vp.cb, J34 = -vp.bdot, J43 = dvd * vp.sb + vp.bdot;
 #pragma unroll
     for (int j = 0; j < NS; j++) {
-      const double ha = h * A4[i * NS + j];
-      a = fma(ha, KS(j, 3), a); b = fma(ha, KS(j, 4), b); c = fma(ha, KS(j, 5), c);
+      const double e = (t == j) ? 1.0 : 0.0;
+      Mv[0][2 * j] = e - ha[j] * J33; Mv[0][2 * j + 1] = -ha[j] * J34;
+      Mv[1][2 * j] = -ha[j] * J43;    Mv[1][2 * j + 1] = e;
     }
-    vxi[i] = a; vyi[i] = b; ri[i] = c;
+    lu4_factor_solve<2>(Mv, R, t);
+    const double k3 = P3 - R[0], k4 = P4 - R[1];
+    const double dmax = g4max(fmax(fabs(R[0]), fabs(R[1]))), kmax = g4max(fmax(fabs(k3), fabs(k4)));
+    if (!conv) {
+      K[3] = k3; K[4] = k4;
+      if (!(dmax == dmax)) { ok = false; conv = true; }
+      else if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) conv = true;
+    }
+    if (__all_sync(FULLW, conv)) break;
   }
-  // ---- (s, n, psi): Newton on 12 unknowns
-  double Rp[12];
+  // ---- r: explicit, r' = l_R v_y' - beta'   (python/models.py:304)
+  K[5] = lR * K[4] - vp.bdot;
+  const double vxi = stage_val(x[3], K[3]), vyi = stage_val(x[4], K[4]), ri = stage_val(x[5], K[5]);
+  // ---- (s, n, psi): Newton on 12 unknowns, rows 3t .. 3t + 2 on this lane
   {
     double kap, dkap, sp, cp;
     kappa_lookup(tr, x[0], kap, dkap);
     sincos(x[2], &sp, &cp);
     const double sdot = (x[3] * cp - x[4] * sp) / (1.0 + kap * x[1]);
-#pragma unroll
-    for (int i = 0; i < NS; i++) { KS(i, 0) = sdot; KS(i, 1) = x[3] * sp + x[4] * cp; KS(i, 2) = x[5] - kap * sdot; }
+    K[0] = sdot; K[1] = x[3] * sp + x[4] * cp; K[2] = x[5] - kap * sdot;
   }
+  double Mp[3][12];
+  double Q0 = K[0], Q1 = K[1], Q2 = K[2];
+  conv = !ok;
 #pragma unroll 1
   for (int it = 0;; it++) {
+    if (!conv) { Q0 = K[0]; Q1 = K[1]; Q2 = K[2]; }
+    const double s_ = stage_val(x[0], Q0), n_ = stage_val(x[1], Q1), psi = stage_val(x[2], Q2);
+    double kap, dkap, sp, cp;
+    kappa_lookup(tr, s_, kap, dkap);
+    sincos(psi, &sp, &cp);
+    const double iD = 1.0 / (1.0 + kap * n_);
+    const double num = vxi * cp - vyi * sp;
+    const double sdot = num * iD;
+    double R[3] = {Q0 - sdot, Q1 - (vxi * sp + vyi * cp), Q2 - (ri - kap * sdot)};
+    double J[3][3];
+    J[0][0] = -sdot * dkap * n_ * iD; J[0][1] = -sdot * kap * iD; J[0][2] = -(vxi * sp + vyi * cp) * iD;
+    J[1][0] = 0.0; J[1][1] = 0.0; J[1][2] = num;
+    J[2][0] = -dkap * sdot - kap * J[0][0]; J[2][1] = -kap * J[0][1]; J[2][2] = -kap * J[0][2];
 #pragma unroll
-    for (int i = 0; i < NS; i++) {
-      double s = x[0], n = x[1], psi = x[2];
+    for (int j = 0; j < NS; j++)
 #pragma unroll
-      for (int j = 0; j < NS; j++) {
-        const double ha = h * A4[i * NS + j];
-        s = fma(ha, KS(j, 0), s); n = fma(ha, KS(j, 1), n); psi = fma(ha, KS(j, 2), psi);
-      }
-      double kap, dkap, sp, cp;
-      kappa_lookup(tr, s, kap, dkap);
-      sincos(psi, &sp, &cp);
-      const double iD = 1.0 / (1.0 + kap * n);
-      const double num = vxi[i] * cp - vyi[i] * sp;
-      const double sdot = num * iD;
-      Rp[3 * i] = KS(i, 0) - sdot;
-      Rp[3 * i + 1] = KS(i, 1) - (vxi[i] * sp + vyi[i] * cp);
-      Rp[3 * i + 2] = KS(i, 2) - (ri[i] - kap * sdot);
-      double J[3][3];
-      J[0][0] = -sdot * dkap * n * iD; J[0][1] = -sdot * kap * iD; J[0][2] = -(vxi[i] * sp + vyi[i] * cp) * iD;
-      J[1][0] = 0.0; J[1][1] = 0.0; J[1][2] = num;
-      J[2][0] = -dkap * sdot - kap * J[0][0]; J[2][1] = -kap * J[0][1]; J[2][2] = -kap * J[0][2];
+      for (int a = 0; a < 3; a++)
 #pragma unroll
-      for (int j = 0; j < NS; j++) {
-        const double ha = h * A4[i * NS + j];
-#pragma unroll
-        for (int a = 0; a < 3; a++)
-#pragma unroll
-          for (int c = 0; c < 3; c++)
-            Mp[((3 * i + a) * 12 + 3 * j + c) * NI] = ((i == j && a == c) ? 1.0 : 0.0) - ha * J[a][c];
-      }
+        for (int c = 0; c < 3; c++) Mp[a][3 * j + c] = ((t == j && a == c) ? 1.0 : 0.0) - ha[j] * J[a][c];
+    lu4_factor_solve<3>(Mp, R, t);
+    const double k0 = Q0 - R[0], k1 = Q1 - R[1], k2 = Q2 - R[2];
+    const double dmax = g4max(fmax(fabs(R[0]), fmax(fabs(R[1]), fabs(R[2]))));
+    const double kmax = g4max(fmax(fabs(k0), fmax(fabs(k1), fabs(k2))));
+    if (!conv) {
+      K[0] = k0; K[1] = k1; K[2] = k2;
+      if (!(dmax == dmax)) { ok = false; conv = true; }
+      else if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) conv = true;
     }
-    lu_factor<12>(Mp);
-    lu_solve<12>(Mp, Rp);
-    double dmax = 0.0, kmax = 0.0;
-#pragma unroll
-    for (int i = 0; i < NS; i++)
-#pragma unroll
-      for (int a = 0; a < 3; a++) {
-        const double kk = KS(i, a) - Rp[3 * i + a];
-        KS(i, a) = kk;
-        dmax = fmax(dmax, fabs(Rp[3 * i + a]));
-        kmax = fmax(kmax, fabs(kk));
-      }
-    if (!(dmax == dmax)) { ok = false; break; }
-    if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) break;
+    if (__all_sync(FULLW, conv)) break;
   }
+  // ---- hand over to phase 2 / 3: x_next, slopes, factors, Jacobian at this lane's collocation point
 #pragma unroll
   for (int a = 0; a < NX; a++) {
-    double v = x[a];
-#pragma unroll
-    for (int i = 0; i < NS; i++) v = fma(h * b4[i], KS(i, a), v);
-    sm[(OFF_XN + a) * NI] = v;
+    const double v = x[a] + g4sum(h * b4[t] * K[a]);
+    if (t == 0) sm[(OFF_XN + a) * NI] = v;
+    sm[(OFF_K + t * 8 + a) * NI] = K[a];
   }
-  // ---- Jacobians at the converged collocation points (kept entries only)
-#pragma unroll 1
-  for (int i = 0; i < NS; i++) {
+#pragma unroll
+  for (int r = 0; r < 2; r++)
+#pragma unroll
+    for (int c = 0; c < 8; c++) sm[(OFF_MV + (2 * t + r) * 8 + c) * NI] = Mv[r][c];
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+#pragma unroll
+    for (int c = 0; c < 12; c++) sm[(OFF_MP + (3 * t + r) * 12 + c) * NI] = Mp[r][c];
+  {
     double xs[NX], f[NX], J[NX][NZ];
 #pragma unroll
-    for (int a = 0; a < NX; a++) {
-      double v = x[a];
-#pragma unroll
-      for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], KS(j, a), v);
-      xs[a] = v;
-    }
+    for (int a = 0; a < NX; a++) xs[a] = stage_val(x[a], K[a]);
     fkin6<true>(xs, u0, u1, p, tr, f, J);
 #pragma unroll
     for (int r = 0; r < 6; r++)
 #pragma unroll
       for (int c = 0; c < NZ; c++)
-        if (jslot(r, c) >= 0) sm[(OFF_J + i * 33 + jslot(r, c)) * NI] = ((JMASK[r] >> c) & 1u) ? J[r][c] : 0.0;
+        if (jslot(r, c) >= 0) sm[(OFF_J + t * 33 + jslot(r, c)) * NI] = ((JMASK[r] >> c) & 1u) ? J[r][c] : 0.0;
   }
-  return ok;
-#undef KS
+  return g4max(ok ? 0.0 : 1.0) == 0.0;
 }
 
 // ---- phase 2: one column of d x_next / d (x, u):  (I - h A (x) J) dK = J_x E + J_u by block forward
@@ -397,18 +426,24 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
   for (int i = 0; i < 8; i++) wa[i] = __ldg(w.actw + (size_t)b * 8 + i);
   const double itT = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TT), itD = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TD);
   const size_t sk = (size_t)b * cf.N + k;
-  if (tid < NI) {
-    bool ok = false;
-    if (live) {
-      const int t = w.track[b];
-      TrackView tr{cf.n_grid, w.s_ref + (size_t)t * cf.n_grid, w.kappa_ref + (size_t)t * cf.n_grid};
-      double p[NP], x[NX];
-      for (int i = 0; i < NP; i++) p[i] = __ldg(w.params + (size_t)b * NP + i);
-      for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
-      const double u0 = w.u[sk * NU], u1 = w.u[sk * NU + 1];
-      ok = irk_newton(x, u0, u1, p, tr, cf.dt, cf.irk_A, cf.irk_b, wa, wa + 4, sm);
+  {
+    // phase 1: lanes 4q .. 4q + 3 of warp wp work on interval 8 wp + q of the block
+    const int t = tid & 3, j1 = (tid >> 5) * 8 + ((tid & 31) >> 2);
+    const int gid1 = blockIdx.x * NI + j1;
+    const bool in1 = gid1 < cf.B * cf.N;
+    const int b1 = in1 ? gid1 / cf.N : 0, k1 = in1 ? gid1 - b1 * cf.N : 0;   // out of range: a valid dummy, results unused
+    const bool live1 = in1 && !(w.active && !w.active[b1]);
+    if (__any_sync(0xffffffffu, live1)) {     // a warp whose 8 intervals are all masked out (SQP / line search / closed loop) skips
+      const int tk = w.track[b1];
+      TrackView tr{cf.n_grid, w.s_ref + (size_t)tk * cf.n_grid, w.kappa_ref + (size_t)tk * cf.n_grid};
+      double p[NP], x[NX], wa1[8];
+      for (int i = 0; i < NP; i++) p[i] = __ldg(w.params + (size_t)b1 * NP + i);
+      for (int i = 0; i < 8; i++) wa1[i] = __ldg(w.actw + (size_t)b1 * 8 + i);
+      for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b1 * (cf.N + 1) + k1) * NX + i];
+      const double u0 = w.u[((size_t)b1 * cf.N + k1) * NU], u1 = w.u[((size_t)b1 * cf.N + k1) * NU + 1];
+      const bool ok = irk_newton4(t, x, u0, u1, p, tr, cf.dt, cf.irk_A, cf.irk_b, wa1, wa1 + 4, smem + j1);
+      if (t == 0) s_ok[j1] = ok;
     }
-    s_ok[j] = ok;
   }
   __syncthreads();
   double* ba = w.BA + sk * NX * NZ;
@@ -441,10 +476,13 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
 void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream) {
   const int total = cf.B * cf.N;
   const int bytes = PER_INT * NI * (int)sizeof(double);
-  static int configured = 0;
-  if (!configured) {
-    cudaFuncSetAttribute(linearize_irk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    configured = 1;
+  // the dynamic shared-memory limit is a per-device attribute: remembered per device
+  static bool configured[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    if (cudaFuncSetAttribute(linearize_irk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return;   // the launch below then reports the error
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   linearize_irk_kernel<<<(total + NI - 1) / NI, NI * NCG, bytes, stream>>>(cf, w);
 }
