@@ -26,6 +26,7 @@ __all__ = [
     "offline_motion_plan",
     "triple_motion_plan_ref",
     "load_packaged_track",
+    "write_track_data_file",
     "PACKAGED_TRACKS",
 ]
 
@@ -193,3 +194,16 @@ def load_packaged_track(name: str, tripled: bool = True) -> MotionPlan:
         lap_length=float(d["lap_length"]),
     )
     return triple_motion_plan_ref(mp) if tripled else mp
+
+
+def write_track_data_file(motion_plan: MotionPlan, outfile: str) -> None:
+    """python/motion_planning.py:431-456 (`generate_track_data_file`): the single-lap tables as the CSV the C++ nodes
+    and dpc/main.py read -- header `s_ref,X_ref,Y_ref,phi_ref,kappa_ref,right_width,left_width`, rows in `%.6f`."""
+    parent = os.path.dirname(outfile)
+    if parent and not os.path.exists(parent):
+        os.makedirs(parent)
+    with open(outfile, "w") as f:
+        f.write("s_ref,X_ref,Y_ref,phi_ref,kappa_ref,right_width,left_width\n")
+        np.savetxt(f, np.column_stack((motion_plan.s_ref, motion_plan.X_ref, motion_plan.Y_ref, motion_plan.phi_ref,
+                                       motion_plan.kappa_ref, motion_plan.right_widths, motion_plan.left_widths)),
+                   delimiter=",", fmt="%.6f")

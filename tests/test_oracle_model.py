@@ -227,3 +227,65 @@ def test_cartesian_dyn6_satisfies_the_reference_implicit_form():
                                         + Fx["RR"] * tw / 2 - Fy["RR"] * lR - Fx["RL"] * tw / 2 - Fy["RL"] * lR)])
             scale = np.array([1, 1, 1, m * 10, m * 10, P[_abi.P_IZ] * 10])
             assert np.abs(res / scale).max() < 5e-4, (i, res)
+
+
+def test_frenet_fdyn6_satisfies_the_reference_implicit_form():
+    """Independent pin of the plant of BASELINE configs[0] and [2]: a numpy transcription of the implicit residual of
+    `fdyn6_model` (python/models.py:455-606: wheel loads with load transfer and downforce :486-515, slip angles with
+    smooth_abs_nonzero :518-540, the CROSSWISE slip-angle assignment :543-546, torque vectoring :548-560, Frenet
+    kinematics :562-575), evaluated at the state derivative the oracle returns, must vanish.  The oracle solves the
+    implicit form for xdot as an affine system in (a_x, a_y), so this is a different route to the same equations."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.track import load_packaged_track
+    from oracle.lib import Oracle
+    mp = load_packaged_track("fsds_default")
+    rng = np.random.default_rng(11)
+    B = 200
+    x = np.stack([rng.uniform(0, 380, B), rng.uniform(-1.5, 1.5, B), rng.uniform(-0.5, 0.5, B), rng.uniform(0.3, 25, B),
+                  rng.uniform(-1.5, 1.5, B), rng.uniform(-1.2, 1.2, B), rng.uniform(-400, 400, B), rng.uniform(-0.45, 0.45, B)], 1)
+    u = np.stack([rng.uniform(-500, 500, B), rng.uniform(-0.5, 0.5, B)], 1)
+    sabs = lambda v: np.tanh(10 * v) * v + 1e-6 * np.exp(-v * v)      # utils.py:23-32 (smooth_sgn = tanh(10 x))
+    for cross in (1.0, 0.0):
+        P = _abi.default_params(); P[_abi.P_CROSS] = cross
+        cfg = _abi.make_config(batch=1, n_grid=len(mp.s_ref))
+        orc = Oracle(cfg, mp.s_ref, mp.kappa_ref, params=P[None, :].copy())
+        m, g, lR, lF, tw, zcg, Iz = [P[i] for i in (_abi.P_M, _abi.P_G, _abi.P_LR, _abi.P_LF, _abi.P_TRACKW, _abi.P_ZCG, _abi.P_IZ)]
+        wb = lR + lF
+        Ba, Ca, Da, Ea = [P[j] for j in (_abi.P_BA, _abi.P_CA, _abi.P_DA, _abi.P_EA)]
+        pac = lambda al: Da * np.sin(Ca * np.arctan(Ba * al - Ea * (Ba * al - np.arctan(Ba * al))))
+        worst = 0.0
+        for i in range(B):
+            xd = orc.fdyn6(x[i], u[i])
+            s, n, psi, vx, vy, r, T, dl = x[i]
+            ax, ay = xd[3] - vy * r, xd[4] + vx * r
+            Fdown = 0.5 * P[_abi.P_CDOWN] * vx * vx
+            stat = 0.5 * m * g * lF / wb
+            lon, lat = 0.5 * m * ax * zcg / wb, 0.5 * m * ay * zcg / tw
+            Fz = dict(FL=-(stat - lon + lat + 0.25 * Fdown), FR=-(stat - lon - lat + 0.25 * Fdown),
+                      RL=-(stat + lon + lat + 0.25 * Fdown), RR=-(stat + lon - lat + 0.25 * Fdown))
+            cd, sd = np.cos(dl), np.sin(dl)
+            vxF = dict(FL=vx - 0.5 * tw * r, FR=vx + 0.5 * tw * r); vyF = vy + lF * r
+            vlon = dict(FL=cd * vxF["FL"] + sd * vyF, FR=cd * vxF["FR"] + sd * vyF, RL=vx - 0.5 * tw * r, RR=vx + 0.5 * tw * r)
+            vlat = dict(FL=-sd * vxF["FL"] + cd * vyF, FR=-sd * vxF["FR"] + cd * vyF, RL=vy - lR * r, RR=vy - lR * r)
+            al = {k: np.arctan2(vlat[k], sabs(vlon[k])) for k in Fz}
+            src = dict(FL="RR", FR="RL", RL="FR", RR="FL") if cross else dict(FL="FL", FR="FR", RL="RL", RR="RR")
+            Fy = {k: Fz[k] * pac(al[src[k]]) for k in Fz}
+            Fdrag = -(P[_abi.P_CR0] + P[_abi.P_CR1] * vx + P[_abi.P_CR2] * vx * vx) * np.tanh(10 * vx)
+            beta = np.arctan(lR / wb * np.tan(dl))
+            dtau = P[_abi.P_KTV] * (np.hypot(vx, vy) * np.sin(beta) / lR - r)
+            dn = -m * g - 0.25 * Fdown
+            Fx = {k: P[_abi.P_CM0] * (T + (dtau if k[1] == "R" else -dtau)) * Fz[k] / dn for k in Fz}
+            i0 = np.searchsorted(mp.s_ref, s, side="right") - 1
+            kap = mp.kappa_ref[i0] + (mp.kappa_ref[i0 + 1] - mp.kappa_ref[i0]) / (mp.s_ref[i0 + 1] - mp.s_ref[i0]) * (s - mp.s_ref[i0])
+            sdot = (vx * np.cos(psi) - vy * np.sin(psi)) / (1 + kap * n)
+            res = np.array([
+                xd[0] - sdot, xd[1] - (vx * np.sin(psi) + vy * np.cos(psi)), xd[2] - (r - kap * sdot),
+                m * ax - ((Fx["FR"] + Fx["FL"]) * cd - (Fy["FR"] + Fy["FL"]) * sd + Fx["RR"] + Fx["RL"] + Fdrag),
+                m * ay - ((Fx["FR"] + Fx["FL"]) * sd + (Fy["FR"] + Fy["FL"]) * cd + Fy["RR"] + Fy["RL"]),
+                Iz * xd[5] - ((Fx["FR"] * cd - Fy["FR"] * sd) * tw / 2 + (Fx["FR"] * sd + Fy["FR"] * cd) * lF
+                              - (Fx["FL"] * cd - Fy["FL"] * sd) * tw / 2 + (Fx["FL"] * sd + Fy["FL"] * cd) * lF
+                              + Fx["RR"] * tw / 2 - Fy["RR"] * lR - Fx["RL"] * tw / 2 - Fy["RL"] * lR),
+                xd[6] - (u[i, 0] - T) / P[_abi.P_TT], xd[7] - (u[i, 1] - dl) / P[_abi.P_TD]])
+            scale = np.array([1, 1, 1, m * 10, m * 10, Iz * 10, 1 + abs(xd[6]), 1 + abs(xd[7])])
+            worst = max(worst, np.abs(res / scale).max())
+        assert worst < 1e-10, (cross, worst)
