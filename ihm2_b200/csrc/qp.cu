@@ -373,8 +373,10 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
   const double iscP = 1.0 / (1.0 + fmin(fabs(Rp.lb), fabs(Rp.ub))), iscT = 1.0 / (1.0 + fmin(fabs(Rt.lb), fabs(Rt.ub)));
   const CtDef ctP = ct_path(a), ctT = ct_term(a);
   const int rounds = (N + 4) >> 2;           // stage-parallel loops: stage k = q + 4 i
-  // ---- NL: row slot 8 + a of a stage is row a of h (a < 5; terminal: a < 2), all soft; of the static rows T and
-  // delta (terminal: the rows on v_y and r) are soft (idxsbx = [2, 3] of idxbx / idxbx_e)
+  // ---- NL: row slot 8 + a of a stage is row a of h, all soft: a = 0, 1 the track boundaries, a = 4 a_lat (path stages).
+  // Rows 2, 3 of h (T_dot, delta_dot) are the linear rows 2, 3 above (u - x within +-t x_dot_max): kept once, in that
+  // form; their slots stay empty.  Of the static rows T and delta (terminal: the rows on v_y and r) are soft
+  // (idxsbx = [2, 3] of idxbx / idxbx_e)
   double itT = 0.0, itD = 0.0;
   if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
   const double Zp = cf.cs * cf.slack_Z, zp = cf.cs * cf.slack_z, Zt = cf.ct * cf.slack_Z, zt = cf.ct * cf.slack_z;
@@ -505,20 +507,26 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       const int k = on ? kk : N;
       const bool term = (k == N);
       const RowDef& R = term ? Rt : Rp;
-      const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+      const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (a < 2 || (a == 4 && !term));
       const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
       const double xa_ = pX[k * 8 + a], u0v = pU[(term ? 0 : k) * 2], u1v = pU[(term ? 0 : k) * 2 + 1];
       const double v0 = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
       const HRow hr = hrow_coef(k);
       const double v1 = hrow_val(hr, xa_, u0v, u1v);
       RowSt r0{0.0, 0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0}, r1 = r0;
+      // the slacks start where they absorb the row's violation at the initial point (t = thr0 there): the soft rows
+      // are primal feasible from the first iterate on, whatever the warm start violates
       if (act0) {
-        if (soft0) { r0.sL = r0.sU = cf.thr0; r0.lsL = r0.lsU = cf.mu0 / cf.thr0; }
+        if (soft0) {
+          r0.sL = fmax(cf.thr0, R.lb - v0 + cf.thr0); r0.sU = fmax(cf.thr0, v0 - R.ub + cf.thr0);
+          r0.lsL = cf.mu0 / r0.sL; r0.lsU = cf.mu0 / r0.sU;
+        }
         r0.tL = fmax(soft0 ? v0 + r0.sL - R.lb : v0 - R.lb, cf.thr0); r0.tU = fmax(soft0 ? R.ub + r0.sU - v0 : R.ub - v0, cf.thr0);
         r0.lamL = cf.mu0 / r0.tL; r0.lamU = cf.mu0 / r0.tU;
       }
       if (act1) {
-        r1.sL = r1.sU = cf.thr0; r1.lsL = r1.lsU = cf.mu0 / cf.thr0;
+        r1.sL = fmax(cf.thr0, hlb - v1 + cf.thr0); r1.sU = fmax(cf.thr0, v1 - hub + cf.thr0);
+        r1.lsL = cf.mu0 / r1.sL; r1.lsU = cf.mu0 / r1.sU;
         r1.tL = fmax(v1 + r1.sL - hlb, cf.thr0); r1.tU = fmax(hub + r1.sU - v1, cf.thr0);
         r1.lamL = cf.mu0 / r1.tL; r1.lamU = cf.mu0 / r1.tU;
       }
@@ -553,8 +561,8 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
     rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
   }
   __syncwarp();
-  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4); NL: 28 at stage 0, 40 on the path, 20 at the end (soft rows count twice)
-  const double inv_n = NL ? 1.0 / (40.0 * N + 8.0) : 1.0 / (16.0 * N);
+  // one-sided inequalities: 2 * (4 + 8 (N-1) + 4); NL: 20 at stage 0, 32 on the path, 20 at the end (soft rows count twice)
+  const double inv_n = NL ? 1.0 / (32.0 * N + 8.0) : 1.0 / (16.0 * N);
   double mu = 0.0, res_g = 0.0, res_b = 0.0, res_d = 0.0, res_m = 0.0;
   int it = 0, qp_status = 1, at_floor = 0, short_steps = 0;
   const double mu_floor = 0.1 * cf.tol_comp;
@@ -838,7 +846,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
           const bool term = (k == N);
           const RowDef& R = term ? Rt : Rp;
           const double Z = term ? Zt : Zp, zz = term ? zt : zp;
-          const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+          const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (a < 2 || (a == 4 && !term));
           const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
           const int e0 = k * 16 + a, e1 = e0 + 8;
           const double xa_ = pX[k * 8 + a], u0v = pU[(term ? 0 : k) * 2], u1v = pU[(term ? 0 : k) * 2 + 1];
@@ -1104,7 +1112,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         const int k = on ? kk : N;
         const bool term = (k == N);
         const RowDef& R = term ? Rt : Rp;
-        const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (term ? (a < 2) : (a < 5));
+        const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (a < 2 || (a == 4 && !term));
         const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
         const int e0 = k * 16 + a, e1 = e0 + 8, ku = term ? 0 : k;
         const double xa_ = pX[k * 8 + a], pia = pPI[k * 8 + a], u0v = pU[ku * 2], u1v = pU[ku * 2 + 1];
@@ -1284,7 +1292,7 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
       const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
       dl = row_res(NL && (term ? (a == 2 || a == 3) : (a >= 6)), v, R.lb, R.ub, k * RS + a, Z, zz);
     }
-    if (NL && (term ? (a < 2) : (a < 5))) {
+    if (NL && (a < 2 || (a == 4 && !term))) {
       const double v1 = hl.value(gHC + k * 16, pX + k * 8, term ? 0.0 : pU[k * 2], term ? 0.0 : pU[k * 2 + 1], a);
       dl1 = row_res(true, v1, hl.lb, hl.ub, k * RS + 8 + a, Z, zz);
     }
@@ -1382,7 +1390,7 @@ __device__ __forceinline__ double cost_lane(const KCfg& cf, const int N, const i
         const double v = row_value(R, term, 0.0, pX[k * 8 + R.ix]);
         m += soft_penalty(zz, Z, fmax(0.0, R.lb - v) + fmax(0.0, v - R.ub));
       }
-      if (term ? (a < 2) : (a < 5)) {
+      if (a < 2 || (a == 4 && !term)) {
         const double v1 = hl.value(gHC + k * 16, pX + k * 8, term ? 0.0 : pU[k * 2], term ? 0.0 : pU[k * 2 + 1], a);
         m += soft_penalty(zz, Z, fmax(0.0, hl.lb - v1) + fmax(0.0, v1 - hl.ub));
       }

@@ -584,6 +584,11 @@ void build_rows(const ihm2b_config& cf, Qp& qp) {
       g0.c[0] = 1.0; g0.c[NU + 6] = -1.0; g0.lb = -cf.g_T_max; g0.ub = cf.g_T_max;
       Row g1; std::memset(&g1, 0, sizeof g1);
       g1.c[1] = 1.0; g1.c[NU + 7] = -1.0; g1.lb = -cf.g_delta_max; g1.ub = cf.g_delta_max;
+      // These two rows ARE the T_dot / delta_dot rows of h (rows 2, 3 of old/generate_acaods_interface.py:312-325:
+      // (u - x) / t within +-x_dot_max, i.e. u - x within +-t x_dot_max = g_max): with the h rows on they are kept
+      // once, in this form (python/mpc.py:91-99, hard, unit coefficients).  Both copies together are linearly
+      // dependent active constraints, on which the interior point stalls at the end, and the h form has
+      // coefficients of 1 / t_T = 1000 next to the O(1) rows.
       R.push_back(g0); R.push_back(g1);
       if (k > 0) {  // idxbx = [1,3,6,7] (mpc.py:78-80); stage 0 carries x0 instead.
         // With the gen-1 slack sets the bounds at positions idxsbx = [2, 3] of idxbx are soft
@@ -619,6 +624,7 @@ void build_h_rows(const ihm2b_config& cf, const double* p, const Track& tr, cons
     con_h(&x[k * NX], uk, p, tr, cf.track_half_L, cf.track_half_W, h, Jh);
     const int nh = (k < N) ? NH : NH_E;
     for (int i = 0; i < nh; i++) {
+      if (i == 2 || i == 3) continue;   // T_dot, delta_dot: see build_rows
       Row r; std::memset(&r, 0, sizeof r);
       double e = h[i];
       for (int a = 0; a < NX; a++) { r.c[NU + a] = Jh[i][a]; e -= Jh[i][a] * x[k * NX + a]; }
@@ -666,8 +672,12 @@ void ipm_solve(const ihm2b_config& cf, const Qp& qp, QpSol& s) {
     for (size_t r = 0; r < R.size(); r++) {
       const double cz = row_val(R[r], &s.z[k * NZ]);
       if (R[r].soft) {
-        s.sL[k][r] = s.sU[k][r] = thr0;
-        s.lamSL[k][r] = s.lamSU[k][r] = cf.qp_mu0 / thr0;
+        // the slacks start where they absorb the row's violation at the initial point (t = thr0 there): the soft rows
+        // are then primal feasible from the first iterate on, whatever the warm start violates
+        s.sL[k][r] = std::max(thr0, R[r].lb - cz + thr0);
+        s.sU[k][r] = std::max(thr0, cz - R[r].ub + thr0);
+        s.lamSL[k][r] = cf.qp_mu0 / s.sL[k][r];
+        s.lamSU[k][r] = cf.qp_mu0 / s.sU[k][r];
         nineq += 2;
       }
       s.tL[k][r] = std::max(cz + s.sL[k][r] - R[r].lb, thr0);

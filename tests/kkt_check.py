@@ -56,7 +56,8 @@ def h_rows(cfg, hc, params, N):
         C[:, :, 4, 2 + ix] = hc[:, :, 8 + j]
     e[:, :, 4] = hc[:, :, 12]
     ub = np.array([0.0, 0.0, cfg.T_dot_max, cfg.delta_dot_max, cfg.a_lat_max]); lb = np.array([-1e3, -1e3, -ub[2], -ub[3], -ub[4]])
-    act = np.ones((N + 1, 5), bool); act[N, 2:] = False
+    # rows 2, 3 (T_dot, delta_dot) are the linear rows 2, 3 of python/mpc.py:91-99, kept once in that form
+    act = np.ones((N + 1, 5), bool); act[:, 2:4] = False; act[N, 4] = False
     return C, e, lb, ub, act
 
 

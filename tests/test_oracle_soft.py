@@ -91,9 +91,11 @@ def test_kkt_certificate_with_slacks(built, fsds, dn):
     x0, xs, us = _nl_problem(fsds, 30, dn)
     q = o.qp_debug(x0, xs, us)
     assert q["status"] == 0
-    assert list(q["nrows"]) == [9] + [13] * (N - 1) + [6]
-    assert q["soft"][0, :9].tolist() == [0, 0, 0, 0, 1, 1, 1, 1, 1]
-    assert q["soft"][5, :13].tolist() == [0] * 6 + [1] * 7 and q["soft"][N, :6].tolist() == [0, 0, 1, 1, 1, 1]
+    # rows: python/mpc.py's (4 at stage 0, 8 on the path, 4 at the end) + h0, h1 (track) and h4 (a_lat); T_dot and
+    # delta_dot of h are the two linear rows of mpc.py:91-99, kept once
+    assert list(q["nrows"]) == [7] + [11] * (N - 1) + [6]
+    assert q["soft"][0, :7].tolist() == [0, 0, 0, 0, 1, 1, 1]
+    assert q["soft"][5, :11].tolist() == [0] * 6 + [1] * 5 and q["soft"][N, :6].tolist() == [0, 0, 1, 1, 1, 1]
     np.testing.assert_allclose(q["zZ"][3], [cfg.dt * 100.0, cfg.dt * 100.0]); np.testing.assert_allclose(q["zZ"][N], [100.0, 100.0])
     z, pi = q["z"], q["pi"]
     scale_g = 1 + np.abs(q["g"]).max()
@@ -224,15 +226,13 @@ def _slots_from_qp_debug(q, nl):
     for k in range(N + 1):
         nst = 4 if k in (0, N) else 8
         for r in range(q["nrows"][k]):
-            slot = r if r < nst else 8 + (r - nst)
+            slot = r if r < nst else 8 + (0, 1, 4)[r - nst]
             for f in out:
                 out[f][0, k, slot] = q[f][k, r]
             if r >= nst:
-                i, Cr = r - nst, q["C"][k, r]
+                i, Cr = (0, 1, 4)[r - nst], q["C"][k, r]
                 if i == 0: hc[0, k, 0:3] = Cr[2:5]; hc[0, k, 3] = q["e"][k, r]
                 if i == 1: hc[0, k, 4:7] = Cr[2:5]; hc[0, k, 7] = q["e"][k, r]
-                if i == 2: hc[0, k, 13] = q["e"][k, r]
-                if i == 3: hc[0, k, 14] = q["e"][k, r]
                 if i == 4: hc[0, k, 8:12] = Cr[[2 + 3, 2 + 4, 2 + 6, 2 + 7]]; hc[0, k, 12] = q["e"][k, r]
     return out, hc
 
