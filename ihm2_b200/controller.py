@@ -233,3 +233,69 @@ class IHM2Controller(Controller):
         self.solver.shift_iterate()
         u0, status = self.solver.solve(x.contiguous())
         return (u0, status) if return_status else u0
+
+
+class BatchedOcpSolver:
+    """The `AcadosOcpSolver` verbs the reference uses on its solver object (new_python/controller.py:320-405,
+    dpc/main.py:226-302) -- `set`, `cost_set`, `constraints_set`, `solve`, `get` -- on whole-batch tensors, for code that
+    pokes `controller.solver` directly.  What acados lets the caller change per call and this engine fixes at creation
+    (weights W, parameters p, yref -- it follows s_0 and s_target) is checked against the engine's configuration instead
+    of being silently ignored.  Stage values are staged on the device and pushed with the next `solve()`."""
+
+    def __init__(self, engine: Engine):
+        self.engine = engine
+        self.B, self.N = engine.B, engine.N
+        self._x, self._u = engine.get_iterate()
+        self._x0 = self._x[:, 0, :].clone()
+        self._dirty = False
+        self.status = None
+
+    def _t(self, v, n):
+        v = torch.as_tensor(v, dtype=torch.float64, device=self._x.device)
+        return v.expand(self.B, n) if v.dim() == 1 else v
+
+    def set(self, stage: int, field: str, value):
+        if field == "x":
+            self._x[:, stage, :] = self._t(value, _abi.NX); self._dirty = True
+        elif field == "u":
+            self._u[:, stage, :] = self._t(value, _abi.NU); self._dirty = True
+        elif field in ("lbx", "ubx"):
+            self.constraints_set(stage, field, value)
+        elif field == "yref":
+            # controller.py:373-385: yref_k = (s_0 + s_target k / N, 0, ...): the engine forms it from x_0 itself
+            v = torch.as_tensor(value, dtype=torch.float64, device=self._x.device)
+            v = v.expand(self.B, v.shape[-1]) if v.dim() == 1 else v
+            want = self._x0[:, 0] + self.engine.cfg.s_target * stage / self.N
+            if not torch.allclose(v[:, 0], want, atol=1e-9) or bool((v[:, 1:] != 0).any()):
+                raise ValueError("yref differs from (s_0 + s_target k / N, 0, ...), the reference trajectory this engine is built for")
+        elif field == "p":
+            pass   # the track tables are given at construction (ihm2b_set_tracks); per-stage copies are redundant
+        else:
+            raise KeyError(f"BatchedOcpSolver.set: unsupported field {field!r}")
+
+    def cost_set(self, stage: int, field: str, value):
+        if field != "W":
+            raise KeyError(f"BatchedOcpSolver.cost_set: unsupported field {field!r}")
+        W = np.asarray(value.cpu() if torch.is_tensor(value) else value, dtype=np.float64)
+        want = np.array(self.engine.cfg.W_e[:] if stage == self.N else self.engine.cfg.W[:])
+        if W.shape != (len(want), len(want)) or not np.allclose(W, np.diag(want)):
+            raise ValueError("W differs from the weights the engine was created with (ihm2b_config.W / W_e)")
+
+    def constraints_set(self, stage: int, field: str, value):
+        if stage != 0 or field not in ("lbx", "ubx"):
+            raise KeyError("BatchedOcpSolver.constraints_set: only the x_0 embedding (stage 0, lbx / ubx) changes per call")
+        self._x0 = self._t(value, _abi.NX).contiguous().clone()   # controller.py:370-371: lbx_0 = ubx_0 = measured state
+
+    def solve(self):
+        if self._dirty:
+            self.engine.set_iterate(self._x, self._u); self._dirty = False
+        _, self.status = self.engine.solve(self._x0)
+        self._x, self._u = self.engine.get_iterate()
+        return self.status
+
+    def get(self, stage: int, field: str):
+        if field == "x":
+            return self._x[:, stage, :]
+        if field == "u":
+            return self._u[:, stage, :]
+        raise KeyError(f"BatchedOcpSolver.get: unsupported field {field!r}")

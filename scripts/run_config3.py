@@ -11,9 +11,9 @@ stops at its first solver failure (status not in {0, 2}), as the reference loop 
 reference's (python/main.py:561-570).
 
 Set-ups:
-  lapping  soft constraints h(x, u) + slacks, acados' tolerance of a QP at its iteration limit
-           (mpc_control_node.cpp:190-197), straight slip-angle assignment in the fdyn6 plant (P_CROSS = 0)
-  literal  the same controller on the literal plant (crosswise slip angles of python/models.py:543-546)
+  literal  soft constraints h(x, u) + slacks, acados' tolerance of a QP at its iteration limit
+           (mpc_control_node.cpp:190-197), literal fdyn6 plant (crosswise slip angles of python/models.py:543-546)
+  lapping  the same controller, straight slip-angle assignment in the plant (P_CROSS = 0)
   hard     the new_python OCP (hard bounds, no h rows) on the literal plant: the round-1 set-up
 """
 import json, os, sys

@@ -447,3 +447,32 @@ def test_history_scheduling_changes_nothing_but_the_order(torch_cuda, skidpad):
         eng.close()
     for a, b in zip(*outs):
         np.testing.assert_array_equal(a, b)
+
+
+def test_solver_object_shim_drives_the_engine_like_acados(torch_cuda, fsds):
+    """Reference code that pokes `controller.solver` (new_python/controller.py:368-405: constraints_set x_0, set yref,
+    shifted set x / u, solve, get) gets the same control as `compute_control`; what the engine fixes at creation is
+    checked, not ignored."""
+    from ihm2_b200.controller import BatchedOcpSolver, IHM2Controller
+    B, N = 4, 40
+    x0 = np.zeros((B, 8)); x0[:, 0] = -6.0 + 0.1 * np.arange(B); x0[:, 3] = 1.0
+    ca = IHM2Controller(fsds.s_ref, fsds.kappa_ref, batch=B)
+    cb = IHM2Controller(fsds.s_ref, fsds.kappa_ref, batch=B)
+    ua, sa = ca.compute_control(torch_cuda.as_tensor(x0, device="cuda"), return_status=True)
+    sv = BatchedOcpSolver(cb.solver)
+    xd = torch_cuda.as_tensor(x0, device="cuda")
+    sv.constraints_set(0, "lbx", xd); sv.constraints_set(0, "ubx", xd)
+    for i in range(N):
+        yref = np.zeros((B, 12)); yref[:, 0] = x0[:, 0] + cb.s_target * i / N
+        sv.set(i, "yref", yref)
+    xp, up = cb.x_pred.clone(), cb.u_pred.clone()
+    for j in range(N - 1):                       # controller.py:388-393
+        sv.set(j, "x", xp[:, j + 1]); sv.set(j, "u", up[:, j + 1])
+    sv.set(N - 1, "x", xp[:, N]); sv.set(N - 1, "u", np.zeros(2)); sv.set(N, "x", xp[:, N])
+    status = sv.solve()
+    assert (status.cpu().numpy() == sa.cpu().numpy()).all() and (status.cpu().numpy() == 0).all()
+    np.testing.assert_array_equal(sv.get(0, "u").cpu().numpy(), ua.cpu().numpy())
+    with pytest.raises(ValueError):
+        sv.cost_set(3, "W", np.eye(12))
+    with pytest.raises(ValueError):
+        sv.set(5, "yref", np.ones((B, 12)))

@@ -95,3 +95,42 @@ def test_two_rank_gloo_shard_and_gather_equals_single_process():
     x0, _, _ = perturbed_batch(np.arange(8.0), np.zeros((41, 8)), np.zeros((40, 2)), total, seed=0)
     np.testing.assert_array_equal(gu, x0[:, :2] * 2.0)     # independent of the number of ranks
     np.testing.assert_array_equal(gs, [0] * 6 + [1] * 5)
+
+
+def test_frenet_to_cartesian_follows_the_track_class():
+    """tracks.cpp:290-306: reference point on the linear splines + n along the normal; inverse of the projection's (s, n)."""
+    import torch
+    from ihm2_b200.projection import frenet_to_cartesian
+    from ihm2_b200.track import load_packaged_track
+    mp = load_packaged_track("fsds_default")
+    tabs = [torch.tensor(getattr(mp, f)) for f in ("s_ref", "X_ref", "Y_ref", "phi_ref")]
+    g = torch.Generator().manual_seed(0)
+    s = torch.rand(200, generator=g, dtype=torch.float64) * mp.lap_length
+    n = (torch.rand(200, generator=g, dtype=torch.float64) - 0.5) * 3
+    X, Y = frenet_to_cartesian(*tabs, s, n)
+    for i in range(0, 200, 17):      # scalar restatement of Track::interp + the normal
+        k = int(np.searchsorted(mp.s_ref, float(s[i]), side="right")) - 1
+        f = lambda t: t[k] + (t[k + 1] - t[k]) / (mp.s_ref[k + 1] - mp.s_ref[k]) * (float(s[i]) - mp.s_ref[k])   # noqa: E731
+        Xr, Yr, pr = f(mp.X_ref), f(mp.Y_ref), f(mp.phi_ref)
+        assert abs(float(X[i]) - (Xr - float(n[i]) * np.sin(pr))) < 1e-12 and abs(float(Y[i]) - (Yr + float(n[i]) * np.cos(pr))) < 1e-12
+    # on a table point with n = 0 it is the table point
+    X0, Y0 = frenet_to_cartesian(*tabs, torch.tensor(mp.s_ref[600:603]), torch.zeros(3, dtype=torch.float64))
+    np.testing.assert_allclose(X0.numpy(), mp.X_ref[600:603], atol=1e-12); np.testing.assert_allclose(Y0.numpy(), mp.Y_ref[600:603], atol=1e-12)
+
+
+def test_start_line_lap_timer_like_the_sim_node():
+    """sim_node.cpp:46-51, 261-274: the first crossing starts the clock, later crossings with v_x > 0 give lap times."""
+    import torch
+    from ihm2_b200.projection import StartLineTimer
+    tm = StartLineTimer([0.0, -2.0], [0.0, 2.0], batch=3)
+    v = torch.tensor([5.0, 5.0, -1.0], dtype=torch.float64)
+    circle = lambda th: torch.stack([10 * torch.sin(th), 10 - 10 * torch.cos(th)], 1)    # noqa: E731  passes (0, 0) heading +x
+    done = []
+    for step in range(0, 260):
+        t = 0.05 * step
+        th = torch.tensor([0.05 * step - 0.3, 0.1 * step - 0.3, 0.05 * step - 0.3], dtype=torch.float64)
+        done.append(tm.update(circle(th), v, t))
+    laps = tm.laps.tolist()
+    assert laps[2] == 0 and np.isnan(float(tm.last_lap_time[2]))          # v_x <= 0 never counts
+    assert laps[0] == 2 and abs(float(tm.last_lap_time[0]) - 2 * np.pi / 0.05 * 0.05) <= 0.05 + 1e-9
+    assert laps[1] == 4 and abs(float(tm.best_lap_time[1]) - 2 * np.pi / 0.1 * 0.05) <= 0.05 + 1e-9
