@@ -9,7 +9,8 @@ import ctypes as C
 
 import numpy as np
 
-NX, NU, NY, NYN, NP = 8, 2, 12, 8, 20
+NX, NU, NY, NYN, NP = 8, 2, 12, 8, 28
+NX10, NU10 = 15, 5   # dyn10 plant
 
 # enum ihm2b_integrator / nlp_solver / globalization / sim_model / status
 ERK4, IRK_GL4 = 0, 1
@@ -20,7 +21,7 @@ SIM_KIN6C, SIM_DYN6C, SIM_KIN6C_DYN6C = 3, 4, 5  # Cartesian plants of the ROS s
 STATUS_SUCCESS, STATUS_FAILURE, STATUS_MAXITER, STATUS_MINSTEP, STATUS_QP_FAILURE = 0, 1, 2, 3, 4
 
 (P_M, P_IZ, P_LR, P_LF, P_CM0, P_CR0, P_CR1, P_CR2, P_TT, P_TD, P_ZCG, P_TRACKW, P_CDOWN,
- P_KTV, P_BA, P_CA, P_DA, P_EA, P_G, P_CROSS) = range(NP)
+ P_KTV, P_BA, P_CA, P_DA, P_EA, P_G, P_CROSS, P_RW, P_IW, P_KD, P_KS, P_BS, P_CS, P_DS, P_ES) = range(NP)
 
 
 class Config(C.Structure):
@@ -94,6 +95,13 @@ def default_params() -> np.ndarray:
     p[P_ZCG], p[P_TRACKW], p[P_CDOWN], p[P_KTV] = 0.295, 1.24, 3.96864, 300.0
     p[P_BA], p[P_CA], p[P_DA], p[P_EA] = Ba, Ca, Da, Ea
     p[P_G], p[P_CROSS] = g, 1.0
+    # dyn10 plant only: wheel parameters and the longitudinal Pacejka coefficients (constants.py:69-74, 85-101)
+    b1s, b2s, b3s, c1s, d1s, d2s, e1s, e2s, e3s = -6.75e-6, 1.35e-1, 1.2e-3, 1.86, 1.12e-4, 1.57, -5.38e-6, 1.11e-2, -4.26
+    BCDs = (b1s * static_weight**2 + b2s * static_weight) * np.exp(-b3s * static_weight)
+    Cs, Ds = c1s, d1s * static_weight + d2s
+    Es = e1s * static_weight**2 + e2s * static_weight + e3s
+    p[P_RW], p[P_IW], p[P_KD], p[P_KS] = 0.20809, 0.3, 0.17, 15.0
+    p[P_BS], p[P_CS], p[P_DS], p[P_ES] = BCDs / (Cs * Ds), Cs, Ds, Es
     return p
 
 

@@ -36,6 +36,8 @@ void launch_merit_trial(const KCfg& cf, const Work& w, const LineSearch& ls, con
                         int32_t* status, cudaStream_t stream);
 void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x,
                      const double* u, double* xn, int32_t* model, int32_t* order_scratch, cudaStream_t stream);
+void launch_sim_step_dyn10(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u, double* xn,
+                           cudaStream_t stream);
 void launch_closed_loop_post(int B, int step, double dt, const int32_t* track, const double* lap, const int32_t* status,
                              const double* u0, const double* xn, const double* stats, double* xs, double* xlog,
                              double* ulog, int32_t* done, int32_t* fail, int32_t* active_mask, int32_t* lap_state,
@@ -591,6 +593,17 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double
   if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
   if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6C_DYN6C) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
   launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, h->sim_order_dev, static_cast<cudaStream_t>(stream));
+  h->launches++;
+  CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+int ihm2b_sim_step_dyn10_dev(ihm2b_handle* h, const double* x, const double* u, double* xn, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
+  if (h->cfg.sim_steps < 1) return fail(IHM2B_EINVAL, "sim_steps %d < 1", h->cfg.sim_steps);
+  launch_sim_step_dyn10(h->cfg, h->k, h->w, x, u, xn, static_cast<cudaStream_t>(stream));
   h->launches++;
   CU(cudaGetLastError());
   return IHM2B_OK;

@@ -226,6 +226,205 @@ __global__ void __launch_bounds__(128) sim_step_kernel(const SimCfg sc, const Wo
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// dyn10 plant: `fdyn10_model`, python/models.py:609-801.  x[15] = (s, n, psi, v_x, v_y, r, omega_FL,
+// omega_FR, omega_RL, omega_RR, tau_FL .. tau_RR, delta), u[5] = (u_tau_FL .. u_tau_RR, u_delta).
+// Rows 0..9 of the right-hand side at a point whose torques / steering angle are given (rows 10..14 are first-order
+// lags, closed form).  As for fdyn6 every tyre force is proportional to its wheel's vertical load, which is affine in
+// (a_x, a_y): one 2 x 2 solve.  dwdw (optional): d omega_w' / d omega_w, the stiff diagonal of the wheel-speed rows.
+// ---------------------------------------------------------------------------------------
+__device__ void fdyn10_rhs(const double* __restrict__ x, const double* __restrict__ tau, const double dl,
+                           const double* __restrict__ p, const TrackView& tr, double* __restrict__ f, double* __restrict__ dwdw) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5];
+  const double m = p[IHM2B_P_M], g = p[IHM2B_P_G], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF], wb = lR + lF, tw = p[IHM2B_P_TRACKW];
+  const double Fdown = 0.5 * p[IHM2B_P_CDOWN] * vx * vx;
+  const double stat = 0.5 * m * g * lF / wb;
+  const double cl = 0.5 * m * p[IHM2B_P_ZCG] / wb, ct = 0.5 * m * p[IHM2B_P_ZCG] / tw;
+  double sd, cd;
+  sincos(dl, &sd, &cd);
+  const double vxL = vx - 0.5 * tw * r, vxR = vx + 0.5 * tw * r, vyF = vy + lF * r, vlatR = vy - lR * r;
+  const double vlon[4] = {cd * vxL + sd * vyF, cd * vxR + sd * vyF, vxL, vxR};
+  const double vlat[4] = {-sd * vxL + cd * vyF, -sd * vxR + cd * vyF, vlatR, vlatR};
+  double mu_lat[4], mu_lon[4], dmu[4];
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    const double va = smooth_abs_nonzero(vlon[w]);
+    mu_lat[w] = lat_pacejka(p, atan2(vlat[w], va));
+    const double iva = p[IHM2B_P_RW] / va;
+    const double Bs = p[IHM2B_P_BS] * (x[6 + w] * iva - 1.0);         // B_s * slip ratio, models.py:723-726
+    const double q = 1.0 / (1.0 + Bs * Bs);
+    const double arg = Bs - p[IHM2B_P_ES] * (Bs - atan(Bs));
+    double sa, ca;
+    sincos(p[IHM2B_P_CS] * atan(arg), &sa, &ca);
+    mu_lon[w] = -p[IHM2B_P_DS] * sa;                                  // F_lon = -F_z lon_pacejka(s), :728-732
+    // d mu_lon / d omega
+    dmu[w] = -p[IHM2B_P_DS] * p[IHM2B_P_CS] * ca / (1.0 + arg * arg) * (1.0 - p[IHM2B_P_ES] * (1.0 - q)) * p[IHM2B_P_BS] * iva;
+  }
+  const double Fdrag = -(p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx) * tanh(1000.0 * vx);
+  double fx[4], fy[4], mz[4];
+  fx[0] = mu_lon[0] * cd - mu_lat[0] * sd; fy[0] = mu_lon[0] * sd + mu_lat[0] * cd;
+  fx[1] = mu_lon[1] * cd - mu_lat[1] * sd; fy[1] = mu_lon[1] * sd + mu_lat[1] * cd;
+  fx[2] = mu_lon[2]; fy[2] = mu_lat[2]; fx[3] = mu_lon[3]; fy[3] = mu_lat[3];
+  mz[0] = -0.5 * tw * fx[0] + lF * fy[0]; mz[1] = 0.5 * tw * fx[1] + lF * fy[1];
+  mz[2] = -0.5 * tw * fx[2] - lR * fy[2]; mz[3] = 0.5 * tw * fx[3] - lR * fy[3];
+  const double z0 = -(stat + 0.25 * Fdown);
+  const double cx[4] = {cl, cl, -cl, -cl}, cy[4] = {-ct, ct, -ct, ct};
+  double Fx0 = Fdrag, Fy0 = 0.0, gxx = 0.0, gxy = 0.0, gyx = 0.0, gyy = 0.0;
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    Fx0 = fma(z0, fx[w], Fx0); Fy0 = fma(z0, fy[w], Fy0);
+    gxx = fma(cx[w], fx[w], gxx); gxy = fma(cy[w], fx[w], gxy); gyx = fma(cx[w], fy[w], gyx); gyy = fma(cy[w], fy[w], gyy);
+  }
+  const double a11 = m - gxx, a12 = -gxy, a21 = -gyx, a22 = m - gyy;
+  const double idet = 1.0 / (a11 * a22 - a12 * a21);
+  const double ax = (Fx0 * a22 - a12 * Fy0) * idet, ay = (a11 * Fy0 - a21 * Fx0) * idet;
+  double Mz = 0.0;
+  const double iIw = 1.0 / p[IHM2B_P_IW];
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    const double Fz = z0 + cx[w] * ax + cy[w] * ay;
+    Mz = fma(Fz, mz[w], Mz);
+    f[6 + w] = (tau[w] - (p[IHM2B_P_KD] * x[6 + w] + p[IHM2B_P_KS] + p[IHM2B_P_RW] * Fz * mu_lon[w])) * iIw;   // :781-784
+    if (dwdw) dwdw[w] = -(p[IHM2B_P_KD] + p[IHM2B_P_RW] * Fz * dmu[w]) * iIw;
+  }
+  double kap, dkap, sp, cp;
+  kappa_lookup(tr, x[0], kap, dkap);
+  sincos(psi, &sp, &cp);
+  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+  f[0] = sdot; f[1] = vx * sp + vy * cp; f[2] = r - kap * sdot;
+  f[3] = ax + vy * r; f[4] = ay - vx * r; f[5] = Mz / p[IHM2B_P_IZ];
+}
+
+// row i of (I - z A)^-1 for the 4-stage tableau A: the stage coupling of a scalar stiff mode z = h lambda
+__device__ __forceinline__ void inv_row4(const double z, const double* __restrict__ A, const int i, double* __restrict__ y) {
+  double M[4][5];   // (I - z A)' y = e_i
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) M[r][c] = ((r == c) ? 1.0 : 0.0) - z * A[c * 4 + r];
+    M[r][4] = (r == i) ? 1.0 : 0.0;
+  }
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const double ip = 1.0 / M[c][c];
+#pragma unroll
+    for (int r = c + 1; r < 4; r++) {
+      const double l = M[r][c] * ip;
+#pragma unroll
+      for (int j = c + 1; j < 5; j++) M[r][j] = fma(-l, M[c][j], M[r][j]);
+    }
+  }
+#pragma unroll
+  for (int r = 3; r >= 0; r--) {
+    double v = M[r][4];
+#pragma unroll
+    for (int c = r + 1; c < 4; c++) v = fma(-M[r][c], y[c], v);
+    y[r] = v / M[r][r];
+  }
+}
+
+// One plant step of the dyn10 model: 4 lanes per car (lane i = collocation stage i), Radau IIA, n_sub sub-steps.  The
+// five actuator lags are closed form; the body rows are solved by fixed-point iteration like the other plants; the four
+// wheel-speed rows are stiff through the tyre slip (|h d omega' / d omega| reaches 1 at h = 0.5 ms below ~3 m/s), so
+// their update goes through the stage coupling (I - h lambda_w A)^-1 of each wheel's own stiff mode, lambda_w taken at
+// the start of the sub-step (a simplified Newton iteration on the diagonal; converges to the same collocation point).
+__global__ void __launch_bounds__(128) sim_step_dyn10_kernel(const SimCfg sc, const Work w, const double* __restrict__ xin,
+                                                              const double* __restrict__ uin, double* __restrict__ xout) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = gid >> 2, i = gid & 3;
+  if (b >= sc.B) return;
+  const unsigned gm = 0xFu << (threadIdx.x & 28);
+  const int t = w.track[b];
+  TrackView tr{sc.n_grid, w.s_ref + (size_t)t * sc.n_grid, w.kappa_ref + (size_t)t * sc.n_grid};
+  double p[NP], x[IHM2B_NX10], u[IHM2B_NU10];
+  for (int j = 0; j < NP; j++) p[j] = __ldg(w.params + (size_t)b * NP + j);
+  for (int j = 0; j < IHM2B_NX10; j++) x[j] = xin[(size_t)b * IHM2B_NX10 + j];
+  for (int j = 0; j < IHM2B_NU10; j++) u[j] = uin[(size_t)b * IHM2B_NU10 + j];
+  double wT[4], wD[4];
+  for (int j = 0; j < 4; j++) { wT[j] = __ldg(w.actw_sim + (size_t)b * 8 + j); wD[j] = __ldg(w.actw_sim + (size_t)b * 8 + 4 + j); }
+  const double h = sc.h, itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
+  double Ai[4], bw[4];
+  for (int j = 0; j < 4; j++) { Ai[j] = h * sc.A[i * 4 + j]; bw[j] = h * sc.b[j]; }
+  double K[10], Kp[10];
+  bool ok = true, first = true, second = true;
+#pragma unroll 1
+  for (int sub = 0; sub < sc.n_sub; sub++) {
+    // actuator lags in closed form
+    double tau_i[4], dtau[4], dl_i = x[14], ddl = 0.0;
+    const double cD = (u[4] - x[14]) * itD;
+    double sA = 0.0, sAd = 0.0, sB = 0.0, sBd = 0.0;
+    for (int j = 0; j < 4; j++) { sA = fma(Ai[j], wT[j], sA); sAd = fma(Ai[j], wD[j], sAd); sB = fma(bw[j], wT[j], sB); sBd = fma(bw[j], wD[j], sBd); }
+    for (int q = 0; q < 4; q++) { const double cT = (u[q] - x[10 + q]) * itT; tau_i[q] = fma(sA, cT, x[10 + q]); dtau[q] = sB * cT; }
+    dl_i = fma(sAd, cD, x[14]); ddl = sBd * cD;
+    // stiff diagonal of the wheel-speed rows at the start of the sub-step, this lane's row of each wheel's stage coupling
+    double f[10], lam[4], inv[4][4];
+    fdyn10_rhs(x, x + 10, x[14], p, tr, f, lam);
+    for (int q = 0; q < 4; q++) inv_row4(h * lam[q], sc.A, i, inv[q]);
+    if (first) {
+      for (int r = 0; r < 10; r++) { K[r] = f[r]; Kp[r] = f[r]; }
+      first = false;
+    } else {
+      for (int r = 0; r < 10; r++) {
+        const double kc = K[r];
+        if (!second) K[r] = 2.0 * kc - Kp[r];
+        Kp[r] = kc;
+      }
+      second = false;
+    }
+    int it = 0;
+    double dprev = 1e300;
+#pragma unroll 1
+    for (;; it++) {
+      double xs[10];
+      for (int r = 0; r < 10; r++) {
+        double v = x[r];
+#pragma unroll
+        for (int j = 0; j < 4; j++) v = fma(Ai[j], __shfl_sync(gm, K[r], j, 4), v);
+        xs[r] = v;
+      }
+      fdyn10_rhs(xs, tau_i, dl_i, p, tr, f, nullptr);
+      double dmax = 0.0, kmax = 0.0;
+      for (int r = 0; r < 6; r++) { dmax = fmax(dmax, fabs(f[r] - K[r])); kmax = fmax(kmax, fabs(f[r])); K[r] = f[r]; }
+      for (int q = 0; q < 4; q++) {
+        const double d = f[6 + q] - K[6 + q];
+        double upd = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) upd = fma(inv[q][j], __shfl_sync(gm, d, j, 4), upd);
+        dmax = fmax(dmax, fabs(d)); kmax = fmax(kmax, fabs(f[6 + q]));
+        K[6 + q] += upd;
+      }
+      if (!(dmax == dmax)) dmax = 1e300;
+      dmax = fmax(dmax, __shfl_xor_sync(gm, dmax, 1)); dmax = fmax(dmax, __shfl_xor_sync(gm, dmax, 2));
+      kmax = fmax(kmax, __shfl_xor_sync(gm, kmax, 1)); kmax = fmax(kmax, __shfl_xor_sync(gm, kmax, 2));
+      if (dmax <= FP_TOL * (1.0 + kmax) || (it >= 3 && dmax >= 0.5 * dprev && dmax <= 1e-10 * (1.0 + kmax))) break;
+      dprev = dmax;
+      if (it >= MAX_FP || dmax >= 1e300) { ok = false; break; }
+    }
+    for (int r = 0; r < 10; r++) {
+      double v = x[r];
+#pragma unroll
+      for (int j = 0; j < 4; j++) v = fma(bw[j], __shfl_sync(gm, K[r], j, 4), v);
+      x[r] = v;
+    }
+    for (int q = 0; q < 4; q++) x[10 + q] += dtau[q];
+    x[14] += ddl;
+    if (!ok) break;
+  }
+  if (i == 0)
+    for (int r = 0; r < IHM2B_NX10; r++) xout[(size_t)b * IHM2B_NX10 + r] = ok ? x[r] : nan("");
+}
+
+void launch_sim_step_dyn10(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u, double* xn,
+                           cudaStream_t stream) {
+  SimCfg sc;
+  sc.B = cf.B; sc.n_grid = cf.n_grid; sc.model = 0; sc.n_sub = cfg.sim_steps;
+  sc.h = cfg.dt / cfg.sim_steps; sc.sw = 0.0;
+  for (int i = 0; i < 16; i++) sc.A[i] = cfg.sim_A[i];
+  for (int i = 0; i < 4; i++) sc.b[i] = cfg.sim_b[i];
+  const int threads = 128, total = cf.B * 4;
+  sim_step_dyn10_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn);
+}
+
 // With a model switch the eight instances of a warp would mix the kinematic and the (several times longer) dynamic
 // right-hand side and every warp would run both; this puts the instances that take the kinematic model first and the
 // others last (order within a class is whatever the atomics give: results do not depend on it).

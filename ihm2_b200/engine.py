@@ -23,7 +23,7 @@ EXPORTS = (
     "ihm2b_create", "ihm2b_destroy", "ihm2b_last_error", "ihm2b_version", "ihm2b_set_tracks",
     "ihm2b_set_track_index", "ihm2b_set_params", "ihm2b_set_iterate_dev", "ihm2b_get_iterate_dev", "ihm2b_get_iterate_host",
     "ihm2b_reset_iterate", "ihm2b_shift_iterate", "ihm2b_solve_dev", "ihm2b_compute_control_host",
-    "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_closed_loop_dev",
+    "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_sim_step_dyn10_dev", "ihm2b_closed_loop_dev",
     "ihm2b_get_multipliers_dev", "ihm2b_get_slacks_dev", "ihm2b_get_h_rows_dev",
     "ihm2b_dpc_rollout_grad_dev", "ihm2b_dpc_rollout_grad_f32_dev", "ihm2b_project_dev", "ihm2b_launch_count",
     "ihm2b_profile_enable", "ihm2b_profile_read", "ihm2b_debug_trace", "ihm2b_measure_fp64_tflops",
@@ -218,6 +218,13 @@ class Engine:
         self._check(self.lib.ihm2b_sim_step_dev(self._h, _dptr(x.contiguous()), _dptr(u.contiguous()),
                                                 _dptr(xn), _dptr(model), _stream()))
         return xn, model
+
+    def sim_step_dyn10(self, x10: torch.Tensor, u5: torch.Tensor):
+        """dyn10 plant: x10 [B,15], u5 [B,5] -> x_next [B,15] (NaN rows where the integrator failed)."""
+        assert x10.shape == (self.B, _abi.NX10) and u5.shape == (self.B, _abi.NU10)
+        xn = self._new(self.B, _abi.NX10)
+        self._check(self.lib.ihm2b_sim_step_dyn10_dev(self._h, _dptr(x10.contiguous()), _dptr(u5.contiguous()), _dptr(xn), _stream()))
+        return xn
 
     def closed_loop(self, x: torch.Tensor, n_steps: int, log: bool = False):
         """n_steps of shift -> solve -> plant step on the device.  x [B,8] is updated in place."""

@@ -32,7 +32,9 @@ extern "C" {
 #define IHM2B_NU 2   /* IHM2_FKIN6_NU */
 #define IHM2B_NY 12  /* IHM2_FKIN6_NY  (python/mpc.py:48) */
 #define IHM2B_NYN 8  /* IHM2_FKIN6_NYN (python/mpc.py:62) */
-#define IHM2B_NP 20  /* per-instance vehicle parameters, see ihm2b_param_index */
+#define IHM2B_NP 28  /* per-instance vehicle parameters, see ihm2b_param_index */
+#define IHM2B_NX10 15 /* states of the dyn10 plant (python/models.py:609-801) */
+#define IHM2B_NU10 5  /* its controls: four wheel torque commands and the steering command */
 
 enum ihm2b_error { IHM2B_OK = 0, IHM2B_EINVAL = 1, IHM2B_ECUDA = 2, IHM2B_ENOMEM = 3 };
 enum ihm2b_integrator { IHM2B_ERK4 = 0, IHM2B_IRK_GL4 = 1 };
@@ -52,7 +54,10 @@ enum ihm2b_param_index {
   IHM2B_P_M = 0, IHM2B_P_IZ, IHM2B_P_LR, IHM2B_P_LF, IHM2B_P_CM0, IHM2B_P_CR0, IHM2B_P_CR1,
   IHM2B_P_CR2, IHM2B_P_TT, IHM2B_P_TD, IHM2B_P_ZCG, IHM2B_P_TRACKW, IHM2B_P_CDOWN,
   IHM2B_P_KTV, IHM2B_P_BA, IHM2B_P_CA, IHM2B_P_DA, IHM2B_P_EA, IHM2B_P_G,
-  IHM2B_P_CROSS /* 1: literal slip-angle cross assignment of python/models.py:543-546 */
+  IHM2B_P_CROSS, /* 1: literal slip-angle cross assignment of python/models.py:543-546 */
+  /* dyn10 plant only (python/constants.py:85-101): wheel radius / inertia, dynamic / static friction of the wheel
+   * bearing, longitudinal Pacejka coefficients */
+  IHM2B_P_RW, IHM2B_P_IW, IHM2B_P_KD, IHM2B_P_KS, IHM2B_P_BS, IHM2B_P_CS, IHM2B_P_DS, IHM2B_P_ES
 };
 
 /* Everything `IHM2Controller.__init__` fixes at construction
@@ -198,6 +203,15 @@ int ihm2b_get_h_rows_dev(ihm2b_handle* h, double* hc_dev, void* stream);
  * x_dev [B][8], u_dev [B][2] -> xnext_dev [B][8]; model_dev (optional) gets the model used. */
 int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev,
                        double* xnext_dev, int32_t* model_dev, void* stream);
+
+/* The dyn10 plant (`fdyn10_model`, python/models.py:609-801): Frenet pose, body velocities, four wheel
+ * speeds with slip-ratio (longitudinal Pacejka) and slip-angle (lateral Pacejka) tyre forces on load-transfer vertical
+ * loads, four torque lags and the steering lag.  x10_dev [B][15] = (s, n, psi, v_x, v_y, r, omega_FL, omega_FR,
+ * omega_RL, omega_RR, tau_FL, tau_FR, tau_RL, tau_RR, delta); u5_dev [B][5] = (u_tau_FL, u_tau_FR, u_tau_RL, u_tau_RR,
+ * u_delta) (python/main.py:490-500 feeds 0.25 u_T to each wheel).  Same integrator as the other plants: Radau IIA,
+ * 4 stages, cfg.sim_steps sub-steps over cfg.dt.  NaN rows where the integrator failed. */
+int ihm2b_sim_step_dyn10_dev(ihm2b_handle* h, const double* x10_dev, const double* u5_dev, double* xnext10_dev,
+                             void* stream);
 
 /* ---- closed loop ---------------------------------------------------------------------
  * python/main.py:448-517 with the NMPC call enabled: n_steps iterations of

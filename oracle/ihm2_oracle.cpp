@@ -53,7 +53,8 @@ constexpr int NX = 8, NU = 2, NZ = 10;
 // ---------------------------------------------------------------------------------------
 enum {
   P_M = 0, P_IZ, P_LR, P_LF, P_CM0, P_CR0, P_CR1, P_CR2, P_TT, P_TD,
-  P_ZCG, P_TRACKW, P_CDOWN, P_KTV, P_BA, P_CA, P_DA, P_EA, P_G, P_CROSS, NP
+  P_ZCG, P_TRACKW, P_CDOWN, P_KTV, P_BA, P_CA, P_DA, P_EA, P_G, P_CROSS,
+  P_RW, P_IW, P_KD, P_KS, P_BS, P_CS, P_DS, P_ES, NP
 };
 
 struct Track {
@@ -377,6 +378,125 @@ void lu_solve(int n, const double* A, const int* piv, double* Bm, int nrhs) {
 }
 
 // ---------------------------------------------------------------------------------------
+// dyn10 plant: `fdyn10_model`, python/models.py:609-801.  x[15] = (s, n, psi, v_x, v_y, r, omega_FL,
+// omega_FR, omega_RL, omega_RR, tau_FL, tau_FR, tau_RL, tau_RR, delta), u[5] = (u_tau_FL .. u_tau_RR, u_delta).
+// The reference states it implicitly (the accelerations feed the vertical loads, :655-684); every tyre force is
+// proportional to its wheel's vertical load, so the force balance is affine in (a_x, a_y): one 2 x 2 solve gives the
+// explicit right-hand side.  Straight slip-angle assignment (:717-720), drag switched by tanh(1000 v_x) (:659).
+// ---------------------------------------------------------------------------------------
+constexpr int NX10 = 15, NU10 = 5;
+void fdyn10(const double* x, const double* u, const double* p, const Track& tr, double* f) {
+  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], dl = x[14];
+  const double* om = x + 6; const double* tau = x + 10;
+  const double m = p[P_M], g = p[P_G], lR = p[P_LR], lF = p[P_LF], wb = lR + lF, tw = p[P_TRACKW];
+  const double Fdown = 0.5 * p[P_CDOWN] * vx * vx;
+  const double stat = 0.5 * m * g * lF / wb;
+  const double cl = 0.5 * m * p[P_ZCG] / wb, ct = 0.5 * m * p[P_ZCG] / tw;
+  const double sd = std::sin(dl), cd = std::cos(dl);
+  auto sabs = [](double v) { return std::tanh(10.0 * v) * v + 1e-6 * std::exp(-v * v); };   // utils.py:27-32
+  const double vxL = vx - 0.5 * tw * r, vxR = vx + 0.5 * tw * r, vyF = vy + lF * r, vlatR = vy - lR * r;
+  // wheel order FL, FR, RL, RR
+  const double vlon[4] = {cd * vxL + sd * vyF, cd * vxR + sd * vyF, vxL, vxR};
+  const double vlat[4] = {-sd * vxL + cd * vyF, -sd * vxR + cd * vyF, vlatR, vlatR};
+  double mu_lat[4], mu_lon[4];
+  for (int w = 0; w < 4; w++) {
+    const double va = sabs(vlon[w]);
+    const double al = std::atan2(vlat[w], va);
+    const double Ba = p[P_BA] * al;
+    mu_lat[w] = p[P_DA] * std::sin(p[P_CA] * std::atan(Ba - p[P_EA] * (Ba - std::atan(Ba))));      // lat_pacejka, :69-74
+    const double sl = om[w] * p[P_RW] / va - 1.0;                                                    // slip ratio, :723-726
+    const double Bs = p[P_BS] * sl;
+    mu_lon[w] = -p[P_DS] * std::sin(p[P_CS] * std::atan(Bs - p[P_ES] * (Bs - std::atan(Bs))));     // F_lon = -F_z lon_pacejka(s)
+  }
+  const double Fdrag = -(p[P_CR0] + p[P_CR1] * vx + p[P_CR2] * vx * vx) * std::tanh(1000.0 * vx);
+  // body-frame force per unit vertical load of each wheel, and its yaw arm
+  double fx[4], fy[4], mz[4];
+  fx[0] = mu_lon[0] * cd - mu_lat[0] * sd; fy[0] = mu_lon[0] * sd + mu_lat[0] * cd;
+  fx[1] = mu_lon[1] * cd - mu_lat[1] * sd; fy[1] = mu_lon[1] * sd + mu_lat[1] * cd;
+  fx[2] = mu_lon[2]; fy[2] = mu_lat[2]; fx[3] = mu_lon[3]; fy[3] = mu_lat[3];
+  mz[0] = -0.5 * tw * fx[0] + lF * fy[0]; mz[1] = 0.5 * tw * fx[1] + lF * fy[1];
+  mz[2] = -0.5 * tw * fx[2] - lR * fy[2]; mz[3] = 0.5 * tw * fx[3] - lR * fy[3];
+  // F_z,w = z0 + cx_w a_x + cy_w a_y  (:661-684)
+  const double z0 = -(stat + 0.25 * Fdown);
+  const double cx[4] = {cl, cl, -cl, -cl}, cy[4] = {-ct, ct, -ct, ct};
+  double Fx0 = Fdrag, Fy0 = 0, gxx = 0, gxy = 0, gyx = 0, gyy = 0;
+  for (int w = 0; w < 4; w++) {
+    Fx0 += z0 * fx[w]; Fy0 += z0 * fy[w];
+    gxx += cx[w] * fx[w]; gxy += cy[w] * fx[w]; gyx += cx[w] * fy[w]; gyy += cy[w] * fy[w];
+  }
+  const double a11 = m - gxx, a12 = -gxy, a21 = -gyx, a22 = m - gyy;
+  const double det = a11 * a22 - a12 * a21;
+  const double ax = (Fx0 * a22 - a12 * Fy0) / det, ay = (a11 * Fy0 - a21 * Fx0) / det;
+  double Mz = 0, Fz[4];
+  for (int w = 0; w < 4; w++) { Fz[w] = z0 + cx[w] * ax + cy[w] * ay; Mz += Fz[w] * mz[w]; }
+  double kap, dkap;
+  kappa_lookup(tr, x[0], kap, dkap);
+  const double sp = std::sin(psi), cp = std::cos(psi);
+  const double sdot = (vx * cp - vy * sp) / (1.0 + kap * n);
+  f[0] = sdot; f[1] = vx * sp + vy * cp; f[2] = r - kap * sdot;
+  f[3] = ax + vy * r; f[4] = ay - vx * r; f[5] = Mz / p[P_IZ];
+  for (int w = 0; w < 4; w++) {
+    f[6 + w] = (tau[w] - (p[P_KD] * om[w] + p[P_KS] + p[P_RW] * Fz[w] * mu_lon[w])) / p[P_IW];   // :781-784
+    f[10 + w] = (u[w] - tau[w]) / p[P_TT];
+  }
+  f[14] = (u[4] - dl) / p[P_TD];
+}
+
+struct Tableau { int ns; const double* A; const double* b; };  // A row-major ns x ns
+
+// Fully implicit collocation step of a plant of any dimension: Newton on all ns * nx stage derivatives with a
+// central-difference Jacobian, converged to round-off (the AcadosSimSolver of python/main.py:395-400 on fdyn10).
+template <class Rhs>
+int irk_step_plant(int nx, Rhs rhs, const Tableau& tb, const double* x, double h, double* xn) {
+  const int ns = tb.ns, n = ns * nx;
+  std::vector<double> K(n), M(n * n), R(n), Js(ns * nx * nx), xs(nx), fs(nx), xp(nx), fp(nx), fm(nx);
+  std::vector<int> piv(n);
+  rhs(x, fs.data());
+  for (int i = 0; i < ns; i++) for (int a = 0; a < nx; a++) K[i * nx + a] = fs[a];
+  double rprev = std::numeric_limits<double>::infinity();
+  bool ok = false;
+  for (int it = 0; it < 60; it++) {
+    double rmax = 0.0, kmax = 0.0;
+    for (int i = 0; i < ns; i++) {
+      for (int a = 0; a < nx; a++) {
+        double v = x[a];
+        for (int j = 0; j < ns; j++) v += h * tb.A[i * ns + j] * K[j * nx + a];
+        xs[a] = v;
+      }
+      rhs(xs.data(), fs.data());
+      for (int c = 0; c < nx; c++) {
+        const double e = 1e-6 * (1.0 + std::fabs(xs[c]));
+        xp = xs; xp[c] = xs[c] + e; rhs(xp.data(), fp.data());
+        xp[c] = xs[c] - e; rhs(xp.data(), fm.data());
+        for (int a = 0; a < nx; a++) Js[(i * nx + a) * nx + c] = (fp[a] - fm[a]) / (2 * e);
+      }
+      for (int a = 0; a < nx; a++) {
+        R[i * nx + a] = K[i * nx + a] - fs[a];
+        rmax = std::max(rmax, std::fabs(R[i * nx + a])); kmax = std::max(kmax, std::fabs(K[i * nx + a]));
+      }
+    }
+    if (!(rmax == rmax)) return -1;
+    if (rmax <= 4e-15 * (1.0 + kmax) || (it >= 2 && rmax >= 0.25 * rprev && rmax <= 1e-9 * (1.0 + kmax))) { ok = true; break; }
+    rprev = rmax;
+    for (int i = 0; i < ns; i++)
+      for (int a = 0; a < nx; a++)
+        for (int j = 0; j < ns; j++)
+          for (int c = 0; c < nx; c++)
+            M[(i * nx + a) * n + j * nx + c] = ((i == j && a == c) ? 1.0 : 0.0) - h * tb.A[i * ns + j] * Js[(i * nx + a) * nx + c];
+    if (!lu_factor(n, M.data(), piv.data())) return -2;
+    lu_solve(n, M.data(), piv.data(), R.data(), 1);
+    for (int q = 0; q < n; q++) K[q] -= R[q];
+  }
+  if (!ok) return -3;
+  for (int a = 0; a < nx; a++) {
+    double v = x[a];
+    for (int i = 0; i < ns; i++) v += h * tb.b[i] * K[i * nx + a];
+    xn[a] = v;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
 // integrators with forward sensitivities.  Output: xn[8], S[8][10] = d xn / d (x,u).
 // ---------------------------------------------------------------------------------------
 // classic RK4, one step (acados ERK, 4 stages, 1 step: old/generate.py:24-26)
@@ -411,7 +531,6 @@ void erk4_sens(const double* x, const double* u, const double* p, const Track& t
   }
 }
 
-struct Tableau { int ns; const double* A; const double* b; };  // A row-major ns x ns
 
 // Fully implicit RK (collocation) step, Newton on all ns*8 stage derivatives, converged
 // to round-off; sensitivities by the implicit-function theorem on the collocation system
@@ -1521,6 +1640,34 @@ int ihm2o_sim_step(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t
     Problem pb = make_problem(cf, tk, track_index, params, i);
     const int m = sim_step(pb, x + (size_t)i * NX, u + (size_t)i * NU, xn + (size_t)i * NX);
     if (model) model[i] = m;
+  }
+  return 0;
+}
+
+// dyn10 plant: right-hand side at one point (track 0, first parameter vector) and the batched step
+void ihm2o_fdyn10(const ihm2b_config* cf, const ihm2o_tracks* tk, const double* params, const double* x, const double* u, double* f) {
+  Problem pb = make_problem(cf, tk, nullptr, params, 0);
+  fdyn10(x, u, pb.p, pb.tr, f);
+}
+
+// x [B][15], u [B][5] -> xn [B][15] (NaN rows on failure): cfg.sim_steps Radau-IIA sub-steps over cfg.dt
+int ihm2o_sim_step_dyn10(const ihm2b_config* cf, const ihm2o_tracks* tk, const int32_t* track_index, const double* params,
+                         const double* x, const double* u, double* xn) {
+#pragma omp parallel for schedule(dynamic)
+  for (int i = 0; i < cf->batch; i++) {
+    Problem pb = make_problem(cf, tk, track_index, params, i);
+    Tableau tb{4, cf->sim_A, cf->sim_b};
+    const double h = cf->dt / cf->sim_steps;
+    double xc[NX10], xt[NX10];
+    std::memcpy(xc, x + (size_t)i * NX10, sizeof xc);
+    const double* ui = u + (size_t)i * NU10;
+    bool ok = true;
+    for (int st = 0; st < cf->sim_steps && ok; st++) {
+      auto rhs = [&](const double* xx, double* ff) { fdyn10(xx, ui, pb.p, pb.tr, ff); };
+      ok = irk_step_plant(NX10, rhs, tb, xc, h, xt) == 0;
+      std::memcpy(xc, xt, sizeof xc);
+    }
+    for (int a = 0; a < NX10; a++) xn[(size_t)i * NX10 + a] = ok ? xc[a] : std::numeric_limits<double>::quiet_NaN();
   }
   return 0;
 }

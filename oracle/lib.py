@@ -9,7 +9,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_build", "libihm2_oracle.so")
-NX, NU, NZ, NP = 8, 2, 10, 20
+NX, NU, NZ, NP = 8, 2, 10, 28
 
 
 def build_oracle(force: bool = False) -> str:
@@ -131,6 +131,17 @@ class Oracle:
         h = np.zeros(5); J = np.zeros((5, NZ))
         self.lib.ihm2o_con_h(C.byref(self.cfg), C.byref(self._tk), _p(self.params), _p(_f(x)), _p(_f(u)), _p(h), _p(J))
         return h, J
+
+    def fdyn10(self, x, u):
+        f = np.zeros(15)
+        self.lib.ihm2o_fdyn10(C.byref(self.cfg), C.byref(self._tk), _p(self.params), _p(_f(x)), _p(_f(u)), _p(f))
+        return f
+
+    def sim_step_dyn10(self, x, u):
+        B = self.cfg.batch
+        xn = np.zeros((B, 15))
+        self.lib.ihm2o_sim_step_dyn10(*self._common(), _p(_f(x)), _p(_f(u)), _p(xn))
+        return xn
 
     def sim_step(self, x, u):
         B = self.cfg.batch

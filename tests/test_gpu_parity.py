@@ -476,3 +476,56 @@ def test_solver_object_shim_drives_the_engine_like_acados(torch_cuda, fsds):
         sv.cost_set(3, "W", np.eye(12))
     with pytest.raises(ValueError):
         sv.set(5, "yref", np.ones((B, 12)))
+
+
+def test_dyn10_plant_step_matches_oracle(torch_cuda, fsds):
+    """`fdyn10_model` (python/models.py:609-801; 15 states, 5 controls) through ihm2b_sim_step_dyn10_dev
+    against the oracle's generic Newton collocation of the same equations: cruising, braking, low speed, cornering."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.engine import Engine
+    from oracle.lib import Oracle
+    B = 96
+    rng = np.random.default_rng(5)
+    Rw = _abi.default_params()[_abi.P_RW]
+    v = np.concatenate([rng.uniform(4, 25, B // 2), rng.uniform(0.8, 4, B // 2)])
+    x = np.concatenate([np.stack([rng.uniform(0, 380, B), rng.uniform(-1.2, 1.2, B), rng.uniform(-0.3, 0.3, B), v,
+                                  rng.uniform(-0.8, 0.8, B), rng.uniform(-0.8, 0.8, B)], 1),
+                        (v / Rw)[:, None] * rng.uniform(0.95, 1.1, (B, 4)), rng.uniform(-60, 100, (B, 4)), rng.uniform(-0.3, 0.3, (B, 1))], 1)
+    u = np.concatenate([rng.uniform(-100, 125, (B, 1)).repeat(4, 1), rng.uniform(-0.4, 0.4, (B, 1))], 1)
+    params = np.tile(_abi.default_params(), (B, 1)); params[:, _abi.P_M] *= rng.uniform(0.9, 1.1, B)
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref))
+    eng = _engine(cfg, fsds, params=params)
+    xn = eng.sim_step_dyn10(torch_cuda.as_tensor(x, device="cuda"), torch_cuda.as_tensor(u, device="cuda")).cpu().numpy()
+    eng.close()
+    xo = Oracle(cfg, fsds.s_ref, fsds.kappa_ref, params=params).sim_step_dyn10(x, u)
+    assert np.isfinite(xo).all() and np.isfinite(xn).all()
+    for c in range(15):
+        assert rel(xn[:, c], xo[:, c]) < 1e-8, c
+    # the step did something: wheel speeds follow the torque, the car moves
+    assert np.abs(xn[:, 6:10] - x[:, 6:10]).max() > 0.1 and (xn[:, 0] > x[:, 0]).all()
+
+
+def test_nmpc_drives_the_dyn10_plant(torch_cuda, fsds):
+    """The controller in closed loop with the dyn10 plant (python/main.py:490-500: u_T spread over the four wheels):
+    the car accelerates down the start straight and stays on the track."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.controller import IHM2Controller
+    from ihm2_b200.simulator import (SimulatorModel, SingleModelSimulator, controller_state_from_dyn10_state,
+                                     dyn10_state_from_controller_state)
+    B = 8
+    ctrl = IHM2Controller(fsds.s_ref, fsds.kappa_ref, batch=B, s_target=24.0, nonlinear_constraints=True,
+                          right_width=fsds.right_widths, left_width=fsds.left_widths, qp_tolerate_maxiter=True)
+    sim = SingleModelSimulator(SimulatorModel.DYN10, fsds.s_ref, fsds.kappa_ref, batch=B)
+    # rolling start: at exact standstill the slip ratio omega R_w / |v| - 1 of fdyn10_model is singular (the dense Newton
+    # collocation of the oracle fails there too)
+    x8 = torch_cuda.zeros(B, 8, dtype=torch_cuda.float64); x8[:, 0] = -6.0; x8[:, 3] = 1.0
+    x10 = dyn10_state_from_controller_state(x8).cuda()
+    for step in range(120):
+        u, status = ctrl.compute_control(controller_state_from_dyn10_state(x10), return_status=True)
+        assert bool(((status == 0) | (status == 2)).all()), (step, status)
+        x10 = sim.simulate(x10, u)
+        assert bool(torch_cuda.isfinite(x10).all()), step
+    xs = x10.cpu().numpy()
+    assert (xs[:, 0] > 15.0).all() and (xs[:, 3] > 4.0).all() and (np.abs(xs[:, 1]) < 2.0).all()
+    slip = xs[:, 6:10] * _abi.default_params()[_abi.P_RW] / xs[:, 3:4] - 1.0
+    assert np.abs(slip).max() < 0.2

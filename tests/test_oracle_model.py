@@ -289,3 +289,65 @@ def test_frenet_fdyn6_satisfies_the_reference_implicit_form():
             scale = np.array([1, 1, 1, m * 10, m * 10, Iz * 10, 1 + abs(xd[6]), 1 + abs(xd[7])])
             worst = max(worst, np.abs(res / scale).max())
         assert worst < 1e-10, (cross, worst)
+
+
+def test_fdyn10_satisfies_the_reference_implicit_form():
+    """Independent pin of the dyn10 plant: numpy transcription of the implicit residual of `fdyn10_model`
+    (python/models.py:609-801: slip ratios and longitudinal Pacejka :722-732, straight slip angles :717-720, wheel-speed
+    rows :781-784, four torque lags) at the oracle's state derivative."""
+    from ihm2_b200 import _abi
+    from ihm2_b200.track import load_packaged_track
+    from oracle.lib import Oracle
+    mp = load_packaged_track("fsds_default")
+    P = _abi.default_params()
+    cfg = _abi.make_config(batch=1, n_grid=len(mp.s_ref))
+    orc = Oracle(cfg, mp.s_ref, mp.kappa_ref)
+    m, g, lR, lF, tw, zcg, Iz = [P[i] for i in (_abi.P_M, _abi.P_G, _abi.P_LR, _abi.P_LF, _abi.P_TRACKW, _abi.P_ZCG, _abi.P_IZ)]
+    Rw, Iw, kd, ks = [P[i] for i in (_abi.P_RW, _abi.P_IW, _abi.P_KD, _abi.P_KS)]
+    wb = lR + lF
+    Ba, Ca, Da, Ea = [P[j] for j in (_abi.P_BA, _abi.P_CA, _abi.P_DA, _abi.P_EA)]
+    Bs, Cs, Ds, Es = [P[j] for j in (_abi.P_BS, _abi.P_CS, _abi.P_DS, _abi.P_ES)]
+    # constants.py:85-95 by value (the parameter vector must carry the reference's numbers)
+    assert abs(Ds - (1.12e-4 * 0.5 * 230 * 9.81 * 0.7853 / 1.5706 + 1.57)) < 1e-12 and Cs == 1.86 and (Rw, Iw, kd, ks) == (0.20809, 0.3, 0.17, 15.0)
+    latp = lambda al: Da * np.sin(Ca * np.arctan(Ba * al - Ea * (Ba * al - np.arctan(Ba * al))))
+    lonp = lambda sl: Ds * np.sin(Cs * np.arctan(Bs * sl - Es * (Bs * sl - np.arctan(Bs * sl))))
+    sabs = lambda v: np.tanh(10 * v) * v + 1e-6 * np.exp(-v * v)
+    rng = np.random.default_rng(12)
+    worst = 0.0
+    for _ in range(200):
+        v = rng.uniform(0.5, 25)
+        x = np.concatenate([[rng.uniform(0, 380), rng.uniform(-1.5, 1.5), rng.uniform(-0.5, 0.5), v, rng.uniform(-1.5, 1.5), rng.uniform(-1.2, 1.2)],
+                            v / Rw * rng.uniform(0.9, 1.15, 4), rng.uniform(-100, 100, 4), [rng.uniform(-0.45, 0.45)]])
+        u = np.concatenate([rng.uniform(-125, 125, 4), [rng.uniform(-0.5, 0.5)]])
+        xd = orc.fdyn10(x, u)
+        s, n, psi, vx, vy, r = x[:6]; om, tau, dl = x[6:10], x[10:14], x[14]
+        ax, ay = xd[3] - vy * r, xd[4] + vx * r
+        Fdrag = -(P[_abi.P_CR0] + P[_abi.P_CR1] * vx + P[_abi.P_CR2] * vx * vx) * np.tanh(1000 * vx)
+        Fdown = 0.5 * P[_abi.P_CDOWN] * vx * vx
+        stat = 0.5 * m * g * lF / wb
+        lon, lat = 0.5 * m * ax * zcg / wb, 0.5 * m * ay * zcg / tw
+        Fz = np.array([-(stat - lon + lat + 0.25 * Fdown), -(stat - lon - lat + 0.25 * Fdown),
+                       -(stat + lon + lat + 0.25 * Fdown), -(stat + lon - lat + 0.25 * Fdown)])
+        cd, sd = np.cos(dl), np.sin(dl)
+        vxFL, vxFR, vyF = vx - 0.5 * tw * r, vx + 0.5 * tw * r, vy + lF * r
+        vlon = np.array([cd * vxFL + sd * vyF, cd * vxFR + sd * vyF, vx - 0.5 * tw * r, vx + 0.5 * tw * r])
+        vlat = np.array([-sd * vxFL + cd * vyF, -sd * vxFR + cd * vyF, vy - lR * r, vy - lR * r])
+        va = sabs(vlon)
+        Flat = Fz * latp(np.arctan2(vlat, va))
+        Flon = -Fz * lonp(om * Rw / va - 1.0)
+        i0 = np.searchsorted(mp.s_ref, s, side="right") - 1
+        kap = mp.kappa_ref[i0] + (mp.kappa_ref[i0 + 1] - mp.kappa_ref[i0]) / (mp.s_ref[i0 + 1] - mp.s_ref[i0]) * (s - mp.s_ref[i0])
+        sdot = (vx * np.cos(psi) - vy * np.sin(psi)) / (1 + kap * n)
+        FL, FR, RL, RR = 0, 1, 2, 3
+        res = np.concatenate([[
+            xd[0] - sdot, xd[1] - (vx * np.sin(psi) + vy * np.cos(psi)), xd[2] - (r - kap * sdot),
+            m * ax - (Fdrag + cd * (Flon[FL] + Flon[FR]) - sd * (Flat[FL] + Flat[FR]) + Flon[RL] + Flon[RR]),
+            m * ay - (sd * (Flon[FL] + Flon[FR]) + cd * (Flat[FL] + Flat[FR]) + Flat[RL] + Flat[RR]),
+            Iz * xd[5] - ((Flon[FR] * cd - Flat[FR] * sd) * tw / 2 + (Flon[FR] * sd + Flat[FR] * cd) * lF
+                          - (Flon[FL] * cd - Flat[FL] * sd) * tw / 2 + (Flon[FL] * sd + Flat[FL] * cd) * lF
+                          + Flon[RR] * tw / 2 - Flat[RR] * lR - Flon[RL] * tw / 2 - Flat[RL] * lR)],
+            Iw * xd[6:10] - (tau - (kd * om + ks + Rw * Flon)),
+            xd[10:14] - (u[:4] - tau) / P[_abi.P_TT], [xd[14] - (u[4] - dl) / P[_abi.P_TD]]])
+        scale = np.concatenate([[1, 1, 1, m * 10, m * 10, Iz * 10], np.full(4, 100.0), 1 + np.abs(xd[10:15])])
+        worst = max(worst, np.abs(res / scale).max())
+    assert worst < 1e-10, worst
