@@ -436,7 +436,7 @@ def main():
         n_cpu = 1024
         cpu_val, cpu_t = cpu_oracle_rate(x0_h, x_h, u_h, mp, n_cpu)
         traffic, traffic_src = None, None   # dram bytes of the QP launch from the committed ncu --set full summary
-        prof = os.path.join(ROOT, "profiles", "r01_qp_rti_kernel_ncu_summary.csv")
+        prof = os.path.join(ROOT, "profiles", "r02_qp_rti_kernel_ncu_summary.csv")
         if os.path.exists(prof) and B == B_PER_GPU:
             unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
             tb = 0.0
@@ -445,7 +445,7 @@ def main():
                 if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     tb += float(f[2]) * unit.get(f[1], 1.0)
             if tb > 0:
-                traffic, traffic_src = tb, "profiles/r01_qp_rti_kernel_ncu_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+                traffic, traffic_src = tb, "profiles/r02_qp_rti_kernel_ncu_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         hbm = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
         out = {
