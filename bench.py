@@ -409,6 +409,28 @@ def main():
                        "status_counts": {str(k): int(v) for k, v in enumerate(np.bincount(st_s.cpu().numpy(), minlength=5)) if v}}
     eng_sqp.close()
 
+    # ---- mixed precision (linearize_fp32: IRK collocation + sensitivities in fp32, QP in fp64), same inputs
+    cfg_mp = _abi.make_config(batch=B, n_grid=len(mp.s_ref), linearize_fp32=True)
+    eng_mp = Engine(cfg_mp, mp.s_ref, mp.kappa_ref)
+    u0_mp = torch.empty_like(u0_d); st_mp = torch.empty_like(st_d)
+    t_mp = []
+    for i in range(3 + max(3, args.steps // 4)):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); eng_mp.set_iterate(x_ws, u_ws); eng_mp.solve(x0_d, u0_mp, st_mp); e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            t_mp.append(e0.elapsed_time(e1))
+    both = (st_mp == 0) & (st_d == 0)
+    dev_u0 = float(((u0_mp - u0_d)[both].abs().max() / u0_d[both].abs().max().clamp(min=1.0)).item())
+    mp_ms = torch.tensor([sum(t_mp) / len(t_mp)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(mp_ms, op=dist.ReduceOp.MAX)
+    mixed_precision = {"what": "linearize_fp32: IRK collocation, Newton solves and sensitivities in fp32; iterate, [B A], c and the QP in fp64",
+                       "ms_per_step": float(mp_ms.item()), "value": world * B / (float(mp_ms.item()) * 1e-3), "unit": "solves/s",
+                       "u0_max_rel_deviation_from_fp64": dev_u0, "stated_tolerance": 1e-4}
+    eng_mp.close()
+
     # per-rank record: the time is the slowest rank's; the shards differ in their interior-point work
     mine = torch.tensor([sum(times) / args.steps, float(stats[:, 0].sum().item())], dtype=torch.float64, device=dev)
     per_rank = [torch.zeros_like(mine) for _ in range(world)]
@@ -472,6 +494,7 @@ def main():
                                       "d2h_bytes_per_step": B * (2 * 8 + 4) + B * ((N_HORIZON + 1) * 8 + N_HORIZON * 2) * 8,
                                       "note": "as e2e plus the read-back of x_pred / u_pred of every stage (new_python/controller.py:402-403) into page-locked host buffers"},
             "reference_setup": reference_setup,
+            "mixed_precision": mixed_precision,
             "gpu_launches": int(launches),
             "kernels_ms": {"linearize_irk": lin_ms, "qp_rti": qp_ms},
             "roofline": {"bound": "tensor", "bound_note": "FP64: the kernel's serial sweeps run on the FP64 tensor pipe (DMMA, mma.m8n8k4.f64), the row passes on the FP64 CUDA cores; both peak at the same rate on B200 and the denominator is the larger of the two, measured in this process -- not the bf16 tensor figure and not HBM (SURVEY.md 8d)", "kernel": "qp_rti_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",

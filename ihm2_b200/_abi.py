@@ -73,6 +73,8 @@ class Config(C.Structure):
         ("qp_split_step", C.c_int32),
         ("qp_infeas_exit", C.c_int32),
         ("qp_thr0", C.c_double),
+        ("linearize_fp32", C.c_int32),
+        ("reserved_", C.c_int32),
     ]
 
 
@@ -182,6 +184,7 @@ def make_config(
     qp_split_step: bool | None = None,
     qp_infeas_exit: bool | None = None,
     qp_thr0: float = 0.1,
+    linearize_fp32: bool = False,
 ) -> Config:
     """Fill ihm2b_config from `IHM2Controller.__init__` style arguments
     (new_python/controller.py:250-309; python/mpc.py:77-99 for the bounds).
@@ -228,4 +231,5 @@ def make_config(
     cf.slack_z = cf.slack_Z = 100.0  # zl = zu = Zl = Zu = 100 (old/generate_acaods_interface.py:383-390)
     cf.T_dot_max, cf.delta_dot_max = T_dot_max, delta_dot_max
     cf.qp_split_step, cf.qp_infeas_exit, cf.qp_thr0 = int(qp_split_step), int(qp_infeas_exit), qp_thr0
+    cf.linearize_fp32 = int(linearize_fp32)
     return cf

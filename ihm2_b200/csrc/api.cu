@@ -151,6 +151,7 @@ void fill_kcfg(const ihm2b_config& c, KCfg& k) {
   k.thr0 = c.qp_thr0 > 0.0 ? c.qp_thr0 : 0.1;
   k.split_step = c.qp_split_step; k.infeas_exit = c.qp_infeas_exit;
   k.nl = c.nonlinear_constraints ? 1 : 0;
+  k.lin_fp32 = c.linearize_fp32 ? 1 : 0;
   k.half_L = c.track_half_L; k.half_W = c.track_half_W; k.a_lat_max = c.a_lat_max;
   k.T_dot_max = c.T_dot_max; k.delta_dot_max = c.delta_dot_max;
   k.slack_z = c.slack_z; k.slack_Z = c.slack_Z;

@@ -16,7 +16,7 @@ constexpr int GROUP = 8;       // lanes per problem in the QP kernel (lane = sta
 // Kernel-side copy of the scalar options of ihm2b_config (passed by value).
 struct KCfg {
   int B, N, n_grid;
-  int integrator, qp_max_iter, qp_tolerate_maxiter;
+  int integrator, qp_max_iter, qp_tolerate_maxiter, lin_fp32;
   double dt, s_target;
   double n_max, v_x_max, T_max, delta_max, g_T_max, g_delta_max;
   double W[IHM2B_NY], We[IHM2B_NYN];

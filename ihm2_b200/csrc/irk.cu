@@ -34,40 +34,40 @@ constexpr int NI = 32;     // intervals per block; shared arrays are [entry][NI]
 
 // in-place LU without pivoting (the matrices are I - h A (x) J, close to the identity);
 // element (r, c) at M[(r * n + c) * NI]; L below the diagonal (unit), U above, reciprocal pivots on it
-template <int n>
-__device__ __forceinline__ void lu_factor(double* M) {
+template <int n, typename Real>
+__device__ __forceinline__ void lu_factor(Real* M) {
   // left-looking, one row at a time in registers: row r is reduced against the finished rows c < r, so the
   // shared-memory loads never wait on a store of the same sweep (the right-looking form is a chain of
   // load - fma - store round trips through shared memory, ~10x slower here)
 #pragma unroll
   for (int r = 0; r < n; r++) {
-    double row[n];
+    Real row[n];
 #pragma unroll
     for (int j = 0; j < n; j++) row[j] = M[(r * n + j) * NI];
 #pragma unroll
     for (int c = 0; c < r; c++) {
-      const double l = row[c] * M[(c * n + c) * NI];   // reciprocal pivot of row c
+      const Real l = row[c] * M[(c * n + c) * NI];   // reciprocal pivot of row c
       row[c] = l;
 #pragma unroll
       for (int j = c + 1; j < n; j++) row[j] = fma(-l, M[(c * n + j) * NI], row[j]);
     }
-    row[r] = 1.0 / row[r];  // store the reciprocal pivot
+    row[r] = Real(1.0) / row[r];  // store the reciprocal pivot
 #pragma unroll
     for (int j = 0; j < n; j++) M[(r * n + j) * NI] = row[j];
   }
 }
-template <int n>
-__device__ __forceinline__ void lu_solve(const double* M, double* b) {
+template <int n, typename Real>
+__device__ __forceinline__ void lu_solve(const Real* M, Real* b) {
 #pragma unroll
   for (int r = 1; r < n; r++) {
-    double v = b[r];
+    Real v = b[r];
 #pragma unroll
     for (int c = 0; c < r; c++) v = fma(-M[(r * n + c) * NI], b[c], v);
     b[r] = v;
   }
 #pragma unroll
   for (int r = n - 1; r >= 0; r--) {
-    double v = b[r];
+    Real v = b[r];
 #pragma unroll
     for (int c = r + 1; c < n; c++) v = fma(-M[(r * n + c) * NI], b[c], v);
     b[r] = v * M[(r * n + r) * NI];
@@ -89,8 +89,9 @@ __device__ __forceinline__ constexpr int jslot(int row, int col) {
 }
 
 // quantities of a collocation point that depend only on (T_i, delta_i, d delta_i / dt)
+template <typename Real>
 struct VPoint {
-  double cb, sb, bdot, cdb, Fm;
+  Real cb, sb, bdot, cdb, Fm;
 };
 
 }  // namespace
@@ -102,34 +103,38 @@ struct VPoint {
 // Jacobians are written for phase 2.  All 32 lanes of the warp (8 intervals) run the same number of Newton iterations;
 // an interval that has converged stops updating and re-evaluates at the point its factors belong to, so its result
 // does not depend on its neighbours in the warp.
+template <typename Real> __device__ __forceinline__ constexpr Real newton_tol() { return sizeof(Real) == 8 ? Real(1e-14) : Real(2e-6); }
 constexpr unsigned FULLW = 0xffffffffu;
-__device__ __forceinline__ double g4(double v, int src) { return __shfl_sync(FULLW, v, src, 4); }
-__device__ __forceinline__ double g4max(double v) {
+template <typename Real>
+__device__ __forceinline__ Real g4(Real v, int src) { return __shfl_sync(FULLW, v, src, 4); }
+template <typename Real>
+__device__ __forceinline__ Real g4max(Real v) {
   v = fmax(v, __shfl_xor_sync(FULLW, v, 1)); v = fmax(v, __shfl_xor_sync(FULLW, v, 2));
   return v;
 }
-__device__ __forceinline__ double g4sum(double v) {
+template <typename Real>
+__device__ __forceinline__ Real g4sum(Real v) {
   v += __shfl_xor_sync(FULLW, v, 1); v += __shfl_xor_sync(FULLW, v, 2);
   return v;
 }
 
 // LU (no pivoting, unit L, reciprocal pivots on the diagonal: the layout lu_solve reads) of the n x n matrix whose rows
 // t * RPL .. t * RPL + RPL - 1 lane t holds, and the solution of M x = b; x returned in b (own rows).
-template <int RPL>
-__device__ __forceinline__ void lu4_factor_solve(double (&M)[RPL][4 * RPL], double (&b)[RPL], const int t) {
+template <int RPL, typename Real>
+__device__ __forceinline__ void lu4_factor_solve(Real (&M)[RPL][4 * RPL], Real (&b)[RPL], const int t) {
   constexpr int n = 4 * RPL;
 #pragma unroll
   for (int p = 0; p < n; p++) {
     const int owner = p / RPL, pr = p % RPL;
-    const double rp = g4(1.0 / M[pr][p], owner);
-    double prow[n];
+    const Real rp = g4(Real(1.0) / M[pr][p], owner);
+    Real prow[n];
 #pragma unroll
     for (int c = p + 1; c < n; c++) prow[c] = g4(M[pr][c], owner);
-    const double pb = g4(b[pr], owner);
+    const Real pb = g4(b[pr], owner);
 #pragma unroll
     for (int r = 0; r < RPL; r++) {
       const bool below = (t * RPL + r > p);
-      const double l = M[r][p] * rp;
+      const Real l = M[r][p] * rp;
       if (below) {
         M[r][p] = l;
 #pragma unroll
@@ -139,145 +144,149 @@ __device__ __forceinline__ void lu4_factor_solve(double (&M)[RPL][4 * RPL], doub
     }
     if (t == owner) M[pr][p] = rp;
   }
-  double xs[n];
+  Real xs[n];
 #pragma unroll
   for (int p = n - 1; p >= 0; p--) {
     const int owner = p / RPL, pr = p % RPL;
-    double v = b[pr];
+    Real v = b[pr];
 #pragma unroll
     for (int c = p + 1; c < n; c++) v = fma(-M[pr][c], xs[c], v);
     xs[p] = g4(v * M[pr][p], owner);
   }
 #pragma unroll
   for (int r = 0; r < RPL; r++) {
-    double v = 0.0;
+    Real v = Real(0.0);
 #pragma unroll
     for (int o = 0; o < 4; o++) v = (t == o) ? xs[o * RPL + r] : v;
     b[r] = v;
   }
 }
 
-__device__ bool irk_newton4(const int t, const double* __restrict__ x, double u0, double u1, const double* __restrict__ p,
-                            const TrackView& tr, double h, const double* __restrict__ A4, const double* __restrict__ b4,
-                            const double* __restrict__ wT, const double* __restrict__ wD, double* __restrict__ sm) {
-  const double m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
-  const double C = lR / (lR + lF), im = 1.0 / m;
-  const double itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD];
-  double ha[NS];
+template <typename Real>
+__device__ bool irk_newton4(const int t, const Real* __restrict__ x, Real u0, Real u1, const Real* __restrict__ p,
+                            const TrackView& tr, Real h, const Real* __restrict__ A4, const Real* __restrict__ b4,
+                            const Real* __restrict__ wT, const Real* __restrict__ wD, const double* __restrict__ lag_d,
+                            Real* __restrict__ sm) {
+  const Real m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
+  const Real C = lR / (lR + lF), im = Real(1.0) / m;
+  const Real itT = Real(1.0) / p[IHM2B_P_TT], itD = Real(1.0) / p[IHM2B_P_TD];
+  Real ha[NS];
 #pragma unroll
   for (int j = 0; j < NS; j++) ha[j] = h * A4[t * NS + j];
   // stage value of a component from the slopes of the four lanes
-  auto stage_val = [&](double x0, double Kown) {
-    double v = x0;
+  auto stage_val = [&](Real x0, Real Kown) {
+    Real v = x0;
 #pragma unroll
     for (int j = 0; j < NS; j++) v = fma(ha[j], g4(Kown, j), v);
     return v;
   };
   // ---- actuators: K = w (u - x) / t  (closed form, every lane knows all four)
-  const double c6 = (u0 - x[6]) * itT, c7 = (u1 - x[7]) * itD;
-  double K[NX];
+  // (u - x) / t of the two lags arrives in fp64 (lag_d): in fp32 the difference of two numbers of size 400 times 1 / t_T = 1000
+  // would cost three digits of the torque rows
+  const Real c6 = (Real)lag_d[0], c7 = (Real)lag_d[1];
+  Real K[NX];
   K[6] = wT[t] * c6; K[7] = wD[t] * c7;
-  double Ti = x[6], Di = x[7];
+  Real Ti = x[6], Di = x[7];
 #pragma unroll
   for (int j = 0; j < NS; j++) { Ti = fma(ha[j], wT[j] * c6, Ti); Di = fma(ha[j], wD[j] * c7, Di); }
   // ---- (v_x, v_y): Newton on 8 unknowns, rows 2t, 2t + 1 on this lane
-  VPoint vp;
+  VPoint<Real> vp;
   {
-    double sd, cd;
+    Real sd, cd;
     sincos(Di, &sd, &cd);
-    const double td = sd / cd, Ctd = C * td, den = 1.0 + Ctd * Ctd;
+    const Real td = sd / cd, Ctd = C * td, den = Real(1.0) + Ctd * Ctd;
     vp.cb = rsqrt(den); vp.sb = Ctd * vp.cb;
-    vp.bdot = C * (1.0 + td * td) / den * K[7];
+    vp.bdot = C * (Real(1.0) + td * td) / den * K[7];
     vp.cdb = cd * vp.cb + sd * vp.sb;
     vp.Fm = p[IHM2B_P_CM0] * Ti;
   }
-  auto veval = [&](double vx, double vy, double& f3, double& f4, double& dvd) {
-    const double th = tanh(10.0 * vx);
-    const double poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
-    const double FRx = 0.5 * vp.Fm - poly * th;
-    const double vdot = (FRx * vp.cb + 0.5 * vp.Fm * vp.cdb) * im;
+  auto veval = [&](Real vx, Real vy, Real& f3, Real& f4, Real& dvd) {
+    const Real th = tanh(Real(10.0) * vx);
+    const Real poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
+    const Real FRx = Real(0.5) * vp.Fm - poly * th;
+    const Real vdot = (FRx * vp.cb + Real(0.5) * vp.Fm * vp.cdb) * im;
     f3 = vdot * vp.cb - vp.bdot * vy;
     f4 = vdot * vp.sb + vp.bdot * vx;
-    dvd = (-(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th)) * vp.cb * im;
+    dvd = (-(p[IHM2B_P_CR1] + Real(2.0) * p[IHM2B_P_CR2] * vx) * th - poly * Real(10.0) * (Real(1.0) - th * th)) * vp.cb * im;
   };
-  { double d; veval(x[3], x[4], K[3], K[4], d); }
+  { Real d; veval(x[3], x[4], K[3], K[4], d); }
   bool ok = true, conv = false;
-  double Mv[2][8];
-  double P3 = K[3], P4 = K[4];      // the point the factors belong to (frozen at convergence)
+  Real Mv[2][8];
+  Real P3 = K[3], P4 = K[4];      // the point the factors belong to (frozen at convergence)
 #pragma unroll 1
   for (int it = 0;; it++) {
     if (!conv) { P3 = K[3]; P4 = K[4]; }
-    const double vx = stage_val(x[3], P3), vy = stage_val(x[4], P4);
-    double f3, f4, dvd;
+    const Real vx = stage_val(x[3], P3), vy = stage_val(x[4], P4);
+    Real f3, f4, dvd;
     veval(vx, vy, f3, f4, dvd);
-    double R[2] = {P3 - f3, P4 - f4};
-    const double J33 = dvd * vp.cb, J34 = -vp.bdot, J43 = dvd * vp.sb + vp.bdot;
+    Real R[2] = {P3 - f3, P4 - f4};
+    const Real J33 = dvd * vp.cb, J34 = -vp.bdot, J43 = dvd * vp.sb + vp.bdot;
 #pragma unroll
     for (int j = 0; j < NS; j++) {
-      const double e = (t == j) ? 1.0 : 0.0;
+      const Real e = (t == j) ? Real(1.0) : Real(0.0);
       Mv[0][2 * j] = e - ha[j] * J33; Mv[0][2 * j + 1] = -ha[j] * J34;
       Mv[1][2 * j] = -ha[j] * J43;    Mv[1][2 * j + 1] = e;
     }
-    lu4_factor_solve<2>(Mv, R, t);
-    const double k3 = P3 - R[0], k4 = P4 - R[1];
-    const double dmax = g4max(fmax(fabs(R[0]), fabs(R[1]))), kmax = g4max(fmax(fabs(k3), fabs(k4)));
+    lu4_factor_solve<2, Real>(Mv, R, t);
+    const Real k3 = P3 - R[0], k4 = P4 - R[1];
+    const Real dmax = g4max(fmax(fabs(R[0]), fabs(R[1]))), kmax = g4max(fmax(fabs(k3), fabs(k4)));
     if (!conv) {
       K[3] = k3; K[4] = k4;
       if (!(dmax == dmax)) { ok = false; conv = true; }
-      else if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) conv = true;
+      else if (dmax <= newton_tol<Real>() * (Real(1.0) + kmax) || it >= MAX_NEWTON) conv = true;
     }
     if (__all_sync(FULLW, conv)) break;
   }
   // ---- r: explicit, r' = l_R v_y' - beta'   (python/models.py:304)
   K[5] = lR * K[4] - vp.bdot;
-  const double vxi = stage_val(x[3], K[3]), vyi = stage_val(x[4], K[4]), ri = stage_val(x[5], K[5]);
+  const Real vxi = stage_val(x[3], K[3]), vyi = stage_val(x[4], K[4]), ri = stage_val(x[5], K[5]);
   // ---- (s, n, psi): Newton on 12 unknowns, rows 3t .. 3t + 2 on this lane
   {
-    double kap, dkap, sp, cp;
+    Real kap, dkap, sp, cp;
     kappa_lookup(tr, x[0], kap, dkap);
     sincos(x[2], &sp, &cp);
-    const double sdot = (x[3] * cp - x[4] * sp) / (1.0 + kap * x[1]);
+    const Real sdot = (x[3] * cp - x[4] * sp) / (Real(1.0) + kap * x[1]);
     K[0] = sdot; K[1] = x[3] * sp + x[4] * cp; K[2] = x[5] - kap * sdot;
   }
-  double Mp[3][12];
-  double Q0 = K[0], Q1 = K[1], Q2 = K[2];
+  Real Mp[3][12];
+  Real Q0 = K[0], Q1 = K[1], Q2 = K[2];
   conv = !ok;
 #pragma unroll 1
   for (int it = 0;; it++) {
     if (!conv) { Q0 = K[0]; Q1 = K[1]; Q2 = K[2]; }
-    const double s_ = stage_val(x[0], Q0), n_ = stage_val(x[1], Q1), psi = stage_val(x[2], Q2);
-    double kap, dkap, sp, cp;
+    const Real s_ = stage_val(x[0], Q0), n_ = stage_val(x[1], Q1), psi = stage_val(x[2], Q2);
+    Real kap, dkap, sp, cp;
     kappa_lookup(tr, s_, kap, dkap);
     sincos(psi, &sp, &cp);
-    const double iD = 1.0 / (1.0 + kap * n_);
-    const double num = vxi * cp - vyi * sp;
-    const double sdot = num * iD;
-    double R[3] = {Q0 - sdot, Q1 - (vxi * sp + vyi * cp), Q2 - (ri - kap * sdot)};
-    double J[3][3];
+    const Real iD = Real(1.0) / (Real(1.0) + kap * n_);
+    const Real num = vxi * cp - vyi * sp;
+    const Real sdot = num * iD;
+    Real R[3] = {Q0 - sdot, Q1 - (vxi * sp + vyi * cp), Q2 - (ri - kap * sdot)};
+    Real J[3][3];
     J[0][0] = -sdot * dkap * n_ * iD; J[0][1] = -sdot * kap * iD; J[0][2] = -(vxi * sp + vyi * cp) * iD;
-    J[1][0] = 0.0; J[1][1] = 0.0; J[1][2] = num;
+    J[1][0] = Real(0.0); J[1][1] = Real(0.0); J[1][2] = num;
     J[2][0] = -dkap * sdot - kap * J[0][0]; J[2][1] = -kap * J[0][1]; J[2][2] = -kap * J[0][2];
 #pragma unroll
     for (int j = 0; j < NS; j++)
 #pragma unroll
       for (int a = 0; a < 3; a++)
 #pragma unroll
-        for (int c = 0; c < 3; c++) Mp[a][3 * j + c] = ((t == j && a == c) ? 1.0 : 0.0) - ha[j] * J[a][c];
-    lu4_factor_solve<3>(Mp, R, t);
-    const double k0 = Q0 - R[0], k1 = Q1 - R[1], k2 = Q2 - R[2];
-    const double dmax = g4max(fmax(fabs(R[0]), fmax(fabs(R[1]), fabs(R[2]))));
-    const double kmax = g4max(fmax(fabs(k0), fmax(fabs(k1), fabs(k2))));
+        for (int c = 0; c < 3; c++) Mp[a][3 * j + c] = ((t == j && a == c) ? Real(1.0) : Real(0.0)) - ha[j] * J[a][c];
+    lu4_factor_solve<3, Real>(Mp, R, t);
+    const Real k0 = Q0 - R[0], k1 = Q1 - R[1], k2 = Q2 - R[2];
+    const Real dmax = g4max(fmax(fabs(R[0]), fmax(fabs(R[1]), fabs(R[2]))));
+    const Real kmax = g4max(fmax(fabs(k0), fmax(fabs(k1), fabs(k2))));
     if (!conv) {
       K[0] = k0; K[1] = k1; K[2] = k2;
       if (!(dmax == dmax)) { ok = false; conv = true; }
-      else if (dmax <= 1e-14 * (1.0 + kmax) || it >= MAX_NEWTON) conv = true;
+      else if (dmax <= newton_tol<Real>() * (Real(1.0) + kmax) || it >= MAX_NEWTON) conv = true;
     }
     if (__all_sync(FULLW, conv)) break;
   }
   // ---- hand over to phase 2 / 3: x_next, slopes, factors, Jacobian at this lane's collocation point
 #pragma unroll
   for (int a = 0; a < NX; a++) {
-    const double v = x[a] + g4sum(h * b4[t] * K[a]);
+    const Real v = g4sum(h * b4[t] * K[a]);           // increment x_next - x: added to the fp64 state in phase 3
     if (t == 0) sm[(OFF_XN + a) * NI] = v;
     sm[(OFF_K + t * 8 + a) * NI] = K[a];
   }
@@ -290,60 +299,61 @@ __device__ bool irk_newton4(const int t, const double* __restrict__ x, double u0
 #pragma unroll
     for (int c = 0; c < 12; c++) sm[(OFF_MP + (3 * t + r) * 12 + c) * NI] = Mp[r][c];
   {
-    double xs[NX], f[NX], J[NX][NZ];
+    Real xs[NX], f[NX], J[NX][NZ];
 #pragma unroll
     for (int a = 0; a < NX; a++) xs[a] = stage_val(x[a], K[a]);
-    fkin6<true>(xs, u0, u1, p, tr, f, J);
+    fkin6<true, Real>(xs, u0, u1, p, tr, f, J);
 #pragma unroll
     for (int r = 0; r < 6; r++)
 #pragma unroll
       for (int c = 0; c < NZ; c++)
-        if (jslot(r, c) >= 0) sm[(OFF_J + t * 33 + jslot(r, c)) * NI] = ((JMASK[r] >> c) & 1u) ? J[r][c] : 0.0;
+        if (jslot(r, c) >= 0) sm[(OFF_J + t * 33 + jslot(r, c)) * NI] = ((JMASK[r] >> c) & 1u) ? J[r][c] : Real(0.0);
   }
-  return g4max(ok ? 0.0 : 1.0) == 0.0;
+  return g4max(ok ? Real(0.0) : Real(1.0)) == Real(0.0);
 }
 
 // ---- phase 2: one column of d x_next / d (x, u):  (I - h A (x) J) dK = J_x E + J_u by block forward
 // substitution through the shared factors.  `col` is uniform over the warp.
-__device__ void irk_sens_column(const int col, const double* __restrict__ sm, double h, const double* __restrict__ A4,
-                                const double* __restrict__ b4, const double* __restrict__ wT,
-                                const double* __restrict__ wD, double itT, double itD, double* __restrict__ Scol) {
-  const double* const Mv = sm + OFF_MV * NI;
-  const double* const Mp = sm + OFF_MP * NI;
+template <typename Real>
+__device__ void irk_sens_column(const int col, const Real* __restrict__ sm, Real h, const Real* __restrict__ A4,
+                                const Real* __restrict__ b4, const Real* __restrict__ wT,
+                                const Real* __restrict__ wD, Real itT, Real itD, Real* __restrict__ Scol) {
+  const Real* const Mv = sm + OFF_MV * NI;
+  const Real* const Mp = sm + OFF_MP * NI;
 #define JC(i, r, c) sm[(OFF_J + (i) * 33 + jslot(r, c)) * NI]
-  double dK[NS], dX6[NS], dX7[NS], dX3[NS], dX4[NS], dX5[NS];
-  auto stage_sum = [&](const double* dk, double* dx) {
+  Real dK[NS], dX6[NS], dX7[NS], dX3[NS], dX4[NS], dX5[NS];
+  auto stage_sum = [&](const Real* dk, Real* dx) {
 #pragma unroll
     for (int i = 0; i < NS; i++) {
-      double v = 0.0;
+      Real v = Real(0.0);
 #pragma unroll
       for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], dk[j], v);
       dx[i] = v;
     }
   };
-  auto out_row = [&](int a, const double* dk) {
-    double v = (a == col) ? 1.0 : 0.0;
+  auto out_row = [&](int a, const Real* dk) {
+    Real v = (a == col) ? Real(1.0) : Real(0.0);
 #pragma unroll
     for (int i = 0; i < NS; i++) v = fma(h * b4[i], dk[i], v);
     Scol[a] = v;
   };
   // actuators (closed form)
 #pragma unroll
-  for (int i = 0; i < NS; i++) dK[i] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : 0.0;
+  for (int i = 0; i < NS; i++) dK[i] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : Real(0.0);
   stage_sum(dK, dX6); out_row(6, dK);
 #pragma unroll
-  for (int i = 0; i < NS; i++) dK[i] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : 0.0;
+  for (int i = 0; i < NS; i++) dK[i] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : Real(0.0);
   stage_sum(dK, dX7); out_row(7, dK);
   // (v_x, v_y)
   const bool vcol = (SMASK[3] >> col) & 1u;
-  double dK3[NS], dK4[NS];
+  Real dK3[NS], dK4[NS];
   if (vcol) {
-    double Rv[8];
+    Real Rv[8];
 #pragma unroll
     for (int i = 0; i < NS; i++)
 #pragma unroll
       for (int a = 0; a < 2; a++) {
-        double v = 0.0;
+        Real v = Real(0.0);
         if (col == 3) v = JC(i, 3 + a, 3);
         else if (col == 4) v = JC(i, 3 + a, 4);
         else if (col == 6) v = JC(i, 3 + a, 6);
@@ -353,19 +363,19 @@ __device__ void irk_sens_column(const int col, const double* __restrict__ sm, do
         v = fma(JC(i, 3 + a, 7), dX7[i], v);
         Rv[2 * i + a] = v;
       }
-    lu_solve<8>(Mv, Rv);
+    lu_solve<8, Real>(Mv, Rv);
 #pragma unroll
     for (int i = 0; i < NS; i++) { dK3[i] = Rv[2 * i]; dK4[i] = Rv[2 * i + 1]; }
   } else {
 #pragma unroll
-    for (int i = 0; i < NS; i++) dK3[i] = dK4[i] = 0.0;
+    for (int i = 0; i < NS; i++) dK3[i] = dK4[i] = Real(0.0);
   }
   stage_sum(dK3, dX3); stage_sum(dK4, dX4);
   out_row(3, dK3); out_row(4, dK4);
   // r
 #pragma unroll
   for (int i = 0; i < NS; i++) {
-    double v = 0.0;
+    Real v = Real(0.0);
     if (col == 3) v = JC(i, 5, 3);
     else if (col == 4) v = JC(i, 5, 4);
     else if (col == 6) v = JC(i, 5, 6);
@@ -374,16 +384,16 @@ __device__ void irk_sens_column(const int col, const double* __restrict__ sm, do
     v = fma(JC(i, 5, 3), dX3[i], v);
     v = fma(JC(i, 5, 6), dX6[i], v);
     v = fma(JC(i, 5, 7), dX7[i], v);
-    dK[i] = vcol ? v : 0.0;
+    dK[i] = vcol ? v : Real(0.0);
   }
   stage_sum(dK, dX5); out_row(5, dK);
   // (s, n, psi)
-  double Rp[12];
+  Real Rp[12];
 #pragma unroll
   for (int i = 0; i < NS; i++)
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-      double v = 0.0;
+      Real v = Real(0.0);
       if (col == 0) v = JC(i, a, 0);
       else if (col == 1) v = JC(i, a, 1);
       else if (col == 2) v = JC(i, a, 2);
@@ -395,10 +405,10 @@ __device__ void irk_sens_column(const int col, const double* __restrict__ sm, do
       v = fma(JC(i, a, 5), dX5[i], v);
       Rp[3 * i + a] = v;
     }
-  lu_solve<12>(Mp, Rp);
+  lu_solve<12, Real>(Mp, Rp);
 #pragma unroll
   for (int a = 0; a < 3; a++) {
-    double dk[NS];
+    Real dk[NS];
 #pragma unroll
     for (int i = 0; i < NS; i++) dk[i] = Rp[3 * i + a];
     out_row(a, dk);
@@ -410,10 +420,16 @@ __device__ void irk_sens_column(const int col, const double* __restrict__ sm, do
 #define LIN_MIN_BLOCKS 2
 #endif
 constexpr int NCG = 4;     // column groups: a thread of phase 2 handles the columns cg, cg + 4, (cg + 8)
-// grid: ceil(B*N / NI) blocks of NI * NCG threads; dynamic shared memory PER_INT * NI doubles.
-// 2 blocks per SM by shared memory; 8 warps per SM leave phase 1 its registers.
+// grid: ceil(B*N / NI) blocks of NI * NCG threads; dynamic shared memory PER_INT * NI scalars.
+// Real = double: 2 blocks per SM by shared memory; 8 warps per SM leave phase 1 its registers.
+// Real = float (ihm2b_config::linearize_fp32, the mixed-precision path): the collocation system, its Newton solves and
+// the sensitivities in fp32; the iterate is read and [B A], c, phi are written in fp64, the state increment of the step
+// is added to the fp64 state and c = phi - A x - B u is formed in fp64, so the QP sees dynamics that are consistent to
+// round-off with an integrator that is accurate to ~1e-6 relative.
+template <typename Real>
 __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel(const KCfg cf, const Work w) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Real* const smem = reinterpret_cast<Real*>(smem_raw);
   __shared__ int s_ok[NI];
   const int tid = threadIdx.x;
   const int j = tid & (NI - 1), cg = tid / NI;           // interval of the block, column group (warp-uniform)
@@ -421,10 +437,13 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
   const bool in_range = gid < cf.B * cf.N;
   const int b = in_range ? gid / cf.N : 0, k = in_range ? gid - b * cf.N : 0;
   const bool live = in_range && !(w.active && !w.active[b]);   // SQP mode: instance already converged or failed
-  double* const sm = smem + j;
-  double wa[8];
-  for (int i = 0; i < 8; i++) wa[i] = __ldg(w.actw + (size_t)b * 8 + i);
-  const double itT = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TT), itD = 1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TD);
+  Real* const sm = smem + j;
+  Real wa[8], tabA[16], tabb[4];
+  for (int i = 0; i < 8; i++) wa[i] = (Real)__ldg(w.actw + (size_t)b * 8 + i);
+  for (int i = 0; i < 16; i++) tabA[i] = (Real)cf.irk_A[i];
+  for (int i = 0; i < 4; i++) tabb[i] = (Real)cf.irk_b[i];
+  const Real itT = (Real)(1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TT)), itD = (Real)(1.0 / __ldg(w.params + (size_t)b * NP + IHM2B_P_TD));
+  const Real hh = (Real)cf.dt;
   const size_t sk = (size_t)b * cf.N + k;
   {
     // phase 1: lanes 4q .. 4q + 3 of warp wp work on interval 8 wp + q of the block
@@ -436,12 +455,14 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
     if (__any_sync(0xffffffffu, live1)) {     // a warp whose 8 intervals are all masked out (SQP / line search / closed loop) skips
       const int tk = w.track[b1];
       TrackView tr{cf.n_grid, w.s_ref + (size_t)tk * cf.n_grid, w.kappa_ref + (size_t)tk * cf.n_grid};
-      double p[NP], x[NX], wa1[8];
-      for (int i = 0; i < NP; i++) p[i] = __ldg(w.params + (size_t)b1 * NP + i);
-      for (int i = 0; i < 8; i++) wa1[i] = __ldg(w.actw + (size_t)b1 * 8 + i);
-      for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b1 * (cf.N + 1) + k1) * NX + i];
-      const double u0 = w.u[((size_t)b1 * cf.N + k1) * NU], u1 = w.u[((size_t)b1 * cf.N + k1) * NU + 1];
-      const bool ok = irk_newton4(t, x, u0, u1, p, tr, cf.dt, cf.irk_A, cf.irk_b, wa1, wa1 + 4, smem + j1);
+      Real p[NP], x[NX], wa1[8];
+      for (int i = 0; i < NP; i++) p[i] = (Real)__ldg(w.params + (size_t)b1 * NP + i);
+      for (int i = 0; i < 8; i++) wa1[i] = (Real)__ldg(w.actw + (size_t)b1 * 8 + i);
+      for (int i = 0; i < NX; i++) x[i] = (Real)w.x[((size_t)b1 * (cf.N + 1) + k1) * NX + i];
+      const Real u0 = (Real)w.u[((size_t)b1 * cf.N + k1) * NU], u1 = (Real)w.u[((size_t)b1 * cf.N + k1) * NU + 1];
+      const double lag_d[2] = {(w.u[((size_t)b1 * cf.N + k1) * NU] - w.x[((size_t)b1 * (cf.N + 1) + k1) * NX + 6]) / __ldg(w.params + (size_t)b1 * NP + IHM2B_P_TT),
+                               (w.u[((size_t)b1 * cf.N + k1) * NU + 1] - w.x[((size_t)b1 * (cf.N + 1) + k1) * NX + 7]) / __ldg(w.params + (size_t)b1 * NP + IHM2B_P_TD)};
+      const bool ok = irk_newton4<Real>(t, x, u0, u1, p, tr, hh, tabA, tabb, wa1, wa1 + 4, lag_d, smem + j1);
       if (t == 0) s_ok[j1] = ok;
     }
   }
@@ -450,11 +471,11 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
   if (live) {
 #pragma unroll 1
     for (int col = cg; col < NZ; col += NCG) {
-      double Scol[NX];
-      irk_sens_column(col, sm, cf.dt, cf.irk_A, cf.irk_b, wa, wa + 4, itT, itD, Scol);
+      Real Scol[NX];
+      irk_sens_column<Real>(col, sm, hh, tabA, tabb, wa, wa + 4, itT, itD, Scol);
       const int oc = (col < NX) ? 2 + col : col - NX;     // [B A] column of d/d(x,u) column `col`
 #pragma unroll
-      for (int a = 0; a < NX; a++) ba[a * NZ + oc] = Scol[a];
+      for (int a = 0; a < NX; a++) ba[a * NZ + oc] = (double)Scol[a];
     }
   }
   __syncthreads();
@@ -464,7 +485,7 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
     for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
     const double u0 = w.u[sk * NU], u1 = w.u[sk * NU + 1];
     for (int i = 0; i < NX; i++) {
-      const double xn = sm[(OFF_XN + i) * NI];
+      const double xn = x[i] + (double)sm[(OFF_XN + i) * NI];     // fp64 state + the step's increment
       double ci = ok ? xn - ba[i * NZ] * u0 - ba[i * NZ + 1] * u1 : nan("");
       for (int c = 0; c < NX; c++) ci = fma(-ba[i * NZ + 2 + c], x[c], ci);
       w.c[sk * NX + i] = ci;
@@ -473,18 +494,26 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
   }
 }
 
-void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream) {
+namespace {
+template <typename Real>
+void launch_irk_instance(int slot, const KCfg& cf, const Work& w, cudaStream_t stream) {
   const int total = cf.B * cf.N;
-  const int bytes = PER_INT * NI * (int)sizeof(double);
-  // the dynamic shared-memory limit is a per-device attribute: remembered per device
-  static bool configured[64] = {};
+  const int bytes = PER_INT * NI * (int)sizeof(Real);
+  // the dynamic shared-memory limit is a per-device attribute of each kernel instance: remembered per (instance, device)
+  static bool configured[2][64] = {};
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return;
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
-    if (cudaFuncSetAttribute(linearize_irk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return;   // the launch below then reports the error
-    if (dev >= 0 && dev < 64) configured[dev] = true;
+  if (dev < 0 || dev >= 64 || !configured[slot][dev]) {
+    if (cudaFuncSetAttribute(linearize_irk_kernel<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return;   // the launch below then reports the error
+    if (dev >= 0 && dev < 64) configured[slot][dev] = true;
   }
-  linearize_irk_kernel<<<(total + NI - 1) / NI, NI * NCG, bytes, stream>>>(cf, w);
+  linearize_irk_kernel<Real><<<(total + NI - 1) / NI, NI * NCG, bytes, stream>>>(cf, w);
+}
+}  // namespace
+
+void launch_linearize_irk(const KCfg& cf, const Work& w, cudaStream_t stream) {
+  if (cf.lin_fp32) launch_irk_instance<float>(1, cf, w, stream);
+  else launch_irk_instance<double>(0, cf, w, stream);
 }
 
 }  // namespace ihm2b

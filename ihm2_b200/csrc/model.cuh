@@ -19,16 +19,17 @@ struct TrackView {
 // Largest i with s[i] <= sq, clamped to [0, n-2] (what the binary search of the "exact"
 // lookup returns); found from a uniform-grid guess plus a local walk, O(1) on the
 // reference's tables (three copies of a uniform lap grid, motion_planning.py:402-409).
-__device__ __forceinline__ void kappa_lookup(const TrackView& tr, double sq, double& kap,
-                                             double& dkap) {
+template <typename Real>
+__device__ __forceinline__ void kappa_lookup(const TrackView& tr, Real sq, Real& kap,
+                                             Real& dkap) {
   const int n = tr.n;
   const double s0 = __ldg(tr.s), s1 = __ldg(tr.s + n - 1);
-  double g = (sq - s0) / (s1 - s0) * (double)(n - 1);
+  double g = ((double)sq - s0) / (s1 - s0) * (double)(n - 1);
   int i = (g > 0.0) ? ((g < (double)(n - 2)) ? (int)g : n - 2) : 0;  // NaN -> 0
   while (i > 0 && __ldg(tr.s + i) > sq) i--;
   while (i < n - 2 && __ldg(tr.s + i + 1) <= sq) i++;
-  const double sa = __ldg(tr.s + i), sb = __ldg(tr.s + i + 1);
-  const double ka = __ldg(tr.k + i), kb = __ldg(tr.k + i + 1);
+  const Real sa = __ldg(tr.s + i), sb = __ldg(tr.s + i + 1);
+  const Real ka = __ldg(tr.k + i), kb = __ldg(tr.k + i + 1);
   dkap = (kb - ka) / (sb - sa);
   kap = ka + dkap * (sq - sa);
 }
@@ -51,47 +52,48 @@ __device__ __forceinline__ int table_segment(const TrackView& tr, double sq) {
 __device__ constexpr unsigned JMASK[NX] = {0x01F, 0x01C, 0x03F, 0x2D8, 0x2C8, 0x2C8, 0x140, 0x280};
 __device__ constexpr unsigned SMASK[NX] = {0x3FF, 0x3FF, 0x3FF, 0x3D8, 0x3D8, 0x3D8, 0x140, 0x280};
 
-// f[8] and, if JAC, J[8][10] (only the JMASK entries are written).
-template <bool JAC>
-__device__ __forceinline__ void fkin6(const double* __restrict__ x, const double u0,
-                                      const double u1, const double* __restrict__ p,
-                                      const TrackView& tr, double* __restrict__ f,
-                                      double (*J)[NZ]) {
-  const double n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
-  const double m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
-  const double C = lR / (lR + lF);
-  const double itT = 1.0 / p[IHM2B_P_TT], itD = 1.0 / p[IHM2B_P_TD], im = 1.0 / m;
+// f[8] and, if JAC, J[8][10] (only the JMASK entries are written).  Real: double, or float for the mixed-precision
+// lineariser (ihm2b_config::linearize_fp32).
+template <bool JAC, typename Real>
+__device__ __forceinline__ void fkin6(const Real* __restrict__ x, const Real u0,
+                                      const Real u1, const Real* __restrict__ p,
+                                      const TrackView& tr, Real* __restrict__ f,
+                                      Real (*J)[NZ]) {
+  const Real n = x[1], psi = x[2], vx = x[3], vy = x[4], r = x[5], T = x[6], dl = x[7];
+  const Real m = p[IHM2B_P_M], lR = p[IHM2B_P_LR], lF = p[IHM2B_P_LF];
+  const Real C = lR / (lR + lF);
+  const Real itT = Real(1.0) / p[IHM2B_P_TT], itD = Real(1.0) / p[IHM2B_P_TD], im = Real(1.0) / m;
 
-  const double ddot = (u1 - dl) * itD;
-  const double Tdot = (u0 - T) * itT;
+  const Real ddot = (u1 - dl) * itD;
+  const Real Tdot = (u0 - T) * itT;
 
-  const double Fm = p[IHM2B_P_CM0] * T;
-  const double th = tanh(10.0 * vx);
-  const double poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
-  const double Fd = -poly * th;
-  const double FRx = 0.5 * Fm + Fd, FFx = 0.5 * Fm;
+  const Real Fm = p[IHM2B_P_CM0] * T;
+  const Real th = tanh(Real(10.0) * vx);
+  const Real poly = p[IHM2B_P_CR0] + p[IHM2B_P_CR1] * vx + p[IHM2B_P_CR2] * vx * vx;
+  const Real Fd = -poly * th;
+  const Real FRx = Real(0.5) * Fm + Fd, FFx = Real(0.5) * Fm;
 
   // beta = atan(C tan(delta)): only sin/cos of beta are needed
-  double sd, cd;
+  Real sd, cd;
   sincos(dl, &sd, &cd);
-  const double td = sd / cd;
-  const double Ctd = C * td;
-  const double den = 1.0 + Ctd * Ctd;
-  const double cb = rsqrt(den), sb = Ctd * cb;
-  const double sec2 = 1.0 + td * td;
-  const double G = C * sec2 / den;  // d beta / d delta
-  const double bdot = G * ddot;
-  const double cdb = cd * cb + sd * sb, sdb = sd * cb - cd * sb;  // cos / sin (delta - beta)
-  const double vdot = (FRx * cb + FFx * cdb) * im;
+  const Real td = sd / cd;
+  const Real Ctd = C * td;
+  const Real den = Real(1.0) + Ctd * Ctd;
+  const Real cb = rsqrt(den), sb = Ctd * cb;
+  const Real sec2 = Real(1.0) + td * td;
+  const Real G = C * sec2 / den;  // d beta / d delta
+  const Real bdot = G * ddot;
+  const Real cdb = cd * cb + sd * sb, sdb = sd * cb - cd * sb;  // cos / sin (delta - beta)
+  const Real vdot = (FRx * cb + FFx * cdb) * im;
 
-  double kap, dkap;
+  Real kap, dkap;
   kappa_lookup(tr, x[0], kap, dkap);
-  double sp, cp;
+  Real sp, cp;
   sincos(psi, &sp, &cp);
-  const double iD = 1.0 / (1.0 + kap * n);
-  const double num = vx * cp - vy * sp;
-  const double sdot = num * iD;
-  const double vydot = vdot * sb + bdot * vx;
+  const Real iD = Real(1.0) / (Real(1.0) + kap * n);
+  const Real num = vx * cp - vy * sp;
+  const Real sdot = num * iD;
+  const Real vydot = vdot * sb + bdot * vx;
 
   f[0] = sdot;
   f[1] = vx * sp + vy * cp;
@@ -103,10 +105,10 @@ __device__ __forceinline__ void fkin6(const double* __restrict__ x, const double
   f[7] = ddot;
   if (!JAC) return;
 
-  const double ds_ds = -sdot * dkap * n * iD;
-  const double ds_dn = -sdot * kap * iD;
-  const double ds_dpsi = -(vx * sp + vy * cp) * iD;
-  const double ds_dvx = cp * iD, ds_dvy = -sp * iD;
+  const Real ds_ds = -sdot * dkap * n * iD;
+  const Real ds_dn = -sdot * kap * iD;
+  const Real ds_dpsi = -(vx * sp + vy * cp) * iD;
+  const Real ds_dvx = cp * iD, ds_dvy = -sp * iD;
   J[0][0] = ds_ds; J[0][1] = ds_dn; J[0][2] = ds_dpsi; J[0][3] = ds_dvx; J[0][4] = ds_dvy;
   J[1][2] = num; J[1][3] = sp; J[1][4] = cp;
   J[2][0] = -dkap * sdot - kap * ds_ds;
@@ -114,15 +116,15 @@ __device__ __forceinline__ void fkin6(const double* __restrict__ x, const double
   J[2][2] = -kap * ds_dpsi;
   J[2][3] = -kap * ds_dvx;
   J[2][4] = -kap * ds_dvy;
-  J[2][5] = 1.0;
-  const double dFd_dvx =
-      -(p[IHM2B_P_CR1] + 2.0 * p[IHM2B_P_CR2] * vx) * th - poly * 10.0 * (1.0 - th * th);
-  const double dG_ddl = 2.0 * C * (1.0 - C * C) * td * sec2 / (den * den);
-  const double dbdot_ddl = dG_ddl * ddot - G * itD;
-  const double dbdot_du = G * itD;
-  const double dvdot_dvx = dFd_dvx * cb * im;
-  const double dvdot_dT = 0.5 * p[IHM2B_P_CM0] * (cb + cdb) * im;
-  const double dvdot_ddl = (-FRx * sb * G - FFx * sdb * (1.0 - G)) * im;
+  J[2][5] = Real(1.0);
+  const Real dFd_dvx =
+      -(p[IHM2B_P_CR1] + Real(2.0) * p[IHM2B_P_CR2] * vx) * th - poly * Real(10.0) * (Real(1.0) - th * th);
+  const Real dG_ddl = Real(2.0) * C * (Real(1.0) - C * C) * td * sec2 / (den * den);
+  const Real dbdot_ddl = dG_ddl * ddot - G * itD;
+  const Real dbdot_du = G * itD;
+  const Real dvdot_dvx = dFd_dvx * cb * im;
+  const Real dvdot_dT = Real(0.5) * p[IHM2B_P_CM0] * (cb + cdb) * im;
+  const Real dvdot_ddl = (-FRx * sb * G - FFx * sdb * (Real(1.0) - G)) * im;
   J[3][3] = dvdot_dvx * cb;
   J[3][4] = -bdot;
   J[3][6] = dvdot_dT * cb;

@@ -97,14 +97,14 @@ __device__ void fdyn6_rhs(const double* __restrict__ x, const double* __restrict
 __device__ __forceinline__ void plant_rhs(const int model, const double* x, const double u0, const double u1,
                                           const double* p, const TrackView& tr, double* f) {
   if (model == IHM2B_SIM_FKIN6) {
-    fkin6<false>(x, u0, u1, p, tr, f, nullptr);
+    fkin6<false, double>(x, u0, u1, p, tr, f, nullptr);
   } else if (model == IHM2B_SIM_KIN6C) {
     // Cartesian kin6 (python/models.py:168-229): the v_x, v_y rows of fkin6, pose kinematics, and r_dot = v_y_dot / l_R
     // (fkin6 has l_R * v_y_dot - beta_dot there, :307)
     double xx[NX];
     for (int r = 0; r < NX; r++) xx[r] = x[r];
     xx[0] = 0.0; xx[1] = 0.0;
-    fkin6<false>(xx, u0, u1, p, tr, f, nullptr);
+    fkin6<false, double>(xx, u0, u1, p, tr, f, nullptr);
     double sp, cp;
     sincos(x[2], &sp, &cp);
     f[0] = x[3] * cp - x[4] * sp;

@@ -109,6 +109,10 @@ typedef struct ihm2b_config {
                              collapsed (status 4 after a few iterations instead of qp_max_iter); HPIPM has no such
                              test, 0 reproduces it */
   double qp_thr0;         /* floor of the initial slacks t (HPIPM thr0 = 0.1) */
+  int32_t linearize_fp32; /* 1: mixed precision -- the IRK collocation system, its Newton solves and the forward sensitivities
+                             in fp32 (the iterate, [B A], c and the QP stay fp64); north_star's reduced-precision bar is
+                             1e-4 relative per SQP-RTI step.  IRK integrator only. */
+  int32_t reserved_;
 } ihm2b_config;
 
 typedef struct ihm2b_handle ihm2b_handle;
