@@ -217,7 +217,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
     ALLOC(h->wr, (size_t)cfg->n_tracks * cfg->n_grid);
     ALLOC(h->wl, (size_t)cfg->n_tracks * cfg->n_grid);
     ALLOC(w.HC, B * (N + 1) * 16);
-    ALLOC(w.SS, B * (N + 1) * 8 * 16);
+    ALLOC(w.SS, B * (N + 1) * 8 * 8);
     ALLOC(w.CAB, B * (N + 1) * 2 * 16);
   }
   ALLOC(w.stats, B * 8);
@@ -573,10 +573,10 @@ int ihm2b_get_slacks_dev(ihm2b_handle* h, double* sL, double* sU, double* lamSL,
   if (!h->k.nl) return fail(IHM2B_EINVAL, "no soft rows without nonlinear_constraints");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t B = h->cfg.batch, N1 = h->cfg.N + 1;
-  const size_t row = N1 * 16 * sizeof(double);
+  const size_t row = N1 * 8 * sizeof(double);
   double* out[4] = {sL, sU, lamSL, lamSU};
   for (int i = 0; i < 4; i++)
-    if (out[i]) CU(cudaMemcpy2DAsync(out[i], row, h->w.SS + i * N1 * 16, 8 * row, row, B, cudaMemcpyDeviceToDevice, s));
+    if (out[i]) CU(cudaMemcpy2DAsync(out[i], row, h->w.SS + i * N1 * 8, 8 * row, row, B, cudaMemcpyDeviceToDevice, s));
   return IHM2B_OK;
 }
 

@@ -58,8 +58,8 @@ struct Work {
   double* HC;               // [B][N+1][16] linearised h rows: [0..2] d h0 / d (s, n, psi), [3] e0; [4..6], [7] the same
                             //              for h1; [8..11] d h4 / d (v_x, v_y, T, delta), [12] e4; [13] e2, [14] e3
                             //              (row value = coefficients . z + e; h2, h3 have the constant coefficients -+1/t)
-  double* SS;               // [B][N+1][8][16] slacks of the soft rows: sL, sU, their multipliers, second-order
-                            //              terms / steps of both, slack steps
+  double* SS;               // [B][8][N+1][8] slacks of the soft rows: sL, sU, their multipliers, second-order terms / steps
+                            //              of both, slack steps; 8 slots per stage (a lane has at most one soft row)
   double* CAB;              // [B][N+1][2][16] corrector terms per state / control: chi = CA - mu_t CB
   // outputs
   double* stats;            // [B][8]

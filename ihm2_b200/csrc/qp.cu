@@ -414,14 +414,16 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
     return fma(r.c0, pGX[k * 8 + hi0], fma(r.c1, X1, fma(r.c2, pGX[k * 8 + hi2], r.c3 * pGX[k * 8 + 7])));
   };
   // SS arrays (NL)
-  double* __restrict__ const pSL = NL ? w.SS + (size_t)b * N1 * 8 * 16 : nullptr;   // [N1][16] each
-  double* __restrict__ const pSU = pSL + N1 * 16;
-  double* __restrict__ const pLSL = pSU + N1 * 16;
-  double* __restrict__ const pLSU = pLSL + N1 * 16;
-  double* __restrict__ const pDS1 = pLSU + N1 * 16;   // dlamS_aff * ds_aff (L) -> dlamSL
-  double* __restrict__ const pDS2 = pDS1 + N1 * 16;
-  double* __restrict__ const pE1 = pDS2 + N1 * 16;    // dsL, dsU of the corrected step
-  double* __restrict__ const pE2 = pE1 + N1 * 16;
+  // a lane has at most one soft row per stage (path: lanes 0, 1, 4 their h row, lanes 6, 7 the T / delta bound;
+  // terminal: lanes 0, 1 their h row, lanes 2, 3 the v_y / r bound): the slack arrays carry 8 slots per stage, slot = lane
+  double* __restrict__ const pSL = NL ? w.SS + (size_t)b * N1 * 8 * 8 : nullptr;   // [N1][8] each
+  double* __restrict__ const pSU = pSL + N1 * 8;
+  double* __restrict__ const pLSL = pSU + N1 * 8;
+  double* __restrict__ const pLSU = pLSL + N1 * 8;
+  double* __restrict__ const pDS1 = pLSU + N1 * 8;   // dlamS_aff * ds_aff (L) -> dlamSL
+  double* __restrict__ const pDS2 = pDS1 + N1 * 8;
+  double* __restrict__ const pE1 = pDS2 + N1 * 8;    // dsL, dsU of the corrected step
+  double* __restrict__ const pE2 = pE1 + N1 * 8;
   double* __restrict__ const pCA = NL ? w.CAB + (size_t)b * N1 * 2 * 16 : nullptr;  // [N1][16]: [a] state a, [8 + a] control a
   double* __restrict__ const pCB = pCA + N1 * 16;
   if (NL) {
@@ -468,8 +470,11 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
     const double Z = term ? Zt : Zp, zz = term ? zt : zp;
     const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
     Norms nm{rd_m, rm_m, rs_m, S0};
-    const RowA A0 = soft_row_A(act0, soft0, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
-    const RowA A1 = soft_row_A(act1, true, v1, hlb, hub, isc1, Z, zz, r1, nm);
+    // a lane has at most one soft row: its h row if it has one (then its static row is hard), else its static row
+    const RowA AS = act1 ? soft_row_A(true, true, v1, hlb, hub, isc1, Z, zz, r1, nm)
+                         : soft_row_A(act0, soft0, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
+    const RowA AH = soft_row_A(act1 && act0, false, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
+    const RowA A0 = act1 ? AH : AS, A1 = act1 ? AS : RowA{0.0, 0.0, 0.0};
     rd_m = nm.rd; rm_m = nm.rm; rs_m = nm.rs; S0 = nm.S0;
     const CtDef& ct = term ? ctT : ctP;
     const double* h = pHC + k * 16;
@@ -533,9 +538,12 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       if (on) {
         const int e0 = k * 16 + a, e1 = e0 + 8;
         pLL[e0] = r0.lamL; pLU[e0] = r0.lamU; pTL[e0] = r0.tL; pTU[e0] = r0.tU;
-        pSL[e0] = r0.sL; pSU[e0] = r0.sU; pLSL[e0] = r0.lsL; pLSU[e0] = r0.lsU;
         pLL[e1] = r1.lamL; pLU[e1] = r1.lamU; pTL[e1] = r1.tL; pTU[e1] = r1.tU;
-        pSL[e1] = r1.sL; pSU[e1] = r1.sU; pLSL[e1] = r1.lsL; pLSU[e1] = r1.lsU;
+        {
+          const RowSt& rs = act1 ? r1 : r0;      // the lane's soft row, if it has one (defaults otherwise)
+          const int es = k * 8 + a;
+          pSL[es] = rs.sL; pSU[es] = rs.sU; pLSL[es] = rs.lsL; pLSU[es] = rs.lsU;
+        }
         pPI[k * 8 + a] = 0.0;
       }
       rows_A_nl(k, on, term, act0, v0, r0, act1, v1, r1);
@@ -848,7 +856,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
           const double Z = term ? Zt : Zp, zz = term ? zt : zp;
           const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (a < 2 || (a == 4 && !term));
           const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
-          const int e0 = k * 16 + a, e1 = e0 + 8;
+          const int e0 = k * 16 + a, e1 = e0 + 8, es = k * 8 + a;
           const double xa_ = pX[k * 8 + a], u0v = pU[(term ? 0 : k) * 2], u1v = pU[(term ? 0 : k) * 2 + 1];
           const double v0 = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
           const HRow hr = hrow_coef(k);
@@ -856,45 +864,69 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
           const double cdz0 = R.cu * pDU[k * 2 + R.iu] + R.cx * pDX[k * 8 + R.ix];
           const double cdz1 = hrow_cdz(hr, k);
           double ddl0 = 0.0, ddl1 = 0.0, A0 = 0.0, B0 = 0.0, A1 = 0.0, B1 = 0.0;
-#pragma unroll
-          for (int hh = 0; hh < 2; hh++) {
-            const bool act = hh ? act1 : act0, soft = hh ? true : soft0;
-            const int e = hh ? e1 : e0;
-            if (act) {
-              const double v = hh ? v1 : v0, lb = hh ? hlb : R.lb, ub = hh ? hub : R.ub, cdz = hh ? cdz1 : cdz0;
+          // the lane's (possibly) soft row S -- its h row if it has one, else its static row -- and, for lanes with an
+          // h row, the static row H (hard).  The slack algebra runs once per lane.
+          {
+            const bool sS = act1, actS = act1 || act0, softS = act1 || soft0;
+            const int e = sS ? e1 : e0;
+            double dS = 0.0, aS = 0.0, bS = 0.0;
+            if (actS) {
+              const double v = sS ? v1 : v0, lb = sS ? hlb : R.lb, ub = sS ? hub : R.ub, cdz = sS ? cdz1 : cdz0;
               RowSt r{pLL[e], pLU[e], pTL[e], pTU[e], 1.0, 1.0, 0.0, 0.0};
-              if (soft) { r.sL = pSL[e]; r.sU = pSU[e]; r.lsL = pLSL[e]; r.lsU = pLSU[e]; }
+              if (softS) { r.sL = pSL[es]; r.sU = pSU[es]; r.lsL = pLSL[es]; r.lsU = pLSU[es]; }
               if (pred) {
-                const RowStep st = soft_row_step(soft, v, lb, ub, cdz, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
+                const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
                 S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
                 const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
                 double dSL = 0.0, dSU = 0.0;
                 S2 += dL + dU;
                 ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
                 ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
-                if (soft) {
+                if (softS) {
                   dSL = st.dlsL * st.dsL; dSU = st.dlsU * st.dsU;
                   S1 += r.lsL * st.dsL + r.lsU * st.dsU; S1d += r.sL * st.dlsL + r.sU * st.dlsU; S2 += dSL + dSU;
                   ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
                   ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
-                  pDS1[e] = dSL; pDS2[e] = dSU;
+                  pDS1[es] = dSL; pDS2[es] = dSU;
                 }
                 pD1[e] = dL; pD2[e] = dU;
-                soft_row_chi(soft, Z, r, dL, dU, dSL, dSU, hh ? A1 : A0, hh ? B1 : B0);
+                soft_row_chi(softS, Z, r, dL, dU, dSL, dSU, aS, bS);
               } else {
-                const double cSL = soft ? pDS1[e] - mu_t : 0.0, cSU = soft ? pDS2[e] - mu_t : 0.0;
-                const RowStep st = soft_row_step(soft, v, lb, ub, cdz, Z, zz, r, pD1[e] - mu_t, pD2[e] - mu_t, cSL, cSU);
+                const double cSL = softS ? pDS1[es] - mu_t : 0.0, cSU = softS ? pDS2[es] - mu_t : 0.0;
+                const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, pD1[e] - mu_t, pD2[e] - mu_t, cSL, cSU);
                 pD1[e] = st.dlL; pD2[e] = st.dlU;
-                (hh ? ddl1 : ddl0) = st.dlL - st.dlU;
+                dS = st.dlL - st.dlU;
                 ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
                 ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
-                if (soft) {
-                  pDS1[e] = st.dlsL; pDS2[e] = st.dlsU; pE1[e] = st.dsL; pE2[e] = st.dsU;
+                if (softS) {
+                  pDS1[es] = st.dlsL; pDS2[es] = st.dlsU; pE1[es] = st.dsL; pE2[es] = st.dsU;
                   ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
                   ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
                 }
               }
             }
+            double dH = 0.0, aH = 0.0, bH = 0.0;
+            if (act1 && act0) {          // static row of a lane that also holds an h row: hard
+              const RowSt r{pLL[e0], pLU[e0], pTL[e0], pTU[e0], 1.0, 1.0, 0.0, 0.0};
+              if (pred) {
+                const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
+                S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
+                const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
+                S2 += dL + dU;
+                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                pD1[e0] = dL; pD2[e0] = dU;
+                soft_row_chi(false, Z, r, dL, dU, 0.0, 0.0, aH, bH);
+              } else {
+                const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, pD1[e0] - mu_t, pD2[e0] - mu_t, 0.0, 0.0);
+                pD1[e0] = st.dlL; pD2[e0] = st.dlU;
+                dH = st.dlL - st.dlU;
+                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+              }
+            }
+            ddl0 = sS ? dH : dS; ddl1 = sS ? dS : 0.0;
+            A0 = sS ? aH : aS; B0 = sS ? bH : bS; A1 = sS ? aS : 0.0; B1 = sS ? bS : 0.0;
           }
           const CtDef& ct = term ? ctT : ctP;
           const double* h = pHC + k * 16;
@@ -1114,7 +1146,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         const RowDef& R = term ? Rt : Rp;
         const bool act0 = on && (term ? (a < 4) : (a < 4 || k > 0)), act1 = on && (a < 2 || (a == 4 && !term));
         const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
-        const int e0 = k * 16 + a, e1 = e0 + 8, ku = term ? 0 : k;
+        const int e0 = k * 16 + a, e1 = e0 + 8, es = k * 8 + a, ku = term ? 0 : k;
         const double xa_ = pX[k * 8 + a], pia = pPI[k * 8 + a], u0v = pU[ku * 2], u1v = pU[ku * 2 + 1];
         const HRow hr = hrow_coef(k);
         const double v0o = row_value(R, term, R.iu ? u1v : u0v, __shfl_sync(FULL, xa_, R.ix, GROUP));
@@ -1127,26 +1159,33 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         const double v0 = row_value(R, term, R.iu ? u1n : u0n, __shfl_sync(FULL, xn_, R.ix, GROUP));
         const double v1 = hrow_val(hr, xn_, u0n, u1n);
         RowSt r0{0.0, 0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0}, r1 = r0;
-#pragma unroll
-        for (int hh = 0; hh < 2; hh++) {
-          const bool act = hh ? act1 : act0, soft = hh ? true : soft0;
-          const int e = hh ? e1 : e0;
-          if (act) {
-            const double vo = hh ? v1o : v0o, lb = hh ? hlb : R.lb, ub = hh ? hub : R.ub, cdz = hh ? cdz1 : cdz0;
+        {
+          const bool sS = act1, actS = act1 || act0, softS = act1 || soft0;
+          const int e = sS ? e1 : e0;
+          if (actS) {
+            const double vo = sS ? v1o : v0o, lb = sS ? hlb : R.lb, ub = sS ? hub : R.ub, cdz = sS ? cdz1 : cdz0;
             RowSt r{pLL[e], pLU[e], pTL[e], pTU[e], 1.0, 1.0, 0.0, 0.0};
             double dsL = 0.0, dsU = 0.0;
-            if (soft) { r.sL = pSL[e]; r.sU = pSU[e]; r.lsL = pLSL[e]; r.lsU = pLSU[e]; dsL = pE1[e]; dsU = pE2[e]; }
-            const double rdL = soft ? vo + r.sL - lb - r.tL : vo - lb - r.tL;
-            const double rdU = soft ? ub + r.sU - vo - r.tU : ub - vo - r.tU;
+            if (softS) { r.sL = pSL[es]; r.sU = pSU[es]; r.lsL = pLSL[es]; r.lsU = pLSU[es]; dsL = pE1[es]; dsU = pE2[es]; }
+            const double rdL = softS ? vo + r.sL - lb - r.tL : vo - lb - r.tL;
+            const double rdU = softS ? ub + r.sU - vo - r.tU : ub - vo - r.tU;
             r.tL = fma(alpha, cdz + dsL + rdL, r.tL); r.tU = fma(alpha, -cdz + dsU + rdU, r.tU);
             r.lamL = fma(alpha_d, pD1[e], r.lamL); r.lamU = fma(alpha_d, pD2[e], r.lamU);
             pLL[e] = r.lamL; pLU[e] = r.lamU; pTL[e] = r.tL; pTU[e] = r.tU;
-            if (soft) {
+            if (softS) {
               r.sL = fma(alpha, dsL, r.sL); r.sU = fma(alpha, dsU, r.sU);
-              r.lsL = fma(alpha_d, pDS1[e], r.lsL); r.lsU = fma(alpha_d, pDS2[e], r.lsU);
-              pSL[e] = r.sL; pSU[e] = r.sU; pLSL[e] = r.lsL; pLSU[e] = r.lsU;
+              r.lsL = fma(alpha_d, pDS1[es], r.lsL); r.lsU = fma(alpha_d, pDS2[es], r.lsU);
+              pSL[es] = r.sL; pSU[es] = r.sU; pLSL[es] = r.lsL; pLSU[es] = r.lsU;
             }
-            if (hh) r1 = r; else r0 = r;
+            if (sS) r1 = r; else r0 = r;
+          }
+          if (act1 && act0) {        // static row of a lane that also holds an h row: hard
+            RowSt r{pLL[e0], pLU[e0], pTL[e0], pTU[e0], 1.0, 1.0, 0.0, 0.0};
+            const double rdL = v0o - R.lb - r.tL, rdU = R.ub - v0o - r.tU;
+            r.tL = fma(alpha, cdz0 + rdL, r.tL); r.tU = fma(alpha, -cdz0 + rdU, r.tU);
+            r.lamL = fma(alpha_d, pD1[e0], r.lamL); r.lamU = fma(alpha_d, pD2[e0], r.lamU);
+            pLL[e0] = r.lamL; pLU[e0] = r.lamU; pTL[e0] = r.tL; pTU[e0] = r.tU;
+            r0 = r;
           }
         }
         rows_A_nl(k, on, term, act0, v0, r0, act1, v1, r1);
@@ -1249,8 +1288,8 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
   const double* pPI = w.xa + (size_t)b * N1 * 8;
   const double* pLL = w.LT + (size_t)b * N1 * 4 * RS;
   const double* pLU = pLL + N1 * RS;
-  const double* pLSL = NL ? w.SS + ((size_t)b * 8 + 2) * N1 * 16 : nullptr;   // multipliers of sL, sU >= 0
-  const double* pLSU = pLSL + N1 * 16;
+  const double* pLSL = NL ? w.SS + ((size_t)b * 8 + 2) * N1 * 8 : nullptr;   // multipliers of sL, sU >= 0, [N1][8]: slot = lane
+  const double* pLSU = pLSL + N1 * 8;
   const double* gHC = NL ? w.HC + (size_t)b * N1 * 16 : nullptr;
   double itT = 0.0, itD = 0.0;
   if (NL) { itT = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TT]; itD = 1.0 / w.params[(size_t)b * NP + IHM2B_P_TD]; }
@@ -1267,14 +1306,14 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
   double rs = 0.0, re = fabs(pX[a] - x0[(size_t)b * 8 + a]), ri = 0.0, rc = 0.0;
   const unsigned seg = 0xffu << (8 * q);   // the segments run different trip counts
   // one two-sided row at value v: residuals; returns lamL - lamU.  Soft rows: slack eliminated, s* = violation
-  auto row_res = [&](bool soft, double v, double lb, double ub, int e, double Z, double zz) {
+  auto row_res = [&](bool soft, double v, double lb, double ub, int e, int es, double Z, double zz) {
     const double sL = soft ? fmax(0.0, lb - v) : 0.0, sU = soft ? fmax(0.0, v - ub) : 0.0;
     ri = nmax(ri, nmax(lb - sL - v, v - ub - sU));
     if (!have_mult) return 0.0;
     const double lamL = pLL[e], lamU = pLU[e];
     rc = nmax(rc, nmax(fabs(lamL * (v + sL - lb)), fabs(lamU * (ub + sU - v))));
     if (NL && soft) {
-      const double lsL = pLSL[e], lsU = pLSU[e];
+      const double lsL = pLSL[es], lsU = pLSU[es];
       rc = nmax(rc, nmax(fabs(lsL * sL), fabs(lsU * sU)));
       rs = nmax(rs, nmax(fabs(Z * sL + zz - lamL - lsL), fabs(Z * sU + zz - lamU - lsU)));
     }
@@ -1290,11 +1329,11 @@ __global__ void __launch_bounds__(32) nlp_residual_kernel(const KCfg cf, const W
     double dl = 0.0, dl1 = 0.0;
     if (act) {
       const double v = row_value(R, term, pU[(term ? 0 : k) * 2 + R.iu], pX[k * 8 + R.ix]);
-      dl = row_res(NL && (term ? (a == 2 || a == 3) : (a >= 6)), v, R.lb, R.ub, k * RS + a, Z, zz);
+      dl = row_res(NL && (term ? (a == 2 || a == 3) : (a >= 6)), v, R.lb, R.ub, k * RS + a, k * 8 + a, Z, zz);
     }
     if (NL && (a < 2 || (a == 4 && !term))) {
       const double v1 = hl.value(gHC + k * 16, pX + k * 8, term ? 0.0 : pU[k * 2], term ? 0.0 : pU[k * 2 + 1], a);
-      dl1 = row_res(true, v1, hl.lb, hl.ub, k * RS + 8 + a, Z, zz);
+      dl1 = row_res(true, v1, hl.lb, hl.ub, k * RS + 8 + a, k * 8 + a, Z, zz);
     }
     // C'(lamL - lamU): the rows of this stage live in the 8 lanes of this segment
     const CtDef& ct = term ? ctT : ctP;

@@ -200,9 +200,18 @@ class Engine:
         return pi, lamL, lamU
 
     def slacks(self):
-        """(sL, sU, lamSL, lamSU) [B,N+1,16] of the soft rows (nonlinear_constraints only)."""
-        out = [self._new(self.B, self.N + 1, 16) for _ in range(4)]
-        self._check(self.lib.ihm2b_get_slacks_dev(self._h, *[_dptr(t) for t in out], _stream()))
+        """(sL, sU, lamSL, lamSU) of the soft rows (nonlinear_constraints only), expanded to the 16 row slots per stage
+        of `multipliers()`: [B,N+1,16], zeros where a slot has no slack.  (The ABI returns 8 packed slots per stage.)"""
+        packed = [self._new(self.B, self.N + 1, 8) for _ in range(4)]
+        self._check(self.lib.ihm2b_get_slacks_dev(self._h, *[_dptr(t) for t in packed], _stream()))
+        out = []
+        N = self.N
+        for pk in packed:
+            t = torch.zeros(self.B, N + 1, 16, dtype=torch.float64, device=self.device)
+            t[:, :, 8] = pk[:, :, 0]; t[:, :, 9] = pk[:, :, 1]; t[:, :N, 12] = pk[:, :N, 4]      # h0, h1, a_lat
+            t[:, 1:N, 6:8] = pk[:, 1:N, 6:8]                                                   # soft bounds on T, delta
+            t[:, N, 2:4] = pk[:, N, 2:4]                                                       # terminal: v_y, r
+            out.append(t)
         return out
 
     def h_rows(self):

@@ -195,8 +195,9 @@ int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats_dev, void* stream);
  * formed, x_0 is eliminated).  lamL_dev / lamU_dev [B][N+1][RS]: multipliers of the lower / upper side of each row.
  * Sign convention: stationarity reads H z + g + [B' pi_{k+1}; A' pi_{k+1} - pi_k] - C'(lamL - lamU) = 0. */
 int ihm2b_get_multipliers_dev(ihm2b_handle* h, double* pi_dev, double* lamL_dev, double* lamU_dev, void* stream);
-/* slacks of the soft rows and the multipliers of s >= 0, [B][N+1][16] each (nonlinear_constraints only; any pointer
- * may be NULL) */
+/* slacks of the soft rows and the multipliers of s >= 0, [B][N+1][8] each (nonlinear_constraints only; any pointer
+ * may be NULL).  Slot j of a path stage: j = 0, 1 the track rows h0, h1; 4 a_lat; 6, 7 the soft bounds on T, delta
+ * (stages >= 1); terminal stage: 0, 1 the track rows, 2, 3 the soft bounds on v_y, r; other slots unused. */
 int ihm2b_get_slacks_dev(ihm2b_handle* h, double* sL_dev, double* sU_dev, double* lamSL_dev, double* lamSU_dev,
                          void* stream);
 /* the linearised rows of h at the last linearisation point, [B][N+1][16] (layout: csrc/common.cuh, Work::HC) */
