@@ -90,6 +90,13 @@ struct ihm2b_handle {
   int64_t launches;
 };
 
+// every entry point runs on the device the handle was created on, whatever the caller's current device is
+static int on_device(ihm2b_handle* h) {
+  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  CU(cudaSetDevice(h->device));
+  return IHM2B_OK;
+}
+
 namespace {
 
 template <typename T>
@@ -350,7 +357,7 @@ int ihm2b_set_params(ihm2b_handle* h, const double* params) {
 }
 
 int ihm2b_set_iterate_dev(ihm2b_handle* h, const double* x, const double* u, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t B = h->cfg.batch, N = h->cfg.N;
   if (x) CU(cudaMemcpyAsync(h->w.x, x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -359,7 +366,7 @@ int ihm2b_set_iterate_dev(ihm2b_handle* h, const double* x, const double* u, voi
 }
 
 int ihm2b_get_iterate_dev(ihm2b_handle* h, double* x, double* u, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t B = h->cfg.batch, N = h->cfg.N;
   if (x) CU(cudaMemcpyAsync(x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -368,7 +375,7 @@ int ihm2b_get_iterate_dev(ihm2b_handle* h, double* x, double* u, void* stream) {
 }
 
 int ihm2b_get_iterate_host(ihm2b_handle* h, double* x, double* u) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   const size_t B = h->cfg.batch, N = h->cfg.N;
   cudaStream_t s = nullptr;
   if (x) CU(cudaMemcpyAsync(x, h->w.x, B * (N + 1) * 8 * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -378,7 +385,7 @@ int ihm2b_get_iterate_host(ihm2b_handle* h, double* x, double* u) {
 }
 
 int ihm2b_reset_iterate(ihm2b_handle* h, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   const int total = h->cfg.batch * (h->cfg.N + 1);
   reset_iterate_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       h->cfg.batch, h->cfg.N, h->cfg.dt, h->cfg.T_max, h->w.x, h->w.u);
@@ -388,7 +395,7 @@ int ihm2b_reset_iterate(ihm2b_handle* h, void* stream) {
 }
 
 int ihm2b_shift_iterate(ihm2b_handle* h, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   const int total = h->cfg.batch * 10;
   shift_iterate_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       h->cfg.batch, h->cfg.N, h->w.x, h->w.u, h->w.active);
@@ -399,6 +406,7 @@ int ihm2b_shift_iterate(ihm2b_handle* h, void* stream) {
 
 static int check_ready(ihm2b_handle* h) {
   if (!h) return fail(IHM2B_EINVAL, "null handle");
+  CU(cudaSetDevice(h->device));
   if (!h->have_tracks) return fail(IHM2B_EINVAL, "ihm2b_set_tracks has not been called");
   if (h->cfg.nonlinear_constraints && !h->have_widths) return fail(IHM2B_EINVAL, "nonlinear_constraints: no track widths set");
   if (!h->have_params) return fail(IHM2B_EINVAL, "ihm2b_set_params has not been called");
@@ -558,7 +566,7 @@ int ihm2b_get_stats_dev(ihm2b_handle* h, double* stats, void* stream) {
 }
 
 int ihm2b_get_multipliers_dev(ihm2b_handle* h, double* pi, double* lamL, double* lamU, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t B = h->cfg.batch, N1 = h->cfg.N + 1, RS = h->k.nl ? 16 : 8;
   if (pi) CU(cudaMemcpyAsync(pi, h->w.xa, B * N1 * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -569,7 +577,7 @@ int ihm2b_get_multipliers_dev(ihm2b_handle* h, double* pi, double* lamL, double*
 }
 
 int ihm2b_get_slacks_dev(ihm2b_handle* h, double* sL, double* sU, double* lamSL, double* lamSU, void* stream) {
-  if (!h) return fail(IHM2B_EINVAL, "null handle");
+  { const int rc_ = on_device(h); if (rc_) return rc_; }
   if (!h->k.nl) return fail(IHM2B_EINVAL, "no soft rows without nonlinear_constraints");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t B = h->cfg.batch, N1 = h->cfg.N + 1;

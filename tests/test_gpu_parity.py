@@ -114,7 +114,7 @@ def test_config2_rti_matches_oracle(config2):
     sg = config2["status"]
     assert np.mean(sg == so) > 0.99                      # borderline-infeasible QPs may flip
     ok = (sg == 0) & (so == 0)
-    assert ok.sum() > 0.6 * len(sg)
+    assert ok.sum() > 0.75 * len(sg)                     # the rest are infeasible QPs (LP-certified in test_oracle_soft.py)
     assert rel(config2["u0"][ok], u0o[ok]) < REL_TOL
     assert rel(config2["x"][ok], xo[ok]) < REL_TOL and rel(config2["u"][ok], uo[ok]) < REL_TOL
     for c in range(8):                                   # per field, as the tolerance is stated
