@@ -312,105 +312,145 @@ __device__ bool irk_newton4(const int t, const Real* __restrict__ x, Real u0, Re
   return g4max(ok ? Real(0.0) : Real(1.0)) == Real(0.0);
 }
 
-// ---- phase 2: one column of d x_next / d (x, u):  (I - h A (x) J) dK = J_x E + J_u by block forward
-// substitution through the shared factors.  `col` is uniform over the warp.
-template <typename Real>
-__device__ void irk_sens_column(const int col, const Real* __restrict__ sm, Real h, const Real* __restrict__ A4,
-                                const Real* __restrict__ b4, const Real* __restrict__ wT,
-                                const Real* __restrict__ wD, Real itT, Real itD, Real* __restrict__ Scol) {
+// ---- phase 2: NC columns of d x_next / d (x, u) at once (columns col0, col0 + 4, ...):  (I - h A (x) J) dK = J_x E + J_u
+// by block forward substitution through the shared factors.  Every factor / Jacobian entry read from shared memory serves
+// all NC right-hand sides.  `col0` is uniform over the warp.
+template <int n, int NC, typename Real>
+__device__ __forceinline__ void lu_solve_multi(const Real* M, Real (&b)[NC][n]) {
+#pragma unroll
+  for (int r = 1; r < n; r++)
+#pragma unroll
+    for (int c = 0; c < r; c++) {
+      const Real l = M[(r * n + c) * NI];
+#pragma unroll
+      for (int q = 0; q < NC; q++) b[q][r] = fma(-l, b[q][c], b[q][r]);
+    }
+#pragma unroll
+  for (int r = n - 1; r >= 0; r--) {
+#pragma unroll
+    for (int c = r + 1; c < n; c++) {
+      const Real m = M[(r * n + c) * NI];
+#pragma unroll
+      for (int q = 0; q < NC; q++) b[q][r] = fma(-m, b[q][c], b[q][r]);
+    }
+    const Real ip = M[(r * n + r) * NI];
+#pragma unroll
+    for (int q = 0; q < NC; q++) b[q][r] *= ip;
+  }
+}
+
+template <int NC, typename Real>
+__device__ void irk_sens_columns(const int col0, const Real* __restrict__ sm, Real h, const Real* __restrict__ A4,
+                                 const Real* __restrict__ b4, const Real* __restrict__ wT,
+                                 const Real* __restrict__ wD, Real itT, Real itD, Real (&Scol)[NC][NX]) {
   const Real* const Mv = sm + OFF_MV * NI;
   const Real* const Mp = sm + OFF_MP * NI;
 #define JC(i, r, c) sm[(OFF_J + (i) * 33 + jslot(r, c)) * NI]
-  Real dK[NS], dX6[NS], dX7[NS], dX3[NS], dX4[NS], dX5[NS];
-  auto stage_sum = [&](const Real* dk, Real* dx) {
+  Real hA[NS][NS], hb[NS];
 #pragma unroll
-    for (int i = 0; i < NS; i++) {
-      Real v = Real(0.0);
+  for (int i = 0; i < NS; i++) {
+    hb[i] = h * b4[i];
 #pragma unroll
-      for (int j = 0; j < NS; j++) v = fma(h * A4[i * NS + j], dk[j], v);
-      dx[i] = v;
+    for (int j = 0; j < NS; j++) hA[i][j] = h * A4[i * NS + j];
+  }
+  // stage sums h A dK and output rows e_a + h b' dK of one quantity, for all columns
+  auto stage_sum = [&](const Real (&dk)[NC][NS], Real (&dx)[NC][NS]) {
+#pragma unroll
+    for (int q = 0; q < NC; q++)
+#pragma unroll
+      for (int i = 0; i < NS; i++) {
+        Real v = Real(0.0);
+#pragma unroll
+        for (int j = 0; j < NS; j++) v = fma(hA[i][j], dk[q][j], v);
+        dx[q][i] = v;
+      }
+  };
+  auto out_row = [&](int a, const Real (&dk)[NC][NS]) {
+#pragma unroll
+    for (int q = 0; q < NC; q++) {
+      Real v = (a == col0 + 4 * q) ? Real(1.0) : Real(0.0);
+#pragma unroll
+      for (int i = 0; i < NS; i++) v = fma(hb[i], dk[q][i], v);
+      Scol[q][a] = v;
     }
   };
-  auto out_row = [&](int a, const Real* dk) {
-    Real v = (a == col) ? Real(1.0) : Real(0.0);
-#pragma unroll
-    for (int i = 0; i < NS; i++) v = fma(h * b4[i], dk[i], v);
-    Scol[a] = v;
+  // direct term of row `row` of the Jacobian at stage i for column col (structural zeros are not stored)
+  auto direct = [&](int i, int row, int col) {
+    Real v = Real(0.0);
+    if (row < 3) {
+      if (col == 0) v = JC(i, row, 0);
+      else if (col == 1) v = JC(i, row, 1);
+      else if (col == 2) v = JC(i, row, 2);
+      else if (col == 3) v = JC(i, row, 3);
+      else if (col == 4) v = JC(i, row, 4);
+      else if (col == 5) v = JC(i, row, 5);
+    } else {
+      if (col == 3) v = JC(i, row, 3);
+      else if (col == 4) v = JC(i, row, 4);
+      else if (col == 6) v = JC(i, row, 6);
+      else if (col == 7) v = JC(i, row, 7);
+      else if (col == 9) v = JC(i, row, 9);
+    }
+    return v;
   };
+  Real dK[NC][NS], dX6[NC][NS], dX7[NC][NS], dX3[NC][NS], dX4[NC][NS], dX5[NC][NS];
   // actuators (closed form)
 #pragma unroll
-  for (int i = 0; i < NS; i++) dK[i] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : Real(0.0);
+  for (int q = 0; q < NC; q++)
+#pragma unroll
+    for (int i = 0; i < NS; i++) { const int col = col0 + 4 * q; dK[q][i] = (col == 6) ? -wT[i] * itT : (col == 8) ? wT[i] * itT : Real(0.0); }
   stage_sum(dK, dX6); out_row(6, dK);
 #pragma unroll
-  for (int i = 0; i < NS; i++) dK[i] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : Real(0.0);
+  for (int q = 0; q < NC; q++)
+#pragma unroll
+    for (int i = 0; i < NS; i++) { const int col = col0 + 4 * q; dK[q][i] = (col == 7) ? -wD[i] * itD : (col == 9) ? wD[i] * itD : Real(0.0); }
   stage_sum(dK, dX7); out_row(7, dK);
-  // (v_x, v_y)
-  const bool vcol = (SMASK[3] >> col) & 1u;
-  Real dK3[NS], dK4[NS];
-  if (vcol) {
-    Real Rv[8];
+  // (v_x, v_y): columns that do not reach these rows have a zero right-hand side and come out zero
+  Real dK3[NC][NS], dK4[NC][NS];
+  {
+    Real Rv[NC][8];
 #pragma unroll
     for (int i = 0; i < NS; i++)
 #pragma unroll
       for (int a = 0; a < 2; a++) {
-        Real v = Real(0.0);
-        if (col == 3) v = JC(i, 3 + a, 3);
-        else if (col == 4) v = JC(i, 3 + a, 4);
-        else if (col == 6) v = JC(i, 3 + a, 6);
-        else if (col == 7) v = JC(i, 3 + a, 7);
-        else if (col == 9) v = JC(i, 3 + a, 9);
-        v = fma(JC(i, 3 + a, 6), dX6[i], v);
-        v = fma(JC(i, 3 + a, 7), dX7[i], v);
-        Rv[2 * i + a] = v;
+        const Real j6 = JC(i, 3 + a, 6), j7 = JC(i, 3 + a, 7);
+#pragma unroll
+        for (int q = 0; q < NC; q++) Rv[q][2 * i + a] = fma(j6, dX6[q][i], fma(j7, dX7[q][i], direct(i, 3 + a, col0 + 4 * q)));
       }
-    lu_solve<8, Real>(Mv, Rv);
+    lu_solve_multi<8, NC, Real>(Mv, Rv);
 #pragma unroll
-    for (int i = 0; i < NS; i++) { dK3[i] = Rv[2 * i]; dK4[i] = Rv[2 * i + 1]; }
-  } else {
+    for (int q = 0; q < NC; q++)
 #pragma unroll
-    for (int i = 0; i < NS; i++) dK3[i] = dK4[i] = Real(0.0);
+      for (int i = 0; i < NS; i++) { dK3[q][i] = Rv[q][2 * i]; dK4[q][i] = Rv[q][2 * i + 1]; }
   }
   stage_sum(dK3, dX3); stage_sum(dK4, dX4);
   out_row(3, dK3); out_row(4, dK4);
   // r
 #pragma unroll
   for (int i = 0; i < NS; i++) {
-    Real v = Real(0.0);
-    if (col == 3) v = JC(i, 5, 3);
-    else if (col == 4) v = JC(i, 5, 4);
-    else if (col == 6) v = JC(i, 5, 6);
-    else if (col == 7) v = JC(i, 5, 7);
-    else if (col == 9) v = JC(i, 5, 9);
-    v = fma(JC(i, 5, 3), dX3[i], v);
-    v = fma(JC(i, 5, 6), dX6[i], v);
-    v = fma(JC(i, 5, 7), dX7[i], v);
-    dK[i] = vcol ? v : Real(0.0);
+    const Real j3 = JC(i, 5, 3), j6 = JC(i, 5, 6), j7 = JC(i, 5, 7);
+#pragma unroll
+    for (int q = 0; q < NC; q++) dK[q][i] = fma(j3, dX3[q][i], fma(j6, dX6[q][i], fma(j7, dX7[q][i], direct(i, 5, col0 + 4 * q))));
   }
   stage_sum(dK, dX5); out_row(5, dK);
   // (s, n, psi)
-  Real Rp[12];
+  Real Rp[NC][12];
 #pragma unroll
   for (int i = 0; i < NS; i++)
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-      Real v = Real(0.0);
-      if (col == 0) v = JC(i, a, 0);
-      else if (col == 1) v = JC(i, a, 1);
-      else if (col == 2) v = JC(i, a, 2);
-      else if (col == 3) v = JC(i, a, 3);
-      else if (col == 4) v = JC(i, a, 4);
-      else if (col == 5) v = JC(i, a, 5);
-      v = fma(JC(i, a, 3), dX3[i], v);
-      v = fma(JC(i, a, 4), dX4[i], v);
-      v = fma(JC(i, a, 5), dX5[i], v);
-      Rp[3 * i + a] = v;
+      const Real j3 = JC(i, a, 3), j4 = JC(i, a, 4), j5 = JC(i, a, 5);
+#pragma unroll
+      for (int q = 0; q < NC; q++) Rp[q][3 * i + a] = fma(j3, dX3[q][i], fma(j4, dX4[q][i], fma(j5, dX5[q][i], direct(i, a, col0 + 4 * q))));
     }
-  lu_solve<12, Real>(Mp, Rp);
+  lu_solve_multi<12, NC, Real>(Mp, Rp);
 #pragma unroll
   for (int a = 0; a < 3; a++) {
-    Real dk[NS];
+    Real dk[NC][NS];
 #pragma unroll
-    for (int i = 0; i < NS; i++) dk[i] = Rp[3 * i + a];
+    for (int q = 0; q < NC; q++)
+#pragma unroll
+      for (int i = 0; i < NS; i++) dk[q][i] = Rp[q][3 * i + a];
     out_row(a, dk);
   }
 #undef JC
@@ -469,13 +509,25 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
   __syncthreads();
   double* ba = w.BA + sk * NX * NZ;
   if (live) {
-#pragma unroll 1
-    for (int col = cg; col < NZ; col += NCG) {
-      Real Scol[NX];
-      irk_sens_column<Real>(col, sm, hh, tabA, tabb, wa, wa + 4, itT, itD, Scol);
-      const int oc = (col < NX) ? 2 + col : col - NX;     // [B A] column of d/d(x,u) column `col`
+    // warps 0, 1 hold three columns (cg, cg + 4, cg + 8), warps 2, 3 two
+    if (cg < 2) {
+      Real Scol[3][NX];
+      irk_sens_columns<3, Real>(cg, sm, hh, tabA, tabb, wa, wa + 4, itT, itD, Scol);
 #pragma unroll
-      for (int a = 0; a < NX; a++) ba[a * NZ + oc] = (double)Scol[a];
+      for (int q = 0; q < 3; q++) {
+        const int col = cg + 4 * q, oc = (col < NX) ? 2 + col : col - NX;     // [B A] column of d/d(x,u) column `col`
+#pragma unroll
+        for (int a = 0; a < NX; a++) ba[a * NZ + oc] = (double)Scol[q][a];
+      }
+    } else {
+      Real Scol[2][NX];
+      irk_sens_columns<2, Real>(cg, sm, hh, tabA, tabb, wa, wa + 4, itT, itD, Scol);
+#pragma unroll
+      for (int q = 0; q < 2; q++) {
+        const int col = cg + 4 * q, oc = 2 + col;
+#pragma unroll
+        for (int a = 0; a < NX; a++) ba[a * NZ + oc] = (double)Scol[q][a];
+      }
     }
   }
   __syncthreads();

@@ -403,6 +403,11 @@ def test_sqp_merit_line_search_matches_oracle(torch_cuda, skidpad, fsds, iters):
         assert (sto[searched, 2] < 1.0).sum() > 0  # and the inputs do make it backtrack
     same = searched & (stg[:, 2] == sto[:, 2])
     assert rel(xg[same], xo[same]) < 1e-5 and rel(ug[same], uo[same]) < 1e-5
+    # the returned control is u_0 of the returned iterate (with a shortened last step it is NOT the QP's control:
+    # the reference returns solver.get(0, "u"), new_python/controller.py:405)
+    u0g = u0.cpu().numpy()
+    np.testing.assert_array_equal(u0g[same], ug[same][:, 0, :])
+    assert rel(u0g[same], u0o[same]) < 1e-5
     # against the fixed step: the merit function of the accepted iterates is what the search is for, so just
     # check that the two modes differ where a step was shortened
     cfg2 = _abi.make_config(batch=B, n_grid=len(mp.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=iters,
@@ -559,3 +564,26 @@ def test_mixed_precision_step_within_stated_tolerance(torch_cuda, skidpad, confi
     for c in range(2):
         err = np.abs(ug[ok][..., c] - uo[ok][..., c]).max(1) / max(1.0, np.abs(uo[ok][..., c]).max())
         assert np.quantile(err, 0.999) < FP32_TOL and err.max() < 3e-4, c
+
+
+def test_closed_loop_in_the_reference_solver_setup_matches_oracle(torch_cuda, fsds):
+    """The closed loop with the solver set-up the reference configures (SQP, 2 iterations, MERIT_BACKTRACKING:
+    new_python/controller.py:301-308): the control applied to the plant is u_0 of the damped iterate, and the device loop
+    follows the oracle's step for step."""
+    import torch
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle, initial_iterate
+    B, n_steps = 4, 30
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), nlp_solver=_abi.SQP, nlp_max_iter=2, globalization=_abi.MERIT_BACKTRACKING)
+    params = np.tile(_abi.default_params(), (B, 1)); params[:, _abi.P_M] *= np.linspace(0.95, 1.05, B)
+    x0 = np.zeros((B, 8)); x0[:, 0] = -6.0; x0[:, 1] = np.linspace(-0.3, 0.3, B)
+    eng = _engine(cfg, fsds, params=params, lap_length=[fsds.lap_length])
+    res = eng.closed_loop(torch.as_tensor(x0, device="cuda").clone(), n_steps, log=True)
+    xlog, ulog, fail = res["xlog"].cpu().numpy(), res["ulog"].cpu().numpy(), res["fail"].cpu().numpy()
+    eng.close()
+    x, u = initial_iterate(cfg)
+    o = Oracle(cfg, fsds.s_ref, fsds.kappa_ref, params=params).closed_loop(x0.copy(), x, u, [fsds.lap_length], n_steps)
+    np.testing.assert_array_equal(fail, o["fail"])
+    last = n_steps if (o["fail"] < 0).all() else int(o["fail"][o["fail"] >= 0].min())
+    assert last >= 10
+    assert rel(ulog[:last], o["ulog"][:last]) < 1e-6 and rel(xlog[:last + 1], o["xlog"][:last + 1]) < 1e-6
