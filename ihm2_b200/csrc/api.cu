@@ -220,6 +220,7 @@ int ihm2b_create(const ihm2b_config* cfg, ihm2b_handle** out) {
   ALLOC(w.LT, B * (N + 1) * 4 * RS);
   ALLOC(w.D, B * (N + 1) * 2 * RS);
   ALLOC(w.xa, B * (N + 1) * 8);
+  ALLOC(w.atp, B * N * 8);
   if (cfg->nonlinear_constraints) {
     ALLOC(h->wr, (size_t)cfg->n_tracks * cfg->n_grid);
     ALLOC(h->wl, (size_t)cfg->n_tracks * cfg->n_grid);

@@ -53,6 +53,7 @@ struct Work {
   double* LT;               // [B][N+1][4][RS]
   double* D;                // [B][N+1][2][RS] second-order terms dlam_aff * dt_aff (L, U) / first-order hand-over
   double* xa;               // [B][N+1][8]     costate pi
+  double* atp;              // [B][N][8]       A_k' pi_{k+1}, carried along the interior-point iterations (qp.cu, phase B)
   // soft nonlinear constraints (nl = 1; the interior-point arrays above then carry 16 row slots per stage:
   // slots 0..7 the rows of python/mpc.py, slots 8..12 the rows of h)
   double* HC;               // [B][N+1][16] linearised h rows: [0..2] d h0 / d (s, n, psi), [3] e0; [4..6], [7] the same

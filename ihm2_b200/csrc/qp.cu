@@ -44,7 +44,8 @@ constexpr int PER_STAGE_NL = PER_STAGE + 20;   // + barrier weights of the dense
 #define PF_ 2
 #endif
 #ifndef QP_MIN_BLOCKS
-#define QP_MIN_BLOCKS 11   // problems (warps) per SM the register allocation is held to
+#define QP_MIN_BLOCKS 12   // problems (warps) per SM the register allocation is held to (168 registers for 9..12: three warps on a
+                           // sub-partition; residency is 11 by shared memory -- 12 is the value ptxas allocates without spills at)
 #endif
 #ifndef QP_MIN_BLOCKS_NL
 #define QP_MIN_BLOCKS_NL 8
@@ -112,7 +113,7 @@ __device__ __forceinline__ void sweep(const int N, Load load, Body body) {
 }
 struct FragB { double a0, a1, b0, b1, e0a, e0b, e1a, e1b, xa, xb, pa, pb, u0, u1; };
 struct ResIn { double xa, pia, p1, p2, l1, l2, u0, u1, c, xn, xj, q0, q1, s0, s1; };
-struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv, xa, pia; };
+struct RowIn { double lamL, lamU, tL, tU, d1, d2, uv, xv, xa, pia, atp, b0, b1; };
 struct Frag4 { double a, b, c, d; };
 struct Frag3 { double a, b, c; };
 struct Frag2 { double a, b; };
@@ -338,6 +339,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
   double* __restrict__ const pX = w.x + (size_t)b * N1 * 8;           // [N1][8]   iterate, updated in place
   double* __restrict__ const pU = w.u + (size_t)b * N * 2;            // [N][2]
   double* __restrict__ const pPI = w.xa + (size_t)b * N1 * 8;         // [N1][8]   costate
+  double* __restrict__ const pATP = w.atp + (size_t)b * N * 8;        // [N][8]    A_k' pi_{k+1}, carried (phase B)
   double* __restrict__ const pLL = w.LT + (size_t)b * N1 * 4 * RS;    // [N1][RS]  lamL, lamU, tL, tU
   double* __restrict__ const pLU = pLL + N1 * RS;
   double* __restrict__ const pTL = pLU + N1 * RS;
@@ -576,6 +578,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
   const double mu_floor = 0.1 * cf.tol_comp;
   double prev_res_g = __longlong_as_double(0x7ff0000000000000LL);
   double mu_hist = 0.0;   // lane i < 8 keeps the barrier parameter of the last iteration with it % 8 == i
+  double om_alpha = 0.0;  // 1 - (primal step length of the last iteration)
 
 #ifdef IHM2B_PHASE_TIMERS
   long long tph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -587,10 +590,15 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
     __syncwarp();
     TICK(0)
     // ================= B: stationarity and dynamics residuals of all stages
-    // B1: the three [B A] products of every stage, A x + B u, A' pi+, B' pi+, as DMMA matrix-vector
-    // products (no dependence between stages: the tensor pipe runs back to back); results parked in the
-    // rb / rg / kfc slots.
-    {
+    // B1, first iteration only: the three [B A] products of every stage, A x + B u, A' pi+, B' pi+, as DMMA
+    // matrix-vector products (no dependence between stages: the tensor pipe runs back to back); results parked in
+    // the rb / rg / kfc slots.  Later iterations carry them along instead: the Newton step satisfies its own
+    // recursions exactly, dx+ = A dx + B du + rb (forward sweep) and dpi = rhs + A' dpi+ (costate sweep), so
+    //   rb <- (1 - alpha) rb,   A' pi+ <- A' pi+ + alpha_d A' dpi+   (the product the costate sweep forms anyway),
+    // and B' pi+ (16 products per stage) is redone next to the costate update in phase J.  Nothing of the
+    // solve error of the factorisation enters: the control rows of the stationarity residual, the only ones the
+    // recursions do not pin, are still evaluated from the new point.
+    if (it == 0) {
       const int g = lane >> 2, t = lane & 3;
       const int ra = (2 * t) * 10;
       const bool lo = (g < 2);
@@ -611,6 +619,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         dmma(R0, R1, f.a1, f.xb); dmma(T0, T1, f.e0b, f.pb); dmma(V0, V1, e1b, f.pb);
         sts_if(t == 0, pRB + k * 8 + g, R0);                 // (A x + B u)[g]
         sts_if(t == 1, pRG + k * 8 + g, T0);                 // (A' pi+)[g]
+        if (t == 1) pATP[k * 8 + g] = T0;
         sts_if(t == 2 && lo, pKF + k * 4 + 2 + g, V0);       // (B' pi+)[g]
       };
       sweep<NT, PF, +1, FragB>(N, load_B, products);
@@ -629,7 +638,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       if (NL) { in.p1 = pD1[k * 16 + a]; in.l1 = pD2[k * 16 + a]; in.p2 = 0.0; in.l2 = 0.0; }   // handed over per state
       else { in.p1 = pD1[k * 8 + ct.i1]; in.p2 = pD1[k * 8 + ct.i2]; in.l1 = pD2[k * 8 + ct.i1]; in.l2 = pD2[k * 8 + ct.i2]; }
       in.u0 = pU[ku * 2]; in.u1 = pU[ku * 2 + 1];
-      in.c = pC[(term ? 0 : k) * 8 + a]; in.xn = pX[kn * 8 + a]; in.xj = pX[k * 8 + 6 + j];
+      in.c = (it == 0) ? pC[(term ? 0 : k) * 8 + a] : 0.0; in.xn = (it == 0) ? pX[kn * 8 + a] : 0.0; in.xj = pX[k * 8 + 6 + j];
       if (NL) { in.q0 = pD2[k * 16 + 8 + j]; in.s0 = pD1[k * 16 + 8 + j]; in.q1 = 0.0; in.s1 = 0.0; }
       else { in.q0 = pD2[k * 8 + j]; in.q1 = pD2[k * 8 + 2 + j]; in.s0 = pD1[k * 8 + j]; in.s1 = pD1[k * 8 + 2 + j]; }
       return in;
@@ -647,7 +656,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         double base_x;
         if (!term) {
           const double u0 = in.u0, u1 = in.u1;
-          const double rb = pRB[k * 8 + a] + in.c - in.xn;
+          const double rb = (it == 0) ? pRB[k * 8 + a] + in.c - in.xn : om_alpha * pRB[k * 8 + a];
           rb_m = nmax(rb_m, fabs(rb));
           pRB[k * 8 + a] = rb;
           const int j = a & 1;
@@ -843,7 +852,7 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
         in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e];
         in.d1 = pred ? 0.0 : pD1[e]; in.d2 = pred ? 0.0 : pD2[e];
         in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
-        in.xa = 0.0; in.pia = 0.0;
+        in.xa = 0.0; in.pia = 0.0; in.atp = 0.0; in.b0 = 0.0; in.b1 = 0.0;
         return in;
       };
       if constexpr (NL) {
@@ -1112,8 +1121,10 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       auto costate_stage = [&](const int k, const Frag2 f) {
         const double E0a = f.a, E0b = f.b;
         const double Xi = pGAM[k * 8 + g];
-        double X0 = Xi, X1 = Xi;
+        double X0 = 0.0, X1 = 0.0;
         dmma(X0, X1, E0a, da); dmma(X0, X1, E0b, db);
+        sts_if(t == 0, pK + k * 16 + g, X0);       // A' dpi+ (the gains are dead by now): carried into A' pi+ in phase J
+        X0 += Xi;
         sts_if(t == 0, pRG + k * 8 + g, X0);       // applied to pi in the update phase
         da = __shfl_sync(FULL, X0, t << 3); db = __shfl_sync(FULL, X0, (t << 3) + 4);
       };
@@ -1134,7 +1145,20 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       in.lamL = pLL[e]; in.lamU = pLU[e]; in.tL = pTL[e]; in.tU = pTU[e]; in.d1 = pD1[e]; in.d2 = pD2[e];
       in.uv = pU[(term ? 0 : k) * 2 + R.iu]; in.xv = pX[k * 8 + R.ix];
       in.xa = pX[e]; in.pia = pPI[e];
+      in.atp = pATP[(term ? 0 : k) * 8 + a];
+      const double2 bb = *reinterpret_cast<const double2*>(gBA + (k > 0 ? k - 1 : 0) * 80 + a * 10);   // B_{k-1}[a][0..1]
+      in.b0 = bb.x; in.b1 = bb.y;
       return in;
+    };
+    // carried products of phase B for the next iteration: (B_{k-1}' pi_k)[0..1] -> kfc slot of stage k - 1,
+    // A_k' pi_{k+1} += alpha_d A_k' dpi_{k+1} -> global copy and the rg slot (where phase B2 picks it up)
+    auto carry_products = [&](int k, bool on, bool term, double pin, double atp, double b0, double b1) {
+      const double bt0 = gsum(b0 * pin), bt1 = gsum(b1 * pin);
+      sts2_if(a == 0 && on && k >= 1, pKF + (k - 1) * 4 + 2, bt0, bt1);
+      if (on && !term) {
+        const double an = fma(alpha_d, pK[k * 16 + a], atp);
+        pATP[k * 8 + a] = an; pRG[k * 8 + a] = an;
+      }
     };
     if constexpr (NL) {
       rs_m = 0.0;
@@ -1189,9 +1213,14 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
           }
         }
         rows_A_nl(k, on, term, act0, v0, r0, act1, v1, r1);
+        const double pin = fma(alpha_d, pRG[k * 8 + a], pia);
+        {
+          const double2 bb = *reinterpret_cast<const double2*>(gBA + (k > 0 ? k - 1 : 0) * 80 + a * 10);
+          carry_products(k, on, term, pin, pATP[(term ? 0 : k) * 8 + a], bb.x, bb.y);
+        }
         if (on) {
           pX[k * 8 + a] = xn_;
-          pPI[k * 8 + a] = fma(alpha_d, pRG[k * 8 + a], pia);
+          pPI[k * 8 + a] = pin;
           if (a < 2 && !term) pU[k * 2 + a] = a ? u1n : u0n;
         }
       }
@@ -1222,15 +1251,18 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
       rows_A(k, on, term, act, R, v, lamL, lamU, tL, tU);
       // step of the primal point and the costate: state a / control a of this stage.  The shuffles inside
       // rows_A separate these stores from the row loads of the stage above.
+      const double pin = fma(alpha_d, pRG[k * 8 + a], cur.pia);
+      carry_products(k, on, term, pin, cur.atp, cur.b0, cur.b1);
       if (on) {
         pX[k * 8 + a] = fma(alpha, pDX[k * 8 + a], cur.xa);
-        pPI[k * 8 + a] = fma(alpha_d, pRG[k * 8 + a], cur.pia);
+        pPI[k * 8 + a] = pin;
         if (a < 2 && !term) pU[k * 2 + a] = fma(alpha, pDU[k * 2 + a], pU[k * 2 + a]);
       }
     }
     }
     __syncwarp();
     TICK(7)
+    om_alpha = 1.0 - alpha;
     it++;
   }
 #ifdef IHM2B_PHASE_TIMERS
