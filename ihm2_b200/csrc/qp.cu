@@ -57,8 +57,10 @@ constexpr int PER_STAGE_NL = PER_STAGE + 20;   // + barrier weights of the dense
 #define PAR_STR(x) PAR_STR_(x)
 #define PAR_LOOP _Pragma(PAR_STR(unroll PAR_UNROLL))
 constexpr int PF = PF_;         // [B A] prefetch distance (stages) of the serial sweeps
-constexpr int S_V = 0;          // scratch: 2 x [8] exchange buffer of the substitution sweeps
-constexpr int S_TOT = 16;
+#ifndef QP_WPB
+#define QP_WPB 4                // problems (warps) per block: 3 blocks of 4 independent warps fit an SM (12 problems; one-warp blocks
+#endif                          // stop at 11, each block paying the 1 KB of shared memory the system reserves), one warp per scheduler and block
+constexpr int WPB = QP_WPB;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -303,21 +305,25 @@ __device__ __forceinline__ void soft_row_chi(const bool soft, const double Z, co
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
-// grid = B, block = 32, dynamic shared memory = ((N+1) * PER_STAGE + S_TOT) doubles.
+// grid = ceil(B / WPB), block = 32 WPB (independent warps, one problem each), dynamic shared memory = (N+1) * PER_STAGE
+// doubles per problem.
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
 // NL: soft nonlinear constraints h(x, u) and soft bounds (16 row slots per stage instead of 8, see Work::HC)
 template <int NT, bool NL>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
-__global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_rti_kernel(const KCfg cf, const Work w,
+__global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) / WPB) qp_rti_kernel(const KCfg cf, const Work w,
                                                      const double* __restrict__ x0,
                                                      double* __restrict__ u0_out,
                                                      int32_t* __restrict__ status_out) {
-  extern __shared__ double smem[];
-  const int lane = threadIdx.x;
+  extern __shared__ double smem_block[];
+  const int lane = threadIdx.x & 31;
   const int a = lane & 7, q = lane >> 3;
-  const int b = w.order ? w.order[blockIdx.x] : blockIdx.x;
+  const int slot = blockIdx.x * WPB + (threadIdx.x >> 5);
+  if (slot >= cf.B) return;
+  const int b = w.order ? w.order[slot] : slot;
   if (w.active && !w.active[b]) return;      // SQP mode: instance already converged or failed
   const int N = (NT > 0) ? NT : cf.N, N1 = N + 1;
+  double* const smem = smem_block + (threadIdx.x >> 5) * (N1 * (NL ? PER_STAGE_NL : PER_STAGE));
   // Shared memory (structure of arrays, stage-major): what the serial sweeps touch.
   double* const pGAM = smem;             // [N1][8]   gamma -> chi -> C'(dlamL - dlamU) per state
   double* const pGX = pGAM + N1 * 8;     // [N1][8]   Newton gradient (state part), later dx
@@ -329,7 +335,6 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
   double* const pMI = pKF + N1 * 4;      // [N1][4]   i00 i01 i11 pad
   double* const pGH = pMI + N1 * 4;      // NL: [N1][4]  barrier weights of the rows h0, h1, h4 (and 0)
   double* const pHC = pGH + (NL ? N1 * 4 : 0);   // NL: [N1][16] linearised h rows (Work::HC)
-  double* const sc = pHC + (NL ? N1 * 16 : 0);
   constexpr int RS = NL ? 16 : 8;        // row slots per stage
   // Global memory (L2-resident while the problem is in flight): what only the stage-parallel
   // phases touch, accessed as 256 contiguous bytes per warp instruction; and [B A], whose operand
@@ -346,7 +351,6 @@ __global__ void __launch_bounds__(32, NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) qp_
   double* __restrict__ const pTU = pTL + N1 * RS;
   double* __restrict__ const pD1 = w.D + (size_t)b * N1 * 2 * RS;     // [N1][RS]  psi -> dlam_aff*dt_aff (L) -> dlamL
   double* __restrict__ const pD2 = pD1 + N1 * RS;                     // [N1][RS]  dl  -> dlam_aff*dt_aff (U) -> dlamU
-  double* const sv = sc + S_V;
   double* const pDX = pGX; double* const pDU = pGU;
 
   // ------------------------------------------------------------------ load the problem
@@ -1670,7 +1674,7 @@ void launch_build_order(int B, const int32_t* last_it, int32_t* order, cudaStrea
   build_order_kernel<<<1, 1024, 0, stream>>>(B, last_it, order);
 }
 
-int qp_smem_bytes(int N, int nl) { return ((N + 1) * (nl ? PER_STAGE_NL : PER_STAGE) + S_TOT) * (int)sizeof(double); }
+int qp_smem_bytes(int N, int nl) { return (N + 1) * (nl ? PER_STAGE_NL : PER_STAGE) * (int)sizeof(double); }   // per problem
 
 namespace {
 // the dynamic shared-memory limit is a per-device attribute of each kernel instance: remembered per (instance, device)
@@ -1678,14 +1682,14 @@ template <class K>
 int launch_qp_instance(K kernel, int slot, const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                        cudaStream_t stream) {
   static int configured[4][64] = {};
-  const int bytes = qp_smem_bytes(cf.N, cf.nl);
+  const int bytes = WPB * qp_smem_bytes(cf.N, cf.nl);
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 1;
   if (dev < 0 || dev >= 64 || configured[slot][dev] < bytes) {
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) { cudaGetLastError(); return 1; }
     if (dev >= 0 && dev < 64) configured[slot][dev] = bytes;
   }
-  kernel<<<cf.B, 32, bytes, stream>>>(cf, w, x0, u0, status);
+  kernel<<<(cf.B + WPB - 1) / WPB, 32 * WPB, bytes, stream>>>(cf, w, x0, u0, status);
   return 0;
 }
 }  // namespace
