@@ -454,6 +454,25 @@ def test_history_scheduling_changes_nothing_but_the_order(torch_cuda, skidpad):
         np.testing.assert_array_equal(a, b)
 
 
+@pytest.mark.parametrize("B", [1, 6, 131])
+def test_ragged_batch_sizes_match_the_big_batch(torch_cuda, skidpad, config2, B):
+    """The QP kernel packs four problems into a block: batch sizes that are not a multiple of four (and a single
+    problem) give, problem by problem, the bits of the 4096 batch -- also on the second solve of the handle, which
+    launches in history order."""
+    from ihm2_b200 import _abi
+    cfg = _abi.make_config(batch=B, n_grid=len(skidpad.s_ref))
+    eng = _engine(cfg, skidpad)
+    x0d = torch_cuda.as_tensor(config2["x0"][:B], device="cuda")
+    for _ in range(2):
+        eng.set_iterate(config2["x_in"][:B], config2["u_in"][:B])
+        u0, status = eng.solve(x0d)
+        np.testing.assert_array_equal(status.cpu().numpy(), config2["status"][:B])
+        np.testing.assert_array_equal(u0.cpu().numpy(), config2["u0"][:B])
+        np.testing.assert_array_equal(eng.get_iterate()[0].cpu().numpy(), config2["x"][:B])
+        np.testing.assert_array_equal(eng.stats().cpu().numpy()[:, 0], config2["stats"][:B, 0])
+    eng.close()
+
+
 def test_solver_object_shim_drives_the_engine_like_acados(torch_cuda, fsds):
     """Reference code that pokes `controller.solver` (new_python/controller.py:368-405: constraints_set x_0, set yref,
     shifted set x / u, solve, get) gets the same control as `compute_control`; what the engine fixes at creation is
