@@ -126,6 +126,14 @@ __device__ __forceinline__ double wmax(double v) {
   for (int m = 1; m < 32; m <<= 1) v = nmax(v, __shfl_xor_sync(FULL, v, m));
   return v;
 }
+// The step-length ratio tests use fmax (three instructions against six, NaNs ignored): a NaN in a step reaches the
+// slacks with the update, and the residual norms / the barrier parameter of the next iteration -- which do propagate
+// it -- end the solve with status 3.
+__device__ __forceinline__ double wmaxf(double v) {
+#pragma unroll
+  for (int m = 1; m < 32; m <<= 1) v = fmax(v, __shfl_xor_sync(FULL, v, m));
+  return v;
+}
 
 // Inequality row r = a of a stage:  v = cu * u[iu] + cx * x[ix]  in [lb, ub]   (branch-free form)
 // python/mpc.py:77-99.  Path stages: (u_T, u_d, u_T - T, u_d - delta, n, v_x, T, delta), rows 4..7
@@ -477,9 +485,11 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
     const bool soft0 = term ? (a == 2 || a == 3) : (a >= 6);
     Norms nm{rd_m, rm_m, rs_m, S0};
     // a lane has at most one soft row: its h row if it has one (then its static row is hard), else its static row
-    const RowA AS = act1 ? soft_row_A(true, true, v1, hlb, hub, isc1, Z, zz, r1, nm)
-                         : soft_row_A(act0, soft0, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
-    const RowA AH = soft_row_A(act1 && act0, false, v0, R.lb, R.ub, term ? iscT : iscP, Z, zz, r0, nm);
+    const double iscR = term ? iscT : iscP;
+    const RowSt& rS = act1 ? r1 : r0;
+    const RowA AS = soft_row_A(act1 || act0, act1 || soft0, act1 ? v1 : v0, act1 ? hlb : R.lb, act1 ? hub : R.ub,
+                               act1 ? isc1 : iscR, Z, zz, rS, nm);
+    const RowA AH = soft_row_A(act1 && act0, false, v0, R.lb, R.ub, iscR, Z, zz, r0, nm);
     const RowA A0 = act1 ? AH : AS, A1 = act1 ? AS : RowA{0.0, 0.0, 0.0};
     rd_m = nm.rd; rm_m = nm.rm; rs_m = nm.rs; S0 = nm.S0;
     const CtDef& ct = term ? ctT : ctP;
@@ -805,7 +815,6 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
     TICK(2)
     // ================= D..H: predictor (pred = 1), corrector (pred = 0)
     double alpha = 1.0, alpha_d = 1.0, mu_t = 0.0;
-    bool bad = false;
     for (int pred = 1; pred >= 0; pred--) {
       // ---- forward substitution: du = K dx + kf, dx+ = A dx + B du + rb
       // Matrix-vector products as DMMAs whose right operand repeats the vector in all 8 columns:
@@ -887,55 +896,55 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
               const double v = sS ? v1 : v0, lb = sS ? hlb : R.lb, ub = sS ? hub : R.ub, cdz = sS ? cdz1 : cdz0;
               RowSt r{pLL[e], pLU[e], pTL[e], pTU[e], 1.0, 1.0, 0.0, 0.0};
               if (softS) { r.sL = pSL[es]; r.sU = pSU[es]; r.lsL = pLSL[es]; r.lsU = pLSU[es]; }
+              const double cL_ = pred ? 0.0 : pD1[e] - mu_t, cU_ = pred ? 0.0 : pD2[e] - mu_t;
+              const double cSL = (softS && !pred) ? pDS1[es] - mu_t : 0.0, cSU = (softS && !pred) ? pDS2[es] - mu_t : 0.0;
+              const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, cL_, cU_, cSL, cSU);
               if (pred) {
-                const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
                 S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
                 const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
                 double dSL = 0.0, dSU = 0.0;
                 S2 += dL + dU;
-                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
                 if (softS) {
                   dSL = st.dlsL * st.dsL; dSU = st.dlsU * st.dsU;
                   S1 += r.lsL * st.dsL + r.lsU * st.dsU; S1d += r.sL * st.dlsL + r.sU * st.dlsU; S2 += dSL + dSU;
-                  ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
-                  ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
+                  ratio_d = fmax(ratio_d, fmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
+                  ratio = fmax(ratio, fmax(-st.dsL / r.sL, -st.dsU / r.sU));
                   pDS1[es] = dSL; pDS2[es] = dSU;
                 }
                 pD1[e] = dL; pD2[e] = dU;
                 soft_row_chi(softS, Z, r, dL, dU, dSL, dSU, aS, bS);
               } else {
-                const double cSL = softS ? pDS1[es] - mu_t : 0.0, cSU = softS ? pDS2[es] - mu_t : 0.0;
-                const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, pD1[e] - mu_t, pD2[e] - mu_t, cSL, cSU);
                 pD1[e] = st.dlL; pD2[e] = st.dlU;
                 dS = st.dlL - st.dlU;
-                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
                 if (softS) {
                   pDS1[es] = st.dlsL; pDS2[es] = st.dlsU; pE1[es] = st.dsL; pE2[es] = st.dsU;
-                  ratio_d = nmax(ratio_d, nmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
-                  ratio = nmax(ratio, nmax(-st.dsL / r.sL, -st.dsU / r.sU));
+                  ratio_d = fmax(ratio_d, fmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
+                  ratio = fmax(ratio, fmax(-st.dsL / r.sL, -st.dsU / r.sU));
                 }
               }
             }
             double dH = 0.0, aH = 0.0, bH = 0.0;
             if (act1 && act0) {          // static row of a lane that also holds an h row: hard
               const RowSt r{pLL[e0], pLU[e0], pTL[e0], pTU[e0], 1.0, 1.0, 0.0, 0.0};
+              const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, pred ? 0.0 : pD1[e0] - mu_t,
+                                               pred ? 0.0 : pD2[e0] - mu_t, 0.0, 0.0);
               if (pred) {
-                const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, 0.0, 0.0, 0.0, 0.0);
                 S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
                 const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
                 S2 += dL + dU;
-                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
                 pD1[e0] = dL; pD2[e0] = dU;
                 soft_row_chi(false, Z, r, dL, dU, 0.0, 0.0, aH, bH);
               } else {
-                const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, pD1[e0] - mu_t, pD2[e0] - mu_t, 0.0, 0.0);
                 pD1[e0] = st.dlL; pD2[e0] = st.dlU;
                 dH = st.dlL - st.dlU;
-                ratio_d = nmax(ratio_d, nmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = nmax(ratio, nmax(-st.dtL / r.tL, -st.dtU / r.tU));
+                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
               }
             }
             ddl0 = sS ? dH : dS; ddl1 = sS ? dS : 0.0;
@@ -992,15 +1001,15 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
             S1 += lamL * dtL + lamU * dtU; S1d += tL * dlL + tU * dlU;
             S2 += dlL * dtL + dlU * dtU;
             pD1[k * 8 + a] = dlL * dtL; pD2[k * 8 + a] = dlU * dtU;
-            ratio_d = nmax(ratio_d, nmax(1.0 + dtL * itL, 1.0 + dtU * itU));
-            ratio = nmax(ratio, nmax(-dtL * itL, -dtU * itU));
+            ratio_d = fmax(ratio_d, fmax(1.0 + dtL * itL, 1.0 + dtU * itU));
+            ratio = fmax(ratio, fmax(-dtL * itL, -dtU * itU));
           } else {
             const double dlL = -lamL - (cur.d1 - mu_t + lamL * dtL) * itL;
             const double dlU = -lamU - (cur.d2 - mu_t + lamU * dtU) * itU;
             pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
             ddl = dlL - dlU;
-            ratio_d = nmax(ratio_d, nmax(-dlL / lamL, -dlU / lamU));
-            ratio = nmax(ratio, nmax(-dtL * itL, -dtU * itU));
+            ratio_d = fmax(ratio_d, fmax(-dlL / lamL, -dlU / lamU));
+            ratio = fmax(ratio, fmax(-dtL * itL, -dtU * itU));
           }
         }
         if (!pred) {
@@ -1015,9 +1024,8 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
         }
       }
       }
-      ratio = wmax(ratio); ratio_d = wmax(ratio_d);
-      if (!(ratio == ratio) || !(ratio_d == ratio_d)) { bad = true; break; }
-      if (!cf.split_step) ratio = ratio_d = nmax(ratio, ratio_d);
+      ratio = wmaxf(ratio); ratio_d = wmaxf(ratio_d);
+      if (!cf.split_step) ratio = ratio_d = fmax(ratio, ratio_d);
       if (!pred) {
         // fraction to the boundary: 0.995 far from the solution, -> 1 with the barrier parameter (Mehrotra)
         const double tau_k = fmax(TAU, 1.0 - mu_t);
@@ -1106,7 +1114,6 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
     }
     TICK(4)
     if (w.dbg && b == 0 && lane == 0 && it < 64) { w.dbg[it * 8 + 5] = alpha; w.dbg[it * 8 + 6] = mu_t; }
-    if (bad) { qp_status = 3; break; }
     if (fmin(alpha, alpha_d) < 1e-12) { qp_status = 2; break; }
     short_steps = (fmin(alpha, alpha_d) < 0.5) ? short_steps + 1 : 0;
     __syncwarp();

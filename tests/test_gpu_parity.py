@@ -473,6 +473,29 @@ def test_ragged_batch_sizes_match_the_big_batch(torch_cuda, skidpad, config2, B)
     eng.close()
 
 
+def test_nan_state_fails_one_instance_only(torch_cuda, skidpad, config2):
+    """A NaN in one car's measured state: that instance returns IHM2B_FAILURE (as the oracle does) and keeps its
+    iterate (new_python/controller.py:397-403 leaves x_pred untouched when the solve fails); the other instances of the
+    batch give the bits they give without it."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    B, bad = 16, 5
+    cfg = _abi.make_config(batch=B, n_grid=len(skidpad.s_ref))
+    x0 = config2["x0"][:B].copy(); x0[bad, 2] = np.nan
+    eng = _engine(cfg, skidpad)
+    eng.set_iterate(config2["x_in"][:B], config2["u_in"][:B])
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    status = status.cpu().numpy(); xg = eng.get_iterate()[0].cpu().numpy()
+    eng.close()
+    so = Oracle(cfg, skidpad.s_ref, skidpad.kappa_ref).solve(x0, config2["x_in"][:B], config2["u_in"][:B])[1]
+    assert status[bad] == _abi.STATUS_FAILURE == so[bad]
+    np.testing.assert_array_equal(xg[bad], config2["x_in"][bad])
+    others = np.arange(B) != bad
+    np.testing.assert_array_equal(status[others], config2["status"][:B][others])
+    np.testing.assert_array_equal(u0.cpu().numpy()[others], config2["u0"][:B][others])
+    np.testing.assert_array_equal(xg[others], config2["x"][:B][others])
+
+
 def test_solver_object_shim_drives_the_engine_like_acados(torch_cuda, fsds):
     """Reference code that pokes `controller.solver` (new_python/controller.py:368-405: constraints_set x_0, set yref,
     shifted set x / u, solve, get) gets the same control as `compute_control`; what the engine fixes at creation is
