@@ -899,18 +899,21 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
               const double cL_ = pred ? 0.0 : pD1[e] - mu_t, cU_ = pred ? 0.0 : pD2[e] - mu_t;
               const double cSL = (softS && !pred) ? pDS1[es] - mu_t : 0.0, cSU = (softS && !pred) ? pDS2[es] - mu_t : 0.0;
               const RowStep st = soft_row_step(softS, v, lb, ub, cdz, Z, zz, r, cL_, cU_, cSL, cSU);
+              // step-length ratios (the reciprocals of t and s are the ones soft_row_step forms)
+              ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+              ratio = fmax(ratio, fmax(-st.dtL * (1.0 / r.tL), -st.dtU * (1.0 / r.tU)));
+              if (softS) {
+                ratio_d = fmax(ratio_d, fmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
+                ratio = fmax(ratio, fmax(-st.dsL * (1.0 / r.sL), -st.dsU * (1.0 / r.sU)));
+              }
               if (pred) {
                 S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
                 const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
                 double dSL = 0.0, dSU = 0.0;
                 S2 += dL + dU;
-                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
                 if (softS) {
                   dSL = st.dlsL * st.dsL; dSU = st.dlsU * st.dsU;
                   S1 += r.lsL * st.dsL + r.lsU * st.dsU; S1d += r.sL * st.dlsL + r.sU * st.dlsU; S2 += dSL + dSU;
-                  ratio_d = fmax(ratio_d, fmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
-                  ratio = fmax(ratio, fmax(-st.dsL / r.sL, -st.dsU / r.sU));
                   pDS1[es] = dSL; pDS2[es] = dSU;
                 }
                 pD1[e] = dL; pD2[e] = dU;
@@ -918,13 +921,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
               } else {
                 pD1[e] = st.dlL; pD2[e] = st.dlU;
                 dS = st.dlL - st.dlU;
-                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
-                if (softS) {
-                  pDS1[es] = st.dlsL; pDS2[es] = st.dlsU; pE1[es] = st.dsL; pE2[es] = st.dsU;
-                  ratio_d = fmax(ratio_d, fmax(-st.dlsL / r.lsL, -st.dlsU / r.lsU));
-                  ratio = fmax(ratio, fmax(-st.dsL / r.sL, -st.dsU / r.sU));
-                }
+                if (softS) { pDS1[es] = st.dlsL; pDS2[es] = st.dlsU; pE1[es] = st.dsL; pE2[es] = st.dsU; }
               }
             }
             double dH = 0.0, aH = 0.0, bH = 0.0;
@@ -932,19 +929,17 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
               const RowSt r{pLL[e0], pLU[e0], pTL[e0], pTU[e0], 1.0, 1.0, 0.0, 0.0};
               const RowStep st = soft_row_step(false, v0, R.lb, R.ub, cdz0, Z, zz, r, pred ? 0.0 : pD1[e0] - mu_t,
                                                pred ? 0.0 : pD2[e0] - mu_t, 0.0, 0.0);
+              ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
+              ratio = fmax(ratio, fmax(-st.dtL * (1.0 / r.tL), -st.dtU * (1.0 / r.tU)));
               if (pred) {
                 S1 += r.lamL * st.dtL + r.lamU * st.dtU; S1d += r.tL * st.dlL + r.tU * st.dlU;
                 const double dL = st.dlL * st.dtL, dU = st.dlU * st.dtU;
                 S2 += dL + dU;
-                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
                 pD1[e0] = dL; pD2[e0] = dU;
                 soft_row_chi(false, Z, r, dL, dU, 0.0, 0.0, aH, bH);
               } else {
                 pD1[e0] = st.dlL; pD2[e0] = st.dlU;
                 dH = st.dlL - st.dlU;
-                ratio_d = fmax(ratio_d, fmax(-st.dlL / r.lamL, -st.dlU / r.lamU));
-                ratio = fmax(ratio, fmax(-st.dtL / r.tL, -st.dtU / r.tU));
               }
             }
             ddl0 = sS ? dH : dS; ddl1 = sS ? dS : 0.0;
@@ -1008,7 +1003,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
             const double dlU = -lamU - (cur.d2 - mu_t + lamU * dtU) * itU;
             pD1[k * 8 + a] = dlL; pD2[k * 8 + a] = dlU;
             ddl = dlL - dlU;
-            ratio_d = fmax(ratio_d, fmax(-dlL / lamL, -dlU / lamU));
+            ratio_d = fmax(ratio_d, fmax(-dlL * (1.0 / lamL), -dlU * (1.0 / lamU)));
             ratio = fmax(ratio, fmax(-dtL * itL, -dtU * itU));
           }
         }
@@ -1065,7 +1060,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
         const bool term = (k == N);
         const bool act = on && (term ? (a < 4) : (a < 4 || k > 0));
         double chi = 0.0;
-        if (act) chi = (cc.a - mu_t) / cc.c - (cc.b - mu_t) / cc.d;
+        if (act) chi = (cc.a - mu_t) * (1.0 / cc.c) - (cc.b - mu_t) * (1.0 / cc.d);   // reciprocals: half the instructions of a division
         const CtDef& ct = term ? ctT : ctP;
         const double c1v = __shfl_sync(FULL, chi, ct.i1, GROUP), c2v = __shfl_sync(FULL, chi, ct.i2, GROUP);
         const double cp2 = __shfl_sync(FULL, chi, (a + 2) & 7, GROUP);
