@@ -38,6 +38,9 @@ void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, con
                      const double* u, double* xn, int32_t* model, int32_t* order_scratch, cudaStream_t stream);
 void launch_sim_step_dyn10(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u, double* xn,
                            cudaStream_t stream);
+cudaError_t launch_sim_step_static(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u,
+                                   double* xn, int32_t* model, cudaStream_t stream);
+int sim_static_max_batch();
 void launch_closed_loop_post(int B, int step, double dt, const int32_t* track, const double* lap, const int32_t* status,
                              const double* u0, const double* xn, const double* stats, double* xs, double* xlog,
                              double* ulog, int32_t* done, int32_t* fail, int32_t* active_mask, int32_t* lap_state,
@@ -605,6 +608,21 @@ int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x, const double* u, double
   launch_sim_step(h->cfg, h->k, h->w, x, u, xn, model, h->sim_order_dev, static_cast<cudaStream_t>(stream));
   h->launches++;
   CU(cudaGetLastError());
+  return IHM2B_OK;
+}
+
+// The plant step with its scratch (launch order of the model partition) in static device memory: allocates nothing.
+int ihm2b_sim_step_static_dev(ihm2b_handle* h, const double* x, const double* u, double* xn, int32_t* model, void* stream) {
+  int rc = check_ready(h);   // selects the handle's device
+  if (rc) return rc;
+  if (!x || !u || !xn) return fail(IHM2B_EINVAL, "null argument");
+  if (h->cfg.sim_model < IHM2B_SIM_FKIN6 || h->cfg.sim_model > IHM2B_SIM_KIN6C_DYN6C) return fail(IHM2B_EINVAL, "unknown sim_model %d", h->cfg.sim_model);
+  if (h->cfg.batch > sim_static_max_batch())
+    return fail(IHM2B_EINVAL, "batch %d exceeds the %d instances the static scratch of ihm2b_sim_step_static_dev holds; use ihm2b_sim_step_dev",
+                (int)h->cfg.batch, sim_static_max_batch());
+  const cudaError_t e = launch_sim_step_static(h->cfg, h->k, h->w, x, u, xn, model, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail(IHM2B_ECUDA, "ihm2b_sim_step_static_dev: %s", cudaGetErrorString(e));
+  h->launches++;
   return IHM2B_OK;
 }
 

@@ -14,6 +14,7 @@
 // force balance is affine in (a_x, a_y), so the tyre terms are evaluated once per point and a
 // 2 x 2 linear solve yields the explicit right-hand side.
 #include "model.cuh"
+#include <mutex>
 
 namespace ihm2b {
 
@@ -463,6 +464,63 @@ void launch_sim_step(const ihm2b_config& cfg, const KCfg& cf, const Work& w, con
     order = order_scratch;
   }
   sim_step_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn, model, order);
+}
+
+// ---- plant step with its scratch in static device memory (ihm2b_sim_step_static_dev) -------------------------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// [B] launch order + 2 counters of the partition above live in a file-scope array instead of a buffer the handle owns.
+// Every GPU that loads the library holds the array (SIM_STATIC_MAX_B + 2 int32 = 256 KB) until the process exits; all
+// calls on a device share it, so calls that overlap on the GPU (different streams) race -- serialise them.  Nothing in
+// it has to survive a call: the counters are cleared and order[0 .. B) is rewritten by every call.
+constexpr int SIM_STATIC_MAX_B = 65536;
+static __device__ __align__(256) int32_t g_sim_static_scratch[SIM_STATIC_MAX_B + 2];
+
+int sim_static_max_batch() { return SIM_STATIC_MAX_B; }
+
+// Device address of the array on the current device.  In host code the array's name is only a stand-in for the symbol:
+// the address a kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static cudaError_t sim_static_scratch(int32_t** out) {
+  static std::mutex mtx;
+  static int32_t* addr[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mtx);
+  if (!addr[dev]) {
+    int32_t* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_sim_static_scratch);
+    if (e != cudaSuccess) return e;
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return cudaSuccess;
+}
+
+// Same launches as launch_sim_step; the partition runs for every batch size of a switching model (also B <= 8), so the
+// scratch is what the call uses.  No allocation: cudaGetSymbolAddress, cudaMemsetAsync and kernel launches only.
+cudaError_t launch_sim_step_static(const ihm2b_config& cfg, const KCfg& cf, const Work& w, const double* x, const double* u,
+                                   double* xn, int32_t* model, cudaStream_t stream) {
+  if (cf.B > SIM_STATIC_MAX_B) return cudaErrorInvalidValue;
+  int32_t* scratch = nullptr;
+  cudaError_t e = sim_static_scratch(&scratch);
+  if (e != cudaSuccess) return e;
+  SimCfg sc;
+  sc.B = cf.B; sc.n_grid = cf.n_grid; sc.model = cfg.sim_model; sc.n_sub = cfg.sim_steps > 0 ? cfg.sim_steps : 1;
+  sc.h = cfg.dt / sc.n_sub; sc.sw = cfg.sim_switch;
+  for (int i = 0; i < 16; i++) sc.A[i] = cfg.sim_A[i];
+  for (int i = 0; i < 4; i++) sc.b[i] = cfg.sim_b[i];
+  const int threads = 128, total = cf.B * 4;
+  const int32_t* order = nullptr;
+  if (cfg.sim_model == IHM2B_SIM_KIN6_DYN6 || cfg.sim_model == IHM2B_SIM_KIN6C_DYN6C) {
+    e = cudaMemsetAsync(scratch + cf.B, 0, 2 * sizeof(int32_t), stream);   // the two counters start at zero
+    if (e != cudaSuccess) return e;
+    sim_partition_kernel<<<(cf.B + 255) / 256, 256, 0, stream>>>(cf.B, cfg.sim_model, cfg.sim_switch, w.params, x, w.active,
+                                                                 scratch + cf.B, scratch);
+    order = scratch;
+  }
+  sim_step_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(sc, w, x, u, xn, model, order);
+  return cudaGetLastError();
 }
 
 // closed-loop bookkeeping after solve + plant step (python/main.py:503-517): an instance stops at

@@ -23,7 +23,7 @@ EXPORTS = (
     "ihm2b_create", "ihm2b_destroy", "ihm2b_last_error", "ihm2b_version", "ihm2b_set_tracks",
     "ihm2b_set_track_index", "ihm2b_set_params", "ihm2b_set_iterate_dev", "ihm2b_get_iterate_dev", "ihm2b_get_iterate_host",
     "ihm2b_reset_iterate", "ihm2b_shift_iterate", "ihm2b_solve_dev", "ihm2b_compute_control_host",
-    "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_sim_step_dyn10_dev", "ihm2b_closed_loop_dev",
+    "ihm2b_linearize_dev", "ihm2b_get_stats_dev", "ihm2b_sim_step_dev", "ihm2b_sim_step_static_dev", "ihm2b_sim_step_dyn10_dev", "ihm2b_closed_loop_dev",
     "ihm2b_get_multipliers_dev", "ihm2b_get_slacks_dev", "ihm2b_get_h_rows_dev",
     "ihm2b_dpc_rollout_grad_dev", "ihm2b_dpc_rollout_grad_f32_dev", "ihm2b_project_dev", "ihm2b_launch_count",
     "ihm2b_profile_enable", "ihm2b_profile_read", "ihm2b_debug_trace", "ihm2b_measure_fp64_tflops",
@@ -227,6 +227,15 @@ class Engine:
         self._check(self.lib.ihm2b_sim_step_dev(self._h, _dptr(x.contiguous()), _dptr(u.contiguous()),
                                                 _dptr(xn), _dptr(model), _stream()))
         return xn, model
+
+    def sim_step_static(self, x: torch.Tensor, u: torch.Tensor, xn: torch.Tensor, model: "torch.Tensor | None" = None):
+        """ihm2b_sim_step_static_dev: the plant step with its scratch in static device memory.  Allocates nothing:
+        the caller passes the outputs xn [B,8] (float64) and, optionally, model [B] (int32); B <= 65536."""
+        assert x.shape == (self.B, NX) and u.shape == (self.B, NU) and xn.shape == (self.B, NX)
+        assert x.is_contiguous() and u.is_contiguous() and xn.is_contiguous() and xn.dtype == torch.float64
+        assert model is None or (model.shape == (self.B,) and model.dtype == torch.int32 and model.is_contiguous())
+        self._check(self.lib.ihm2b_sim_step_static_dev(self._h, _dptr(x), _dptr(u), _dptr(xn), _dptr(model), _stream()))
+        return xn
 
     def sim_step_dyn10(self, x10: torch.Tensor, u5: torch.Tensor):
         """dyn10 plant: x10 [B,15], u5 [B,5] -> x_next [B,15] (NaN rows where the integrator failed)."""

@@ -209,6 +209,19 @@ int ihm2b_get_h_rows_dev(ihm2b_handle* h, double* hc_dev, void* stream);
 int ihm2b_sim_step_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev,
                        double* xnext_dev, int32_t* model_dev, void* stream);
 
+/* The same plant step for callers that cannot allocate device memory around the call (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Its scratch -- the launch order of the kinematic / dynamic model partition, [B] + 2 counters of int32 --
+ * lives in a static device array inside the library (256 KB, held by every GPU that loads the library until the process
+ * exits) instead of a buffer of the handle; the call itself makes no cudaMalloc / cudaFree or other allocating call.
+ * Limit: cfg.batch <= IHM2B_SIM_STATIC_MAX_BATCH, larger handles get IHM2B_EINVAL.  Same arguments and results as
+ * ihm2b_sim_step_dev (the caller passes inputs and outputs; model_dev optional).  All calls on a device share the array:
+ * calls that overlap on the GPU (different streams, or two handles from two threads) race -- serialise them.  Nothing
+ * is carried from call to call (counters cleared, the order rewritten each time). */
+#define IHM2B_SIM_STATIC_MAX_BATCH 65536
+int ihm2b_sim_step_static_dev(ihm2b_handle* h, const double* x_dev, const double* u_dev,
+                              double* xnext_dev, int32_t* model_dev, void* stream);
+
 /* The dyn10 plant (`fdyn10_model`, python/models.py:609-801): Frenet pose, body velocities, four wheel
  * speeds with slip-ratio (longitudinal Pacejka) and slip-angle (lateral Pacejka) tyre forces on load-transfer vertical
  * loads, four torque lags and the steering lag.  x10_dev [B][15] = (s, n, psi, v_x, v_y, r, omega_FL, omega_FR,
