@@ -50,6 +50,9 @@ constexpr int PER_STAGE_NL = PER_STAGE + 20;   // + barrier weights of the dense
 #ifndef QP_MIN_BLOCKS_NL
 #define QP_MIN_BLOCKS_NL 8
 #endif
+#ifndef QP_EXACT_MU
+#define QP_EXACT_MU 1e-3
+#endif
 #ifndef PAR_UNROLL
 #define PAR_UNROLL 1
 #endif
@@ -604,7 +607,15 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
     __syncwarp();
     TICK(0)
     // ================= B: stationarity and dynamics residuals of all stages
-    // B1, first iteration only: the three [B A] products of every stage, A x + B u, A' pi+, B' pi+, as DMMA
+    S0 = wsum(S0);
+    mu = S0 * inv_n;
+    // the carried products below are exact up to rounding that accumulates over the iterations; the first iteration and
+    // the second half of a solve (barrier parameter below QP_EXACT_MU: thin interiors make the iterates sensitive to the last
+    // bits there -- with the carried products a borderline problem can end on the other side of a failure than the oracle --
+    // and the residuals are
+    // compared with the tolerances) form them anew
+    const bool exact = (it == 0) || !(mu > QP_EXACT_MU);
+    // B1, first iteration and end game only: the three [B A] products of every stage, A x + B u, A' pi+, B' pi+, as DMMA
     // matrix-vector products (no dependence between stages: the tensor pipe runs back to back); results parked in
     // the rb / rg / kfc slots.  Later iterations carry them along instead: the Newton step satisfies its own
     // recursions exactly, dx+ = A dx + B du + rb (forward sweep) and dpi = rhs + A' dpi+ (costate sweep), so
@@ -612,7 +623,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
     // and B' pi+ (16 products per stage) is redone next to the costate update in phase J.  Nothing of the
     // solve error of the factorisation enters: the control rows of the stationarity residual, the only ones the
     // recursions do not pin, are still evaluated from the new point.
-    if (it == 0) {
+    if (exact) {
       const int g = lane >> 2, t = lane & 3;
       const int ra = (2 * t) * 10;
       const bool lo = (g < 2);
@@ -652,7 +663,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
       if (NL) { in.p1 = pD1[k * 16 + a]; in.l1 = pD2[k * 16 + a]; in.p2 = 0.0; in.l2 = 0.0; }   // handed over per state
       else { in.p1 = pD1[k * 8 + ct.i1]; in.p2 = pD1[k * 8 + ct.i2]; in.l1 = pD2[k * 8 + ct.i1]; in.l2 = pD2[k * 8 + ct.i2]; }
       in.u0 = pU[ku * 2]; in.u1 = pU[ku * 2 + 1];
-      in.c = (it == 0) ? pC[(term ? 0 : k) * 8 + a] : 0.0; in.xn = (it == 0) ? pX[kn * 8 + a] : 0.0; in.xj = pX[k * 8 + 6 + j];
+      in.c = exact ? pC[(term ? 0 : k) * 8 + a] : 0.0; in.xn = exact ? pX[kn * 8 + a] : 0.0; in.xj = pX[k * 8 + 6 + j];
       if (NL) { in.q0 = pD2[k * 16 + 8 + j]; in.s0 = pD1[k * 16 + 8 + j]; in.q1 = 0.0; in.s1 = 0.0; }
       else { in.q0 = pD2[k * 8 + j]; in.q1 = pD2[k * 8 + 2 + j]; in.s0 = pD1[k * 8 + j]; in.s1 = pD1[k * 8 + 2 + j]; }
       return in;
@@ -670,7 +681,7 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
         double base_x;
         if (!term) {
           const double u0 = in.u0, u1 = in.u1;
-          const double rb = (it == 0) ? pRB[k * 8 + a] + in.c - in.xn : om_alpha * pRB[k * 8 + a];
+          const double rb = exact ? pRB[k * 8 + a] + in.c - in.xn : om_alpha * pRB[k * 8 + a];
           rb_m = nmax(rb_m, fabs(rb));
           pRB[k * 8 + a] = rb;
           const int j = a & 1;
@@ -691,8 +702,6 @@ __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOC
       }
     }
     res_g = wmax(NL ? nmax(rg_m, rs_m) : rg_m); res_b = wmax(rb_m); res_d = wmax(rd_m); res_m = wmax(rm_m);
-    S0 = wsum(S0);
-    mu = S0 * inv_n;
     if (w.dbg && b == 0 && lane == 0 && it < 64) {
       double* d = w.dbg + it * 8;
       d[0] = res_g; d[1] = res_b; d[2] = res_d; d[3] = res_m; d[4] = mu;
