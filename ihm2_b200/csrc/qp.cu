@@ -63,7 +63,6 @@ constexpr int PF = PF_;         // [B A] prefetch distance (stages) of the seria
 #ifndef QP_WPB
 #define QP_WPB 4                // problems (warps) per block: 3 blocks of 4 independent warps fit an SM (12 problems; one-warp blocks
 #endif                          // stop at 11, each block paying the 1 KB of shared memory the system reserves), one warp per scheduler and block
-constexpr int WPB = QP_WPB;
 
 __device__ __forceinline__ double gsum(double v) {   // over the 8 lanes of a segment
   v += __shfl_xor_sync(FULL, v, 1);
@@ -317,11 +316,13 @@ __device__ __forceinline__ void soft_row_chi(const bool soft, const double Z, co
 
 // ---------------------------------------------------------------------------------------
 // grid = ceil(B / WPB), block = 32 WPB (independent warps, one problem each), dynamic shared memory = (N+1) * PER_STAGE
+// WPB = QP_WPB for the N = 40 instances, 1 for the instances with the horizon as a run-time value (a long horizon would
+// not fit four problems into the shared memory of a block: N up to 480 hard-bounded / 360 with soft rows stays possible).
 // doubles per problem.
 // x0 [B][8]; on exit the iterate w.x / w.u holds the QP solution (RTI full step).
 // ---------------------------------------------------------------------------------------
 // NL: soft nonlinear constraints h(x, u) and soft bounds (16 row slots per stage instead of 8, see Work::HC)
-template <int NT, bool NL>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
+template <int NT, bool NL, int WPB>  // NT > 0: horizon known at compile time (all shared-memory offsets fold into immediates)
 __global__ void __launch_bounds__(32 * WPB, (NL ? QP_MIN_BLOCKS_NL : QP_MIN_BLOCKS) / WPB) qp_rti_kernel(const KCfg cf, const Work w,
                                                      const double* __restrict__ x0,
                                                      double* __restrict__ u0_out,
@@ -1689,7 +1690,7 @@ int qp_smem_bytes(int N, int nl) { return (N + 1) * (nl ? PER_STAGE_NL : PER_STA
 
 namespace {
 // the dynamic shared-memory limit is a per-device attribute of each kernel instance: remembered per (instance, device)
-template <class K>
+template <int WPB, class K>
 int launch_qp_instance(K kernel, int slot, const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                        cudaStream_t stream) {
   static int configured[4][64] = {};
@@ -1708,11 +1709,11 @@ int launch_qp_instance(K kernel, int slot, const KCfg& cf, const Work& w, const 
 int launch_qp_rti(const KCfg& cf, const Work& w, const double* x0, double* u0, int32_t* status,
                   cudaStream_t stream) {
   if (cf.nl) {
-    if (cf.N == 40) return launch_qp_instance(qp_rti_kernel<40, true>, 2, cf, w, x0, u0, status, stream);
-    return launch_qp_instance(qp_rti_kernel<0, true>, 3, cf, w, x0, u0, status, stream);
+    if (cf.N == 40) return launch_qp_instance<QP_WPB>(qp_rti_kernel<40, true, QP_WPB>, 2, cf, w, x0, u0, status, stream);
+    return launch_qp_instance<1>(qp_rti_kernel<0, true, 1>, 3, cf, w, x0, u0, status, stream);
   }
-  if (cf.N == 40) return launch_qp_instance(qp_rti_kernel<40, false>, 0, cf, w, x0, u0, status, stream);
-  return launch_qp_instance(qp_rti_kernel<0, false>, 1, cf, w, x0, u0, status, stream);
+  if (cf.N == 40) return launch_qp_instance<QP_WPB>(qp_rti_kernel<40, false, QP_WPB>, 0, cf, w, x0, u0, status, stream);
+  return launch_qp_instance<1>(qp_rti_kernel<0, false, 1>, 1, cf, w, x0, u0, status, stream);
 }
 
 }  // namespace ihm2b

@@ -478,6 +478,30 @@ def test_ragged_batch_sizes_match_the_big_batch(torch_cuda, skidpad, config2, B)
     eng.close()
 
 
+def test_long_horizon_rti_matches_oracle(torch_cuda, fsds):
+    """N = 120: the instance of the QP kernel with the horizon as a run-time value holds one problem per block, so a
+    horizon whose stage data would not fit four problems into a block's shared memory still runs."""
+    from ihm2_b200 import _abi
+    from oracle.lib import Oracle
+    Nf, B = 120, 16
+    rng = np.random.default_rng(9)
+    v0, dt = 5.0, 1 / 20
+    x = np.zeros((B, Nf + 1, 8)); u = np.zeros((B, Nf, 2))
+    x[:, :, 0] = -6 + v0 * dt * np.arange(Nf + 1)[None, :]; x[:, :, 3] = v0; x[:, :, 6] = 30.0; u[:, :, 0] = 30.0
+    x0 = x[:, 0, :] + rng.uniform(-1, 1, (B, 8)) * np.array([0.5, 0.3, 0.05, 1.0, 0.1, 0.1, 20, 0.02])
+    cfg = _abi.make_config(batch=B, n_grid=len(fsds.s_ref), Nf=Nf, s_target=60.0)
+    eng = _engine(cfg, fsds); eng.set_iterate(x, u)
+    u0, status = eng.solve(torch_cuda.as_tensor(x0, device="cuda"))
+    sg, xg = status.cpu().numpy(), eng.get_iterate()[0].cpu().numpy()
+    eng.close()
+    u0o, so, sto, xo, uo = Oracle(cfg, fsds.s_ref, fsds.kappa_ref).solve(x0, x, u)
+    print("status gpu", sg, "oracle", so)
+    assert np.mean(sg == so) >= 0.9
+    ok = (sg == 0) & (so == 0)
+    assert ok.sum() >= B // 2
+    assert rel(u0.cpu().numpy()[ok], u0o[ok]) < REL_TOL and rel(xg[ok], xo[ok]) < REL_TOL
+
+
 def test_nan_state_fails_one_instance_only(torch_cuda, skidpad, config2):
     """A NaN in one car's measured state: that instance returns IHM2B_FAILURE (as the oracle does) and keeps its
     iterate (new_python/controller.py:397-403 leaves x_pred untouched when the solve fails); the other instances of the
