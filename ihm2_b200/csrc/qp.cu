@@ -192,8 +192,6 @@ __device__ __forceinline__ CtDef ct_term(int a) {
   d.i2 = 0; d.c2 = 0.0;
   return d;
 }
-__device__ __forceinline__ double ct_apply(const CtDef& d, const double* q) { return d.c1 * q[d.i1] + d.c2 * q[d.i2]; }
-__device__ __forceinline__ double ctc_apply(const CtDef& d, const double* q) { return d.c1 * q[d.i1] + fabs(d.c2) * q[d.i2]; }
 
 
 // ---------------------------------------------------------------------------------------
