@@ -18,7 +18,7 @@
 // registers, exchanging slopes and pivot rows by shuffles.  Phase 2: one
 // thread per (interval, 2-3 columns of d/d(x,u)) -- 128 threads, the column is warp-uniform -- runs
 // the block forward substitution of its column through the shared factors and writes its
-// column of [B A].  Phase 3: one thread per interval forms c and phi.  (A thread-per-interval
+// column of [B A].  Phase 3: four threads per interval form c and phi (two rows each).  (A thread-per-interval
 // version with the factors in a 5.4 KB local-memory frame was bound by local-memory misses:
 // 5.3 GB of DRAM traffic per launch against 126 MB algorithmic.)
 #include "model.cuh"
@@ -531,13 +531,15 @@ __global__ void __launch_bounds__(NI * NCG, LIN_MIN_BLOCKS) linearize_irk_kernel
     }
   }
   __syncthreads();
-  if (tid < NI && live) {
+  if (live) {   // phase 3: the thread of column group cg forms rows 2 cg, 2 cg + 1 of c and phi (all four warps at work)
     const bool ok = s_ok[j] != 0;
     double x[NX];
     for (int i = 0; i < NX; i++) x[i] = w.x[((size_t)b * (cf.N + 1) + k) * NX + i];
     const double u0 = w.u[sk * NU], u1 = w.u[sk * NU + 1];
-    for (int i = 0; i < NX; i++) {
-      const double xn = x[i] + (double)sm[(OFF_XN + i) * NI];     // fp64 state + the step's increment
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+      const int i = 2 * cg + ii;
+      const double xn = w.x[((size_t)b * (cf.N + 1) + k) * NX + i] + (double)sm[(OFF_XN + i) * NI];     // fp64 state + the step's increment
       double ci = ok ? xn - ba[i * NZ] * u0 - ba[i * NZ + 1] * u1 : nan("");
       for (int c = 0; c < NX; c++) ci = fma(-ba[i * NZ + 2 + c], x[c], ci);
       w.c[sk * NX + i] = ci;
